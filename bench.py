@@ -1,0 +1,426 @@
+#!/usr/bin/env python
+"""bench.py — kNN queries/sec of the B200 flat-search hot path (BASELINE.json metric), one JSON line.
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle port), rank 0 only
+  torchrun --nproc-per-node N bench.py --gpus N ...          # N > 1: one process per GPU, NCCL gather + device merge
+
+Workload (default `c4`, the configuration BASELINE.json's metric "queries/sec (k=10) at 1/2/4/8 B200" is quoted on,
+and it fits one GPU): flat dot-product search, 100M x 128 fp32 rows sharded by contiguous row ranges over the
+N GPUs, batch of 1024 queries replicated to every GPU, k=10.  A "step" = one batch through the hot path:
+local top-k on every shard, all_gather of the per-shard lists, final device-side select.  Strong scaling
+(total rows fixed).  Other workloads (`--workload c1|c2|c3|c5`) are BASELINE.json's remaining configs.
+
+`value`   : queries/s with queries, rows and results resident in HBM (CUDA events, max over ranks).
+`e2e`     : same metric through the reference-facing C-ABI call with HOST buffers: pinned host queries are
+            copied H2D and the final (label, distance) lists D2H inside the timed region, every step.
+`roofline`: the dominant kernel's algorithmic bytes (or flops) / its CUDA-event duration, vs MEASURED_PEAKS.json.
+`cpu_baseline`: the oracle's OpenMP fp32 batch search timed on this box's host cores on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: rows, dim, metric, batch, k, kind
+    "c1": dict(rows=100_000, dim=128, metric="l2", batch=1, k=10, kind="flat",
+               desc="lance_search flat L2 k=10, 100Kx128 fp32, single query"),
+    "c2": dict(rows=1_000_000, dim=768, metric="cosine", batch=4096, k=100, kind="flat",
+               desc="flat cosine k=100, 1Mx768 fp32, query batch 4096 (also 1/64 via --batch)"),
+    "c3": dict(rows=10_000_000, dim=768, metric="l2", batch=1, k=10, kind="ivfpq", P=4096, M=96, nprobes=32,
+               desc="IVF_PQ (4096 partitions, 96 sub-quantizers) 10Mx768, nprobes=32, k=10"),
+    "c4": dict(rows=100_000_000, dim=128, metric="dot", batch=1024, k=10, kind="flat",
+               desc="flat dot-product 100Mx128 fp32 sharded by rows across the GPUs, batch 1024, k=10"),
+    "c5": dict(rows=10_000_000, dim=384, metric="l2", batch=1, k=10, kind="flat", selectivity=0.8,
+               desc="ORDER BY array_distance LIMIT 10 with WHERE prefilter (80% selectivity bitmap), 10Mx384"),
+}
+SEED = 0xC0FFEE
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm_gbs=d["hbm_gbs"], bf16_tflops=d["bf16_tflops"],
+                    bf16_tflops_sustained=d.get("bf16_tflops_sustained", d["bf16_tflops"]), source="measured")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device = device
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def shard_range(rows, rank, world):
+    """Contiguous row ranges [rows*r/W, rows*(r+1)/W): labels are sequential (lance_manager.rs:232-233), so a
+    shard is a label range and the global label is base + local row."""
+    return rows * rank // world, rows * (rank + 1) // world
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def cpu_search_sample(wl, sample_rows, sample_q, threads, seed=SEED):
+    """The oracle's OpenMP fp32 flat search on a bounded sample; returns (seconds, rows, queries)."""
+    import oracle
+
+    rng = np.random.default_rng(seed)
+    X = rng.standard_normal((sample_rows, wl["dim"]), dtype=np.float32)
+    Q = rng.standard_normal((sample_q, wl["dim"]), dtype=np.float32)
+    allow = None
+    if wl.get("selectivity"):
+        allow = oracle.make_bitmap(rng.random(sample_rows) < wl["selectivity"])
+    oracle.flat_search_batch_f32(X[:1000], Q[:1], wl["k"], wl["metric"], nthreads=threads)  # warm the pool
+    t0 = time.perf_counter()
+    oracle.flat_search_batch_f32(X, Q, wl["k"], wl["metric"], allow=allow, nthreads=threads)
+    return time.perf_counter() - t0, sample_rows, sample_q
+
+
+def cpu_sample_shape(wl, budget_pairs):
+    """Pick (rows, queries) of the sample so that rows*queries*dim ~ budget, keeping the batch shape when possible."""
+    q = min(wl["batch"], 64)
+    rows = int(min(wl["rows"], max(10_000, budget_pairs // (q * wl["dim"]))))
+    return rows, q
+
+
+def cpu_baseline(wl, seconds_target=12.0):
+    import oracle
+
+    oracle.build()
+    threads = oracle.num_threads()
+    # calibrate: ~0.3 s probe, then scale to the target
+    rows, q = cpu_sample_shape(wl, 2_000_000_000)
+    dt, r, qq = cpu_search_sample(wl, min(rows, 200_000), q, threads)
+    rate = r * qq * wl["dim"] / dt
+    rows, q = cpu_sample_shape(wl, int(rate * seconds_target))
+    dt, r, qq = cpu_search_sample(wl, rows, q, threads)
+    # queries/s on the full table: time scales with rows (one pass over X per batch)
+    qps = qq / (dt * (wl["rows"] / r))
+    return {"value": qps, "unit": "queries/s", "cores": threads, "kind": "port",
+            "sample": f"oracle_flat_search_batch_f32 (OpenMP fp32 port, oracle/oracle.c) on {r} of {wl['rows']} rows x "
+                      f"{qq} queries, {dt:.2f} s, scaled by rows"}
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+
+    oracle.build()
+    threads = oracle.num_threads()
+    rows, q = cpu_sample_shape(wl, 1_500_000_000)
+    times = []
+    for i in range(args.warmup + args.steps):
+        dt, r, qq = cpu_search_sample(wl, rows, q, threads)
+        if i >= args.warmup:
+            times.append(dt)
+    dt = sum(times) / len(times)
+    qps = q / (dt * (wl["rows"] / rows))
+    sample = (f"oracle OpenMP fp32 port of the reference's CPU flat search, {rows} of {wl['rows']} rows x {q} queries per "
+              f"step, scaled by rows (LanceDB itself cannot be built here: no Rust toolchain, crates not vendored)")
+    line = {"impl": "reference", "metric": "kNN queries/sec", "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wl["batch"] / qps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(wl, args),
+            "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def workload_config(wl, args):
+    return {"workload": f"{args.workload}: {wl['desc']}", "rows": wl["rows"], "dim": wl["dim"], "metric": wl["metric"],
+            "batch": wl["batch"], "k": wl["k"], "sharding": f"rows/{args.gpus}", "l2_hygiene": "inputs larger than L2"
+            if wl["rows"] * wl["dim"] * 4 // max(args.gpus, 1) > 200e6 else "L2 flushed between steps"}
+
+
+# ------------------------------------------------------------------------------------------------ product arm
+def run_b200(args, wl):
+    import torch
+    import torch.distributed as dist
+
+    from __graft_entry__ import load_package
+
+    pkg = load_package()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch N>1 with torchrun: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    pkg.set_default_device(local)
+    peaks = load_peaks()
+
+    rows, dim, metric, B, k = wl["rows"], wl["dim"], wl["metric"], wl["batch"], wl["k"]
+    lo, hi = shard_range(rows, rank, world)
+    n_local = hi - lo
+    stream = torch.cuda.current_stream()
+    sp = stream.cuda_stream
+
+    # ---- build the shard in HBM (synthetic N(0,1), seeded per chunk so any sharding sees the same table)
+    h = pkg.LanceHandle(dim, metric)
+    h.set_label_base(lo)
+    h.reserve(n_local)
+    chunk = 1 << 22
+    g = torch.Generator(device=dev)
+    c0 = lo // chunk
+    pos = lo
+    while pos < hi:
+        cidx = pos // chunk
+        g.manual_seed(SEED + 7919 * cidx)
+        blk = torch.randn((chunk, dim), generator=g, device=dev, dtype=torch.float32)
+        a, b = pos - cidx * chunk, min(hi, (cidx + 1) * chunk) - cidx * chunk
+        h.add_batch_device(blk[a:b].data_ptr(), b - a, dim, sp)
+        pos += b - a
+        del blk
+    assert h.count() == n_local
+    g.manual_seed(SEED + 1)
+    Qd = torch.randn((B, dim), generator=g, device=dev, dtype=torch.float32)
+    Qh = Qd.cpu().pin_memory()
+
+    d_allow, allow_bits, allow_host = 0, 0, None
+    if wl.get("selectivity"):
+        g.manual_seed(SEED + 2)
+        mask = (torch.rand(rows, generator=g, device=dev) < wl["selectivity"])[lo:hi]
+        allow_host = pkg.make_bitmap(mask.cpu().numpy())
+        allow_t = torch.from_numpy(allow_host.view(np.int32)).to(dev)
+        d_allow, allow_bits = allow_t.data_ptr(), allow_host.shape[0] * 32
+
+    if wl["kind"] == "ivfpq":
+        h.create_index(wl["P"], wl["M"])
+    nprobes = wl.get("nprobes", 20)
+
+    L = torch.empty((B, k), dtype=torch.int64, device=dev)
+    D = torch.empty((B, k), dtype=torch.float32, device=dev)
+    C = torch.empty(B, dtype=torch.int32, device=dev)
+    if world > 1:
+        GL = torch.empty((world, B, k), dtype=torch.int64, device=dev)
+        GD = torch.empty((world, B, k), dtype=torch.float32, device=dev)
+        GC = torch.empty((world, B), dtype=torch.int32, device=dev)
+        ML = torch.empty((B, k), dtype=torch.int64, device=dev)
+        MD = torch.empty((B, k), dtype=torch.float32, device=dev)
+        MC = torch.empty(B, dtype=torch.int32, device=dev)
+    Lh = torch.empty((B, k), dtype=torch.int64).pin_memory()
+    Dh = torch.empty((B, k), dtype=torch.float32).pin_memory()
+    Ch = torch.empty(B, dtype=torch.int32).pin_memory()
+    Qstage = torch.empty_like(Qd)
+    merge_launches = [0]
+
+    def step_device(q_ptr):
+        """local top-k -> (N>1) NCCL all_gather of the lists -> final device select."""
+        h.search_device(q_ptr, B, k, L.data_ptr(), D.data_ptr(), C.data_ptr(), nprobes=nprobes, refine_factor=1,
+                        d_allow=d_allow, allow_bits=allow_bits, stream=sp)
+        if world > 1:
+            dist.all_gather_into_tensor(GL, L)
+            dist.all_gather_into_tensor(GD, D)
+            dist.all_gather_into_tensor(GC, C)
+            pkg.merge_topk_device(local, GL.data_ptr(), GD.data_ptr(), GC.data_ptr(), world, B, k, ML.data_ptr(),
+                                  MD.data_ptr(), MC.data_ptr(), stream=sp)
+            merge_launches[0] += 3
+            return ML, MD, MC
+        return L, D, C
+
+    def step_e2e():
+        if world == 1:
+            # the reference-facing call: host buffers in, host buffers out (lance_detached_search_batch)
+            h.search_batch(Qh.numpy(), k, nprobes=nprobes, refine_factor=1, allow=allow_host,
+                           out=(Lh.numpy(), Dh.numpy(), Ch.numpy()))
+        else:
+            Qstage.copy_(Qh, non_blocking=True)
+            oL, oD, oC = step_device(Qstage.data_ptr())
+            Lh.copy_(oL, non_blocking=True)
+            Dh.copy_(oD, non_blocking=True)
+            Ch.copy_(oC, non_blocking=True)
+            stream.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms
+
+    # ---- warm-up, then the timed region (device-resident)
+    for _ in range(max(args.warmup, 3)):
+        step_device(Qd.data_ptr())
+    barrier()
+    st0 = h.stats()
+    h.profile_enable(True)
+    h.profile_read()
+    merge_launches[0] = 0
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms = timed(lambda: step_device(Qd.data_ptr()), args.steps)
+    prof = h.profile_read()
+    h.profile_enable(False)
+    st1 = h.stats()
+    # ---- end-to-end (host buffers) timed region
+    for _ in range(2):
+        step_e2e()
+    wall0 = time.perf_counter()
+    ms_e2e_dev = timed(step_e2e, args.steps)
+    wall = (time.perf_counter() - wall0) * 1e3
+    ms_e2e = max(ms_e2e_dev, wall if world == 1 else ms_e2e_dev)  # N=1: the call is synchronous, wall clock bounds it
+    clocks = sampler.stop() if rank == 0 else None
+
+    launches = st1["kernel_launches"] - st0["kernel_launches"] + merge_launches[0]
+    qps = B * args.steps / (ms / 1e3)
+    qps_e2e = B * args.steps / (ms_e2e / 1e3)
+
+    # ---- roofline of the dominant kernel (algorithmic bytes / flops per launch)
+    roof = None
+    if prof["flat_gemm_launches"] > 0:
+        t = prof["flat_gemm_ms"] / prof["flat_gemm_launches"] / 1e3
+        # one launch = the whole batch against the whole shard: 2*B*n*d flops (one pass, norms/re-rank excluded)
+        flops = 2.0 * B * n_local * dim * (prof["flat_gemm_launches"] and 1)
+        launches_per_step = prof["flat_gemm_launches"] / args.steps
+        achieved = flops / launches_per_step / t / 1e12
+        ridge = B / 2.0  # flop per byte of bf16 X read once
+        peak = peaks["bf16_tflops_sustained"]
+        bound = "tensor" if ridge >= peak * 1e12 / (peaks["hbm_gbs"] * 1e9) else "hbm"
+        if bound == "tensor":
+            roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                    "traffic": None, "kernel": "flat_gemm_kernel (tcgen05 bf16)", "peak_source": peaks["source"] + " bf16 sustained"}
+        else:
+            bytes_ = (n_local * dim * 2.0) / launches_per_step
+            a = bytes_ / t / 1e9
+            roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
+                    "traffic": None, "kernel": "flat_gemm_kernel (tcgen05 bf16, HBM-bound batch)", "peak_source": peaks["source"]}
+    elif prof["adc_scan_launches"] > 0:
+        roof = {"bound": "hbm", "achieved": None, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": None, "traffic": None,
+                "kernel": "adc_scan_kernel"}
+    elif prof["flat_scan_launches"] > 0:
+        t = prof["flat_scan_ms"] / prof["flat_scan_launches"] / 1e3
+        sel = wl.get("selectivity") or 1.0
+        bytes_ = n_local * dim * 4.0  # X read once per pass of <= 4 queries
+        a = bytes_ / t / 1e9
+        roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
+                "traffic": None, "kernel": "flat_scan_kernel (fp32, <=4 queries per pass)", "peak_source": peaks["source"],
+                "launches_per_step": prof["flat_scan_launches"] / args.steps, "avg_launch_ms": t * 1e3,
+                "selectivity": sel}
+
+    if rank == 0:
+        base = cpu_baseline(wl) if world == 1 and not args.no_cpu_baseline else None
+        line = {"metric": "kNN queries/sec", "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32" if st1["flat_tc_batches"] == st0["flat_tc_batches"]
+                else "bf16 candidates + f32 re-rank", "data": "synthetic N(0,1), seeded", "config": workload_config(wl, args),
+                "clocks": clocks,
+                "e2e": {"value": qps_e2e, "unit": "queries/s", "h2d_bytes_per_step": int(Qh.numel() * 4 + (allow_host.nbytes if allow_host is not None and world == 1 else 0)),
+                        "d2h_bytes_per_step": int(Lh.numel() * 8 + Dh.numel() * 4 + Ch.numel() * 4), "ms_per_step": ms_e2e / args.steps},
+                "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": base,
+                "paths": {"flat_simt_batches": st1["flat_simt_batches"] - st0["flat_simt_batches"],
+                          "flat_tc_batches": st1["flat_tc_batches"] - st0["flat_tc_batches"],
+                          "tc_fallback_queries": st1["tc_fallback_queries"] - st0["tc_fallback_queries"],
+                          "ivfpq_batches": st1["ivfpq_batches"] - st0["ivfpq_batches"]},
+                "profile_ms": {kk: vv for kk, vv in prof.items()}}
+        print(json.dumps(line))
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=None, help="override the workload's query batch")
+    ap.add_argument("--rows", type=int, default=None, help="override the workload's row count (experiments only)")
+    ap.add_argument("--k", type=int, default=None)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = dict(WORKLOADS[args.workload])
+    if args.batch:
+        wl["batch"] = args.batch
+    if args.rows:
+        wl["rows"] = args.rows
+    if args.k:
+        wl["k"] = args.k
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_b200(args, wl)
+
+
+if __name__ == "__main__":
+    main()

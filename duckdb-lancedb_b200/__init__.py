@@ -1,0 +1,378 @@
+"""ctypes harness over liblance_b200.so — the C ABI declared in include/lance_b200.h.
+
+The product is the shared library (CUDA kernels + C++ host code under csrc/); this module only
+exists so that tests/, bench.py and __graft_entry__.py can drive the very entry points the DuckDB
+extension's C++ side binds (/root/reference/src/rust_ffi.cpp:9-41).  It never computes anything
+itself and never imports oracle/: if the library or a CUDA device is missing, calls raise.
+
+The directory name carries a hyphen, so load it with `__graft_entry__.load_package()` (importlib),
+which registers it as module `duckdb_lancedb_b200`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblance_b200.so")
+CSRC = os.path.join(_HERE, "csrc")
+HEADER = os.path.join(os.path.dirname(_HERE), "include", "lance_b200.h")
+
+ERR_LEN = 2048  # src/rust_ffi.cpp:46 uses a 2048-byte stack buffer
+
+
+class LanceError(IOError):
+    """Mirrors duckdb::IOException("Lance <op>: ...") thrown by src/rust_ffi.cpp:44-206."""
+
+
+def build(force: bool = False) -> str:
+    """Compile the CUDA library for sm_100a (nvcc cross-compiles without a GPU)."""
+    if force:
+        subprocess.run(["make", "-C", CSRC, "clean"], check=True, capture_output=True)
+    r = subprocess.run(["make", "-C", CSRC, "-j8"], capture_output=True, text=True, env={**os.environ, "MAKEFLAGS": ""})
+    if r.returncode != 0:
+        raise RuntimeError("building liblance_b200.so failed:\n" + r.stdout[-4000:] + r.stderr[-4000:])
+    return LIB_PATH
+
+
+class IvfPqInfo(C.Structure):
+    _fields_ = [("metric", C.c_int32), ("dim", C.c_int32), ("P", C.c_int32), ("M", C.c_int32),
+                ("n_indexed", C.c_int64)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("kernel_launches", C.c_int64), ("searches", C.c_int64), ("flat_simt_batches", C.c_int64),
+                ("flat_tc_batches", C.c_int64), ("tc_fallback_queries", C.c_int64), ("ivfpq_batches", C.c_int64),
+                ("rows", C.c_int64), ("live_rows", C.c_int64), ("device", C.c_int32), ("has_index", C.c_int32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class Profile(C.Structure):
+    _fields_ = [("flat_scan_ms", C.c_double), ("flat_scan_launches", C.c_int64), ("flat_gemm_ms", C.c_double),
+                ("flat_gemm_launches", C.c_int64), ("adc_scan_ms", C.c_double), ("adc_scan_launches", C.c_int64),
+                ("rerank_ms", C.c_double), ("rerank_launches", C.c_int64)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+_lib = None
+_vp, _cp, _i32, _i64 = C.c_void_p, C.c_char_p, C.c_int32, C.c_int64
+_ERR = [C.c_char_p, C.c_int]
+
+# name -> (restype, argtypes): one entry per declaration in include/lance_b200.h
+SIGNATURES = {
+    "lance_create_detached": (_vp, [_cp, _i32, _cp, _cp] + _ERR),
+    "lance_create_detached_from_arrow": (_vp, [_cp, _vp, _cp, _cp] + _ERR),
+    "lance_open_detached": (_vp, [_cp, _cp, _cp] + _ERR),
+    "lance_free_detached": (None, [_vp]),
+    "lance_detached_has_extra_columns": (_i32, [_vp]),
+    "lance_detached_dimension": (_i32, [_vp]),
+    "lance_detached_add": (_i64, [_vp, _vp, _i32] + _ERR),
+    "lance_detached_add_batch": (_i32, [_vp, _vp, _i32, _i32, _vp] + _ERR),
+    "lance_detached_add_batch_arrow": (_i32, [_vp, _vp, _vp, _vp] + _ERR),
+    "lance_detached_merge": (_i32, [_vp, _vp, _vp, _i32, _vp, _vp] + _ERR),
+    "lance_detached_search": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp] + _ERR),
+    "lance_detached_count": (_i64, [_vp] + _ERR),
+    "lance_detached_delete": (_i32, [_vp, _i64] + _ERR),
+    "lance_detached_delete_batch": (_i32, [_vp, _vp, _i32] + _ERR),
+    "lance_detached_create_index": (_i32, [_vp, _i32, _i32] + _ERR),
+    "lance_detached_create_hnsw_index": (_i32, [_vp, _i32, _i32] + _ERR),
+    "lance_detached_compact": (_i32, [_vp] + _ERR),
+    "lance_detached_get_vector": (_i32, [_vp, _i64, _vp, _i32] + _ERR),
+    "lance_detached_get_all_vectors": (_i32, [_vp, _vp, _vp, _vp] + _ERR),
+    "lance_detached_search_filtered": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _vp] + _ERR),
+    "lance_detached_search_batch": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _vp, _vp] + _ERR),
+    "lance_b200_search_device": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp] + _ERR),
+    "lance_b200_merge_topk_device": (_i32, [_i32, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp] + _ERR),
+    "lance_b200_set_label_base": (_i32, [_vp, _i64] + _ERR),
+    "lance_b200_reserve": (_i32, [_vp, _i64] + _ERR),
+    "lance_b200_add_batch_device": (_i64, [_vp, _vp, _i64, _i32, _vp] + _ERR),
+    "lance_b200_set_ivfpq": (_i32, [_vp, _i32, _i32, _i64, _vp, _vp, _vp, _vp, _vp] + _ERR),
+    "lance_b200_get_ivfpq": (_i32, [_vp, C.POINTER(IvfPqInfo), _vp, _vp, _vp, _vp, _vp] + _ERR),
+    "lance_b200_drop_index": (_i32, [_vp] + _ERR),
+    "lance_b200_ivfpq_search_debug": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp] + _ERR),
+    "lance_b200_save": (_i32, [_vp] + _ERR),
+    "lance_b200_stats": (_i32, [_vp, C.POINTER(Stats)]),
+    "lance_b200_profile_enable": (_i32, [_vp, _i32]),
+    "lance_b200_profile_read": (_i32, [_vp, C.POINTER(Profile)]),
+    "lance_b200_set_flat_path": (_i32, [_vp, _i32]),
+    "lance_b200_set_default_device": (_i32, [_i32]),
+    "lance_b200_device_count": (_i32, []),
+    "lance_b200_version": (_cp, []),
+}
+
+
+def lib():
+    """dlopen the library (never builds implicitly on the GPU box: a missing .so is an error)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise LanceError(f"{LIB_PATH} is missing: run __graft_entry__.build() (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    return C.c_void_p(int(a))  # a raw device/host address (e.g. torch.Tensor.data_ptr())
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def make_bitmap(mask) -> np.ndarray:
+    """bool[n] -> uint32 words, bit (i & 31) of word (i >> 5): the layout of the allow_bitmap arguments."""
+    mask = np.asarray(mask, dtype=bool)
+    n = mask.shape[0]
+    padded = np.zeros(((n + 31) // 32) * 32, dtype=bool)
+    padded[:n] = mask
+    if padded.size == 0:
+        return np.zeros(1, np.uint32)
+    return np.packbits(padded.reshape(-1, 32), axis=1, bitorder="little").view(np.uint32).reshape(-1).copy()
+
+
+class LanceHandle:
+    """One `lance_*` handle.  Method names follow the wrappers of src/include/rust_ffi.hpp:9-58."""
+
+    def __init__(self, dimension: int, metric: str = "l2", db_path: str = "", table_name: str = "vectors", _raw=None):
+        self._err = C.create_string_buffer(ERR_LEN)
+        self.metric = metric
+        if _raw is not None:
+            self._h = _raw
+        else:
+            self._h = lib().lance_create_detached(db_path.encode(), int(dimension), metric.encode(), table_name.encode(),
+                                                  self._err, ERR_LEN)
+            if not self._h:
+                raise LanceError("Lance create: " + self._err.value.decode())
+        self.dim = int(lib().lance_detached_dimension(self._h))
+
+    @classmethod
+    def open(cls, db_path: str, table_name: str = "vectors", metric: str = "l2"):
+        err = C.create_string_buffer(ERR_LEN)
+        h = lib().lance_open_detached(db_path.encode(), table_name.encode(), metric.encode(), err, ERR_LEN)
+        if not h:
+            raise LanceError("Lance open: " + err.value.decode())
+        return cls(0, metric, _raw=h)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().lance_free_detached(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc, op):
+        if rc is None or rc < 0:
+            raise LanceError(f"Lance {op}: " + self._err.value.decode())
+        return rc
+
+    # ---- ingest / lifecycle
+    def add_batch(self, vectors) -> np.ndarray:
+        v = _f32(vectors)
+        if v.ndim == 1:
+            v = v.reshape(1, -1)
+        labels = np.empty(v.shape[0], np.int64)
+        self._check(lib().lance_detached_add_batch(self._h, _ptr(v), v.shape[0], v.shape[1], _ptr(labels), self._err,
+                                                   ERR_LEN), "add_batch")
+        return labels
+
+    def add(self, vector) -> int:
+        v = _f32(vector)
+        return int(self._check(lib().lance_detached_add(self._h, _ptr(v), v.shape[0], self._err, ERR_LEN), "add"))
+
+    def add_batch_device(self, dev_ptr: int, num: int, dim: int, stream: int = 0) -> int:
+        return int(self._check(lib().lance_b200_add_batch_device(self._h, _ptr(dev_ptr), num, dim, _ptr(stream),
+                                                                 self._err, ERR_LEN), "add_batch"))
+
+    def reserve(self, rows: int):
+        self._check(lib().lance_b200_reserve(self._h, rows, self._err, ERR_LEN), "reserve")
+
+    def set_label_base(self, base: int):
+        self._check(lib().lance_b200_set_label_base(self._h, base, self._err, ERR_LEN), "set_label_base")
+
+    def count(self) -> int:
+        return int(self._check(lib().lance_detached_count(self._h, self._err, ERR_LEN), "count"))
+
+    def delete_batch(self, labels):
+        l = np.ascontiguousarray(labels, np.int64)
+        self._check(lib().lance_detached_delete_batch(self._h, _ptr(l), l.shape[0], self._err, ERR_LEN), "delete_batch")
+
+    def delete(self, label: int):
+        self._check(lib().lance_detached_delete(self._h, int(label), self._err, ERR_LEN), "delete")
+
+    def get_vector(self, label: int) -> np.ndarray:
+        out = np.empty(self.dim, np.float32)
+        self._check(lib().lance_detached_get_vector(self._h, int(label), _ptr(out), self.dim, self._err, ERR_LEN),
+                    "get_vector")
+        return out
+
+    def get_all_vectors(self):
+        cnt = C.c_int64(0)
+        self._check(lib().lance_detached_get_all_vectors(self._h, None, None, C.addressof(cnt), self._err, ERR_LEN),
+                    "get_all_vectors")
+        labels = np.empty(cnt.value, np.int64)
+        vecs = np.empty((cnt.value, self.dim), np.float32)
+        self._check(lib().lance_detached_get_all_vectors(self._h, _ptr(labels), _ptr(vecs), C.addressof(cnt), self._err,
+                                                         ERR_LEN), "get_all_vectors")
+        return labels, vecs
+
+    def save(self):
+        self._check(lib().lance_b200_save(self._h, self._err, ERR_LEN), "save")
+
+    def compact(self):
+        self._check(lib().lance_detached_compact(self._h, self._err, ERR_LEN), "compact")
+
+    # ---- search
+    def search(self, query, k: int, nprobes: int = 20, refine_factor: int = 1, allow=None):
+        """LanceDetachedSearch (src/rust_ffi.cpp:130-139): returns (labels int64[c], distances float32[c])."""
+        q = _f32(query)
+        kk = max(int(k), 1)
+        labels = np.empty(kk, np.int64)
+        dist = np.empty(kk, np.float32)
+        if allow is None:
+            c = lib().lance_detached_search(self._h, _ptr(q), q.shape[0], int(k), nprobes, refine_factor, _ptr(labels),
+                                            _ptr(dist), self._err, ERR_LEN)
+        else:
+            bm = np.ascontiguousarray(allow, np.uint32)
+            c = lib().lance_detached_search_filtered(self._h, _ptr(q), q.shape[0], int(k), nprobes, refine_factor,
+                                                     _ptr(bm), bm.shape[0] * 32, _ptr(labels), _ptr(dist), self._err,
+                                                     ERR_LEN)
+        self._check(c, "search")
+        return labels[:c].copy(), dist[:c].copy()
+
+    def search_batch(self, queries, k: int, nprobes: int = 20, refine_factor: int = 1, allow=None, out=None):
+        """Returns (labels[nq,k], distances[nq,k], counts[nq]).  `out` = preallocated (labels, dist, counts)."""
+        Q = queries if (isinstance(queries, np.ndarray) and queries.dtype == np.float32 and queries.flags.c_contiguous) \
+            else _f32(queries)
+        nq, d = Q.shape
+        kk = max(int(k), 1)
+        if out is None:
+            labels = np.empty((nq, kk), np.int64)
+            dist = np.empty((nq, kk), np.float32)
+            counts = np.empty(nq, np.int32)
+        else:
+            labels, dist, counts = out
+        bm = None if allow is None else np.ascontiguousarray(allow, np.uint32)
+        rc = lib().lance_detached_search_batch(self._h, _ptr(Q), nq, d, int(k), nprobes, refine_factor, _ptr(bm),
+                                               0 if bm is None else bm.shape[0] * 32, _ptr(labels), _ptr(dist),
+                                               _ptr(counts), self._err, ERR_LEN)
+        self._check(rc, "search")
+        return labels, dist, counts
+
+    def search_device(self, d_queries: int, nq: int, k: int, d_labels: int, d_dist: int, d_counts: int,
+                      nprobes: int = 20, refine_factor: int = 1, d_allow: int = 0, allow_bits: int = 0, stream: int = 0):
+        rc = lib().lance_b200_search_device(self._h, _ptr(d_queries), nq, k, nprobes, refine_factor,
+                                            _ptr(d_allow) if d_allow else None, allow_bits, _ptr(d_labels), _ptr(d_dist),
+                                            _ptr(d_counts), _ptr(stream) if stream else None, self._err, ERR_LEN)
+        self._check(rc, "search")
+
+    # ---- IVF_PQ
+    def create_index(self, num_partitions: int = 0, num_sub_vectors: int = 0):
+        self._check(lib().lance_detached_create_index(self._h, num_partitions, num_sub_vectors, self._err, ERR_LEN),
+                    "create_index")
+
+    def create_hnsw_index(self, m: int = 16, ef: int = 100):
+        self._check(lib().lance_detached_create_hnsw_index(self._h, m, ef, self._err, ERR_LEN), "create_hnsw_index")
+
+    def drop_index(self):
+        self._check(lib().lance_b200_drop_index(self._h, self._err, ERR_LEN), "drop_index")
+
+    def set_ivfpq(self, centroids, codebook, part_offsets, row_ids, codes):
+        cen = _f32(centroids)
+        P = cen.shape[0]
+        codes = np.ascontiguousarray(codes, np.uint8)
+        M = codes.shape[1]
+        cb = _f32(codebook)
+        off = np.ascontiguousarray(part_offsets, np.int64)
+        ids = np.ascontiguousarray(row_ids, np.int64)
+        self._check(lib().lance_b200_set_ivfpq(self._h, P, M, ids.shape[0], _ptr(cen), _ptr(cb), _ptr(off), _ptr(ids),
+                                               _ptr(codes), self._err, ERR_LEN), "set_ivfpq")
+
+    def get_ivfpq(self):
+        info = IvfPqInfo()
+        self._check(lib().lance_b200_get_ivfpq(self._h, C.byref(info), None, None, None, None, None, self._err, ERR_LEN),
+                    "get_ivfpq")
+        cen = np.empty((info.P, info.dim), np.float32)
+        cb = np.empty((info.M, 256, info.dim // info.M), np.float32)
+        off = np.empty(info.P + 1, np.int64)
+        ids = np.empty(info.n_indexed, np.int64)
+        codes = np.empty((info.n_indexed, info.M), np.uint8)
+        self._check(lib().lance_b200_get_ivfpq(self._h, C.byref(info), _ptr(cen), _ptr(cb), _ptr(off), _ptr(ids),
+                                               _ptr(codes), self._err, ERR_LEN), "get_ivfpq")
+        return dict(metric=info.metric, dim=info.dim, P=info.P, M=info.M, n_indexed=info.n_indexed, centroids=cen,
+                    codebook=cb, part_offsets=off, row_ids=ids, codes=codes)
+
+    def ivfpq_search_debug(self, query, k, nprobes, refine_factor=1, allow=None):
+        q = _f32(query)
+        rf = max(int(refine_factor), 1)
+        parts = np.full(max(nprobes, 1), -1, np.int32)
+        cl = np.empty(k * rf, np.int64)
+        ca = np.empty(k * rf, np.float32)
+        nc = C.c_int32(0)
+        labels = np.empty(k, np.int64)
+        dist = np.empty(k, np.float32)
+        bm = None if allow is None else np.ascontiguousarray(allow, np.uint32)
+        c = lib().lance_b200_ivfpq_search_debug(self._h, _ptr(q), q.shape[0], k, nprobes, refine_factor, _ptr(bm),
+                                                0 if bm is None else bm.shape[0] * 32, _ptr(parts), _ptr(cl), _ptr(ca),
+                                                C.addressof(nc), _ptr(labels), _ptr(dist), self._err, ERR_LEN)
+        self._check(c, "search")
+        return dict(parts=parts[parts >= 0], cand_labels=cl[:nc.value].copy(), cand_adc=ca[:nc.value].copy(),
+                    labels=labels[:c].copy(), dist=dist[:c].copy())
+
+    # ---- introspection / hooks
+    def stats(self) -> dict:
+        s = Stats()
+        lib().lance_b200_stats(self._h, C.byref(s))
+        return s.as_dict()
+
+    def profile_enable(self, on: bool = True):
+        lib().lance_b200_profile_enable(self._h, 1 if on else 0)
+
+    def profile_read(self) -> dict:
+        p = Profile()
+        lib().lance_b200_profile_read(self._h, C.byref(p))
+        return p.as_dict()
+
+    def set_flat_path(self, mode: int):
+        """0 auto, 1 fp32 streaming scan, 2 tcgen05 candidate GEMM + re-rank."""
+        if lib().lance_b200_set_flat_path(self._h, mode) != 0:
+            raise LanceError("Lance set_flat_path: bad mode")
+
+
+def merge_topk_device(device: int, d_labels: int, d_dists: int, d_counts: int, G: int, nq: int, k: int,
+                      d_out_labels: int, d_out_dists: int, d_out_counts: int, stream: int = 0):
+    err = C.create_string_buffer(ERR_LEN)
+    rc = lib().lance_b200_merge_topk_device(device, _ptr(d_labels), _ptr(d_dists), _ptr(d_counts), G, nq, k,
+                                            _ptr(d_out_labels), _ptr(d_out_dists), _ptr(d_out_counts),
+                                            _ptr(stream) if stream else None, err, ERR_LEN)
+    if rc != 0:
+        raise LanceError("Lance merge: " + err.value.decode())
+
+
+def device_count() -> int:
+    return int(lib().lance_b200_device_count())
+
+
+def set_default_device(device: int):
+    lib().lance_b200_set_default_device(int(device))

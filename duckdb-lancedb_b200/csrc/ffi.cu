@@ -1,0 +1,375 @@
+// ffi.cu — the C boundary (include/lance_b200.h).  Same symbols, argument meaning and error
+// convention as the Rust crate's exports (rust_lib/src/ffi.rs:37-541) that src/rust_ffi.cpp:9-41 binds.
+// Nothing throws across this file: every entry catches and writes err_buf.
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "store.h"
+
+using lb::Store;
+
+static void write_err(char *buf, int len, const std::string &msg) {
+	// rust_lib/src/ffi.rs:15-24
+	if (!buf || len <= 0) return;
+	size_t n = msg.size() < (size_t)(len - 1) ? msg.size() : (size_t)(len - 1);
+	memcpy(buf, msg.data(), n);
+	buf[n] = '\0';
+}
+static std::string cstr(const char *s) { return s ? std::string(s) : std::string(); }
+
+#define LB_TRY(prefix, fail_value, body)                         \
+	try {                                                        \
+		body                                                     \
+	} catch (const std::exception &e) {                          \
+		write_err(err_buf, err_buf_len, std::string(prefix) + e.what()); \
+		return fail_value;                                       \
+	} catch (...) {                                              \
+		write_err(err_buf, err_buf_len, std::string(prefix) + "unknown error"); \
+		return fail_value;                                       \
+	}
+
+#define LB_HANDLE(fail_value)                               \
+	if (!handle) {                                          \
+		write_err(err_buf, err_buf_len, "null handle");     \
+		return fail_value;                                  \
+	}                                                       \
+	Store *h = static_cast<Store *>(handle);
+
+extern "C" {
+
+void *lance_create_detached(const char *db_path, int32_t dimension, const char *metric, const char *table_name,
+                            char *err_buf, int err_buf_len) {
+	LB_TRY("create failed: ", nullptr, {
+		return new Store(cstr(db_path), cstr(table_name), dimension, cstr(metric), lb::default_device());
+	})
+}
+
+void *lance_create_detached_from_arrow(const char *, void *, const char *, const char *, char *err_buf,
+                                       int err_buf_len) {
+	write_err(err_buf, err_buf_len,
+	          "create_from_arrow failed: multi-column Arrow tables are outside the kNN path of the B200 backend");
+	return nullptr;
+}
+
+void *lance_open_detached(const char *db_path, const char *table_name, const char *metric, char *err_buf,
+                          int err_buf_len) {
+	LB_TRY("open failed: ", nullptr,
+	       { return Store::open(cstr(db_path), cstr(table_name), cstr(metric), lb::default_device()); })
+}
+
+void lance_free_detached(void *handle) {
+	if (!handle) return;
+	try {
+		delete static_cast<Store *>(handle);
+	} catch (...) {
+	}
+}
+
+int32_t lance_detached_has_extra_columns(void *) { return 0; }
+
+int32_t lance_detached_dimension(void *handle) { return handle ? static_cast<Store *>(handle)->dim() : 0; }
+
+int64_t lance_detached_add(void *handle, const float *vector, int32_t dimension, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("add failed: ", -1, {
+		if (dimension != h->dim())
+			throw lb::Error("expected dimension " + std::to_string(h->dim()) + ", got " + std::to_string(dimension));
+		return h->add_host(vector, 1);
+	})
+}
+
+int32_t lance_detached_add_batch(void *handle, const float *vectors, int32_t num, int32_t dim, int64_t *out_labels,
+                                 char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("add_batch failed: ", -1, {
+		if (dim != h->dim())
+			throw lb::Error("expected dimension " + std::to_string(h->dim()) + ", got " + std::to_string(dim));
+		if (num < 0) throw lb::Error("negative batch size");
+		int64_t first = h->add_host(vectors, num);
+		if (out_labels)
+			for (int32_t i = 0; i < num; i++) out_labels[i] = first + i;
+		return num;
+	})
+}
+
+int32_t lance_detached_add_batch_arrow(void *, void *, void *, int64_t *, char *err_buf, int err_buf_len) {
+	write_err(err_buf, err_buf_len,
+	          "add_batch_arrow failed: multi-column Arrow batches are outside the kNN path of the B200 backend");
+	return -1;
+}
+
+int32_t lance_detached_merge(void *, void *, const int64_t *, int32_t, int64_t *, int64_t *, char *err_buf,
+                             int err_buf_len) {
+	write_err(err_buf, err_buf_len, "merge failed: not supported by the B200 backend");
+	return -1;
+}
+
+int32_t lance_detached_search_batch(void *handle, const float *queries, int32_t nq, int32_t dim, int32_t k,
+                                    int32_t nprobes, int32_t refine_factor, const uint32_t *allow_bitmap,
+                                    int64_t bitmap_bits, int64_t *out_labels, float *out_distances,
+                                    int32_t *out_counts, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("search failed: ", -1, {
+		// rust_lib/src/lance_manager.rs:401-407
+		if (dim != h->dim())
+			throw lb::Error("expected query dimension " + std::to_string(h->dim()) + ", got " + std::to_string(dim));
+		if (nq < 0 || k < 0) throw lb::Error("negative batch size or k");
+		if (nq == 0) return 0;
+		if (!queries || !out_labels || !out_distances || !out_counts) throw lb::Error("null buffer");
+		h->search_host(queries, nq, k, nprobes, refine_factor, allow_bitmap, bitmap_bits, out_labels, out_distances,
+		               out_counts);
+		return nq;
+	})
+}
+
+int32_t lance_detached_search_filtered(void *handle, const float *query, int32_t dim, int32_t k, int32_t nprobes,
+                                       int32_t refine_factor, const uint32_t *allow_bitmap, int64_t bitmap_bits,
+                                       int64_t *out_labels, float *out_distances, char *err_buf, int err_buf_len) {
+	int32_t count = 0;
+	int32_t rc = lance_detached_search_batch(handle, query, 1, dim, k, nprobes, refine_factor, allow_bitmap,
+	                                         bitmap_bits, out_labels, out_distances, &count, err_buf, err_buf_len);
+	return rc < 0 ? -1 : count;
+}
+
+int32_t lance_detached_search(void *handle, const float *query, int32_t dim, int32_t k, int32_t nprobes,
+                              int32_t refine_factor, int64_t *out_labels, float *out_distances, char *err_buf,
+                              int err_buf_len) {
+	return lance_detached_search_filtered(handle, query, dim, k, nprobes, refine_factor, nullptr, 0, out_labels,
+	                                      out_distances, err_buf, err_buf_len);
+}
+
+int64_t lance_detached_count(void *handle, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("count failed: ", -1, { return h->live_rows(); })
+}
+
+int32_t lance_detached_delete_batch(void *handle, const int64_t *labels, int32_t count, char *err_buf,
+                                    int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("delete_batch failed: ", -1, {
+		h->delete_labels(labels, count);
+		return 0;
+	})
+}
+
+int32_t lance_detached_delete(void *handle, int64_t label, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("delete failed: ", -1, {
+		h->delete_labels(&label, 1);
+		return 0;
+	})
+}
+
+int32_t lance_detached_create_index(void *handle, int32_t num_partitions, int32_t num_sub_vectors, char *err_buf,
+                                    int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("create_index failed: ", -1, {
+		h->create_index(num_partitions, num_sub_vectors);
+		return 0;
+	})
+}
+
+int32_t lance_detached_create_hnsw_index(void *handle, int32_t, int32_t, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	(void)h;
+	write_err(err_buf, err_buf_len,
+	          "create_hnsw_index failed: IVF_HNSW_SQ is not part of the B200 backend (use lance_create_ann_index)");
+	return -1;
+}
+
+int32_t lance_detached_compact(void *handle, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	(void)h;
+	return 0; // nothing to compact: one contiguous device store, tombstones are bits
+}
+
+int32_t lance_detached_get_vector(void *handle, int64_t label, float *out_vec, int32_t capacity, char *err_buf,
+                                  int err_buf_len) {
+	LB_HANDLE(-1)
+	if (capacity < h->dim()) {
+		write_err(err_buf, err_buf_len, "output buffer too small");
+		return -1;
+	}
+	LB_TRY("get_vector failed: ", -1, {
+		h->get_vector(label, out_vec);
+		return h->dim();
+	})
+}
+
+int32_t lance_detached_get_all_vectors(void *handle, int64_t *out_labels, float *out_vectors, int64_t *out_count,
+                                       char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("get_all_vectors failed: ", -1, {
+		int64_t c = h->get_all(out_labels, out_vectors);
+		if (out_count) *out_count = c;
+		return 0;
+	})
+}
+
+// ------------------------------------------------------------------ Part 2
+
+int32_t lance_b200_search_device(void *handle, const float *d_queries, int32_t nq, int32_t k, int32_t nprobes,
+                                 int32_t refine_factor, const uint32_t *d_allow, int64_t bitmap_bits,
+                                 int64_t *d_out_labels, float *d_out_distances, int32_t *d_out_counts, void *stream,
+                                 char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("search failed: ", -1, {
+		h->search_device(d_queries, nq, k, nprobes, refine_factor, d_allow, bitmap_bits, d_out_labels, d_out_distances,
+		                 d_out_counts, static_cast<cudaStream_t>(stream));
+		return 0;
+	})
+}
+
+int32_t lance_b200_merge_topk_device(int32_t device, const int64_t *d_labels, const float *d_dists,
+                                     const int32_t *d_counts, int32_t G, int32_t nq, int32_t k,
+                                     int64_t *d_out_labels, float *d_out_dists, int32_t *d_out_counts, void *stream,
+                                     char *err_buf, int err_buf_len) {
+	LB_TRY("merge failed: ", -1, {
+		if (G <= 0 || nq < 0 || k < 0) throw lb::Error("bad shape");
+		if (nq == 0 || k == 0) return 0;
+		LB_CUDA(cudaSetDevice(device));
+		cudaStream_t s = static_cast<cudaStream_t>(stream);
+		size_t nkeys = (size_t)nq * G * k + (size_t)nq * k;
+		void *scratch = nullptr;
+		LB_CUDA(cudaMallocAsync(&scratch, nkeys * sizeof(lb::u64), s));
+		lb::u64 *keys = static_cast<lb::u64 *>(scratch);
+		try {
+			lb::launch_merge_lists(d_labels, d_dists, d_counts, G, nq, k, keys, keys + (size_t)nq * G * k, d_out_labels,
+			                       d_out_dists, d_out_counts, s, nullptr);
+		} catch (...) {
+			cudaFreeAsync(scratch, s);
+			throw;
+		}
+		LB_CUDA(cudaFreeAsync(scratch, s));
+		return 0;
+	})
+}
+
+int32_t lance_b200_set_label_base(void *handle, int64_t base, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("set_label_base failed: ", -1, {
+		h->set_label_base(base);
+		return 0;
+	})
+}
+
+int32_t lance_b200_reserve(void *handle, int64_t rows, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("reserve failed: ", -1, {
+		h->reserve(rows);
+		return 0;
+	})
+}
+
+int64_t lance_b200_add_batch_device(void *handle, const float *d_vectors, int64_t num, int32_t dim, void *stream,
+                                    char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("add_batch failed: ", -1, {
+		if (dim != h->dim())
+			throw lb::Error("expected dimension " + std::to_string(h->dim()) + ", got " + std::to_string(dim));
+		return h->add_device(d_vectors, num, static_cast<cudaStream_t>(stream));
+	})
+}
+
+int32_t lance_b200_set_ivfpq(void *handle, int32_t P, int32_t M, int64_t n_indexed, const float *centroids,
+                             const float *codebook, const int64_t *part_offsets, const int64_t *row_ids,
+                             const uint8_t *codes, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("set_ivfpq failed: ", -1, {
+		h->set_index(P, M, n_indexed, centroids, codebook, part_offsets, row_ids, codes);
+		return 0;
+	})
+}
+
+int32_t lance_b200_get_ivfpq(void *handle, lance_b200_ivfpq_info *info, float *centroids, float *codebook,
+                             int64_t *part_offsets, int64_t *row_ids, uint8_t *codes, char *err_buf,
+                             int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("get_ivfpq failed: ", -1, {
+		h->get_index(info, centroids, codebook, part_offsets, row_ids, codes);
+		return 0;
+	})
+}
+
+int32_t lance_b200_drop_index(void *handle, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("drop_index failed: ", -1, {
+		h->drop_index();
+		return 0;
+	})
+}
+
+int32_t lance_b200_ivfpq_search_debug(void *handle, const float *query, int32_t dim, int32_t k, int32_t nprobes,
+                                      int32_t refine_factor, const uint32_t *allow_bitmap, int64_t bitmap_bits,
+                                      int32_t *out_parts, int64_t *out_cand_labels, float *out_cand_adc,
+                                      int32_t *out_ncand, int64_t *out_labels, float *out_distances, char *err_buf,
+                                      int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("search failed: ", -1, {
+		if (dim != h->dim())
+			throw lb::Error("expected query dimension " + std::to_string(h->dim()) + ", got " + std::to_string(dim));
+		int32_t count = 0;
+		h->ivfpq_search_debug(query, k, nprobes, refine_factor, allow_bitmap, bitmap_bits, out_parts, out_cand_labels,
+		                      out_cand_adc, out_ncand, out_labels, out_distances, &count);
+		return count;
+	})
+}
+
+int32_t lance_b200_save(void *handle, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("save failed: ", -1, {
+		h->save();
+		return 0;
+	})
+}
+
+int32_t lance_b200_stats(void *handle, lance_b200_stats_t *out) {
+	if (!handle || !out) return -1;
+	try {
+		static_cast<Store *>(handle)->stats(out);
+		return 0;
+	} catch (...) {
+		return -1;
+	}
+}
+
+int32_t lance_b200_profile_enable(void *handle, int32_t on) {
+	if (!handle) return -1;
+	static_cast<Store *>(handle)->set_profile(on != 0);
+	return 0;
+}
+
+int32_t lance_b200_profile_read(void *handle, lance_b200_profile_t *out) {
+	if (!handle || !out) return -1;
+	try {
+		static_cast<Store *>(handle)->read_profile(out);
+		return 0;
+	} catch (...) {
+		return -1;
+	}
+}
+
+int32_t lance_b200_set_flat_path(void *handle, int32_t mode) {
+	if (!handle || mode < 0 || mode > 2) return -1;
+	static_cast<Store *>(handle)->set_flat_path(mode);
+	return 0;
+}
+
+int32_t lance_b200_set_default_device(int32_t device) {
+	lb::set_default_device(device);
+	return 0;
+}
+
+int32_t lance_b200_device_count(void) {
+	int c = 0;
+	if (cudaGetDeviceCount(&c) != cudaSuccess) {
+		(void)cudaGetLastError();
+		return 0;
+	}
+	return c;
+}
+
+const char *lance_b200_version(void) { return "lance_b200 0.1 (sm_100a)"; }
+
+} // extern "C"

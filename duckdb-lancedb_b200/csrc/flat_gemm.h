@@ -1,0 +1,32 @@
+// flat_gemm.h — batched flat search on the tensor cores: bf16 tcgen05 candidate GEMM with a fused
+// threshold filter, then an exact fp32 re-rank (see flat_gemm.cu for the design).
+#pragma once
+#include "store.h"
+
+namespace lb {
+
+class FlatGemm {
+public:
+	FlatGemm(int device, int num_sms, int dim, int metric);
+	~FlatGemm();
+
+	// is the tensor path implemented for this shape at all
+	static bool supported(int dim, int k);
+	// is it the faster choice (auto mode)
+	static bool worthwhile(int nq, long long n, int dim, int k);
+
+	// the bf16 shadow copy of X and the per-row norms follow the store: convert rows [done, n)
+	void sync_rows(const float *X, long long n, long long cap_rows, cudaStream_t s, int64_t *launches);
+	void invalidate(); // X was reallocated
+
+	void search(const float *X, long long n, const uint32_t *deleted, const float *d_queries, int nq, int k,
+	            const uint32_t *d_allow, long long allow_bits, long long label_base, int64_t *d_out_labels,
+	            float *d_out_dist, int32_t *d_out_counts, Workspace &ws, cudaStream_t s, int64_t *launches,
+	            int64_t *fallback_queries);
+
+private:
+	struct Impl;
+	Impl *impl_;
+};
+
+} // namespace lb

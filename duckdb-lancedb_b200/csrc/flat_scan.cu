@@ -1,0 +1,444 @@
+// flat_scan.cu — exact fp32 flat kNN scan for small query batches (1..4 queries per pass).
+//
+// Replaces the CPU hot loop the reference enters at rust_lib/src/lance_manager.rs:411-419 when the
+// table has no ANN index: for every live row d(q,x), keep the k smallest.
+//   L2 = sum (q-x)^2 (squared, test/sql/lance_basic.test:40-42), cosine = 1 - q.x/(|q||x|),
+//   dot = 1 - q.x.
+//
+// Roofline: HBM.  One pass over X (n*d*4 bytes) per batch of <= 4 queries; arithmetic intensity is
+// <= 2 flop/B, far under the fp32 ridge, so no tensor cores here (the batched tcgen05 path lives in
+// flat_gemm.cu).  Layout/mapping:
+//   * X is row-major fp32 [n][d]; a warp takes 8 consecutive rows (8*d*4 contiguous bytes) and reads
+//     them with 128-bit loads, lane l covering float4 chunks l, l+32, ... of every row -> each load
+//     instruction of the warp covers 512 contiguous bytes, 8 independent loads in flight per lane;
+//   * queries sit in shared memory (one conflict-free LDS.128 per chunk, reused for the 8 rows);
+//   * the 8 per-row partial sums are combined with a transposed butterfly (9 shuffles per 8 rows
+//     instead of 40), after which lane l holds the total of row (l>>2)&7;
+//   * selection is fused (topk.cuh): nothing but the k best keys per block leaves the SM;
+//   * blocks share their k-th best key through one global word per query (atomicMin) so late
+//     blocks reject almost everything with a single compare.
+#include "kernels.h"
+#include "topk.cuh"
+
+namespace lb {
+
+// Transposed warp reduction: v[i] = this lane's partial sum for row i (8 rows).  Returns the full
+// 32-lane sum of row (lane>>2)&7.  7 + 2 shuffles.
+__device__ __forceinline__ float reduce8(float (&v)[8]) {
+	const unsigned lane = lane_id();
+	{
+		const bool up = lane & 16;
+#pragma unroll
+		for (int i = 0; i < 4; i++) {
+			float send = up ? v[i] : v[i + 4];
+			float keep = up ? v[i + 4] : v[i];
+			v[i] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 16);
+		}
+	}
+	{
+		const bool up = lane & 8;
+#pragma unroll
+		for (int i = 0; i < 2; i++) {
+			float send = up ? v[i] : v[i + 2];
+			float keep = up ? v[i + 2] : v[i];
+			v[i] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 8);
+		}
+	}
+	{
+		const bool up = lane & 4;
+		float send = up ? v[0] : v[1];
+		float keep = up ? v[1] : v[0];
+		v[0] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 4);
+	}
+	float s = v[0];
+	s += __shfl_xor_sync(0xFFFFFFFFu, s, 2);
+	s += __shfl_xor_sync(0xFFFFFFFFu, s, 1);
+	return s;
+}
+
+template <int VEC>
+struct XVec;
+template <>
+struct XVec<4> {
+	float4 v;
+	__device__ __forceinline__ void zero() { v = make_float4(0.f, 0.f, 0.f, 0.f); }
+	__device__ __forceinline__ void load(const float *p) { v = __ldg(reinterpret_cast<const float4 *>(p)); }
+	__device__ __forceinline__ void load_shared(const float *p) { v = *reinterpret_cast<const float4 *>(p); }
+};
+template <>
+struct XVec<1> {
+	float v;
+	__device__ __forceinline__ void zero() { v = 0.f; }
+	__device__ __forceinline__ void load(const float *p) { v = __ldg(p); }
+	__device__ __forceinline__ void load_shared(const float *p) { v = *p; }
+};
+
+template <int METRIC>
+__device__ __forceinline__ void accum(float &acc, const XVec<4> &q, const XVec<4> &x) {
+	if (METRIC == METRIC_L2) {
+		float a = q.v.x - x.v.x, b = q.v.y - x.v.y, c = q.v.z - x.v.z, e = q.v.w - x.v.w;
+		acc = fmaf(a, a, acc);
+		acc = fmaf(b, b, acc);
+		acc = fmaf(c, c, acc);
+		acc = fmaf(e, e, acc);
+	} else {
+		acc = fmaf(q.v.x, x.v.x, acc);
+		acc = fmaf(q.v.y, x.v.y, acc);
+		acc = fmaf(q.v.z, x.v.z, acc);
+		acc = fmaf(q.v.w, x.v.w, acc);
+	}
+}
+template <int METRIC>
+__device__ __forceinline__ void accum(float &acc, const XVec<1> &q, const XVec<1> &x) {
+	if (METRIC == METRIC_L2) {
+		float a = q.v - x.v;
+		acc = fmaf(a, a, acc);
+	} else {
+		acc = fmaf(q.v, x.v, acc);
+	}
+}
+__device__ __forceinline__ void accum_norm(float &acc, const XVec<4> &x) {
+	acc = fmaf(x.v.x, x.v.x, acc);
+	acc = fmaf(x.v.y, x.v.y, acc);
+	acc = fmaf(x.v.z, x.v.z, acc);
+	acc = fmaf(x.v.w, x.v.w, acc);
+}
+__device__ __forceinline__ void accum_norm(float &acc, const XVec<1> &x) { acc = fmaf(x.v, x.v, acc); }
+
+// distance in the reference's reported units from the accumulated sums
+template <int METRIC>
+__device__ __forceinline__ float finish_distance(float acc, float qnorm2, float xnorm2) {
+	if (METRIC == METRIC_L2) return acc;
+	if (METRIC == METRIC_DOT) return 1.0f - acc;
+	float den = sqrtf(qnorm2) * sqrtf(xnorm2);
+	if (!(den > 0.f)) return 1.0f;
+	float sim = acc / den;
+	sim = fminf(1.f, fmaxf(-1.f, sim));
+	return 1.0f - sim;
+}
+
+// liveness of the 8 rows [row0, row0+8), row0 % 8 == 0
+__device__ __forceinline__ unsigned live_mask8(long long row0, long long row_begin, long long n,
+                                               const uint32_t *allow, long long allow_bits,
+                                               const uint32_t *deleted) {
+	unsigned m = 0xFFu;
+	long long left = n - row0;
+	if (left < 8) m = (1u << (int)left) - 1u;
+	if (row0 < row_begin) m &= ~((1u << (int)(row_begin - row0)) - 1u);
+	const int sh = (int)(row0 & 31);
+	if (deleted) m &= ~(__ldg(deleted + (row0 >> 5)) >> sh);
+	if (allow) {
+		unsigned a = 0;
+		if (row0 < allow_bits) {
+			a = (__ldg(allow + (row0 >> 5)) >> sh) & 0xFFu;
+			long long aleft = allow_bits - row0;
+			if (aleft < 8) a &= (1u << (int)aleft) - 1u;
+		}
+		m &= a;
+	}
+	return m & 0xFFu;
+}
+
+template <int METRIC, int QB, int VEC>
+__global__ void __launch_bounds__(256) flat_scan_kernel(const float *__restrict__ X, long long row_begin, long long n,
+                                                         int d, const float *__restrict__ Q, int nq_valid, int k, int cap,
+                                                         const uint32_t *__restrict__ allow, long long allow_bits,
+                                                         const uint32_t *__restrict__ deleted,
+                                                         u64 *__restrict__ partials, u64 *g_tau) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int nwarps = blockDim.x >> 5;
+	const int warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	const int dpad = (d + 3) & ~3;
+	float *qs = reinterpret_cast<float *>(smem_raw);                  // [QB][dpad]
+	float *qn = qs + QB * dpad;                                       // [QB] (padded to 4)
+	int *cnts = reinterpret_cast<int *>(qn + 4);                      // [nwarps][QB]
+	u64 *bufs = reinterpret_cast<u64 *>(smem_raw + (((size_t)(QB * dpad + 4) * 4 + (size_t)nwarps * QB * 4 + 15) & ~(size_t)15));
+
+	for (int i = threadIdx.x; i < QB * dpad; i += blockDim.x) {
+		int j = i / dpad, c = i - j * dpad;
+		qs[i] = (j < nq_valid && c < d) ? Q[(size_t)j * d + c] : 0.f;
+	}
+	__syncthreads();
+	if (warp == 0) {
+		for (int j = 0; j < QB; j++) {
+			float s = 0.f;
+			for (int c = lane; c < d; c += 32) s = fmaf(qs[j * dpad + c], qs[j * dpad + c], s);
+			for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+			if (lane == 0) qn[j] = s;
+		}
+	}
+	__syncthreads();
+
+	WarpSelect sel[QB];
+#pragma unroll
+	for (int j = 0; j < QB; j++) sel[j].init(bufs + ((size_t)warp * QB + j) * cap, cap, k);
+
+	const int nvec = d / VEC;
+	const long long ngroups = (n + 7) >> 3;
+	const long long gstride = (long long)gridDim.x * nwarps;
+	int iter = 0;
+	for (long long g = (row_begin >> 3) + (long long)blockIdx.x * nwarps + warp; g < ngroups; g += gstride, iter++) {
+		const long long row0 = g << 3;
+		const unsigned live = live_mask8(row0, row_begin, n, allow, allow_bits, deleted);
+		if (live == 0) continue;
+		float acc[QB][8];
+		float nx[8];
+#pragma unroll
+		for (int r = 0; r < 8; r++) {
+			nx[r] = 0.f;
+#pragma unroll
+			for (int j = 0; j < QB; j++) acc[j][r] = 0.f;
+		}
+		// Rows that are filtered out (or beyond n) are redirected to the group's first live row: the load
+		// stays unconditional (so the 8 loads issue back to back) but touches no extra cache line.
+		const int first_live = __ffs(live) - 1;
+		const float *rp[8];
+#pragma unroll
+		for (int r = 0; r < 8; r++)
+			rp[r] = X + ((size_t)row0 + (((live >> r) & 1u) ? r : first_live)) * d + (size_t)lane * VEC;
+		for (int c = lane; c < nvec; c += 32) {
+			XVec<VEC> xv[8];
+#pragma unroll
+			for (int r = 0; r < 8; r++) {
+				xv[r].load(rp[r]);
+				rp[r] += 32 * VEC;
+			}
+			XVec<VEC> qv[QB];
+#pragma unroll
+			for (int j = 0; j < QB; j++) qv[j].load_shared(qs + j * dpad + c * VEC);
+#pragma unroll
+			for (int r = 0; r < 8; r++) {
+#pragma unroll
+				for (int j = 0; j < QB; j++) accum<METRIC>(acc[j][r], qv[j], xv[r]);
+				if (METRIC == METRIC_COSINE) accum_norm(nx[r], xv[r]);
+			}
+		}
+		float xn = 0.f;
+		if (METRIC == METRIC_COSINE) xn = reduce8(nx);
+		const int r = (lane >> 2) & 7;
+		const bool row_live = (live >> r) & 1u;
+		const uint32_t row = (uint32_t)(row0 + r);
+#pragma unroll
+		for (int j = 0; j < QB; j++) {
+			float s = reduce8(acc[j]);
+			float dist = finish_distance<METRIC>(s, qn[j], xn);
+			bool mine = row_live && ((lane & 3u) == (unsigned)(j & 3)) && (j < nq_valid);
+			sel[j].push(mine, make_key(dist, row));
+		}
+		if ((iter & 15) == 15) {
+#pragma unroll
+			for (int j = 0; j < QB; j++) {
+				u64 gt = *reinterpret_cast<volatile u64 *>(g_tau + j);
+				if (sel[j].tau < gt) {
+					if (lane == 0) atomicMin(g_tau + j, sel[j].tau);
+				} else {
+					sel[j].tighten(gt);
+				}
+			}
+		}
+	}
+
+#pragma unroll
+	for (int j = 0; j < QB; j++) {
+		sel[j].finalize();
+		if (lane == 0) cnts[warp * QB + j] = sel[j].cnt;
+	}
+	__syncthreads();
+	// block merge: warp (j % nwarps) folds the other warps' lists of query j into its own
+#pragma unroll
+	for (int j = 0; j < QB; j++) {
+		if (warp != (j % nwarps)) continue;
+		for (int w = 0; w < nwarps; w++) {
+			if (w == warp) continue;
+			const u64 *src = bufs + ((size_t)w * QB + j) * cap;
+			const int c = cnts[w * QB + j];
+			for (int i0 = 0; i0 < c; i0 += 32) {
+				int i = i0 + lane;
+				u64 key = (i < c) ? src[i] : KEY_INVALID;
+				sel[j].push(i < c, key);
+			}
+		}
+		sel[j].finalize();
+		u64 *dst = partials + ((size_t)j * gridDim.x + blockIdx.x) * k;
+		for (int i = lane; i < k; i += 32) dst[i] = (i < sel[j].cnt) ? sel[j].buf[i] : KEY_INVALID;
+		if (lane == 0 && sel[j].cnt == k) atomicMin(g_tau + j, sel[j].tau);
+	}
+}
+
+// Final select: keys[q][m] (KEY_INVALID entries ignored) -> sorted (label, distance) lists.
+// One block per query; also used for the multi-GPU merge (keys rebuilt from gathered lists).
+__global__ void __launch_bounds__(256) topk_merge_kernel(const u64 *__restrict__ keys, long long m, int k, int cap,
+                                                          long long label_base, int64_t *__restrict__ out_labels,
+                                                          float *__restrict__ out_dist, int32_t *__restrict__ out_counts,
+                                                          u64 *__restrict__ out_keys) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int nwarps = blockDim.x >> 5;
+	const int warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	int *cnts = reinterpret_cast<int *>(smem_raw);
+	u64 *bufs = reinterpret_cast<u64 *>(smem_raw + 64);
+	const int q = blockIdx.x;
+	const u64 *src = keys + (size_t)q * m;
+
+	WarpSelect sel;
+	sel.init(bufs + (size_t)warp * cap, cap, k);
+	for (long long i0 = (long long)warp * 32; i0 < m; i0 += (long long)nwarps * 32) {
+		long long i = i0 + lane;
+		u64 key = (i < m) ? src[i] : KEY_INVALID;
+		sel.push(key != KEY_INVALID, key);
+	}
+	sel.finalize();
+	if (lane == 0) cnts[warp] = sel.cnt;
+	__syncthreads();
+	if (warp != 0) return;
+	for (int w = 1; w < nwarps; w++) {
+		const u64 *s2 = bufs + (size_t)w * cap;
+		const int c = cnts[w];
+		for (int i0 = 0; i0 < c; i0 += 32) {
+			int i = i0 + lane;
+			u64 key = (i < c) ? s2[i] : KEY_INVALID;
+			sel.push(i < c, key);
+		}
+	}
+	sel.finalize();
+	for (int i = lane; i < k; i += 32) {
+		bool ok = i < sel.cnt;
+		u64 key = ok ? sel.buf[i] : KEY_INVALID;
+		if (out_labels) out_labels[(size_t)q * k + i] = ok ? (int64_t)(label_base + (long long)key_row(key)) : -1;
+		if (out_dist) out_dist[(size_t)q * k + i] = ok ? key_dist(key) : __int_as_float(0x7F800000);
+		if (out_keys) out_keys[(size_t)q * k + i] = key;
+	}
+	if (lane == 0 && out_counts) out_counts[q] = sel.cnt;
+}
+
+__global__ void fill_u64_kernel(u64 *p, long long n, u64 v) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) p[i] = v;
+}
+
+// ------------------------------------------------------------------------------------------------ host
+
+typedef void (*scan_kernel_t)(const float *, long long, long long, int, const float *, int, int, int, const uint32_t *, long long,
+                              const uint32_t *, u64 *, u64 *);
+
+template <int METRIC, int QB>
+static scan_kernel_t scan_kernel_vec(bool vec4) {
+	return vec4 ? (scan_kernel_t)flat_scan_kernel<METRIC, QB, 4> : (scan_kernel_t)flat_scan_kernel<METRIC, QB, 1>;
+}
+template <int QB>
+static scan_kernel_t scan_kernel_metric(int metric, bool vec4) {
+	switch (metric) {
+	case METRIC_COSINE: return scan_kernel_vec<METRIC_COSINE, QB>(vec4);
+	case METRIC_DOT: return scan_kernel_vec<METRIC_DOT, QB>(vec4);
+	default: return scan_kernel_vec<METRIC_L2, QB>(vec4);
+	}
+}
+static scan_kernel_t scan_kernel(int metric, int QB, bool vec4) {
+	switch (QB) {
+	case 4: return scan_kernel_metric<4>(metric, vec4);
+	case 2: return scan_kernel_metric<2>(metric, vec4);
+	default: return scan_kernel_metric<1>(metric, vec4);
+	}
+}
+
+static size_t scan_smem_bytes(int QB, int d, int nwarps, int cap) {
+	int dpad = (d + 3) & ~3;
+	size_t head = (((size_t)(QB * dpad + 4) * 4 + (size_t)nwarps * QB * 4 + 15) & ~(size_t)15);
+	return head + (size_t)nwarps * QB * cap * sizeof(u64);
+}
+
+static const size_t SMEM_BUDGET = 200 * 1024;
+
+FlatScanPlan plan_flat_scan(const float *X, int metric, int d, int k, int nq, long long n_scan, int num_sms) {
+	const long long n = n_scan;
+	FlatScanPlan p;
+	p.cap = warpsel_cap(k);
+	int QB = nq >= 4 ? 4 : (nq >= 2 ? 2 : 1);
+	int nwarps = 8;
+	while (true) {
+		while (nwarps > 1 && scan_smem_bytes(QB, d, nwarps, p.cap) > SMEM_BUDGET) nwarps >>= 1;
+		if (scan_smem_bytes(QB, d, nwarps, p.cap) <= SMEM_BUDGET) break;
+		if (QB == 1)
+			throw Error("k=" + std::to_string(k) + " with dimension " + std::to_string(d) +
+			            " is too large for the device scan");
+		QB >>= 1;
+		nwarps = 8;
+	}
+	p.QB = QB;
+	p.nwarps = nwarps;
+	p.smem = scan_smem_bytes(QB, d, nwarps, p.cap);
+	p.vec4 = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
+	p.kernel = (const void *)scan_kernel(metric, QB, p.vec4);
+	if (p.smem > 48 * 1024)
+		LB_CUDA(cudaFuncSetAttribute(p.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
+	int per_sm = 1;
+	LB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, p.kernel, nwarps * 32, p.smem));
+	if (per_sm < 1) per_sm = 1;
+	long long ngroups = (n + 7) / 8;
+	long long want = (ngroups + nwarps - 1) / nwarps;
+	long long full = (long long)num_sms * per_sm;
+	p.grid = (int)(want < full ? (want < 1 ? 1 : want) : full);
+	return p;
+}
+
+size_t flat_scan_scratch_bytes(const FlatScanPlan &p, int k) {
+	return ((size_t)p.QB * p.grid * k + 8) * sizeof(u64);
+}
+
+static void merge_launch_params(long long m, int k, int &nwarps, int &cap, size_t &smem) {
+	cap = warpsel_cap(k);
+	nwarps = 8;
+	while (nwarps > 1 && (long long)(nwarps / 2) * 32 >= m) nwarps >>= 1;
+	while (nwarps > 1 && 64 + (size_t)nwarps * cap * 8 > SMEM_BUDGET) nwarps >>= 1;
+	smem = 64 + (size_t)nwarps * cap * 8;
+	if (smem > SMEM_BUDGET) throw Error("k too large for the device merge");
+}
+
+void launch_topk_merge(const u64 *keys, int nq, long long m, int k, long long label_base, int64_t *out_labels,
+                       float *out_dist, int32_t *out_counts, u64 *out_keys, cudaStream_t s, int64_t *launches) {
+	if (nq <= 0) return;
+	int nwarps, cap;
+	size_t smem;
+	merge_launch_params(m, k, nwarps, cap, smem);
+	if (smem > 48 * 1024)
+		LB_CUDA(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	topk_merge_kernel<<<nq, nwarps * 32, smem, s>>>(keys, m, k, cap, label_base, out_labels, out_dist, out_counts,
+	                                                  out_keys);
+	LB_CUDA(cudaGetLastError());
+	if (launches) (*launches)++;
+}
+
+void fill_u64(u64 *p, long long n, u64 v, cudaStream_t s, int64_t *launches) {
+	if (n <= 0) return;
+	fill_u64_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p, n, v);
+	LB_CUDA(cudaGetLastError());
+	if (launches) (*launches)++;
+}
+
+// Runs the scan for a.nq queries (any count) in passes of plan.QB; results land in the out_* device buffers.
+void run_flat_scan(const FlatScanArgs &a, const FlatScanPlan &p, void *scratch, cudaStream_t s, int64_t *launches) {
+	u64 *g_tau = reinterpret_cast<u64 *>(scratch);
+	u64 *partials = g_tau + 8;
+	for (int q0 = 0; q0 < a.nq; q0 += p.QB) {
+		int nv = a.nq - q0 < p.QB ? a.nq - q0 : p.QB;
+		LB_CUDA(cudaMemsetAsync(g_tau, 0xFF, 8 * sizeof(u64), s)); // KEY_INVALID
+		const float *dQ = a.dQ + (size_t)q0 * a.d;
+		const float *X = a.X;
+		long long n = a.n, allow_bits = a.allow_bits, row_begin = a.row_begin;
+		int d = a.d, k = a.k, cap = p.cap;
+		const uint32_t *allow = a.allow, *deleted = a.deleted;
+		void *args[] = {&X, &row_begin, &n, &d, &dQ, &nv, &k, &cap, &allow, &allow_bits, &deleted, &partials, &g_tau};
+		int tix = a.timer ? a.timer->begin(KC_FLAT_SCAN, s) : -1;
+		LB_CUDA(cudaLaunchKernel(p.kernel, dim3(p.grid), dim3(p.nwarps * 32), args, p.smem, s));
+		if (a.timer) a.timer->end(tix, s);
+		if (launches) (*launches)++;
+		launch_topk_merge(partials, nv, (long long)p.grid * a.k, a.k, a.label_base,
+		                  a.out_labels ? a.out_labels + (size_t)q0 * a.k : nullptr,
+		                  a.out_dist ? a.out_dist + (size_t)q0 * a.k : nullptr,
+		                  a.out_counts ? a.out_counts + q0 : nullptr,
+		                  a.out_keys ? a.out_keys + (size_t)q0 * a.k : nullptr, s, launches);
+	}
+}
+
+} // namespace lb

@@ -1,0 +1,120 @@
+// kernels.h — host-side launch interfaces of the CUDA kernels (internal to liblance_b200).
+#pragma once
+#include "common.cuh"
+
+#include <mutex>
+#include <vector>
+
+namespace lb {
+
+// Optional CUDA-event bracket around the dominant kernels (bench.py's roofline.achieved): events are
+// recorded on the launching stream, read back after a synchronise.
+enum KernelClass : int { KC_FLAT_SCAN = 0, KC_FLAT_GEMM = 1, KC_ADC_SCAN = 2, KC_RERANK = 3, KC_COUNT = 4 };
+struct KernelTimer {
+	bool on = false;
+	std::mutex mu;
+	struct Rec {
+		cudaEvent_t a, b;
+		int cls;
+	};
+	std::vector<Rec> recs;
+	std::vector<cudaEvent_t> free_events;
+	cudaEvent_t get_event() {
+		if (!free_events.empty()) {
+			cudaEvent_t e = free_events.back();
+			free_events.pop_back();
+			return e;
+		}
+		cudaEvent_t e;
+		LB_CUDA(cudaEventCreate(&e));
+		return e;
+	}
+	// returns an index to pass to end(), or -1 when off
+	int begin(int cls, cudaStream_t s) {
+		if (!on) return -1;
+		std::lock_guard<std::mutex> g(mu);
+		Rec r{get_event(), get_event(), cls};
+		LB_CUDA(cudaEventRecord(r.a, s));
+		recs.push_back(r);
+		return (int)recs.size() - 1;
+	}
+	void end(int idx, cudaStream_t s) {
+		if (idx < 0) return;
+		std::lock_guard<std::mutex> g(mu);
+		LB_CUDA(cudaEventRecord(recs[idx].b, s));
+	}
+	// sums and clears; the caller has synchronised the device
+	void read(double ms[KC_COUNT], int64_t n[KC_COUNT]) {
+		std::lock_guard<std::mutex> g(mu);
+		for (int i = 0; i < KC_COUNT; i++) ms[i] = 0, n[i] = 0;
+		for (auto &r : recs) {
+			float t = 0.f;
+			if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) {
+				ms[r.cls] += t;
+				n[r.cls]++;
+			}
+			free_events.push_back(r.a);
+			free_events.push_back(r.b);
+		}
+		recs.clear();
+	}
+	~KernelTimer() {
+		for (auto &r : recs) {
+			cudaEventDestroy(r.a);
+			cudaEventDestroy(r.b);
+		}
+		for (auto e : free_events) cudaEventDestroy(e);
+	}
+};
+
+// ------------------------------------------------------------------ flat_scan.cu
+struct FlatScanArgs {
+	const float *X = nullptr; // [n][d] fp32, device
+	long long n = 0;
+	int d = 0;
+	int metric = METRIC_L2;
+	const float *dQ = nullptr; // [nq][d] fp32, device
+	int nq = 0;
+	int k = 0;
+	const uint32_t *allow = nullptr; // device bitmap or null
+	long long allow_bits = 0;
+	const uint32_t *deleted = nullptr; // device tombstones or null
+	long long label_base = 0;
+	int64_t *out_labels = nullptr; // [nq][k] device (nullable)
+	float *out_dist = nullptr;     // [nq][k] device (nullable)
+	int32_t *out_counts = nullptr; // [nq] device (nullable)
+	u64 *out_keys = nullptr;       // [nq][k] device (nullable): raw keys, row-relative
+	long long row_begin = 0;       // only rows >= row_begin are scanned (IVF_PQ's unindexed tail)
+	KernelTimer *timer = nullptr;
+};
+
+struct FlatScanPlan {
+	int QB = 1;     // queries per pass (1, 2 or 4)
+	int nwarps = 8; // warps per block
+	int cap = 64;   // per-warp selection buffer entries
+	int grid = 1;
+	size_t smem = 0;
+	bool vec4 = true;
+	const void *kernel = nullptr;
+};
+
+FlatScanPlan plan_flat_scan(const float *X, int metric, int d, int k, int nq, long long n, int num_sms);
+size_t flat_scan_scratch_bytes(const FlatScanPlan &p, int k);
+void run_flat_scan(const FlatScanArgs &a, const FlatScanPlan &p, void *scratch, cudaStream_t s, int64_t *launches);
+
+// keys[nq][m] -> sorted lists; any out pointer may be null
+void launch_topk_merge(const u64 *keys, int nq, long long m, int k, long long label_base, int64_t *out_labels,
+                       float *out_dist, int32_t *out_counts, u64 *out_keys, cudaStream_t s, int64_t *launches);
+void fill_u64(u64 *p, long long n, u64 v, cudaStream_t s, int64_t *launches);
+
+// ------------------------------------------------------------------ store_kernels.cu
+void launch_set_bits(uint32_t *bitmap, const int64_t *d_rows, int count, long long nrows, cudaStream_t s,
+                     int64_t *launches);
+// Final select over G gathered per-shard lists (labels, dists)[G][nq][k], counts[G][nq].  Keys carry the
+// index g*k+i, which orders ties like the label does because shard g holds a lower label range than
+// shard g+1 and every list is already (distance, label)-sorted.  scratch: (nq*G*k + nq*k) u64.
+void launch_merge_lists(const int64_t *labels, const float *dists, const int32_t *counts, int G, int nq, int k,
+                        u64 *scratch_keys, u64 *scratch_sel, int64_t *out_labels, float *out_dists,
+                        int32_t *out_counts, cudaStream_t s, int64_t *launches);
+
+} // namespace lb

@@ -1,0 +1,455 @@
+// store.cu — device store lifecycle and the flat-search orchestration (see store.h).
+#include "store.h"
+
+#include <sys/stat.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "ivfpq.h"
+#include "flat_gemm.h"
+
+namespace lb {
+
+// ------------------------------------------------------------------ device selection
+static std::atomic<int> g_default_device{-1};
+
+int default_device() {
+	int d = g_default_device.load();
+	if (d >= 0) return d;
+	const char *e = getenv("LANCE_B200_DEVICE");
+	if (!e) e = getenv("LOCAL_RANK"); // one process per GPU under torchrun
+	int count = 0;
+	if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0)
+		throw Error("no CUDA device available: liblance_b200 has no CPU fallback");
+	d = e ? atoi(e) : 0;
+	if (d < 0 || d >= count) d = 0;
+	return d;
+}
+void set_default_device(int d) { g_default_device.store(d); }
+
+// ------------------------------------------------------------------ buffers
+void DevBuf::release() {
+	if (p) cudaFree(p);
+	p = nullptr;
+	bytes = 0;
+}
+void DevBuf::alloc(size_t n) {
+	release();
+	if (n == 0) return;
+	cudaError_t e = cudaMalloc(&p, n);
+	if (e != cudaSuccess) {
+		p = nullptr;
+		(void)cudaGetLastError();
+		throw Error("device allocation of " + std::to_string(n) + " bytes failed: " + cudaGetErrorString(e));
+	}
+	bytes = n;
+}
+void DevBuf::ensure(size_t n) {
+	if (n > bytes) alloc(n + n / 4 + 256);
+}
+
+Workspace::Workspace(bool own_stream) {
+	if (own_stream) LB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+}
+Workspace::~Workspace() {
+	if (stream) cudaStreamDestroy(stream);
+}
+
+// ------------------------------------------------------------------ Store
+static int metric_from_string(const std::string &m) {
+	// rust_lib/src/lance_manager.rs:493-497
+	if (m == "cosine") return METRIC_COSINE;
+	if (m == "dot" || m == "ip") return METRIC_DOT;
+	return METRIC_L2;
+}
+
+Store::Store(const std::string &db_path, const std::string &table, int dim, const std::string &metric, int device)
+    : db_path_(db_path), table_(table), dim_(dim), metric_(metric_from_string(metric)), device_(device) {
+	if (dim <= 0) throw Error("dimension must be positive");
+	LB_CUDA(cudaSetDevice(device_));
+	cudaDeviceProp prop;
+	LB_CUDA(cudaGetDeviceProperties(&prop, device_));
+	num_sms_ = prop.multiProcessorCount;
+	if (prop.major < 10)
+		throw Error(std::string("liblance_b200 targets sm_100a (B200); device is ") + prop.name);
+	LB_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+	if (!db_path_.empty()) dir_ = db_path_ + "/" + (table_.empty() ? std::string("vectors") : table_) + ".b200";
+}
+
+Store::~Store() {
+	cudaSetDevice(device_);
+	cudaDeviceSynchronize();
+	stream_ws_.clear();
+	io_pool_.clear();
+	flat_gemm_.reset();
+	index_.reset();
+	if (copy_stream_) cudaStreamDestroy(copy_stream_);
+}
+
+std::unique_ptr<Workspace> Store::acquire_io() {
+	{
+		std::lock_guard<std::mutex> g(ws_mu_);
+		if (!io_pool_.empty()) {
+			auto ws = std::move(io_pool_.back());
+			io_pool_.pop_back();
+			return ws;
+		}
+	}
+	return std::unique_ptr<Workspace>(new Workspace(true));
+}
+void Store::release_io(std::unique_ptr<Workspace> ws) {
+	std::lock_guard<std::mutex> g(ws_mu_);
+	io_pool_.push_back(std::move(ws));
+}
+Workspace *Store::scratch_for(cudaStream_t s) {
+	std::lock_guard<std::mutex> g(ws_mu_);
+	for (auto &e : stream_ws_)
+		if (e.first == s) return e.second.get();
+	stream_ws_.emplace_back(s, std::unique_ptr<Workspace>(new Workspace(false)));
+	return stream_ws_.back().second.get();
+}
+
+void Store::set_label_base(int64_t base) {
+	std::unique_lock<std::shared_mutex> lk(mu_);
+	if (n_rows_ != 0) throw Error("label base can only be set on an empty store");
+	label_base_ = base;
+}
+
+void Store::ensure_capacity(int64_t rows) {
+	if (rows <= cap_rows_) return;
+	if (rows >= (1ll << 32)) throw Error("more than 2^32 rows per device store are not supported");
+	int64_t ncap = std::max<int64_t>(rows, std::max<int64_t>(cap_rows_ * 2, 4096));
+	ncap = (ncap + 255) & ~255ll;
+	if (ncap >= (1ll << 32)) ncap = (1ll << 32) - 256;
+	DevBuf nx, nd;
+	nx.alloc((size_t)ncap * dim_ * sizeof(float));
+	nd.alloc((size_t)(ncap / 32) * sizeof(uint32_t));
+	LB_CUDA(cudaMemsetAsync(nd.p, 0, nd.bytes, copy_stream_));
+	if (n_rows_ > 0) {
+		LB_CUDA(cudaMemcpyAsync(nx.p, X_.p, (size_t)n_rows_ * dim_ * sizeof(float), cudaMemcpyDeviceToDevice, copy_stream_));
+		LB_CUDA(cudaMemcpyAsync(nd.p, deleted_.p, (size_t)((n_rows_ + 31) / 32) * sizeof(uint32_t),
+		                        cudaMemcpyDeviceToDevice, copy_stream_));
+	}
+	LB_CUDA(cudaStreamSynchronize(copy_stream_));
+	std::swap(X_.p, nx.p);
+	std::swap(X_.bytes, nx.bytes);
+	std::swap(deleted_.p, nd.p);
+	std::swap(deleted_.bytes, nd.bytes);
+	cap_rows_ = ncap;
+	deleted_host_.resize((size_t)(ncap / 32), 0u);
+	if (flat_gemm_) flat_gemm_->invalidate();
+}
+
+void Store::reserve(int64_t rows) {
+	std::unique_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	ensure_capacity(rows);
+}
+
+int64_t Store::add_host(const float *vectors, int64_t num) {
+	std::unique_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	if (num <= 0) return label_base_ + n_rows_;
+	ensure_capacity(n_rows_ + num);
+	LB_CUDA(cudaMemcpyAsync(X_.as<float>() + (size_t)n_rows_ * dim_, vectors, (size_t)num * dim_ * sizeof(float),
+	                        cudaMemcpyHostToDevice, copy_stream_));
+	LB_CUDA(cudaStreamSynchronize(copy_stream_));
+	int64_t first = label_base_ + n_rows_;
+	n_rows_ += num;
+	return first;
+}
+
+int64_t Store::add_device(const float *d_vectors, int64_t num, cudaStream_t s) {
+	std::unique_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	if (num <= 0) return label_base_ + n_rows_;
+	ensure_capacity(n_rows_ + num);
+	LB_CUDA(cudaMemcpyAsync(X_.as<float>() + (size_t)n_rows_ * dim_, d_vectors, (size_t)num * dim_ * sizeof(float),
+	                        cudaMemcpyDeviceToDevice, s));
+	LB_CUDA(cudaStreamSynchronize(s));
+	int64_t first = label_base_ + n_rows_;
+	n_rows_ += num;
+	return first;
+}
+
+void Store::delete_labels(const int64_t *labels, int count) {
+	std::unique_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	if (count <= 0) return;
+	std::vector<int64_t> rows;
+	rows.reserve(count);
+	for (int i = 0; i < count; i++) {
+		int64_t r = labels[i] - label_base_;
+		if (r < 0 || r >= n_rows_) continue; // deleting an unknown label matches nothing (lance_manager.rs:461-471)
+		uint32_t &w = deleted_host_[(size_t)(r >> 5)];
+		uint32_t bit = 1u << (r & 31);
+		if (w & bit) continue;
+		w |= bit;
+		n_deleted_++;
+		rows.push_back(r);
+	}
+	if (rows.empty()) return;
+	DevBuf tmp;
+	tmp.alloc(rows.size() * sizeof(int64_t));
+	LB_CUDA(cudaMemcpyAsync(tmp.p, rows.data(), rows.size() * sizeof(int64_t), cudaMemcpyHostToDevice, copy_stream_));
+	int64_t l = 0;
+	launch_set_bits(deleted_.as<uint32_t>(), tmp.as<int64_t>(), (int)rows.size(), n_rows_, copy_stream_, &l);
+	LB_CUDA(cudaStreamSynchronize(copy_stream_));
+	add_launches(l);
+}
+
+int64_t Store::live_rows() {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	return n_rows_ - n_deleted_;
+}
+int64_t Store::rows() {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	return n_rows_;
+}
+
+void Store::get_vector(int64_t label, float *out) {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	int64_t r = label - label_base_;
+	if (r < 0 || r >= n_rows_ || ((deleted_host_[(size_t)(r >> 5)] >> (r & 31)) & 1u))
+		throw Error("label " + std::to_string(label) + " not found");
+	LB_CUDA(cudaMemcpy(out, X_.as<float>() + (size_t)r * dim_, (size_t)dim_ * sizeof(float), cudaMemcpyDeviceToHost));
+}
+
+int64_t Store::get_all(int64_t *out_labels, float *out_vectors) {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	int64_t live = n_rows_ - n_deleted_;
+	if (!out_labels && !out_vectors) return live;
+	// copy runs of live rows
+	int64_t w = 0, r = 0;
+	while (r < n_rows_) {
+		while (r < n_rows_ && ((deleted_host_[(size_t)(r >> 5)] >> (r & 31)) & 1u)) r++;
+		int64_t b = r;
+		while (r < n_rows_ && !((deleted_host_[(size_t)(r >> 5)] >> (r & 31)) & 1u)) r++;
+		if (r > b) {
+			if (out_vectors)
+				LB_CUDA(cudaMemcpy(out_vectors + (size_t)w * dim_, X_.as<float>() + (size_t)b * dim_,
+				                   (size_t)(r - b) * dim_ * sizeof(float), cudaMemcpyDeviceToHost));
+			if (out_labels)
+				for (int64_t i = b; i < r; i++) out_labels[w + (i - b)] = label_base_ + i;
+			w += r - b;
+		}
+	}
+	return live;
+}
+
+// ------------------------------------------------------------------ search
+void Store::search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
+                          int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
+                          cudaStream_t s) {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	if (nq <= 0) return;
+	if (k <= 0) {
+		LB_CUDA(cudaMemsetAsync(d_out_counts, 0, (size_t)nq * sizeof(int32_t), s));
+		return;
+	}
+	// scratch is keyed by stream: everything enqueued on one stream is ordered, so back-to-back searches
+	// reuse it without a host synchronisation (growing a buffer frees the old one, which synchronises).
+	Workspace *ws = scratch_for(s);
+	std::lock_guard<std::mutex> wg(ws->mu);
+	if (index_)
+		ivfpq_search_locked(d_queries, nq, k, nprobes, refine, d_allow, allow_bits, d_out_labels, d_out_dist,
+		                    d_out_counts, *ws, s, nullptr, nullptr, nullptr);
+	else
+		flat_search_locked(d_queries, nq, k, d_allow, allow_bits, d_out_labels, d_out_dist, d_out_counts, *ws, s);
+	std::lock_guard<std::mutex> g(stat_mu_);
+	searches_++;
+}
+
+void Store::search_host(const float *queries, int nq, int k, int nprobes, int refine, const uint32_t *allow,
+                        int64_t allow_bits, int64_t *out_labels, float *out_dist, int32_t *out_counts) {
+	if (nq <= 0) return;
+	if (k <= 0) {
+		for (int i = 0; i < nq; i++) out_counts[i] = 0;
+		return;
+	}
+	LB_CUDA(cudaSetDevice(device_));
+	auto io = acquire_io();
+	try {
+		cudaStream_t s = io->stream;
+		io->q.ensure((size_t)nq * dim_ * sizeof(float));
+		io->out_labels.ensure((size_t)nq * k * sizeof(int64_t));
+		io->out_dist.ensure((size_t)nq * k * sizeof(float));
+		io->out_counts.ensure((size_t)nq * sizeof(int32_t));
+		LB_CUDA(cudaMemcpyAsync(io->q.p, queries, (size_t)nq * dim_ * sizeof(float), cudaMemcpyHostToDevice, s));
+		const uint32_t *d_allow = nullptr;
+		if (allow) {
+			size_t words = (size_t)((allow_bits + 31) / 32);
+			io->allow.ensure(std::max<size_t>(words, 1) * sizeof(uint32_t));
+			LB_CUDA(cudaMemcpyAsync(io->allow.p, allow, words * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+			d_allow = io->allow.as<uint32_t>();
+		}
+		search_device(io->q.as<float>(), nq, k, nprobes, refine, d_allow, allow_bits, io->out_labels.as<int64_t>(),
+		              io->out_dist.as<float>(), io->out_counts.as<int32_t>(), s);
+		LB_CUDA(cudaMemcpyAsync(out_labels, io->out_labels.p, (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+		LB_CUDA(cudaMemcpyAsync(out_dist, io->out_dist.p, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, s));
+		LB_CUDA(cudaMemcpyAsync(out_counts, io->out_counts.p, (size_t)nq * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+		LB_CUDA(cudaStreamSynchronize(s));
+	} catch (...) {
+		release_io(std::move(io));
+		throw;
+	}
+	release_io(std::move(io));
+}
+
+void Store::flat_search_locked(const float *d_queries, int nq, int k, const uint32_t *d_allow, int64_t allow_bits,
+                               int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts, Workspace &ws,
+                               cudaStream_t s) {
+	int64_t launches = 0;
+	const int mode = flat_path_.load();
+	bool use_tc = false;
+	if (mode == 2)
+		use_tc = true;
+	else if (mode == 0)
+		use_tc = FlatGemm::worthwhile(nq, n_rows_, dim_, k);
+	if (use_tc && !FlatGemm::supported(dim_, k)) {
+		if (mode == 2) throw Error("the tcgen05 flat path needs dim % 8 == 0, dim >= 64 and k <= 1024");
+		use_tc = false;
+	}
+	if (use_tc) {
+		{
+			std::lock_guard<std::mutex> g(gemm_mu_);
+			if (!flat_gemm_) flat_gemm_.reset(new FlatGemm(device_, num_sms_, dim_, metric_));
+			flat_gemm_->sync_rows(X_.as<float>(), n_rows_, cap_rows_, s, &launches);
+		}
+		int64_t fallback = 0;
+		flat_gemm_->search(X_.as<float>(), n_rows_, deleted_.as<uint32_t>(), d_queries, nq, k, d_allow, allow_bits,
+		                   label_base_, d_out_labels, d_out_dist, d_out_counts, ws, s, &launches, &fallback);
+		std::lock_guard<std::mutex> g(stat_mu_);
+		tc_batches_++;
+		tc_fallback_ += fallback;
+		launches_ += launches;
+		return;
+	}
+	FlatScanArgs a;
+	a.X = X_.as<float>();
+	a.n = n_rows_;
+	a.d = dim_;
+	a.metric = metric_;
+	a.dQ = d_queries;
+	a.nq = nq;
+	a.k = k;
+	a.allow = d_allow;
+	a.allow_bits = allow_bits;
+	a.deleted = n_deleted_ > 0 ? deleted_.as<uint32_t>() : nullptr;
+	a.label_base = label_base_;
+	a.out_labels = d_out_labels;
+	a.out_dist = d_out_dist;
+	a.out_counts = d_out_counts;
+	a.timer = &timer_;
+	FlatScanPlan p = plan_flat_scan(a.X, metric_, dim_, k, nq, n_rows_, num_sms_);
+	ws.work.ensure(flat_scan_scratch_bytes(p, k));
+	run_flat_scan(a, p, ws.work.p, s, &launches);
+	std::lock_guard<std::mutex> g(stat_mu_);
+	simt_batches_++;
+	launches_ += launches;
+}
+
+void Store::stats(lance_b200_stats_t *out) {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	std::lock_guard<std::mutex> g(stat_mu_);
+	memset(out, 0, sizeof(*out));
+	out->kernel_launches = launches_;
+	out->searches = searches_;
+	out->flat_simt_batches = simt_batches_;
+	out->flat_tc_batches = tc_batches_;
+	out->tc_fallback_queries = tc_fallback_;
+	out->ivfpq_batches = ivfpq_batches_;
+	out->rows = n_rows_;
+	out->live_rows = n_rows_ - n_deleted_;
+	out->device = device_;
+	out->has_index = index_ ? 1 : 0;
+}
+
+void Store::read_profile(lance_b200_profile_t *out) {
+	LB_CUDA(cudaSetDevice(device_));
+	LB_CUDA(cudaDeviceSynchronize());
+	double ms[KC_COUNT];
+	int64_t n[KC_COUNT];
+	timer_.read(ms, n);
+	out->flat_scan_ms = ms[KC_FLAT_SCAN], out->flat_scan_launches = n[KC_FLAT_SCAN];
+	out->flat_gemm_ms = ms[KC_FLAT_GEMM], out->flat_gemm_launches = n[KC_FLAT_GEMM];
+	out->adc_scan_ms = ms[KC_ADC_SCAN], out->adc_scan_launches = n[KC_ADC_SCAN];
+	out->rerank_ms = ms[KC_RERANK], out->rerank_launches = n[KC_RERANK];
+}
+
+// ------------------------------------------------------------------ persistence (own format)
+static const char MAGIC[8] = {'L', 'B', '2', '0', '0', 'v', '1', '\0'};
+
+void Store::save() {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	if (dir_.empty()) throw Error("store has no db_path to save under");
+	mkdir(db_path_.c_str(), 0777);
+	mkdir(dir_.c_str(), 0777);
+	std::string path = dir_ + "/store.bin";
+	FILE *f = fopen((path + ".tmp").c_str(), "wb");
+	if (!f) throw Error("cannot write " + path);
+	int64_t hdr[6] = {dim_, metric_, n_rows_, n_deleted_, label_base_, 0};
+	bool ok = fwrite(MAGIC, 1, 8, f) == 8 && fwrite(hdr, sizeof(int64_t), 6, f) == 6;
+	size_t words = (size_t)((n_rows_ + 31) / 32);
+	ok = ok && fwrite(deleted_host_.data(), sizeof(uint32_t), words, f) == words;
+	const int64_t chunk = std::max<int64_t>(1, (64ll << 20) / ((int64_t)dim_ * 4));
+	std::vector<float> buf((size_t)chunk * dim_);
+	for (int64_t r = 0; r < n_rows_ && ok; r += chunk) {
+		int64_t c = std::min(chunk, n_rows_ - r);
+		LB_CUDA(cudaMemcpy(buf.data(), X_.as<float>() + (size_t)r * dim_, (size_t)c * dim_ * sizeof(float),
+		                   cudaMemcpyDeviceToHost));
+		ok = fwrite(buf.data(), sizeof(float), (size_t)c * dim_, f) == (size_t)c * dim_;
+	}
+	ok = (fclose(f) == 0) && ok;
+	if (!ok || rename((path + ".tmp").c_str(), path.c_str()) != 0) throw Error("short write to " + path);
+}
+
+Store *Store::open(const std::string &db_path, const std::string &table, const std::string &metric, int device) {
+	std::string dir = db_path + "/" + (table.empty() ? std::string("vectors") : table) + ".b200";
+	std::string path = dir + "/store.bin";
+	FILE *f = fopen(path.c_str(), "rb");
+	if (!f) throw Error("no saved store at " + path);
+	char magic[8];
+	int64_t hdr[6];
+	if (fread(magic, 1, 8, f) != 8 || memcmp(magic, MAGIC, 8) != 0 || fread(hdr, sizeof(int64_t), 6, f) != 6) {
+		fclose(f);
+		throw Error("not a lance_b200 store: " + path);
+	}
+	std::unique_ptr<Store> st;
+	try {
+		// the caller's metric wins, as in lance_manager.rs:117-161 (open takes the metric from the index options)
+		std::string m = !metric.empty() ? metric : (hdr[1] == METRIC_COSINE ? "cosine" : hdr[1] == METRIC_DOT ? "dot" : "l2");
+		st.reset(new Store(db_path, table, (int)hdr[0], m, device));
+		int64_t n = hdr[2];
+		st->label_base_ = hdr[4];
+		st->ensure_capacity(std::max<int64_t>(n, 1));
+		size_t words = (size_t)((n + 31) / 32);
+		if (fread(st->deleted_host_.data(), sizeof(uint32_t), words, f) != words) throw Error("truncated store: " + path);
+		LB_CUDA(cudaMemcpy(st->deleted_.p, st->deleted_host_.data(), words * sizeof(uint32_t), cudaMemcpyHostToDevice));
+		const int64_t chunk = std::max<int64_t>(1, (64ll << 20) / ((int64_t)st->dim_ * 4));
+		std::vector<float> buf((size_t)chunk * st->dim_);
+		for (int64_t r = 0; r < n; r += chunk) {
+			int64_t c = std::min(chunk, n - r);
+			if (fread(buf.data(), sizeof(float), (size_t)c * st->dim_, f) != (size_t)c * st->dim_)
+				throw Error("truncated store: " + path);
+			LB_CUDA(cudaMemcpy(st->X_.as<float>() + (size_t)r * st->dim_, buf.data(), (size_t)c * st->dim_ * sizeof(float),
+			                   cudaMemcpyHostToDevice));
+		}
+		st->n_rows_ = n;
+		st->n_deleted_ = hdr[3];
+	} catch (...) {
+		fclose(f);
+		throw;
+	}
+	fclose(f);
+	return st.release();
+}
+
+} // namespace lb

@@ -1,0 +1,148 @@
+// store.h — the device-resident index behind one `lance_*` handle.
+//
+// Takes the place of rust_lib/src/lance_manager.rs's `LanceIndex` (fields :20-31, search :394-451,
+// add_batch :227-242, delete_batch :461-471, count :473-478, create_ann_index :483-515) for the kNN
+// path: vectors live in HBM as row-major fp32 [rows][dim] (the layout they arrive in from
+// src/lance_index.cpp:361-367 / :941-946), labels are consecutive from an atomic counter so
+// label == label_base + row, deletes are tombstone bits applied as a prefilter.
+#pragma once
+#include <atomic>
+#include <memory>
+#include <mutex>
+#include <shared_mutex>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "kernels.h"
+#include "../../include/lance_b200.h"
+
+namespace lb {
+
+struct DevBuf {
+	void *p = nullptr;
+	size_t bytes = 0;
+	DevBuf() = default;
+	DevBuf(const DevBuf &) = delete;
+	DevBuf &operator=(const DevBuf &) = delete;
+	~DevBuf() { release(); }
+	void release();
+	void alloc(size_t n);          // exact size, contents undefined
+	void ensure(size_t n);         // grow (contents lost) if smaller than n
+	template <class T>
+	T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+// per-call scratch: its own stream and buffers, so concurrent searches on one handle do not share state
+struct Workspace {
+	cudaStream_t stream = nullptr; // owned (io workspaces only)
+	std::mutex mu;                 // held while work that uses the buffers is being enqueued
+	DevBuf q, allow, out_labels, out_dist, out_counts, work, work2, work3, work4;
+	explicit Workspace(bool own_stream);
+	~Workspace();
+};
+
+struct IvfPqIndex; // ivfpq.h
+class FlatGemm;    // flat_gemm.h
+
+class Store {
+public:
+	Store(const std::string &db_path, const std::string &table, int dim, const std::string &metric, int device);
+	~Store();
+
+	int dim() const { return dim_; }
+	int metric() const { return metric_; }
+	int device() const { return device_; }
+	const std::string &dir() const { return dir_; }
+
+	void set_label_base(int64_t base);
+	void reserve(int64_t rows);
+	int64_t add_host(const float *vectors, int64_t num);                    // returns first label
+	int64_t add_device(const float *d_vectors, int64_t num, cudaStream_t s); // returns first label
+	void delete_labels(const int64_t *labels, int count);
+	int64_t live_rows();
+	int64_t rows();
+	void get_vector(int64_t label, float *out);
+	int64_t get_all(int64_t *out_labels, float *out_vectors); // returns live count
+
+	// host buffers in, host buffers out (the reference-facing call)
+	void search_host(const float *queries, int nq, int k, int nprobes, int refine, const uint32_t *allow,
+	                 int64_t allow_bits, int64_t *out_labels, float *out_dist, int32_t *out_counts);
+	// everything on the device, enqueued on s
+	void search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
+	                   int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
+	                   cudaStream_t s);
+
+	// IVF_PQ (ivfpq.cu)
+	void create_index(int num_partitions, int num_sub_vectors);
+	void set_index(int P, int M, int64_t n_indexed, const float *centroids, const float *codebook,
+	               const int64_t *part_offsets, const int64_t *row_ids, const uint8_t *codes);
+	void get_index(lance_b200_ivfpq_info *info, float *centroids, float *codebook, int64_t *part_offsets,
+	               int64_t *row_ids, uint8_t *codes);
+	void drop_index();
+	void ivfpq_search_debug(const float *query, int k, int nprobes, int refine, const uint32_t *allow,
+	                        int64_t allow_bits, int32_t *out_parts, int64_t *out_cand_labels, float *out_cand_adc,
+	                        int32_t *out_ncand, int64_t *out_labels, float *out_dist, int32_t *out_count);
+
+	void save();
+	static Store *open(const std::string &db_path, const std::string &table, const std::string &metric, int device);
+
+	void stats(lance_b200_stats_t *out);
+	void set_profile(bool on) { timer_.on = on; }
+	void read_profile(lance_b200_profile_t *out);
+	void set_flat_path(int mode) { flat_path_ = mode; }
+
+private:
+	friend struct IvfPqSearch;
+	void ensure_capacity(int64_t rows); // exclusive lock held
+	std::unique_ptr<Workspace> acquire_io();
+	void release_io(std::unique_ptr<Workspace> ws);
+	Workspace *scratch_for(cudaStream_t s); // work issued on one stream is ordered, so it can share scratch
+	void flat_search_locked(const float *d_queries, int nq, int k, const uint32_t *d_allow, int64_t allow_bits,
+	                        int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts, Workspace &ws,
+	                        cudaStream_t s);
+	void ivfpq_search_locked(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
+	                         int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
+	                         Workspace &ws, cudaStream_t s, int32_t *d_dbg_parts, u64 *d_dbg_cand, int32_t *d_dbg_ncand);
+
+	std::string db_path_, table_, dir_;
+	int dim_;
+	int metric_;
+	int device_;
+	int num_sms_ = 148;
+
+	std::shared_mutex mu_; // shared: searches; exclusive: add / delete / index build
+	DevBuf X_;             // fp32 [cap_rows_][dim_]
+	DevBuf deleted_;       // uint32 [cap_rows_/32]
+	int64_t cap_rows_ = 0;
+	int64_t n_rows_ = 0;
+	int64_t n_deleted_ = 0;
+	int64_t label_base_ = 0;
+	std::vector<uint32_t> deleted_host_; // mirror of the tombstones (count + save)
+	cudaStream_t copy_stream_ = nullptr;
+
+	std::unique_ptr<IvfPqIndex> index_;
+
+	std::mutex ws_mu_;
+	std::vector<std::unique_ptr<Workspace>> io_pool_;
+	std::vector<std::pair<cudaStream_t, std::unique_ptr<Workspace>>> stream_ws_;
+
+	std::mutex gemm_mu_;
+	std::unique_ptr<FlatGemm> flat_gemm_;
+
+	std::atomic<int> flat_path_{0};
+	KernelTimer timer_;
+	// counters
+	int64_t launches_ = 0; // guarded by launches_mu_ when merged from a workspace
+	std::mutex stat_mu_;
+	int64_t searches_ = 0, simt_batches_ = 0, tc_batches_ = 0, tc_fallback_ = 0, ivfpq_batches_ = 0;
+	void add_launches(int64_t n) {
+		std::lock_guard<std::mutex> g(stat_mu_);
+		launches_ += n;
+	}
+};
+
+int default_device();
+void set_default_device(int d);
+
+} // namespace lb
