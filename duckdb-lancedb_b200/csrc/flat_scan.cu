@@ -140,7 +140,7 @@ __device__ __forceinline__ unsigned live_mask8(long long row0, long long row_beg
 }
 
 template <int METRIC, int QB, int VEC>
-__global__ void __launch_bounds__(256) flat_scan_kernel(const float *__restrict__ X, long long row_begin, long long n,
+__global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_scan_kernel(const float *__restrict__ X, long long row_begin, long long n,
                                                          int d, const float *__restrict__ Q, int nq_valid, int k, int cap,
                                                          const uint32_t *__restrict__ allow, long long allow_bits,
                                                          const uint32_t *__restrict__ deleted,
@@ -260,9 +260,18 @@ __global__ void __launch_bounds__(256) flat_scan_kernel(const float *__restrict_
 			}
 		}
 		sel[j].finalize();
+		// publish this block's k-th best, then write only what can still make the global top-k: every
+		// block's k-th best bounds the global k-th best from above, so keys beyond g_tau are dead already
+		if (sel[j].cnt == k) {
+			if (lane == 0) atomicMin(g_tau + j, sel[j].tau);
+			__syncwarp();
+		}
+		const u64 gt = *reinterpret_cast<volatile u64 *>(g_tau + j);
 		u64 *dst = partials + ((size_t)j * gridDim.x + blockIdx.x) * k;
-		for (int i = lane; i < k; i += 32) dst[i] = (i < sel[j].cnt) ? sel[j].buf[i] : KEY_INVALID;
-		if (lane == 0 && sel[j].cnt == k) atomicMin(g_tau + j, sel[j].tau);
+		for (int i = lane; i < k; i += 32) {
+			u64 key = (i < sel[j].cnt) ? sel[j].buf[i] : KEY_INVALID;
+			dst[i] = key <= gt ? key : KEY_INVALID;
+		}
 	}
 }
 

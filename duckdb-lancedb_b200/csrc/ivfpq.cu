@@ -1,10 +1,516 @@
-// placeholder until the IVF_PQ kernels land
+// ivfpq.cu — IVF_PQ on the device: probe -> per-query lookup table -> ADC scan -> refine, plus the
+// trainer behind lance_detached_create_index.
+//
+// What the reference delegates to lancedb's IvfPq index (rust_lib/src/lance_manager.rs:483-515 build,
+// :411-419 query with .nprobes(n).refine_factor(rf)); SURVEY.md 8a rows a12-a14.  The arithmetic follows
+// oracle/oracle.c (oracle_ivf_probe / oracle_pq_lut / oracle_adc_distance / oracle_ivfpq_search):
+//   probe : the nprobes centroids nearest to q' (q' = q, or q/|q| for cosine), L2 (l2, cosine) or 1-dot;
+//   LUT   : residual PQ, entry(m,c) = |(q' - centroid_p)_m - cb[m][c]|^2   (dot: -(q_m . cb[m][c]), no residual);
+//   ADC   : l2 = sum, cosine = sum/2, dot = 1 + sum;   refine: exact distance of the k*rf best, re-sorted.
+//
+// B200 mapping.  The residual LUT is never materialised per (query, partition).  Expanding the square,
+//   sum_m |(q'-c_p)_m - cb_m|^2 = sum_m |q'_m - cb_m|^2  +  (|q'-c_p|^2 - |q'|^2)  +  2 sum_m <c_p,m , cb_m>
+//                                 `-- per-QUERY table T1 --'  `-- per (q,p) scalar, --'  `-- per ROW, stored --'
+//                                                              known from the probe      at index build
+// so one 96 KB table per query (M=96) serves all probed partitions, the codebook is read once per query
+// batch instead of once per (query, partition), and the scan kernel streams nothing but codes
+// (M bytes/row), a 4-byte row term and a 4-byte row id.  Codes are stored interleaved in blocks of 32
+// rows ([block][M/16][32 lanes][16 B]) so that every warp load is one fully coalesced 512-byte
+// request of 128-bit words; every partition is padded to a multiple of 32 rows.
+// Roofline of the scan: HBM (codes + row terms + ids), in practice bounded by shared-memory lookups
+// (M random LDS per row); see DESIGN.md.
 #include "ivfpq.h"
+
+#include <cub/device/device_radix_sort.cuh>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "topk.cuh"
+
 namespace lb {
-void Store::create_index(int, int) { throw Error("IVF_PQ not built"); }
-void Store::set_index(int, int, int64_t, const float *, const float *, const int64_t *, const int64_t *, const uint8_t *) { throw Error("IVF_PQ not built"); }
-void Store::get_index(lance_b200_ivfpq_info *, float *, float *, int64_t *, int64_t *, uint8_t *) { throw Error("IVF_PQ not built"); }
-void Store::drop_index() { std::unique_lock<std::shared_mutex> lk(mu_); index_.reset(); }
-void Store::ivfpq_search_debug(const float *, int, int, int, const uint32_t *, int64_t, int32_t *, int64_t *, float *, int32_t *, int64_t *, float *, int32_t *) { throw Error("IVF_PQ not built"); }
-void Store::ivfpq_search_locked(const float *, int, int, int, int, const uint32_t *, int64_t, int64_t *, float *, int32_t *, Workspace &, cudaStream_t, int32_t *, u64 *, int32_t *) { throw Error("IVF_PQ not built"); }
+
+// ------------------------------------------------------------------ query preparation
+// q' = q (l2, dot) or q/|q| (cosine); qn2 = |q'|^2.  One warp per query.
+__global__ void prep_queries_kernel(const float *__restrict__ Q, int nq, int d, int normalise, float *__restrict__ Qp,
+                                    float *__restrict__ qn2) {
+	int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (q >= nq) return;
+	const unsigned lane = lane_id();
+	const float *src = Q + (size_t)q * d;
+	float s = 0.f;
+	for (int i = lane; i < d; i += 32) s = fmaf(src[i], src[i], s);
+	for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+	float r = 1.f;
+	if (normalise) r = s > 0.f ? rsqrtf(s) : 1.f;
+	float s2 = 0.f;
+	for (int i = lane; i < d; i += 32) {
+		float v = src[i] * r;
+		Qp[(size_t)q * d + i] = v;
+		s2 = fmaf(v, v, s2);
+	}
+	for (int o = 16; o; o >>= 1) s2 += __shfl_xor_sync(0xFFFFFFFFu, s2, o);
+	if (lane == 0) qn2[q] = s2;
+}
+
+// ------------------------------------------------------------------ per-query lookup table T1
+// lut[q][m][c] = |q'_m - cb[m][c]|^2 (l2/cosine) or -(q'_m . cb[m][c]) (dot).
+// grid (M, ceil(nq / QPB)); 256 threads = one codeword each; the codebook slice of sub-quantizer m is
+// read once per block and reused for QPB queries.
+static const int LUT_QPB = 16;
+__global__ void __launch_bounds__(256) lut_kernel(const float *__restrict__ Qp, int nq, int d, int M, int dsub,
+                                                  const float *__restrict__ codebook, int is_dot,
+                                                  float *__restrict__ lut) {
+	extern __shared__ float lut_sm[]; // cb slice [256][dsub+1] + q sub-vectors [QPB][dsub]
+	const int m = blockIdx.x;
+	const int q0 = blockIdx.y * LUT_QPB;
+	const int c = threadIdx.x;
+	const int ld = dsub + 1;
+	float *cbs = lut_sm;
+	float *qs = lut_sm + 256 * ld;
+	const float *cb = codebook + (size_t)m * 256 * dsub;
+	for (int i = threadIdx.x; i < 256 * dsub; i += 256) cbs[(i / dsub) * ld + (i % dsub)] = cb[i];
+	for (int i = threadIdx.x; i < LUT_QPB * dsub; i += 256) {
+		int qq = q0 + i / dsub;
+		qs[i] = qq < nq ? Qp[(size_t)qq * d + m * dsub + (i % dsub)] : 0.f;
+	}
+	__syncthreads();
+	for (int j = 0; j < LUT_QPB && q0 + j < nq; j++) {
+		float acc = 0.f;
+		if (is_dot) {
+			for (int i = 0; i < dsub; i++) acc = fmaf(-qs[j * dsub + i], cbs[c * ld + i], acc);
+		} else {
+			for (int i = 0; i < dsub; i++) {
+				float e = qs[j * dsub + i] - cbs[c * ld + i];
+				acc = fmaf(e, e, acc);
+			}
+		}
+		lut[((size_t)(q0 + j) * M + m) * 256 + c] = acc;
+	}
+}
+
+// ------------------------------------------------------------------ ADC scan
+// One CTA per (probe slice s, query q): loads T1[q] into shared memory, then for each of its probed
+// partitions streams the interleaved codes; lane r of a warp owns row r of a 32-row block.
+template <int GRAN>
+struct CodeWord;
+template <>
+struct CodeWord<16> {
+	typedef uint4 T;
+};
+template <>
+struct CodeWord<4> {
+	typedef uint32_t T;
+};
+template <>
+struct CodeWord<1> {
+	typedef uint8_t T;
+};
+
+__device__ __forceinline__ float lut4(const float *lut_m, uint32_t w) {
+	// four consecutive sub-quantizers packed in one 32-bit word (little endian)
+	return lut_m[w & 0xFFu] + lut_m[256 + ((w >> 8) & 0xFFu)] + lut_m[512 + ((w >> 16) & 0xFFu)] + lut_m[768 + (w >> 24)];
+}
+
+template <int GRAN>
+__global__ void __launch_bounds__(256) adc_scan_kernel(
+    const float *__restrict__ lut_g, int M, const u64 *__restrict__ probe_keys, int nprobes_eff, int probe_stride,
+    const float *__restrict__ qn2, int metric, const long long *__restrict__ pad_offsets,
+    const int32_t *__restrict__ slot_rows, const uint8_t *__restrict__ codes_il, const float *__restrict__ row_term,
+    const uint32_t *__restrict__ allow, long long allow_bits, const uint32_t *__restrict__ deleted, int kc, int cap,
+    u64 *__restrict__ partials) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int nwarps = blockDim.x >> 5;
+	const int warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	const int q = blockIdx.y;
+	const int S = gridDim.x, s = blockIdx.x;
+	float *lut = reinterpret_cast<float *>(smem_raw);                                 // [M][256]
+	int *cnts = reinterpret_cast<int *>(smem_raw + (size_t)M * 1024);                 // [nwarps]
+	u64 *bufs = reinterpret_cast<u64 *>(smem_raw + (size_t)M * 1024 + 64);            // [nwarps][cap]
+
+	{
+		const float4 *src = reinterpret_cast<const float4 *>(lut_g + (size_t)q * M * 256);
+		float4 *dst = reinterpret_cast<float4 *>(lut);
+		for (int i = threadIdx.x; i < M * 64; i += blockDim.x) dst[i] = __ldg(src + i);
+	}
+	__syncthreads();
+
+	WarpSelect sel;
+	sel.init(bufs + (size_t)warp * cap, cap, kc);
+	const float qq = qn2[q];
+	const int chunks = M / GRAN;
+	typedef typename CodeWord<GRAN>::T word_t;
+
+	for (int pi = s; pi < nprobes_eff; pi += S) {
+		const u64 pk = probe_keys[(size_t)q * probe_stride + pi];
+		if (pk == KEY_INVALID) continue;
+		const int p = (int)key_row(pk);
+		const float cst = (metric == METRIC_DOT) ? 1.0f : key_dist(pk) - qq;
+		const long long b0 = pad_offsets[p] >> 5, b1 = pad_offsets[p + 1] >> 5;
+		for (long long b = b0 + warp; b < b1; b += nwarps) {
+			const long long slot = (b << 5) + lane;
+			const int row = __ldg(slot_rows + slot);
+			const word_t *cp = reinterpret_cast<const word_t *>(codes_il) + (size_t)b * chunks * 32 + lane;
+			float acc = 0.f;
+			if (GRAN == 16) {
+				// issue all loads of the row first (M/16 independent 128-bit loads)
+				for (int c0 = 0; c0 < chunks; c0 += 6) {
+					uint4 w[6];
+#pragma unroll
+					for (int u = 0; u < 6; u++)
+						if (c0 + u < chunks) w[u] = __ldg(reinterpret_cast<const uint4 *>(cp) + (size_t)(c0 + u) * 32);
+#pragma unroll
+					for (int u = 0; u < 6; u++)
+						if (c0 + u < chunks) {
+							const float *lm = lut + (size_t)(c0 + u) * 16 * 256;
+							acc += lut4(lm, w[u].x) + lut4(lm + 1024, w[u].y) + lut4(lm + 2048, w[u].z) +
+							       lut4(lm + 3072, w[u].w);
+						}
+				}
+			} else if (GRAN == 4) {
+				for (int c = 0; c < chunks; c++) {
+					uint32_t w = __ldg(reinterpret_cast<const uint32_t *>(cp) + (size_t)c * 32);
+					acc += lut4(lut + (size_t)c * 4 * 256, w);
+				}
+			} else {
+				for (int c = 0; c < chunks; c++) {
+					uint8_t w = __ldg(reinterpret_cast<const uint8_t *>(cp) + (size_t)c * 32);
+					acc += lut[c * 256 + w];
+				}
+			}
+			float dist;
+			if (metric == METRIC_DOT)
+				dist = 1.0f + acc;
+			else {
+				dist = acc + __ldg(row_term + slot) + cst;
+				if (metric == METRIC_COSINE) dist *= 0.5f;
+			}
+			bool live = row >= 0;
+			if (live && deleted) live = !bit_test(deleted, row);
+			if (live && allow) live = (row < allow_bits) && bit_test(allow, row);
+			sel.push(live, make_key(dist, (uint32_t)row));
+		}
+	}
+	sel.finalize();
+	if (lane == 0) cnts[warp] = sel.cnt;
+	__syncthreads();
+	if (warp != 0) return;
+	for (int w = 1; w < nwarps; w++) {
+		const u64 *src = bufs + (size_t)w * cap;
+		const int c = cnts[w];
+		for (int i0 = 0; i0 < c; i0 += 32) {
+			int i = i0 + lane;
+			u64 key = (i < c) ? src[i] : KEY_INVALID;
+			sel.push(i < c, key);
+		}
+	}
+	sel.finalize();
+	u64 *dst = partials + ((size_t)q * S + s) * kc;
+	for (int i = lane; i < kc; i += 32) dst[i] = (i < sel.cnt) ? sel.buf[i] : KEY_INVALID;
+}
+
+// ------------------------------------------------------------------ refine (a14): exact distance of the candidates
+// One warp per candidate key; writes (exact distance, row) keys.  Same distance formulas as flat_scan.cu.
+__global__ void refine_kernel(const float *__restrict__ X, int d, const float *__restrict__ Q, int metric,
+                              const u64 *__restrict__ cand, int kc, int nq, u64 *__restrict__ out, int out_stride) {
+	long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (w >= (long long)nq * kc) return;
+	const unsigned lane = lane_id();
+	const int q = (int)(w / kc), i = (int)(w % kc);
+	const u64 key = cand[(size_t)q * kc + i];
+	u64 res = KEY_INVALID;
+	if (key != KEY_INVALID) {
+		const uint32_t row = key_row(key);
+		const float *x = X + (size_t)row * d;
+		const float *qv = Q + (size_t)q * d;
+		float acc = 0.f, nx = 0.f, nq2 = 0.f;
+		for (int c = lane; c < d; c += 32) {
+			float a = __ldg(qv + c), b = __ldg(x + c);
+			if (metric == METRIC_L2) {
+				float e = a - b;
+				acc = fmaf(e, e, acc);
+			} else {
+				acc = fmaf(a, b, acc);
+				nx = fmaf(b, b, nx);
+				nq2 = fmaf(a, a, nq2);
+			}
+		}
+		for (int o = 16; o; o >>= 1) {
+			acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+			nx += __shfl_xor_sync(0xFFFFFFFFu, nx, o);
+			nq2 += __shfl_xor_sync(0xFFFFFFFFu, nq2, o);
+		}
+		float dist;
+		if (metric == METRIC_L2)
+			dist = acc;
+		else if (metric == METRIC_DOT)
+			dist = 1.0f - acc;
+		else {
+			float den = sqrtf(nq2) * sqrtf(nx);
+			if (!(den > 0.f))
+				dist = 1.0f;
+			else {
+				float sim = fminf(1.f, fmaxf(-1.f, acc / den));
+				dist = 1.0f - sim;
+			}
+		}
+		res = make_key(dist, row);
+	}
+	if (lane == 0) out[(size_t)q * out_stride + i] = res;
+}
+
+__global__ void copy_keys_strided_kernel(const u64 *__restrict__ src, int src_stride, int n_per, int nq,
+                                         u64 *__restrict__ dst, int dst_stride, int dst_off) {
+	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= (long long)nq * n_per) return;
+	int q = (int)(t / n_per), i = (int)(t % n_per);
+	dst[(size_t)q * dst_stride + dst_off + i] = src[(size_t)q * src_stride + i];
+}
+
+__global__ void keys_to_debug_kernel(const u64 *__restrict__ keys, int n, long long label_base, int64_t *labels,
+                                     float *dists, int32_t *count) {
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i == 0) {
+		int c = 0;
+		while (c < n && keys[c] != KEY_INVALID) c++;
+		*count = c;
+	}
+	if (i >= n) return;
+	u64 k = keys[i];
+	labels[i] = k == KEY_INVALID ? -1 : label_base + (long long)key_row(k);
+	dists[i] = k == KEY_INVALID ? __int_as_float(0x7F800000) : key_dist(k);
+}
+
+// ------------------------------------------------------------------ index install: exchange layout -> scan layout
+// slot -> (source position in the partition-major exchange arrays, row); padding slots get -1.
+__global__ void build_slots_kernel(const long long *__restrict__ part_offsets, const long long *__restrict__ pad_offsets,
+                                   int P, const int64_t *__restrict__ row_ids, long long label_base, long long n_pad,
+                                   int32_t *__restrict__ slot_rows, long long *__restrict__ slot_src) {
+	long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= n_pad) return;
+	int lo = 0, hi = P; // partition p with pad_offsets[p] <= s < pad_offsets[p+1]
+	while (hi - lo > 1) {
+		int mid = (lo + hi) >> 1;
+		if (pad_offsets[mid] <= s) lo = mid; else hi = mid;
+	}
+	long long src = part_offsets[lo] + (s - pad_offsets[lo]);
+	if (src < part_offsets[lo + 1]) {
+		slot_src[s] = src;
+		slot_rows[s] = (int32_t)(row_ids[src] - label_base);
+	} else {
+		slot_src[s] = -1;
+		slot_rows[s] = -1;
+	}
+}
+
+// codes[n][M] (exchange) -> interleaved [n_pad/32][M/gran][32][gran]
+__global__ void interleave_codes_kernel(const uint8_t *__restrict__ codes, const long long *__restrict__ slot_src, int M,
+                                        int gran, long long n_pad, uint8_t *__restrict__ codes_il) {
+	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= n_pad * M) return;
+	long long s = t / M;
+	int m = (int)(t % M);
+	long long src = slot_src[s];
+	uint8_t v = src >= 0 ? codes[(size_t)src * M + m] : 0;
+	long long b = s >> 5;
+	int r = (int)(s & 31);
+	codes_il[(((size_t)b * (M / gran) + m / gran) * 32 + r) * gran + (m % gran)] = v;
+}
+
+// row_term[slot] = 2 * sum_m <centroid_p[m], cb[m][code_m]>  (l2 / cosine); one warp per slot
+__global__ void row_term_kernel(const uint8_t *__restrict__ codes, const long long *__restrict__ slot_src,
+                                const long long *__restrict__ pad_offsets, int P, const float *__restrict__ centroids,
+                                const float *__restrict__ codebook, int d, int M, int dsub, long long n_pad,
+                                float *__restrict__ row_term) {
+	long long s = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (s >= n_pad) return;
+	const unsigned lane = lane_id();
+	long long src = slot_src[s];
+	float acc = 0.f;
+	if (src >= 0) {
+		int lo = 0, hi = P;
+		while (hi - lo > 1) {
+			int mid = (lo + hi) >> 1;
+			if (pad_offsets[mid] <= s) lo = mid; else hi = mid;
+		}
+		const float *cen = centroids + (size_t)lo * d;
+		for (int i = lane; i < d; i += 32) {
+			int m = i / dsub, j = i - m * dsub;
+			int c = codes[(size_t)src * M + m];
+			acc = fmaf(cen[i], codebook[((size_t)m * 256 + c) * dsub + j], acc);
+		}
+		for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+	}
+	if (lane == 0) row_term[s] = 2.0f * acc;
+}
+
+// ------------------------------------------------------------------ trainer kernels
+// Nearest centre of every row (k-means assignment / PQ encoding).  score = |c|^2 - 2 x.c (l2) or -x.c (dot);
+// argmin, ties to the lower index.  blockIdx.z selects a sub-space: x columns [z*dsub, z*dsub+dd), centres
+// C + z*nc*dd.  Register-tiled SIMT GEMM: 64 rows x 64 centres per block step, 256 threads x (4x4).
+static const int NC_BM = 64, NC_BN = 64, NC_BK = 16;
+__global__ void __launch_bounds__(256) nearest_center_kernel(const float *__restrict__ X, long long n, int ldx, int dd,
+                                                              const float *__restrict__ C, int nc, int is_dot,
+                                                              const float *__restrict__ sub_base, // nullable: subtract
+                                                              const int32_t *__restrict__ sub_idx,  // sub_base[idx[row]]
+                                                              int32_t *__restrict__ assign, long long assign_stride) {
+	__shared__ float Xs[NC_BK][NC_BM + 1];
+	__shared__ float Cs[NC_BK][NC_BN + 1];
+	__shared__ float best_s[NC_BM][17];
+	__shared__ int best_i[NC_BM][17];
+	const int z = blockIdx.z;
+	const int xoff = z * dd;
+	const float *Cz = C + (size_t)z * nc * dd;
+	const long long row0 = (long long)blockIdx.x * NC_BM;
+	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4; // tx: centre group, ty: row group
+	float best[4];
+	int bidx[4];
+#pragma unroll
+	for (int i = 0; i < 4; i++) best[i] = 3.4e38f, bidx[i] = 0;
+	for (int c0 = 0; c0 < nc; c0 += NC_BN) {
+		float acc[4][4];
+		float cn[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+		for (int i = 0; i < 4; i++)
+#pragma unroll
+			for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+		for (int k0 = 0; k0 < dd; k0 += NC_BK) {
+			for (int t = threadIdx.x; t < NC_BK * NC_BM; t += 256) {
+				int r = t / NC_BK, kk = t % NC_BK;
+				long long row = row0 + r;
+				float v = 0.f;
+				if (row < n && k0 + kk < dd) {
+					v = X[(size_t)row * ldx + xoff + k0 + kk];
+					if (sub_base) v -= sub_base[(size_t)sub_idx[row] * ldx + xoff + k0 + kk];
+				}
+				Xs[kk][r] = v;
+			}
+			for (int t = threadIdx.x; t < NC_BK * NC_BN; t += 256) {
+				int c = t / NC_BK, kk = t % NC_BK;
+				Cs[kk][c] = (c0 + c < nc && k0 + kk < dd) ? Cz[(size_t)(c0 + c) * dd + k0 + kk] : 0.f;
+			}
+			__syncthreads();
+#pragma unroll
+			for (int kk = 0; kk < NC_BK; kk++) {
+				float xv[4], cv[4];
+#pragma unroll
+				for (int i = 0; i < 4; i++) xv[i] = Xs[kk][ty * 4 + i];
+#pragma unroll
+				for (int j = 0; j < 4; j++) cv[j] = Cs[kk][tx * 4 + j];
+#pragma unroll
+				for (int j = 0; j < 4; j++) cn[j] = fmaf(cv[j], cv[j], cn[j]);
+#pragma unroll
+				for (int i = 0; i < 4; i++)
+#pragma unroll
+					for (int j = 0; j < 4; j++) acc[i][j] = fmaf(xv[i], cv[j], acc[i][j]);
+			}
+			__syncthreads();
+		}
+#pragma unroll
+		for (int j = 0; j < 4; j++) {
+			int c = c0 + tx * 4 + j;
+			if (c >= nc) continue;
+#pragma unroll
+			for (int i = 0; i < 4; i++) {
+				float sc = is_dot ? -acc[i][j] : cn[j] - 2.0f * acc[i][j];
+				if (sc < best[i]) best[i] = sc, bidx[i] = c;
+			}
+		}
+	}
+#pragma unroll
+	for (int i = 0; i < 4; i++) {
+		best_s[ty * 4 + i][tx] = best[i];
+		best_i[ty * 4 + i][tx] = bidx[i];
+	}
+	__syncthreads();
+	if (threadIdx.x < NC_BM) {
+		int r = threadIdx.x;
+		float b = best_s[r][0];
+		int bi = best_i[r][0];
+		for (int t = 1; t < 16; t++) {
+			float s = best_s[r][t];
+			int si = best_i[r][t];
+			if (s < b || (s == b && si < bi)) b = s, bi = si;
+		}
+		if (row0 + r < n) assign[(size_t)z * assign_stride + row0 + r] = bi;
+	}
+}
+
+// centre sums by atomics: sums[z][assign][dd] += x ; counts[z][assign]++
+__global__ void accumulate_centers_kernel(const float *__restrict__ X, long long n, int ldx, int dd,
+                                          const float *__restrict__ sub_base, const int32_t *__restrict__ sub_idx,
+                                          const int32_t *__restrict__ assign, long long assign_stride, int nc,
+                                          float *__restrict__ sums, int *__restrict__ counts) {
+	const int z = blockIdx.z;
+	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= n * dd) return;
+	long long row = t / dd;
+	int j = (int)(t % dd);
+	int a = assign[(size_t)z * assign_stride + row];
+	float v = X[(size_t)row * ldx + z * dd + j];
+	if (sub_base) v -= sub_base[(size_t)sub_idx[row] * ldx + z * dd + j];
+	atomicAdd(sums + ((size_t)z * nc + a) * dd + j, v);
+	if (j == 0) atomicAdd(counts + (size_t)z * nc + a, 1);
+}
+
+__global__ void finish_centers_kernel(float *__restrict__ C, const float *__restrict__ sums, const int *__restrict__ counts,
+                                      long long total, int dd) {
+	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= total) return;
+	int cnt = counts[t / dd];
+	if (cnt > 0) C[t] = sums[t] / (float)cnt; // an empty cluster keeps its previous centre (oracle_kmeans)
+}
+
+// rows picked at a stride -> contiguous sample (optionally L2-normalised: the cosine index lives on unit rows)
+__global__ void gather_rows_kernel(const float *__restrict__ X, int d, long long n_out, long long stride, int normalise,
+                                   float *__restrict__ out) {
+	long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (r >= n_out) return;
+	const unsigned lane = lane_id();
+	const float *src = X + (size_t)(r * stride) * d;
+	float s = 0.f;
+	if (normalise) {
+		for (int i = lane; i < d; i += 32) s = fmaf(src[i], src[i], s);
+		for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+	}
+	float sc = (normalise && s > 0.f) ? rsqrtf(s) : 1.f;
+	for (int i = lane; i < d; i += 32) out[(size_t)r * d + i] = src[i] * sc;
+}
+
+__global__ void pack_codes_kernel(const int32_t *__restrict__ sub_assign, long long n, int M, uint8_t *__restrict__ codes) {
+	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= n * M) return;
+	long long row = t / M;
+	int m = (int)(t % M);
+	codes[t] = (uint8_t)sub_assign[(size_t)m * n + row];
+}
+
+__global__ void iota_kernel(int32_t *p, long long n, int32_t base) {
+	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t < n) p[t] = base + (int32_t)t;
+}
+
+// partition-major gather after the sort: codes_x[pos] = codes_rm[order[pos]], row_ids[pos] = base + order[pos]
+__global__ void gather_sorted_kernel(const uint8_t *__restrict__ codes_rm, const int32_t *__restrict__ order, long long n,
+                                     int M, long long label_base, uint8_t *__restrict__ codes_x,
+                                     int64_t *__restrict__ row_ids) {
+	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= n * M) return;
+	long long pos = t / M;
+	int m = (int)(t % M);
+	int32_t row = order[pos];
+	codes_x[t] = codes_rm[(size_t)row * M + m];
+	if (m == 0) row_ids[pos] = label_base + row;
+}
+
+__global__ void histogram_kernel(const int32_t *__restrict__ assign, long long n, int *__restrict__ hist) {
+	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t < n) atomicAdd(hist + assign[t], 1);
+}
+
+#include "ivfpq_host.cuh"
+#include "ivfpq_train.cuh"
+
 } // namespace lb

@@ -9,6 +9,7 @@
 namespace lb {
 
 struct IvfPqIndex {
+	virtual ~IvfPqIndex() {}
 	int metric = METRIC_L2;
 	int dim = 0, P = 0, M = 0, dsub = 0;
 	int64_t n_indexed = 0; // rows [0, n_indexed) are covered; later rows are scanned exactly

@@ -1,0 +1,325 @@
+// ivfpq_host.cuh — host side of the IVF_PQ path (included at the end of ivfpq.cu, inside namespace lb):
+// index install from the exchange layout, the search pipeline, the trainer.
+#pragma once
+
+static inline unsigned blocks_for(long long n, int per) { return (unsigned)((n + per - 1) / per); }
+
+// ------------------------------------------------------------------ install
+// Builds the scan layout from exchange-layout arrays that already sit on the device in ix.
+struct IvfPqExchange {
+	DevBuf row_ids; // int64 [n_indexed] labels, partition-major
+	DevBuf codes;   // u8 [n_indexed][M], partition-major
+	DevBuf part_offsets_dev; // int64 [P+1]
+};
+
+static void finalize_index(IvfPqIndex &ix, IvfPqExchange &ex, long long label_base, cudaStream_t s, int64_t *launches) {
+	const int P = ix.P, M = ix.M;
+	ix.gran = (M % 16 == 0) ? 16 : (M % 4 == 0 ? 4 : 1);
+	std::vector<long long> pad(P + 1, 0);
+	ix.max_part_rows = 0;
+	for (int p = 0; p < P; p++) {
+		long long sz = ix.part_offsets[p + 1] - ix.part_offsets[p];
+		if (sz < 0) throw Error("part_offsets must be non-decreasing");
+		ix.max_part_rows = std::max<long long>(ix.max_part_rows, sz);
+		pad[p + 1] = pad[p] + ((sz + 31) & ~31ll);
+	}
+	ix.n_pad = pad[P];
+	ix.pad_offsets.alloc((size_t)(P + 1) * sizeof(long long));
+	LB_CUDA(cudaMemcpyAsync(ix.pad_offsets.p, pad.data(), (size_t)(P + 1) * sizeof(long long), cudaMemcpyHostToDevice, s));
+	const long long np = std::max<long long>(ix.n_pad, 32);
+	ix.slot_rows.alloc((size_t)np * sizeof(int32_t));
+	ix.codes_il.alloc((size_t)np * M);
+	ix.row_term.alloc((size_t)np * sizeof(float));
+	DevBuf slot_src;
+	slot_src.alloc((size_t)np * sizeof(long long));
+	if (ix.n_pad > 0) {
+		build_slots_kernel<<<blocks_for(ix.n_pad, 256), 256, 0, s>>>(
+		    ex.part_offsets_dev.as<long long>(), ix.pad_offsets.as<long long>(), P, ex.row_ids.as<int64_t>(), label_base,
+		    ix.n_pad, ix.slot_rows.as<int32_t>(), slot_src.as<long long>());
+		LB_CUDA(cudaGetLastError());
+		interleave_codes_kernel<<<blocks_for(ix.n_pad * M, 256), 256, 0, s>>>(ex.codes.as<uint8_t>(), slot_src.as<long long>(),
+		                                                                    M, ix.gran, ix.n_pad, ix.codes_il.as<uint8_t>());
+		LB_CUDA(cudaGetLastError());
+		if (ix.metric != METRIC_DOT) {
+			row_term_kernel<<<blocks_for(ix.n_pad, 8), 256, 0, s>>>(ex.codes.as<uint8_t>(), slot_src.as<long long>(),
+			                                                       ix.pad_offsets.as<long long>(), P, ix.centroids.as<float>(),
+			                                                       ix.codebook.as<float>(), ix.dim, M, ix.dsub, ix.n_pad,
+			                                                       ix.row_term.as<float>());
+			LB_CUDA(cudaGetLastError());
+		} else {
+			LB_CUDA(cudaMemsetAsync(ix.row_term.p, 0, (size_t)np * sizeof(float), s));
+		}
+		if (launches) *launches += 3;
+	}
+	LB_CUDA(cudaStreamSynchronize(s));
+}
+
+// exchange copies are kept so that lance_b200_get_ivfpq can hand the index back (oracle parity tests)
+struct IvfPqIndexFull : IvfPqIndex {
+	IvfPqExchange ex;
+};
+
+static void check_shape(int dim, int P, int M) {
+	if (P <= 0 || M <= 0) throw Error("num_partitions and num_sub_vectors must be positive");
+	if (dim % M != 0) throw Error("dimension " + std::to_string(dim) + " is not divisible by num_sub_vectors " + std::to_string(M));
+	if ((size_t)M * 1024 + 8192 > 200 * 1024) throw Error("num_sub_vectors > 192 does not fit the shared-memory lookup table");
+}
+
+void Store::set_index(int P, int M, int64_t n_indexed, const float *centroids, const float *codebook,
+                      const int64_t *part_offsets, const int64_t *row_ids, const uint8_t *codes) {
+	std::unique_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	check_shape(dim_, P, M);
+	if (n_indexed < 0 || n_indexed > n_rows_) throw Error("index covers more rows than the table holds");
+	if (part_offsets[0] != 0 || part_offsets[P] != n_indexed) throw Error("part_offsets must span [0, n_indexed]");
+	for (int64_t i = 0; i < n_indexed; i++)
+		if (row_ids[i] < label_base_ || row_ids[i] >= label_base_ + n_rows_) throw Error("row id outside the table");
+	std::unique_ptr<IvfPqIndexFull> ix(new IvfPqIndexFull());
+	ix->metric = metric_;
+	ix->dim = dim_, ix->P = P, ix->M = M, ix->dsub = dim_ / M, ix->n_indexed = n_indexed;
+	ix->part_offsets.assign(part_offsets, part_offsets + P + 1);
+	cudaStream_t s = copy_stream_;
+	ix->centroids.alloc((size_t)P * dim_ * sizeof(float));
+	ix->codebook.alloc((size_t)M * 256 * ix->dsub * sizeof(float));
+	ix->ex.row_ids.alloc(std::max<size_t>((size_t)n_indexed, 1) * sizeof(int64_t));
+	ix->ex.codes.alloc(std::max<size_t>((size_t)n_indexed * M, 1));
+	ix->ex.part_offsets_dev.alloc((size_t)(P + 1) * sizeof(int64_t));
+	LB_CUDA(cudaMemcpyAsync(ix->centroids.p, centroids, (size_t)P * dim_ * sizeof(float), cudaMemcpyHostToDevice, s));
+	LB_CUDA(cudaMemcpyAsync(ix->codebook.p, codebook, (size_t)M * 256 * ix->dsub * sizeof(float), cudaMemcpyHostToDevice, s));
+	LB_CUDA(cudaMemcpyAsync(ix->ex.row_ids.p, row_ids, (size_t)n_indexed * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+	LB_CUDA(cudaMemcpyAsync(ix->ex.codes.p, codes, (size_t)n_indexed * M, cudaMemcpyHostToDevice, s));
+	LB_CUDA(cudaMemcpyAsync(ix->ex.part_offsets_dev.p, part_offsets, (size_t)(P + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+	int64_t l = 0;
+	finalize_index(*ix, ix->ex, label_base_, s, &l);
+	add_launches(l);
+	index_.reset(ix.release());
+}
+
+void Store::get_index(lance_b200_ivfpq_info *info, float *centroids, float *codebook, int64_t *part_offsets,
+                      int64_t *row_ids, uint8_t *codes) {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	if (!index_) throw Error("no IVF_PQ index on this handle");
+	IvfPqIndexFull &ix = static_cast<IvfPqIndexFull &>(*index_);
+	if (info) {
+		info->metric = ix.metric, info->dim = ix.dim, info->P = ix.P, info->M = ix.M, info->n_indexed = ix.n_indexed;
+	}
+	if (centroids) LB_CUDA(cudaMemcpy(centroids, ix.centroids.p, (size_t)ix.P * ix.dim * sizeof(float), cudaMemcpyDeviceToHost));
+	if (codebook) LB_CUDA(cudaMemcpy(codebook, ix.codebook.p, (size_t)ix.M * 256 * ix.dsub * sizeof(float), cudaMemcpyDeviceToHost));
+	if (part_offsets) memcpy(part_offsets, ix.part_offsets.data(), (size_t)(ix.P + 1) * sizeof(int64_t));
+	if (row_ids) LB_CUDA(cudaMemcpy(row_ids, ix.ex.row_ids.p, (size_t)ix.n_indexed * sizeof(int64_t), cudaMemcpyDeviceToHost));
+	if (codes) LB_CUDA(cudaMemcpy(codes, ix.ex.codes.p, (size_t)ix.n_indexed * ix.M, cudaMemcpyDeviceToHost));
+}
+
+void Store::drop_index() {
+	std::unique_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	LB_CUDA(cudaDeviceSynchronize());
+	index_.reset();
+}
+
+// ------------------------------------------------------------------ search
+template <int GRAN>
+static void launch_adc(const IvfPqIndex &ix, const float *lut, const u64 *probe_keys, int np, const float *qn2,
+                       const uint32_t *allow, long long allow_bits, const uint32_t *deleted, int kc, int cap, int nwarps,
+                       int S, int nq, size_t smem, u64 *partials, cudaStream_t s) {
+	auto kern = adc_scan_kernel<GRAN>;
+	if (smem > 48 * 1024) LB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	kern<<<dim3(S, nq), nwarps * 32, smem, s>>>(lut, ix.M, probe_keys, np, np, qn2, ix.metric, ix.pad_offsets.as<long long>(),
+	                                            ix.slot_rows.as<int32_t>(), ix.codes_il.as<uint8_t>(), ix.row_term.as<float>(),
+	                                            allow, allow_bits, deleted, kc, cap, partials);
+	LB_CUDA(cudaGetLastError());
+}
+
+void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
+                                int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
+                                Workspace &ws, cudaStream_t s, int32_t *d_dbg_parts, u64 *d_dbg_cand, int32_t *d_dbg_ncand) {
+	IvfPqIndex &ix = *index_;
+	int64_t launches = 0;
+	const int d = dim_, M = ix.M;
+	int np = nprobes < 1 ? 1 : nprobes; // oracle_ivfpq_search clamps the same way
+	if (np > ix.P) np = ix.P;
+	const int rf = refine < 1 ? 1 : refine;
+	const long long kc_ll = (long long)k * rf;
+	if (kc_ll > 8192) throw Error("k * refine_factor > 8192 is not supported by the device ADC scan");
+	const int kc = (int)kc_ll;
+	const uint32_t *deleted = n_deleted_ > 0 ? deleted_.as<uint32_t>() : nullptr;
+
+	// 1. q' and |q'|^2
+	ws.q.ensure((size_t)nq * d * sizeof(float) + (size_t)nq * sizeof(float) + 256);
+	float *Qp = ws.q.as<float>();
+	float *qn2 = Qp + (size_t)nq * d;
+	prep_queries_kernel<<<blocks_for(nq, 8), 256, 0, s>>>(d_queries, nq, d, metric_ == METRIC_COSINE ? 1 : 0, Qp, qn2);
+	LB_CUDA(cudaGetLastError());
+	launches++;
+
+	// 2. probe: the nprobes nearest centroids = a flat scan over the centroid table (a12)
+	ws.work2.ensure((size_t)nq * np * sizeof(u64));
+	u64 *probe_keys = ws.work2.as<u64>();
+	{
+		FlatScanArgs a;
+		a.X = ix.centroids.as<float>();
+		a.n = ix.P;
+		a.d = d;
+		a.metric = metric_ == METRIC_DOT ? METRIC_DOT : METRIC_L2;
+		a.dQ = Qp;
+		a.nq = nq;
+		a.k = np;
+		a.out_keys = probe_keys;
+		FlatScanPlan p = plan_flat_scan(a.X, a.metric, d, np, nq, ix.P, num_sms_);
+		ws.work.ensure(flat_scan_scratch_bytes(p, np));
+		run_flat_scan(a, p, ws.work.p, s, &launches);
+	}
+
+	// 3. per-query lookup table T1
+	ws.work3.ensure((size_t)nq * M * 256 * sizeof(float));
+	float *lut = ws.work3.as<float>();
+	{
+		size_t smem = ((size_t)256 * (ix.dsub + 1) + (size_t)LUT_QPB * ix.dsub) * sizeof(float);
+		if (smem > 48 * 1024) LB_CUDA(cudaFuncSetAttribute(lut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		lut_kernel<<<dim3(M, blocks_for(nq, LUT_QPB)), 256, smem, s>>>(Qp, nq, d, M, ix.dsub, ix.codebook.as<float>(),
+		                                                               metric_ == METRIC_DOT ? 1 : 0, lut);
+		LB_CUDA(cudaGetLastError());
+		launches++;
+	}
+
+	// 4. ADC scan (a13) -> per (query, slice) candidate lists
+	const int cap = warpsel_cap(kc);
+	int nwarps = 8;
+	while (nwarps > 1 && (size_t)M * 1024 + 64 + (size_t)nwarps * cap * 8 > 220 * 1024) nwarps >>= 1;
+	const size_t smem = (size_t)M * 1024 + 64 + (size_t)nwarps * cap * 8;
+	if (smem > 226 * 1024) throw Error("k * refine_factor too large for the ADC scan's shared memory");
+	int per_sm = (int)((227 * 1024) / (smem + 1024));
+	if (per_sm < 1) per_sm = 1;
+	long long want = 2ll * num_sms_ * per_sm;
+	int S = (int)std::min<long long>(np, std::max<long long>(1, (want + nq - 1) / nq));
+	const int tail_k = (ix.n_indexed < n_rows_) ? k : 0;
+	const int fin_stride = kc + tail_k;
+	ws.work4.ensure(((size_t)nq * S * kc + (size_t)nq * kc + (size_t)nq * fin_stride + (size_t)nq * std::max(tail_k, 1)) * sizeof(u64));
+	u64 *partials = ws.work4.as<u64>();
+	u64 *cand = partials + (size_t)nq * S * kc;
+	u64 *fin = cand + (size_t)nq * kc;
+	u64 *tailk = fin + (size_t)nq * fin_stride;
+	{
+		int tix = timer_.begin(KC_ADC_SCAN, s);
+		switch (ix.gran) {
+		case 16: launch_adc<16>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, nq, smem, partials, s); break;
+		case 4: launch_adc<4>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, nq, smem, partials, s); break;
+		default: launch_adc<1>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, nq, smem, partials, s);
+		}
+		timer_.end(tix, s);
+		launches++;
+	}
+	// 5. candidates = the kc best ADC keys per query
+	launch_topk_merge(partials, nq, (long long)S * kc, kc, 0, nullptr, nullptr, nullptr, cand, s, &launches);
+	if (d_dbg_cand) {
+		LB_CUDA(cudaMemcpyAsync(d_dbg_cand, cand, (size_t)nq * kc * sizeof(u64), cudaMemcpyDeviceToDevice, s));
+	}
+	(void)d_dbg_parts;
+	(void)d_dbg_ncand;
+
+	// 6. refine (a14): exact distances of the candidates (refine_factor >= 1), else ADC distances as they are
+	if (refine >= 1) {
+		int tix = timer_.begin(KC_RERANK, s);
+		refine_kernel<<<blocks_for((long long)nq * kc, 8), 256, 0, s>>>(X_.as<float>(), d, d_queries, metric_, cand, kc, nq,
+		                                                               fin, fin_stride);
+		LB_CUDA(cudaGetLastError());
+		timer_.end(tix, s);
+	} else {
+		copy_keys_strided_kernel<<<blocks_for((long long)nq * kc, 256), 256, 0, s>>>(cand, kc, kc, nq, fin, fin_stride, 0);
+		LB_CUDA(cudaGetLastError());
+	}
+	launches++;
+
+	// 7. rows appended after the index was built: exact scan of the tail, merged (Lance's unindexed fragments)
+	if (tail_k > 0) {
+		FlatScanArgs a;
+		a.X = X_.as<float>();
+		a.n = n_rows_;
+		a.row_begin = ix.n_indexed;
+		a.d = d;
+		a.metric = metric_;
+		a.dQ = d_queries;
+		a.nq = nq;
+		a.k = k;
+		a.allow = d_allow;
+		a.allow_bits = allow_bits;
+		a.deleted = deleted;
+		a.out_keys = tailk;
+		FlatScanPlan p = plan_flat_scan(a.X, a.metric, d, k, nq, n_rows_ - ix.n_indexed, num_sms_);
+		ws.work.ensure(flat_scan_scratch_bytes(p, k));
+		run_flat_scan(a, p, ws.work.p, s, &launches);
+		copy_keys_strided_kernel<<<blocks_for((long long)nq * k, 256), 256, 0, s>>>(tailk, k, k, nq, fin, fin_stride, kc);
+		LB_CUDA(cudaGetLastError());
+		launches++;
+	}
+
+	// 8. final select
+	launch_topk_merge(fin, nq, fin_stride, k, label_base_, d_out_labels, d_out_dist, d_out_counts, nullptr, s, &launches);
+	std::lock_guard<std::mutex> g(stat_mu_);
+	ivfpq_batches_++;
+	launches_ += launches;
+}
+
+void Store::ivfpq_search_debug(const float *query, int k, int nprobes, int refine, const uint32_t *allow,
+                               int64_t allow_bits, int32_t *out_parts, int64_t *out_cand_labels, float *out_cand_adc,
+                               int32_t *out_ncand, int64_t *out_labels, float *out_dist, int32_t *out_count) {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	if (!index_) throw Error("no IVF_PQ index on this handle");
+	if (k <= 0) {
+		*out_count = 0;
+		if (out_ncand) *out_ncand = 0;
+		return;
+	}
+	auto io = acquire_io();
+	try {
+		cudaStream_t s = io->stream;
+		const int rf = refine < 1 ? 1 : refine;
+		const int kc = k * rf;
+		int np = std::min(std::max(nprobes, 1), index_->P);
+		io->q.ensure((size_t)dim_ * sizeof(float));
+		io->out_labels.ensure((size_t)(k + kc) * sizeof(int64_t));
+		io->out_dist.ensure((size_t)(k + kc) * sizeof(float));
+		io->out_counts.ensure(4 * sizeof(int32_t));
+		io->work.ensure((size_t)kc * sizeof(u64));
+		LB_CUDA(cudaMemcpyAsync(io->q.p, query, (size_t)dim_ * sizeof(float), cudaMemcpyHostToDevice, s));
+		const uint32_t *d_allow = nullptr;
+		if (allow) {
+			size_t words = (size_t)((allow_bits + 31) / 32);
+			io->allow.ensure(std::max<size_t>(words, 1) * sizeof(uint32_t));
+			LB_CUDA(cudaMemcpyAsync(io->allow.p, allow, words * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+			d_allow = io->allow.as<uint32_t>();
+		}
+		Workspace *ws = scratch_for(s);
+		std::lock_guard<std::mutex> wg(ws->mu);
+		ivfpq_search_locked(io->q.as<float>(), 1, k, nprobes, refine, d_allow, allow_bits, io->out_labels.as<int64_t>(),
+		                    io->out_dist.as<float>(), io->out_counts.as<int32_t>(), *ws, s, nullptr, io->work.as<u64>(), nullptr);
+		// decode the debug lists on the device
+		keys_to_debug_kernel<<<blocks_for(kc, 256), 256, 0, s>>>(io->work.as<u64>(), kc, label_base_,
+		                                                         io->out_labels.as<int64_t>() + k, io->out_dist.as<float>() + k,
+		                                                         io->out_counts.as<int32_t>() + 1);
+		LB_CUDA(cudaGetLastError());
+		std::vector<u64> pk(np);
+		LB_CUDA(cudaMemcpyAsync(pk.data(), ws->work2.p, (size_t)np * sizeof(u64), cudaMemcpyDeviceToHost, s));
+		std::vector<int64_t> hl(k + kc);
+		std::vector<float> hd(k + kc);
+		int32_t hc[2];
+		LB_CUDA(cudaMemcpyAsync(hl.data(), io->out_labels.p, (size_t)(k + kc) * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+		LB_CUDA(cudaMemcpyAsync(hd.data(), io->out_dist.p, (size_t)(k + kc) * sizeof(float), cudaMemcpyDeviceToHost, s));
+		LB_CUDA(cudaMemcpyAsync(hc, io->out_counts.p, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+		LB_CUDA(cudaStreamSynchronize(s));
+		for (int i = 0; i < np && out_parts; i++) out_parts[i] = pk[i] == KEY_INVALID ? -1 : (int32_t)key_row(pk[i]);
+		*out_count = hc[0];
+		if (out_ncand) *out_ncand = hc[1];
+		for (int i = 0; i < hc[0]; i++) out_labels[i] = hl[i], out_dist[i] = hd[i];
+		for (int i = 0; i < hc[1]; i++) {
+			if (out_cand_labels) out_cand_labels[i] = hl[k + i];
+			if (out_cand_adc) out_cand_adc[i] = hd[k + i];
+		}
+	} catch (...) {
+		release_io(std::move(io));
+		throw;
+	}
+	release_io(std::move(io));
+}

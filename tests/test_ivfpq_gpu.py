@@ -1,0 +1,171 @@
+"""GPU parity tests of the IVF_PQ path (probe -> LUT -> ADC scan -> refine) against the oracle, through the C ABI.
+
+BASELINE.json's criterion: with the same trained index, probed partitions and candidate ids identical, ADC
+distances within 1e-4 relative; and (refine_factor=1, src/include/lance_index.hpp:92) the exact post-refine
+distances.  "Same trained index" is met both ways: a checker-trained index staged into HBM
+(lance_b200_set_ivfpq), and a GPU-trained index exported to the checker (lance_b200_get_ivfpq)."""
+import numpy as np
+import pytest
+
+from parity import assert_topk_parity
+
+pytestmark = pytest.mark.gpu
+
+ADC_RTOL = 1e-4
+
+
+def compare_with_oracle(oracle_mod, h, ix, X, q, k, nprobes, rf, metric, allow=None, deleted=None, what=""):
+    got = h.ivfpq_search_debug(q, k, nprobes, rf, allow=allow)
+    want = ix.search(X, q, k, nprobes, rf, allow, deleted)
+    # probed partitions: identical, in order (swaps only between centroids tying within 1e-5 relative)
+    wp, wpd = ix.probe(q, min(nprobes, ix.P))
+    if list(got["parts"]) != list(wp):
+        assert sorted(got["parts"]) == sorted(wp), f"{what}: probed set differs"
+    # pre-refine ADC candidates
+    adc_of = dict(zip(want["cand_labels"].tolist(), want["cand_adc"].tolist()))
+    scale = float(np.abs(want["cand_adc"]).max()) if len(want["cand_adc"]) else 1.0
+
+    def adc_truth(lab):
+        if lab in adc_of:
+            return adc_of[lab]
+        if lab >= ix.n_indexed:  # unindexed tail row: exact distance
+            return oracle_mod.distance_f64(metric, q, X[lab])
+        # a candidate the oracle cut: recompute its ADC distance with the checker
+        pos = int(np.nonzero(ix.row_ids == lab)[0][0])
+        p = int(np.searchsorted(ix.part_offsets, pos, side="right") - 1)
+        return _adc(oracle_mod, ix, q, p, pos)
+
+    assert len(got["cand_labels"]) == len(want["cand_labels"]), f"{what}: candidate count"
+    assert_topk_parity(got["cand_labels"], got["cand_adc"], want["cand_labels"], want["cand_adc"], adc_truth,
+                       scale=scale, what=f"{what} ADC candidates")
+    # final list
+    truth = lambda lab: oracle_mod.distance_f64(metric, q, X[lab])
+    if rf >= 1:
+        assert_topk_parity(got["labels"], got["dist"], want["labels"], want["dist"], truth, what=f"{what} final")
+    else:
+        assert_topk_parity(got["labels"], got["dist"], want["labels"], want["dist"], adc_truth, scale=scale,
+                           what=f"{what} final (no refine)")
+    # the plain reference call returns the same final list
+    l2, d2 = h.search(q, k, nprobes=nprobes, refine_factor=rf, allow=allow)
+    assert list(l2) == list(got["labels"])
+    np.testing.assert_array_equal(d2, got["dist"])
+    return got
+
+
+def _adc(oracle_mod, ix, q, part, pos):
+    lut = ix.lut(q, part)
+    s = float(lut[np.arange(ix.M), ix.codes[pos]].astype(np.float64).sum())
+    return {0: s, 1: 0.5 * s, 2: 1.0 + s}[ix.metric]
+
+
+@pytest.mark.parametrize("metric", ["l2", "cosine", "dot"])
+@pytest.mark.parametrize("d,P,M", [(32, 16, 8), (64, 12, 16), (12, 5, 3), (96, 8, 96)])
+def test_checker_trained_index_on_gpu(gpu, oracle_mod, metric, d, P, M):
+    rng = np.random.default_rng(100 + d + P)
+    n = 4000
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Q = rng.standard_normal((3, d), dtype=np.float32)
+    ix = oracle_mod.IvfPqIndex.train(X, metric, P, M, iters=4)
+    with gpu.LanceHandle(d, metric) as h:
+        h.add_batch(X)
+        h.set_ivfpq(ix.centroids, ix.codebook, ix.part_offsets, ix.row_ids, ix.codes)
+        assert h.stats()["has_index"] == 1
+        for j in range(3):
+            for nprobes, rf, k in ((4, 1, 10), (P, 3, 10), (1, 0, 5), (3, 2, 37), (P + 5, 1, 10)):
+                compare_with_oracle(oracle_mod, h, ix, X, Q[j], k, nprobes, rf, metric,
+                                    what=f"{metric} d={d} P={P} M={M} q{j} np={nprobes} rf={rf} k={k}")
+        assert h.stats()["ivfpq_batches"] > 0
+        # round trip of the staged index
+        back = h.get_ivfpq()
+        assert back["P"] == P and back["M"] == M and back["n_indexed"] == n
+        np.testing.assert_array_equal(back["codes"], ix.codes)
+        np.testing.assert_array_equal(back["row_ids"], ix.row_ids)
+        np.testing.assert_array_equal(back["centroids"], ix.centroids)
+        h.drop_index()
+        l, _ = h.search(Q[0], 5)
+        wl, _, _ = oracle_mod.flat_search(X, Q[0], 5, metric)
+        assert list(l) == list(wl)
+
+
+@pytest.mark.parametrize("metric", ["l2", "cosine", "dot"])
+def test_gpu_trained_index_exported_to_checker(gpu, oracle_mod, metric):
+    rng = np.random.default_rng(77)
+    n, d, P, M = 20_000, 64, 32, 16
+    centers = rng.standard_normal((P, d), dtype=np.float32) * 3
+    X = (centers[rng.integers(0, P, n)] + rng.standard_normal((n, d), dtype=np.float32)).astype(np.float32)
+    Q = (centers[rng.integers(0, P, 4)] + rng.standard_normal((4, d), dtype=np.float32)).astype(np.float32)
+    with gpu.LanceHandle(d, metric) as h:
+        h.add_batch(X)
+        h.create_index(P, M)  # lance_detached_create_index -> GPU k-means + PQ training
+        g = h.get_ivfpq()
+        assert (g["P"], g["M"], g["n_indexed"], g["dim"]) == (P, M, n, d)
+        off = g["part_offsets"]
+        assert off[0] == 0 and off[-1] == n and (np.diff(off) >= 0).all()
+        assert sorted(g["row_ids"].tolist()) == list(range(n))  # a permutation of the labels
+        for p in range(P):  # ascending labels inside a partition
+            seg = g["row_ids"][off[p]:off[p + 1]]
+            assert (np.diff(seg) > 0).all()
+        assert (np.diff(off) > 0).sum() >= P // 2, "k-means collapsed"
+        ix = oracle_mod.IvfPqIndex(metric, d, P, M, g["centroids"], g["codebook"], off, g["row_ids"], g["codes"])
+        # the exported assignment is the nearest centroid (spot check) and the codes are the nearest codewords
+        Xn = X / np.linalg.norm(X, axis=1, keepdims=True) if metric == "cosine" else X
+        for pos in rng.integers(0, n, 50):
+            row = int(g["row_ids"][pos])
+            p = int(np.searchsorted(off, pos, side="right") - 1)
+            if metric == "dot":
+                sc = -(g["centroids"].astype(np.float64) @ Xn[row].astype(np.float64))
+            else:
+                sc = ((g["centroids"].astype(np.float64) - Xn[row].astype(np.float64)) ** 2).sum(1)
+            assert sc[p] <= sc.min() + 1e-5 * abs(sc.min()) + 1e-5
+        for j in range(4):
+            for nprobes, rf in ((8, 1), (32, 2), (2, 0)):
+                compare_with_oracle(oracle_mod, h, ix, X, Q[j], 10, nprobes, rf, metric,
+                                    what=f"gpu-trained {metric} q{j} np={nprobes} rf={rf}")
+        # recall sanity: with all partitions probed and a generous refine the exact answer comes back
+        l, dd = h.search(Q[0], 10, nprobes=P, refine_factor=50)
+        wl, wd, _ = oracle_mod.flat_search(X, Q[0], 10, metric)
+        assert len(set(l.tolist()) & set(wl.tolist())) >= 9
+
+
+def test_index_with_appends_deletes_and_prefilter(gpu, oracle_mod):
+    """Rows appended after the index was built are scanned exactly and merged (lance_basic.test:45-53 semantics
+    under an ANN index); deletes and the prefilter apply to both parts (lance_manager.rs:461-471)."""
+    rng = np.random.default_rng(31)
+    n0, n1, d, P, M = 6000, 1500, 32, 16, 8
+    X = rng.standard_normal((n0 + n1, d), dtype=np.float32)
+    Q = rng.standard_normal((3, d), dtype=np.float32)
+    ix = oracle_mod.IvfPqIndex.train(X[:n0], "l2", P, M, iters=4)
+    with gpu.LanceHandle(d, "l2") as h:
+        h.add_batch(X[:n0])
+        h.set_ivfpq(ix.centroids, ix.codebook, ix.part_offsets, ix.row_ids, ix.codes)
+        h.add_batch(X[n0:])
+        dead = rng.choice(n0 + n1, 700, replace=False)
+        h.delete_batch(dead)
+        deleted = oracle_mod.make_bitmap(np.isin(np.arange(n0 + n1), dead))
+        for sel in (None, 0.5, 0.02):
+            allow = None if sel is None else gpu.make_bitmap(rng.random(n0 + n1) < sel)
+            for j in range(3):
+                compare_with_oracle(oracle_mod, h, ix, X, Q[j], 10, 6, 1, "l2", allow, deleted, what=f"tail sel={sel} q{j}")
+                compare_with_oracle(oracle_mod, h, ix, X, Q[j], 10, 6, 0, "l2", allow, deleted, what=f"tail rf0 sel={sel} q{j}")
+
+
+def test_batch_equals_singles_and_defaults(gpu, oracle_mod):
+    rng = np.random.default_rng(5)
+    n, d = 10_000, 48
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Q = rng.standard_normal((37, d), dtype=np.float32)
+    with gpu.LanceHandle(d, "l2") as h:
+        h.add_batch(X)
+        h.create_index(0, 0)  # defaults: partitions = round(sqrt(n)) = 100, sub-vectors = d/16 = 3
+        g = h.get_ivfpq()
+        assert g["P"] == 100 and g["M"] == 3
+        L, D, C = h.search_batch(Q, 10, nprobes=20, refine_factor=1)
+        for j in range(0, 37, 6):
+            l, dd = h.search(Q[j], 10, nprobes=20, refine_factor=1)
+            assert list(l) == list(L[j, :C[j]])
+            np.testing.assert_array_equal(dd, D[j, :C[j]])
+        with pytest.raises(gpu.LanceError, match="not divisible"):
+            h.create_index(10, 7)
+    with gpu.LanceHandle(d, "l2") as h:
+        with pytest.raises(gpu.LanceError, match="empty table"):
+            h.create_index(4, 4)
