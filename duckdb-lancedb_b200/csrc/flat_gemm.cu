@@ -1,15 +1,276 @@
-// placeholder until the tcgen05 path lands
+// flat_gemm.cu — batched exact flat search on the tensor cores (sm_100a tcgen05 / TMEM / TMA).
+//
+// Replaces, for query batches, the CPU loop the reference enters at rust_lib/src/lance_manager.rs:411-419
+// (SURVEY.md 8a row a11).  The contraction q.x is GEMM-shaped, so it runs as bf16 UMMA over a bf16 shadow of
+// the table; exactness is recovered with an error bound and an fp32 re-rank:
+//
+//   1. shadow rows (once per appended row): bf16 of x (dot), x/|x| (cosine) or [x, -|x|^2/2] (l2), so that
+//      every metric ranks by ONE inner product  score = <Qs[q], Xs[row]>  (larger = nearer);
+//   2. |score - exact| <= err(q) = ERR_C |q| max|x|  (flat_gemm_aux.cuh).  If A_k is the k-th best approximate
+//      score over any set of live rows, every true top-k row has score >= A_k - 2 err(q): that is the
+//      candidate threshold.  Rows are processed in geometrically growing segments; after each one the
+//      threshold of every query is refreshed from its candidate list and the list is compacted, so the
+//      large final segments emit a few dozen candidates per query;
+//   3. flat_gemm_kernel (flat_gemm_kernel.cuh) streams a segment: TMA -> smem -> tcgen05.mma -> TMEM ->
+//      fused threshold filter.  No distance matrix reaches HBM;
+//   4. rerank_kernel computes the exact fp32 distance of the surviving candidates and selects the top k
+//      under the library's (distance, label) order — the result is the exact flat search, not an approximation;
+//   5. a query whose candidate list overflowed (degenerate data: masses of ties) is re-run by the fp32 scan.
+//
+// Roofline: tensor pipe for large batches (2*B*n*d flops), HBM for small ones (n*Kpad*2 shadow bytes).
 #include "flat_gemm.h"
+
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "flat_gemm_aux.cuh"
+#include "flat_gemm_kernel.cuh"
+
 namespace lb {
-struct FlatGemm::Impl {};
-FlatGemm::FlatGemm(int, int, int, int) : impl_(nullptr) {}
-FlatGemm::~FlatGemm() {}
-bool FlatGemm::supported(int, int) { return false; }
-bool FlatGemm::worthwhile(int, long long, int, int) { return false; }
-void FlatGemm::sync_rows(const float *, long long, long long, cudaStream_t, int64_t *) {}
-void FlatGemm::invalidate() {}
-void FlatGemm::search(const float *, long long, const uint32_t *, const float *, int, int, const uint32_t *, long long,
-                      long long, int64_t *, float *, int32_t *, Workspace &, cudaStream_t, int64_t *, int64_t *) {
-	throw Error("tcgen05 flat path not built");
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static encode_tiled_fn get_encode_fn() {
+	static encode_tiled_fn fn = nullptr;
+	if (fn) return fn;
+	void *p = nullptr;
+	cudaDriverEntryPointQueryResult qres;
+	LB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+	if (!p || qres != cudaDriverEntryPointSuccess) throw Error("cuTensorMapEncodeTiled is not available in this driver");
+	fn = reinterpret_cast<encode_tiled_fn>(p);
+	return fn;
 }
+
+// bf16 row-major [rows][Kpad] -> tiled map with a {64, 128} box and the 128-byte swizzle the UMMA descriptors expect
+static void encode_rows_map(CUtensorMap *m, const void *base, long long rows, int Kpad) {
+	cuuint64_t dims[2] = {(cuuint64_t)Kpad, (cuuint64_t)rows};
+	cuuint64_t strides[1] = {(cuuint64_t)Kpad * 2};
+	cuuint32_t box[2] = {64, 128};
+	cuuint32_t estr[2] = {1, 1};
+	CUresult r = get_encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+	                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+	                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+	if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+}
+
+static constexpr int TC_CAP = 16384;      // candidate slots per query
+static constexpr int TC_QCHUNK = 4096;    // queries per pipeline pass (candidate buffer = 512 MB)
+static constexpr int TC_SEED_TILES = 16;  // first segment: 2048 rows, everything is a candidate
+static constexpr size_t TC_SMEM_MAX = 232448;
+
+struct FlatGemm::Impl {
+	int device, num_sms, dim, metric;
+	int Kreal16, Kpad, nkb, ksteps_last;
+	DevBuf shadow;   // bf16 [cap_rows][Kpad]
+	DevBuf max_norm; // one float (as bits)
+	long long rows_done = 0, cap_rows = 0;
+	CUtensorMap tmX;
+	const void *tmX_base = nullptr;
+	long long tmX_rows = -1;
+	bool attr_set = false;
+};
+
+static void shape_for(int dim, int metric, int &Kreal16, int &Kpad, int &nkb, int &ksteps_last) {
+	int kr = metric == METRIC_L2 ? dim + 3 : dim;
+	Kreal16 = (kr + 15) & ~15;
+	Kpad = (Kreal16 + 63) & ~63;
+	nkb = Kpad / 64;
+	ksteps_last = (Kreal16 - (nkb - 1) * 64) / 16;
+}
+
+FlatGemm::FlatGemm(int device, int num_sms, int dim, int metric) : impl_(new Impl()) {
+	impl_->device = device;
+	impl_->num_sms = num_sms;
+	impl_->dim = dim;
+	impl_->metric = metric;
+	shape_for(dim, metric, impl_->Kreal16, impl_->Kpad, impl_->nkb, impl_->ksteps_last);
+	impl_->max_norm.alloc(16);
+	LB_CUDA(cudaMemset(impl_->max_norm.p, 0, 16));
+}
+FlatGemm::~FlatGemm() { delete impl_; }
+
+bool FlatGemm::supported(int dim, int metric, int k) {
+	int Kreal16, Kpad, nkb, ks;
+	shape_for(dim, metric, Kreal16, Kpad, nkb, ks);
+	if (dim < 16 || k < 1 || k > 1024) return false;
+	// one resident query tile + two single-k-block stages must fit
+	return gemm_smem_bytes(1, nkb, 1, 2) <= TC_SMEM_MAX;
+}
+
+bool FlatGemm::worthwhile(int nq, long long n, int dim, int k) {
+	(void)dim;
+	(void)k;
+	return nq >= 8 && n >= 65536 && n < (1ll << 31) - 256;
+}
+
+void FlatGemm::invalidate() {
+	impl_->rows_done = 0;
+	impl_->tmX_base = nullptr;
+}
+
+void FlatGemm::sync_rows(const float *X, long long n, long long cap_rows, cudaStream_t s, int64_t *launches) {
+	Impl &im = *impl_;
+	if (im.cap_rows < cap_rows || !im.shadow.p) {
+		// the store grew (and called invalidate()): rebuild the shadow at the new capacity
+		im.shadow.alloc((size_t)cap_rows * im.Kpad * 2 + 1024);
+		im.cap_rows = cap_rows;
+		im.rows_done = 0;
+		im.tmX_base = nullptr;
+		LB_CUDA(cudaMemsetAsync(im.max_norm.p, 0, 16, s));
+	}
+	if (im.rows_done < n) {
+		long long cnt = n - im.rows_done;
+		shadow_rows_kernel<<<(unsigned)((cnt + 7) / 8), 256, 0, s>>>(X, im.rows_done, n, im.dim, im.metric, im.Kpad,
+		                                                             im.shadow.as<__nv_bfloat16>(),
+		                                                             im.max_norm.as<uint32_t>());
+		LB_CUDA(cudaGetLastError());
+		if (launches) (*launches)++;
+		im.rows_done = n;
+	}
+	if (im.tmX_base != im.shadow.p || im.tmX_rows != n) {
+		encode_rows_map(&im.tmX, im.shadow.p, n, im.Kpad); // rows beyond n read as zeros (TMA out-of-bounds fill)
+		im.tmX_base = im.shadow.p;
+		im.tmX_rows = n;
+	}
+}
+
+struct GemmPlan {
+	int QT, KS, S, NG, R;
+	size_t smem;
+};
+
+static GemmPlan plan_gemm(int tilesQ, int nkb, int num_sms) {
+	GemmPlan best{};
+	// largest resident query block that still leaves two whole-tile stages
+	int qt_max = 1;
+	for (int qt = 2; qt <= 8; qt++)
+		if (gemm_smem_bytes(qt, nkb, nkb, 2) <= TC_SMEM_MAX) qt_max = qt;
+	if (qt_max > tilesQ) qt_max = tilesQ;
+	int NG = (tilesQ + qt_max - 1) / qt_max;
+	int QT = (tilesQ + NG - 1) / NG;
+	best.QT = QT;
+	best.NG = NG;
+	if (QT > 1) {
+		best.KS = nkb;
+		best.S = 2;
+		while (best.S < 4 && gemm_smem_bytes(QT, nkb, nkb, best.S + 1) <= TC_SMEM_MAX) best.S++;
+	} else {
+		// one query tile: stages may be single k-blocks; prefer >= 3 stages
+		best.KS = nkb;
+		while (best.KS > 1 && (nkb % best.KS != 0 || gemm_smem_bytes(1, nkb, best.KS, 3) > TC_SMEM_MAX)) best.KS--;
+		best.S = 2;
+		while (best.S < 6 && gemm_smem_bytes(1, nkb, best.KS, best.S + 1) <= TC_SMEM_MAX) best.S++;
+		if (gemm_smem_bytes(1, nkb, best.KS, best.S) > TC_SMEM_MAX) throw Error("dimension too large for the tcgen05 flat path");
+	}
+	best.R = std::max(1, num_sms / NG);
+	best.smem = gemm_smem_bytes(best.QT, nkb, best.KS, best.S);
+	return best;
+}
+
+void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, const float *d_queries, int nq_total, int k,
+                      const uint32_t *d_allow, long long allow_bits, long long label_base, int64_t *d_out_labels,
+                      float *d_out_dist, int32_t *d_out_counts, Workspace &ws, cudaStream_t s, int64_t *launches,
+                      int64_t *fallback_queries, KernelTimer *timer) {
+	Impl &im = *impl_;
+	const int d = im.dim, Kpad = im.Kpad;
+	if (!im.attr_set) {
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(refresh_threshold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
+		LB_CUDA(cudaFuncSetAttribute(rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
+		im.attr_set = true;
+	}
+	const int cap = warpsel_cap(k);
+	const size_t sel_smem = (size_t)8 * cap * sizeof(u64);
+	const long long ntiles = (n + GEMM_BN - 1) / GEMM_BN;
+	// segment growth: candidates per refresh ~ k * growth * (margin inflation); keep that well under TC_CAP
+	int growth = TC_CAP / (8 * k);
+	growth = std::max(2, std::min(16, growth));
+
+	for (int q0 = 0; q0 < nq_total; q0 += TC_QCHUNK) {
+		const int nq = std::min(TC_QCHUNK, nq_total - q0);
+		const int tilesQ = (nq + 127) / 128;
+		GemmPlan pl = plan_gemm(tilesQ, im.nkb, im.num_sms);
+		const int nslots = pl.NG * pl.QT * 128;
+
+		ws.work2.ensure((size_t)nslots * Kpad * 2 + 1024);
+		ws.work3.ensure((size_t)nslots * 5 * 4 + 64);
+		ws.work.ensure((size_t)nslots * TC_CAP * sizeof(uint2));
+		__nv_bfloat16 *Qs = ws.work2.as<__nv_bfloat16>();
+		float *margin = ws.work3.as<float>();
+		float *thr = margin + nslots;
+		uint32_t *cnt = reinterpret_cast<uint32_t *>(thr + nslots);
+		uint32_t *flag = cnt + nslots;
+		uint32_t *flag_out = flag + nslots; // + one total counter behind it
+		uint32_t *total = flag_out + nslots;
+		uint2 *cand = ws.work.as<uint2>();
+		const float *Qchunk = d_queries + (size_t)q0 * d;
+
+		prep_query_tiles_kernel<<<(nslots + 7) / 8, 256, 0, s>>>(Qchunk, nq, nslots, d, im.metric, Kpad,
+		                                                         im.max_norm.as<uint32_t>(), Qs, margin, thr, cnt, flag);
+		LB_CUDA(cudaGetLastError());
+		(*launches)++;
+		CUtensorMap tmQ;
+		encode_rows_map(&tmQ, Qs, nslots, Kpad);
+
+		GemmParams p;
+		p.nkb = im.nkb, p.ksteps_last = im.ksteps_last, p.QT = pl.QT, p.KS = pl.KS, p.S = pl.S, p.NG = pl.NG;
+		p.n_rows = n, p.thr = thr, p.cnt = cnt, p.cand = cand, p.CAP = TC_CAP;
+		p.deleted = deleted, p.allow = d_allow, p.allow_bits = allow_bits;
+		long long t0 = 0, seg = TC_SEED_TILES;
+		while (t0 < ntiles) {
+			long long t1 = std::min(ntiles, t0 + seg);
+			if (ntiles - t1 < seg) t1 = ntiles; // do not leave a short tail segment
+			p.tile_lo = t0, p.tile_hi = t1;
+			p.R = (int)std::min<long long>(pl.R, t1 - t0);
+			int tix = timer ? timer->begin(KC_FLAT_GEMM, s) : -1;
+			flat_gemm_kernel<<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(tmQ, im.tmX, p);
+			LB_CUDA(cudaGetLastError());
+			if (timer) timer->end(tix, s);
+			refresh_threshold_kernel<<<nq, 256, sel_smem, s>>>(cand, TC_CAP, cnt, thr, margin, flag, k, cap);
+			LB_CUDA(cudaGetLastError());
+			(*launches) += 2;
+			t0 = t1;
+			seg *= growth;
+		}
+		int tix = timer ? timer->begin(KC_RERANK, s) : -1;
+		rerank_kernel<<<nq, 256, sel_smem, s>>>(X, d, im.metric, Qchunk, cand, TC_CAP, cnt, flag, k, cap, label_base,
+		                                        d_out_labels + (size_t)q0 * k, d_out_dist + (size_t)q0 * k,
+		                                        d_out_counts + q0);
+		LB_CUDA(cudaGetLastError());
+		if (timer) timer->end(tix, s);
+		LB_CUDA(cudaMemsetAsync(total, 0, 4, s));
+		count_flags_kernel<<<(nq + 255) / 256, 256, 0, s>>>(flag, cnt, TC_CAP, nq, flag_out, total);
+		LB_CUDA(cudaGetLastError());
+		(*launches) += 2;
+
+		// overflowed lists (degenerate data) -> exact fp32 scan for those queries.  One small read-back per pass.
+		uint32_t h_total = 0;
+		LB_CUDA(cudaMemcpyAsync(&h_total, total, 4, cudaMemcpyDeviceToHost, s));
+		LB_CUDA(cudaStreamSynchronize(s));
+		if (h_total > 0) {
+			std::vector<uint32_t> hf(nq);
+			LB_CUDA(cudaMemcpyAsync(hf.data(), flag_out, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+			LB_CUDA(cudaStreamSynchronize(s));
+			for (int q = 0; q < nq; q++) {
+				if (!hf[q]) continue;
+				FlatScanArgs a;
+				a.X = X, a.n = n, a.d = d, a.metric = im.metric;
+				a.dQ = Qchunk + (size_t)q * d;
+				a.nq = 1, a.k = k;
+				a.allow = d_allow, a.allow_bits = allow_bits, a.deleted = deleted, a.label_base = label_base;
+				a.out_labels = d_out_labels + (size_t)(q0 + q) * k;
+				a.out_dist = d_out_dist + (size_t)(q0 + q) * k;
+				a.out_counts = d_out_counts + q0 + q;
+				FlatScanPlan fp = plan_flat_scan(X, im.metric, d, k, 1, n, im.num_sms);
+				ws.work4.ensure(flat_scan_scratch_bytes(fp, k));
+				run_flat_scan(a, fp, ws.work4.p, s, launches);
+				(*fallback_queries)++;
+			}
+		}
+	}
+}
+
 } // namespace lb

@@ -11,7 +11,7 @@ public:
 	~FlatGemm();
 
 	// is the tensor path implemented for this shape at all
-	static bool supported(int dim, int k);
+	static bool supported(int dim, int metric, int k);
 	// is it the faster choice (auto mode)
 	static bool worthwhile(int nq, long long n, int dim, int k);
 
@@ -22,7 +22,7 @@ public:
 	void search(const float *X, long long n, const uint32_t *deleted, const float *d_queries, int nq, int k,
 	            const uint32_t *d_allow, long long allow_bits, long long label_base, int64_t *d_out_labels,
 	            float *d_out_dist, int32_t *d_out_counts, Workspace &ws, cudaStream_t s, int64_t *launches,
-	            int64_t *fallback_queries);
+	            int64_t *fallback_queries, KernelTimer *timer);
 
 private:
 	struct Impl;

@@ -1,0 +1,280 @@
+// flat_gemm_aux.cuh — the small kernels around flat_gemm_kernel (included by flat_gemm.cu):
+// bf16 shadow of the table, bf16 query tiles + error margins, threshold refresh / list compaction between
+// row segments, and the exact fp32 re-rank that produces the returned (label, distance) lists.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "topk.cuh"
+
+namespace lb {
+
+// Worst-case |bf16 score - exact score| <= ERR_C * |q| * |x|: both operands are rounded to bf16 (2^-9
+// relative each, 2^-8 + 2^-18 on a product, Cauchy-Schwarz over the sum) plus the fp32 accumulation in
+// the tensor core; 2^-8 = 0.00390625, the rest is slack.
+static constexpr float GEMM_ERR_C = 0.0041f;
+
+__device__ __forceinline__ float warp_sum(float v) {
+	for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+	return v;
+}
+
+// ------------------------------------------------------------------ shadow rows
+// One warp per row: Xs[row] = bf16 of  x (dot) | x/|x| (cosine) | [x, -|x|^2/2 as three bf16 terms] (l2),
+// zero padded to Kpad.  max_norm = max |x| over the converted rows (float bits, non-negative -> uint max).
+__global__ void __launch_bounds__(256) shadow_rows_kernel(const float *__restrict__ X, long long row_lo, long long row_hi,
+                                                          int d, int metric, int Kpad, __nv_bfloat16 *__restrict__ Xs,
+                                                          uint32_t *__restrict__ max_norm_bits) {
+	long long row = row_lo + (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (row >= row_hi) return;
+	const unsigned lane = lane_id();
+	const float *x = X + (size_t)row * d;
+	__nv_bfloat16 *o = Xs + (size_t)row * Kpad;
+	float s = 0.f;
+	for (int i = lane; i < d; i += 32) {
+		float v = __ldg(x + i);
+		s = fmaf(v, v, s);
+	}
+	s = warp_sum(s);
+	const float nrm = sqrtf(s);
+	float scale = 1.f;
+	if (metric == METRIC_COSINE) scale = nrm > 0.f ? 1.0f / nrm : 0.f;
+	for (int i = lane; i < Kpad; i += 32) {
+		float v = 0.f;
+		if (i < d) v = __ldg(x + i) * scale;
+		o[i] = __float2bfloat16_rn(v);
+	}
+	if (metric == METRIC_L2 && lane == 0) {
+		float h = -0.5f * s;
+		__nv_bfloat16 h1 = __float2bfloat16_rn(h);
+		float r1 = h - __bfloat162float(h1);
+		__nv_bfloat16 h2 = __float2bfloat16_rn(r1);
+		float r2 = r1 - __bfloat162float(h2);
+		__nv_bfloat16 h3 = __float2bfloat16_rn(r2);
+		o[d] = h1, o[d + 1] = h2, o[d + 2] = h3;
+	}
+	if (lane == 0 && metric != METRIC_COSINE) atomicMax(max_norm_bits, __float_as_uint(nrm));
+}
+
+// ------------------------------------------------------------------ query tiles
+// One warp per padded query slot: Qs[q] = bf16(q) (+ three 1.0 columns for l2), margin[q] = 2 * err bound,
+// thr[q] = -inf (+inf for padding slots, which then never emit), cnt[q] = 0, flag[q] = 0.
+__global__ void __launch_bounds__(256) prep_query_tiles_kernel(const float *__restrict__ Q, int nq, int nslots, int d,
+                                                               int metric, int Kpad, const uint32_t *__restrict__ max_norm_bits,
+                                                               __nv_bfloat16 *__restrict__ Qs, float *__restrict__ margin,
+                                                               float *__restrict__ thr, uint32_t *__restrict__ cnt,
+                                                               uint32_t *__restrict__ flag) {
+	int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (q >= nslots) return;
+	const unsigned lane = lane_id();
+	__nv_bfloat16 *o = Qs + (size_t)q * Kpad;
+	const bool real = q < nq;
+	float s = 0.f;
+	for (int i = lane; i < Kpad; i += 32) {
+		float v = (real && i < d) ? __ldg(Q + (size_t)q * d + i) : 0.f;
+		if (real && metric == METRIC_L2 && i >= d && i < d + 3) v = 1.0f;
+		else s = fmaf(v, v, s);
+		o[i] = __float2bfloat16_rn(v);
+	}
+	s = warp_sum(s);
+	if (lane == 0) {
+		float xn = metric == METRIC_COSINE ? 1.01f : __uint_as_float(*max_norm_bits);
+		float qn = sqrtf(s);
+		// l2: the folded -|x|^2/2 term is exact to ~2^-24 relative; covered by the absolute slack below
+		margin[q] = 2.0f * (GEMM_ERR_C * qn * xn + 1e-6f * (1.0f + xn * xn));
+		thr[q] = real ? -__int_as_float(0x7F800000) : __int_as_float(0x7F800000);
+		cnt[q] = 0;
+		flag[q] = 0;
+	}
+}
+
+// ------------------------------------------------------------------ threshold refresh between segments
+// One block per query.  A_k = k-th best approximate score among the candidates gathered so far (all live
+// rows): every true top-k row scores >= A_k - margin, so thr = A_k - margin and the list is compacted to
+// the entries that still pass.  A list that overflowed its capacity flags the query (exact re-run).
+__global__ void __launch_bounds__(256) refresh_threshold_kernel(uint2 *__restrict__ cand, int CAP, uint32_t *__restrict__ cnt,
+                                                                float *__restrict__ thr, const float *__restrict__ margin,
+                                                                uint32_t *__restrict__ flag, int k, int cap) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	__shared__ int cnts[8];
+	__shared__ float s_thr;
+	__shared__ int s_base;
+	const int q = blockIdx.x;
+	const int warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	const uint32_t c_raw = cnt[q];
+	if (flag[q]) return;
+	if (c_raw > (uint32_t)CAP) {
+		if (threadIdx.x == 0) flag[q] = 1;
+		return;
+	}
+	const int c = (int)c_raw;
+	if (c < k) return; // fewer than k live candidates so far: keep everything, threshold stays
+	uint2 *list = cand + (size_t)q * CAP;
+	u64 *bufs = reinterpret_cast<u64 *>(smem_raw);
+	WarpSelect sel;
+	sel.init(bufs + (size_t)warp * cap, cap, k);
+	for (int i0 = warp * 32; i0 < c; i0 += 256) {
+		int i = i0 + lane;
+		float sc = i < c ? __uint_as_float(list[i].x) : 0.f;
+		sel.push(i < c, make_key(-sc, (uint32_t)i));
+	}
+	sel.finalize();
+	if (lane == 0) cnts[warp] = sel.cnt;
+	__syncthreads();
+	if (warp == 0) {
+		for (int w = 1; w < 8; w++) {
+			const u64 *s2 = bufs + (size_t)w * cap;
+			const int cw = cnts[w];
+			for (int i0 = 0; i0 < cw; i0 += 32) {
+				int i = i0 + lane;
+				sel.push(i < cw, i < cw ? s2[i] : KEY_INVALID);
+			}
+		}
+		sel.finalize();
+		if (lane == 0) {
+			float ak = -key_dist(sel.buf[k - 1]);
+			float t = ak - margin[q];
+			s_thr = fmaxf(t, thr[q]);
+			s_base = 0;
+		}
+	}
+	__syncthreads();
+	const float t = s_thr;
+	// in-place compaction, chunk by chunk (writes never pass the reads of the same or a later chunk)
+	for (int i0 = 0; i0 < c; i0 += 256) {
+		int i = i0 + threadIdx.x;
+		uint2 e = make_uint2(0, 0);
+		bool keep = false;
+		if (i < c) {
+			e = list[i];
+			keep = __uint_as_float(e.x) >= t;
+		}
+		unsigned m = __ballot_sync(0xFFFFFFFFu, keep);
+		if (lane == 0) cnts[warp] = __popc(m);
+		__syncthreads();
+		int off = s_base;
+		for (int w = 0; w < warp; w++) off += cnts[w];
+		if (keep) list[off + __popc(m & ((1u << lane) - 1u))] = e;
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			int tot = 0;
+			for (int w = 0; w < 8; w++) tot += cnts[w];
+			s_base += tot;
+		}
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) {
+		cnt[q] = (uint32_t)s_base;
+		thr[q] = t;
+	}
+}
+
+// ------------------------------------------------------------------ exact re-rank
+// exact distance of (q, x) by one warp, in the reference's reported units (same formulas as flat_scan.cu)
+__device__ __forceinline__ float warp_exact_distance(int metric, const float *__restrict__ q, const float *__restrict__ x,
+                                                     int d, bool vec4) {
+	const unsigned lane = lane_id();
+	float acc = 0.f, nx = 0.f, nq = 0.f;
+	if (vec4) {
+		const float4 *q4 = reinterpret_cast<const float4 *>(q), *x4 = reinterpret_cast<const float4 *>(x);
+		for (int c = lane; c < (d >> 2); c += 32) {
+			float4 a = __ldg(q4 + c), b = __ldg(x4 + c);
+			if (metric == METRIC_L2) {
+				float e0 = a.x - b.x, e1 = a.y - b.y, e2 = a.z - b.z, e3 = a.w - b.w;
+				acc = fmaf(e0, e0, acc), acc = fmaf(e1, e1, acc), acc = fmaf(e2, e2, acc), acc = fmaf(e3, e3, acc);
+			} else {
+				acc = fmaf(a.x, b.x, acc), acc = fmaf(a.y, b.y, acc), acc = fmaf(a.z, b.z, acc), acc = fmaf(a.w, b.w, acc);
+				if (metric == METRIC_COSINE) {
+					nx = fmaf(b.x, b.x, nx), nx = fmaf(b.y, b.y, nx), nx = fmaf(b.z, b.z, nx), nx = fmaf(b.w, b.w, nx);
+					nq = fmaf(a.x, a.x, nq), nq = fmaf(a.y, a.y, nq), nq = fmaf(a.z, a.z, nq), nq = fmaf(a.w, a.w, nq);
+				}
+			}
+		}
+	} else {
+		for (int c = lane; c < d; c += 32) {
+			float a = __ldg(q + c), b = __ldg(x + c);
+			if (metric == METRIC_L2) {
+				float e = a - b;
+				acc = fmaf(e, e, acc);
+			} else {
+				acc = fmaf(a, b, acc);
+				nx = fmaf(b, b, nx);
+				nq = fmaf(a, a, nq);
+			}
+		}
+	}
+	acc = warp_sum(acc);
+	if (metric == METRIC_L2) return acc;
+	if (metric == METRIC_DOT) return 1.0f - acc;
+	nx = warp_sum(nx);
+	nq = warp_sum(nq);
+	float den = sqrtf(nq) * sqrtf(nx);
+	if (!(den > 0.f)) return 1.0f;
+	float sim = fminf(1.f, fmaxf(-1.f, acc / den));
+	return 1.0f - sim;
+}
+
+// One block per query: exact fp32 distance of every surviving candidate, fused top-k, sorted output.
+__global__ void __launch_bounds__(256) rerank_kernel(const float *__restrict__ X, int d, int metric,
+                                                     const float *__restrict__ Q, const uint2 *__restrict__ cand, int CAP,
+                                                     const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ flag,
+                                                     int k, int cap, long long label_base, int64_t *__restrict__ out_labels,
+                                                     float *__restrict__ out_dist, int32_t *__restrict__ out_counts) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	__shared__ int cnts[8];
+	const int q = blockIdx.x;
+	const int warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	u64 *bufs = reinterpret_cast<u64 *>(smem_raw);
+	const bool bad = flag[q] != 0 || cnt[q] > (uint32_t)CAP;
+	const int c = bad ? 0 : (int)cnt[q];
+	const uint2 *list = cand + (size_t)q * CAP;
+	const float *qv = Q + (size_t)q * d;
+	const bool vec4 = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0) && ((reinterpret_cast<uintptr_t>(Q) & 15) == 0);
+	WarpSelect sel;
+	sel.init(bufs + (size_t)warp * cap, cap, k);
+	for (int i0 = warp * 32; i0 < c; i0 += 256) {
+		const int mine = i0 + lane;
+		const uint32_t myrow = mine < c ? list[mine].y : 0u;
+		float mydist = 0.f;
+		const int nb = min(32, c - i0);
+		for (int j = 0; j < nb; j++) {
+			const uint32_t row = __shfl_sync(0xFFFFFFFFu, myrow, j);
+			float dist = warp_exact_distance(metric, qv, X + (size_t)row * d, d, vec4);
+			if ((int)lane == j) mydist = dist;
+		}
+		sel.push(mine < c, make_key(mydist, myrow));
+	}
+	sel.finalize();
+	if (lane == 0) cnts[warp] = sel.cnt;
+	__syncthreads();
+	if (warp != 0) return;
+	for (int w = 1; w < 8; w++) {
+		const u64 *s2 = bufs + (size_t)w * cap;
+		const int cw = cnts[w];
+		for (int i0 = 0; i0 < cw; i0 += 32) {
+			int i = i0 + lane;
+			sel.push(i < cw, i < cw ? s2[i] : KEY_INVALID);
+		}
+	}
+	sel.finalize();
+	for (int i = lane; i < k; i += 32) {
+		bool ok = i < sel.cnt;
+		u64 key = ok ? sel.buf[i] : KEY_INVALID;
+		out_labels[(size_t)q * k + i] = ok ? (int64_t)(label_base + (long long)key_row(key)) : -1;
+		out_dist[(size_t)q * k + i] = ok ? key_dist(key) : __int_as_float(0x7F800000);
+	}
+	if (lane == 0) out_counts[q] = sel.cnt;
+}
+
+// number of flagged queries -> *out (read by the host to run the exact scan for them)
+__global__ void count_flags_kernel(const uint32_t *__restrict__ flag, const uint32_t *__restrict__ cnt, int CAP, int nq,
+                                   uint32_t *__restrict__ flag_out, uint32_t *__restrict__ total) {
+	int q = blockIdx.x * blockDim.x + threadIdx.x;
+	if (q >= nq) return;
+	uint32_t f = (flag[q] != 0 || cnt[q] > (uint32_t)CAP) ? 1u : 0u;
+	flag_out[q] = f;
+	if (f) atomicAdd(total, 1u);
+}
+
+} // namespace lb

@@ -1,0 +1,232 @@
+// flat_gemm_kernel.cuh — the tcgen05 candidate kernel of the batched flat search (included by flat_gemm.cu).
+//
+// score[q][row] = <Qs[q], Xs[row]> over bf16 shadow operands (fp32 accumulate in TMEM); every (q,row) whose
+// score reaches the query's threshold is appended to that query's candidate list.  No score matrix is ever
+// written: the epilogue reads each 128x128 accumulator out of TMEM once, takes a 3-input max over 32-column
+// chunks and only walks a chunk when its max passes the threshold (rare once the threshold is warm).
+//
+// Mapping ("query-stationary"): a CTA keeps QT query tiles (QT x 128 queries x K, bf16, 128B-swizzled) resident
+// in shared memory for its whole life and streams X tiles of BN=128 rows through S TMA stages, so each X byte
+// fetched from L2/HBM is used for QT*128 queries.  UMMA: A = queries (M=128 -> TMEM lanes = queries),
+// B = rows (N=128 -> TMEM columns = rows): an epilogue thread owns ONE query, its threshold sits in a register.
+//
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
+// warps 2..9 = two epilogue groups of 4 warps (warp%4 = TMEM lane quadrant); accumulators are
+// quadruple-buffered in TMEM (4 x 128 columns), group e drains accumulators with (index & 1) == e.
+#pragma once
+#include "tc_ptx.cuh"
+
+namespace lb {
+
+struct GemmParams {
+	int nkb;          // 64-wide k-blocks per row (Kpad / 64)
+	int ksteps_last;  // MMA k-steps (16 wide) to issue in the last k-block (1..4); the rest is zero padding
+	int QT;           // resident query tiles per CTA
+	int KS;           // k-blocks per X stage
+	int S;            // X stages
+	int NG;           // query groups (QT*128 queries each); gridDim.x = NG * R
+	int R;            // CTAs per query group
+	long long tile_lo, tile_hi; // X tiles [tile_lo, tile_hi) of 128 rows
+	long long n_rows;
+	const float *thr;     // [NG*QT*128] a score >= thr passes
+	uint32_t *cnt;        // [NG*QT*128] candidates appended (may exceed CAP: overflow)
+	uint2 *cand;          // [NG*QT*128][CAP] {score bits, row}
+	int CAP;
+	const uint32_t *deleted; // tombstones or null
+	const uint32_t *allow;   // prefilter bitmap or null
+	long long allow_bits;
+};
+
+static constexpr int GEMM_BN = 128;
+static constexpr int GEMM_NBUF = 4;
+static constexpr int GEMM_THREADS = 320;
+static constexpr int GEMM_KB_BYTES = 128 * 128; // one 64-wide k-block of a 128-row tile
+
+__device__ __noinline__ void gemm_emit(const GemmParams &p, int q, long long row, float score) {
+	if (row >= p.n_rows) return; // TMA zero-fill beyond the table
+	if (p.deleted && bit_test(p.deleted, row)) return;
+	if (p.allow && !(row < p.allow_bits && bit_test(p.allow, row))) return;
+	uint32_t pos = atomicAdd(p.cnt + q, 1u);
+	if (pos < (uint32_t)p.CAP) p.cand[(size_t)q * p.CAP + pos] = make_uint2(__float_as_uint(score), (uint32_t)row);
+}
+
+__device__ __forceinline__ void tmem_wait_regs(uint32_t (&r)[32]) {
+	// tcgen05.wait::ld with the destination registers as in/out operands, so that no use is scheduled above it
+	asm volatile("tcgen05.wait::ld.sync.aligned;"
+	             : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+	               "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+	               "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]),
+	               "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]),
+	               "+r"(r[30]), "+r"(r[31])::"memory");
+}
+
+__device__ __forceinline__ void gemm_process_chunk(const GemmParams &p, const uint32_t (&r)[32], float thr, int q,
+                                                   long long row0) {
+	float a[10];
+#pragma unroll
+	for (int i = 0; i < 10; i++)
+		a[i] = tc::fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
+	float m1 = tc::fmax3(a[0], a[1], a[2]), m2 = tc::fmax3(a[3], a[4], a[5]), m3 = tc::fmax3(a[6], a[7], a[8]);
+	float m4 = tc::fmax3(a[9], __uint_as_float(r[30]), __uint_as_float(r[31]));
+	float m = fmaxf(tc::fmax3(m1, m2, m3), m4);
+	if (m >= thr) {
+#pragma unroll
+		for (int i = 0; i < 32; i++) {
+			float v = __uint_as_float(r[i]);
+			if (v >= thr) gemm_emit(p, q, row0 + i, v);
+		}
+	}
+}
+
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+flat_gemm_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const GemmParams p) {
+	extern __shared__ uint8_t smem_raw[];
+	const int warp = threadIdx.x >> 5;
+	const int lane = threadIdx.x & 31;
+	const int g = blockIdx.x % p.NG;
+	const int r = blockIdx.x / p.NG;
+	const int nst = p.nkb / p.KS;
+	const uint32_t stage_bytes = (uint32_t)p.KS * GEMM_KB_BYTES;
+
+	const uint32_t sbase = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+	uint8_t *sgen = smem_raw + (sbase - tc::smem_u32(smem_raw));
+	const uint32_t Qs = sbase;
+	const uint32_t Xs = Qs + (uint32_t)p.QT * p.nkb * GEMM_KB_BYTES;
+	const uint32_t ctl_off = (uint32_t)p.QT * p.nkb * GEMM_KB_BYTES + (uint32_t)p.S * stage_bytes;
+	const uint32_t bars = sbase + ctl_off;
+	// barrier slots (8 B each): full[S] | empty[S] | qfull | tfull[4] | tempty[4]
+	const uint32_t bar_full = bars, bar_empty = bars + 8u * p.S, bar_q = bars + 16u * p.S;
+	const uint32_t bar_tfull = bar_q + 8, bar_tempty = bar_tfull + 8 * GEMM_NBUF;
+	uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(sgen + ctl_off + 16u * p.S + 8 + 16 * GEMM_NBUF);
+	float *thr_s = reinterpret_cast<float *>(sgen + ctl_off + 16u * p.S + 8 + 16 * GEMM_NBUF + 16);
+
+	if (warp == 0 && lane == 0) {
+		tc::tma_prefetch_desc(&tmQ);
+		tc::tma_prefetch_desc(&tmX);
+		for (int s = 0; s < p.S; s++) {
+			tc::mbar_init(bar_full + 8u * s, 1);
+			tc::mbar_init(bar_empty + 8u * s, 1);
+		}
+		tc::mbar_init(bar_q, 1);
+		for (int b = 0; b < GEMM_NBUF; b++) {
+			tc::mbar_init(bar_tfull + 8u * b, 1);
+			tc::mbar_init(bar_tempty + 8u * b, 4);
+		}
+		tc::fence_barrier_init();
+	}
+	if (warp == 1) {
+		tc::tmem_alloc(tc::smem_u32(tmem_slot), 512);
+		tc::tmem_relinquish();
+	}
+	for (int i = threadIdx.x; i < p.QT * 128; i += GEMM_THREADS) thr_s[i] = p.thr[(size_t)g * p.QT * 128 + i];
+	tc::tc_fence_before();
+	__syncthreads();
+	tc::tc_fence_after();
+	const uint32_t tmem_base = *tmem_slot;
+
+	if (warp == 0) {
+		if (lane == 0) {
+			// ---------------- TMA producer
+			tc::mbar_expect_tx(bar_q, (uint32_t)p.QT * p.nkb * GEMM_KB_BYTES);
+			for (int t = 0; t < p.QT; t++)
+				for (int kb = 0; kb < p.nkb; kb++)
+					tc::tma_load_2d(Qs + (uint32_t)(t * p.nkb + kb) * GEMM_KB_BYTES, &tmQ, kb * 64, (g * p.QT + t) * 128,
+					                bar_q);
+			uint32_t it = 0;
+			for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
+				for (int c = 0; c < nst; c++, it++) {
+					const uint32_t s = it % p.S, ph = (it / p.S) & 1u;
+					tc::mbar_wait(bar_empty + 8u * s, ph ^ 1u);
+					tc::mbar_expect_tx(bar_full + 8u * s, stage_bytes);
+					for (int kk = 0; kk < p.KS; kk++)
+						tc::tma_load_2d(Xs + s * stage_bytes + (uint32_t)kk * GEMM_KB_BYTES, &tmX, (c * p.KS + kk) * 64,
+						                (int)(tile * GEMM_BN), bar_full + 8u * s);
+				}
+			}
+		}
+	} else if (warp == 1) {
+		if (lane == 0) {
+			// ---------------- MMA issuer (one thread)
+			const uint32_t idesc = tc::umma_idesc_bf16(128, GEMM_BN);
+			tc::mbar_wait(bar_q, 0);
+			tc::tc_fence_after();
+			uint32_t it = 0, acc = 0;
+			for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
+				for (int t = 0; t < p.QT; t++, acc++) {
+					const uint32_t b = acc % GEMM_NBUF, n = acc / GEMM_NBUF;
+					tc::mbar_wait(bar_tempty + 8u * b, (n & 1u) ^ 1u);
+					tc::tc_fence_after();
+					const uint32_t d = tmem_base + b * GEMM_BN;
+					for (int c = 0; c < nst; c++) {
+						const uint32_t ic = it + c, s = ic % p.S, ph = (ic / p.S) & 1u;
+						if (t == 0) {
+							tc::mbar_wait(bar_full + 8u * s, ph);
+							tc::tc_fence_after();
+						}
+						for (int kk = 0; kk < p.KS; kk++) {
+							const int kb = c * p.KS + kk;
+							const int nk = (kb == p.nkb - 1) ? p.ksteps_last : 4;
+							const uint32_t a0 = Qs + (uint32_t)(t * p.nkb + kb) * GEMM_KB_BYTES;
+							const uint32_t b0 = Xs + s * stage_bytes + (uint32_t)kk * GEMM_KB_BYTES;
+							for (int k4 = 0; k4 < nk; k4++)
+								tc::umma_bf16(d, tc::umma_smem_desc(a0 + k4 * 32), tc::umma_smem_desc(b0 + k4 * 32), idesc,
+								              (uint32_t)((kb | k4) != 0));
+						}
+						if (t == p.QT - 1) tc::umma_commit(bar_empty + 8u * s);
+					}
+					tc::umma_commit(bar_tfull + 8u * b);
+				}
+				it += nst;
+			}
+		}
+		__syncwarp();
+	} else {
+		// ---------------- epilogue: TMEM -> registers -> threshold filter -> candidate lists
+		const int e = (warp - 2) >> 2;
+		const int quad = warp & 3;
+		const int lrow = quad * 32 + lane;
+		uint32_t acc = 0;
+		for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
+			for (int t = 0; t < p.QT; t++, acc++) {
+				if ((int)(acc & 1u) != e) continue;
+				const uint32_t b = acc % GEMM_NBUF, n = acc / GEMM_NBUF;
+				tc::mbar_wait(bar_tfull + 8u * b, n & 1u);
+				tc::tc_fence_after();
+				const float thr = thr_s[t * 128 + lrow];
+				const int q = (g * p.QT + t) * 128 + lrow;
+				const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + b * GEMM_BN;
+				const long long row0 = tile * GEMM_BN;
+				uint32_t va[32], vb[32];
+				tc::tmem_ld32(taddr, va);
+				tmem_wait_regs(va);
+				tc::tmem_ld32(taddr + 32, vb);
+				gemm_process_chunk(p, va, thr, q, row0);
+				tmem_wait_regs(vb);
+				tc::tmem_ld32(taddr + 64, va);
+				gemm_process_chunk(p, vb, thr, q, row0 + 32);
+				tmem_wait_regs(va);
+				tc::tmem_ld32(taddr + 96, vb);
+				gemm_process_chunk(p, va, thr, q, row0 + 64);
+				tmem_wait_regs(vb);
+				// the accumulator is in registers: hand the TMEM buffer back before the last chunk is examined
+				tc::tc_fence_before();
+				__syncwarp();
+				if (lane == 0) tc::mbar_arrive(bar_tempty + 8u * b);
+				gemm_process_chunk(p, vb, thr, q, row0 + 96);
+			}
+		}
+	}
+	tc::tc_fence_before();
+	__syncthreads();
+	if (warp == 1) {
+		tc::tc_fence_after();
+		tc::tmem_dealloc(tmem_base, 512);
+	}
+}
+
+static inline size_t gemm_smem_bytes(int QT, int nkb, int KS, int S) {
+	return 1024 /*alignment slack*/ + (size_t)QT * nkb * GEMM_KB_BYTES + (size_t)S * KS * GEMM_KB_BYTES + 16u * S + 8 +
+	       16 * GEMM_NBUF + 16 + (size_t)QT * 128 * 4;
+}
+
+} // namespace lb

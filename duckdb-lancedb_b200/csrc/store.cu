@@ -312,8 +312,8 @@ void Store::flat_search_locked(const float *d_queries, int nq, int k, const uint
 		use_tc = true;
 	else if (mode == 0)
 		use_tc = FlatGemm::worthwhile(nq, n_rows_, dim_, k);
-	if (use_tc && !FlatGemm::supported(dim_, k)) {
-		if (mode == 2) throw Error("the tcgen05 flat path needs dim % 8 == 0, dim >= 64 and k <= 1024");
+	if (use_tc && !FlatGemm::supported(dim_, metric_, k)) {
+		if (mode == 2) throw Error("the tcgen05 flat path needs 16 <= dim (<= 768; 704 for l2) and k <= 1024");
 		use_tc = false;
 	}
 	if (use_tc) {
@@ -323,8 +323,8 @@ void Store::flat_search_locked(const float *d_queries, int nq, int k, const uint
 			flat_gemm_->sync_rows(X_.as<float>(), n_rows_, cap_rows_, s, &launches);
 		}
 		int64_t fallback = 0;
-		flat_gemm_->search(X_.as<float>(), n_rows_, deleted_.as<uint32_t>(), d_queries, nq, k, d_allow, allow_bits,
-		                   label_base_, d_out_labels, d_out_dist, d_out_counts, ws, s, &launches, &fallback);
+		flat_gemm_->search(X_.as<float>(), n_rows_, n_deleted_ > 0 ? deleted_.as<uint32_t>() : nullptr, d_queries, nq, k, d_allow, allow_bits,
+		                   label_base_, d_out_labels, d_out_dist, d_out_counts, ws, s, &launches, &fallback, &timer_);
 		std::lock_guard<std::mutex> g(stat_mu_);
 		tc_batches_++;
 		tc_fallback_ += fallback;
