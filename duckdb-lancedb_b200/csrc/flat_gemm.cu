@@ -186,8 +186,8 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	const size_t sel_smem = (size_t)8 * cap * sizeof(u64);
 	const long long ntiles = (n + GEMM_BN - 1) / GEMM_BN;
 	// segment growth: candidates per refresh ~ k * growth * (margin inflation); keep that well under TC_CAP
-	int growth = TC_CAP / (8 * k);
-	growth = std::max(2, std::min(16, growth));
+	// total slow-path hits per query ~ (#segments) * growth * k: small k affords few, large segments
+	int growth = std::max(2, std::min(16, std::min(TC_CAP / (8 * k), 512 / k)));
 
 	for (int q0 = 0; q0 < nq_total; q0 += TC_QCHUNK) {
 		const int nq = std::min(TC_QCHUNK, nq_total - q0);

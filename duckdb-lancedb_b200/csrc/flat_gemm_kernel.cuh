@@ -70,8 +70,19 @@ __device__ __forceinline__ void gemm_process_chunk(const GemmParams &p, const ui
 	float m4 = tc::fmax3(a[9], __uint_as_float(r[30]), __uint_as_float(r[31]));
 	float m = fmaxf(tc::fmax3(m1, m2, m3), m4);
 	if (m >= thr) {
+		// rare: walk only the triples whose max passed
 #pragma unroll
-		for (int i = 0; i < 32; i++) {
+		for (int i = 0; i < 10; i++) {
+			if (a[i] >= thr) {
+#pragma unroll
+				for (int j = 0; j < 3; j++) {
+					float v = __uint_as_float(r[3 * i + j]);
+					if (v >= thr) gemm_emit(p, q, row0 + 3 * i + j, v);
+				}
+			}
+		}
+#pragma unroll
+		for (int i = 30; i < 32; i++) {
 			float v = __uint_as_float(r[i]);
 			if (v >= thr) gemm_emit(p, q, row0 + i, v);
 		}
