@@ -112,8 +112,7 @@ class ClockSampler:
 
 
 def shard_range(rows, rank, world):
-    """Contiguous row ranges [rows*r/W, rows*(r+1)/W): labels are sequential (lance_manager.rs:232-233), so a
-    shard is a label range and the global label is base + local row."""
+    """Contiguous row ranges (duckdb-lancedb_b200/sharding.py)."""
     return rows * rank // world, rows * (rank + 1) // world
 
 
@@ -134,6 +133,40 @@ def cpu_search_sample(wl, sample_rows, sample_q, threads, seed=SEED):
     return time.perf_counter() - t0, sample_rows, sample_q
 
 
+_IVF_CACHE = {}
+
+
+def cpu_ivfpq_sample(wl, nq, threads, seed=SEED):
+    """The oracle's IVF_PQ search (probe -> residual LUT per probed list -> ADC scan -> refine) on an index of the
+    workload's full shape (P lists, N rows of M-byte codes).  Codebooks / codes are random: the arithmetic and
+    the bytes scanned per query are those of a trained index, only recall is meaningless.  Queries run
+    concurrently, one per host thread.  Returns (seconds, queries)."""
+    import oracle
+    from concurrent.futures import ThreadPoolExecutor
+
+    key = (wl["rows"], wl["dim"], wl["P"], wl["M"])
+    if key not in _IVF_CACHE:
+        rng = np.random.default_rng(seed)
+        n, d, P, M = wl["rows"], wl["dim"], wl["P"], wl["M"]
+        nx = 100_000  # rows kept for the refine step; labels wrap into it
+        X = rng.standard_normal((nx, d), dtype=np.float32)
+        cen = rng.standard_normal((P, d), dtype=np.float32)
+        cb = rng.standard_normal((M, 256, d // M), dtype=np.float32)
+        off = (np.arange(P + 1, dtype=np.int64) * n) // P
+        ids = np.arange(n, dtype=np.int64) % nx
+        codes = rng.integers(0, 256, size=(n, M), dtype=np.uint8)
+        ix = oracle.IvfPqIndex(wl["metric"], d, P, M, cen, cb, off, ids, codes, n_indexed=nx)
+        _IVF_CACHE[key] = (ix, X)
+    ix, X = _IVF_CACHE[key]
+    rng = np.random.default_rng(seed + 1)
+    Q = rng.standard_normal((nq, wl["dim"]), dtype=np.float32)
+    ix.search(X, Q[0], wl["k"], wl["nprobes"], 1)
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(lambda j: ix.search(X, Q[j], wl["k"], wl["nprobes"], 1), range(nq)))
+    return time.perf_counter() - t0, nq
+
+
 def cpu_sample_shape(wl, budget_pairs):
     """Pick (rows, queries) of the sample so that rows*queries*dim ~ budget, keeping the batch shape when possible."""
     q = min(wl["batch"], 64)
@@ -146,6 +179,13 @@ def cpu_baseline(wl, seconds_target=12.0):
 
     oracle.build()
     threads = oracle.num_threads()
+    if wl["kind"] == "ivfpq":
+        dt, nq = cpu_ivfpq_sample(wl, 4 * threads, threads)
+        nq = int(max(4 * threads, min(4096, nq * seconds_target / max(dt, 1e-3))))
+        dt, nq = cpu_ivfpq_sample(wl, nq, threads)
+        return {"value": nq / dt, "unit": "queries/s", "cores": threads, "kind": "port",
+                "sample": f"oracle_ivfpq_search (oracle/oracle.c) on a full-shape index (P={wl['P']}, M={wl['M']}, "
+                          f"{wl['rows']} coded rows, random codebooks/codes), {nq} queries, one per host thread, {dt:.2f} s"}
     # calibrate: ~0.3 s probe, then scale to the target
     rows, q = cpu_sample_shape(wl, 2_000_000_000)
     dt, r, qq = cpu_search_sample(wl, min(rows, 200_000), q, threads)
@@ -167,6 +207,24 @@ def run_reference(args, wl):
 
     oracle.build()
     threads = oracle.num_threads()
+    if wl["kind"] == "ivfpq":
+        times = []
+        nq = 8 * threads
+        for i in range(args.warmup + args.steps):
+            dt, _ = cpu_ivfpq_sample(wl, nq, threads)
+            if i >= args.warmup:
+                times.append(dt)
+        qps = nq / (sum(times) / len(times))
+        sample = (f"oracle IVF_PQ port on a full-shape index (P={wl['P']}, M={wl['M']}, {wl['rows']} coded rows, random "
+                  f"codebooks/codes), {nq} queries per step, one per host thread (LanceDB itself cannot be built here)")
+        line = {"impl": "reference", "metric": "kNN queries/sec", "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wl["batch"] / qps,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": workload_config(wl, args),
+                "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": threads, "kind": "port", "sample": sample},
+                "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
     rows, q = cpu_sample_shape(wl, 1_500_000_000)
     times = []
     for i in range(args.warmup + args.steps):
@@ -249,20 +307,34 @@ def run_b200(args, wl):
         allow_t = torch.from_numpy(allow_host.view(np.int32)).to(dev)
         d_allow, allow_bits = allow_t.data_ptr(), allow_host.shape[0] * 32
 
+    nprobes = wl.get("nprobes", 20)
+    adc_bytes = None
     if wl["kind"] == "ivfpq":
         h.create_index(wl["P"], wl["M"])
-    nprobes = wl.get("nprobes", 20)
+        offs = h.ivfpq_part_offsets()
+        sizes = np.diff(offs)
+        probed_rows = 0
+        for j in range(min(B, 16)):
+            dbg = h.ivfpq_search_debug(Qh[j].numpy(), k, nprobes, 1)
+            probed_rows += int(sizes[dbg["parts"]].sum())
+        probed_rows /= min(B, 16)
+        # per query: codes (M B/row) + row term (4) + row id (4) of the probed lists + the query's lookup table
+        adc_bytes = probed_rows * (wl["M"] + 8) + wl["M"] * 256 * 4
+        ivf_query_bytes = adc_bytes + wl["P"] * dim * 4 + wl["M"] * 256 * (dim // wl["M"]) * 4 + k * dim * 4
 
     L = torch.empty((B, k), dtype=torch.int64, device=dev)
     D = torch.empty((B, k), dtype=torch.float32, device=dev)
     C = torch.empty(B, dtype=torch.int32, device=dev)
     if world > 1:
-        GL = torch.empty((world, B, k), dtype=torch.int64, device=dev)
-        GD = torch.empty((world, B, k), dtype=torch.float32, device=dev)
-        GC = torch.empty((world, B), dtype=torch.int32, device=dev)
-        ML = torch.empty((B, k), dtype=torch.int64, device=dev)
-        MD = torch.empty((B, k), dtype=torch.float32, device=dev)
-        MC = torch.empty(B, dtype=torch.int32, device=dev)
+        import importlib
+
+        sharding = importlib.import_module("duckdb_lancedb_b200.sharding")
+        gatherer = sharding.ShardGather(world, B, k, dev)
+
+        def device_merge(GL, GD, GC, G, nq_, k_, ML, MD, MC):
+            pkg.merge_topk_device(local, GL.data_ptr(), GD.data_ptr(), GC.data_ptr(), G, nq_, k_, ML.data_ptr(),
+                                  MD.data_ptr(), MC.data_ptr(), stream=sp)
+            merge_launches[0] += 3
     Lh = torch.empty((B, k), dtype=torch.int64).pin_memory()
     Dh = torch.empty((B, k), dtype=torch.float32).pin_memory()
     Ch = torch.empty(B, dtype=torch.int32).pin_memory()
@@ -274,13 +346,7 @@ def run_b200(args, wl):
         h.search_device(q_ptr, B, k, L.data_ptr(), D.data_ptr(), C.data_ptr(), nprobes=nprobes, refine_factor=1,
                         d_allow=d_allow, allow_bits=allow_bits, stream=sp)
         if world > 1:
-            dist.all_gather_into_tensor(GL, L)
-            dist.all_gather_into_tensor(GD, D)
-            dist.all_gather_into_tensor(GC, C)
-            pkg.merge_topk_device(local, GL.data_ptr(), GD.data_ptr(), GC.data_ptr(), world, B, k, ML.data_ptr(),
-                                  MD.data_ptr(), MC.data_ptr(), stream=sp)
-            merge_launches[0] += 3
-            return ML, MD, MC
+            return gatherer.gather_and_merge(L, D, C, device_merge)
         return L, D, C
 
     def step_e2e():
@@ -301,15 +367,30 @@ def run_b200(args, wl):
             dist.barrier()
         torch.cuda.synchronize()
 
+    shard_bytes = n_local * dim * 4 if wl["kind"] == "flat" else 1 << 40
+    need_flush = shard_bytes <= 200e6  # the 126 MB L2 would otherwise serve the table on every step after the first
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if need_flush else None
+
     def timed(fn, steps):
         barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(steps):
-            fn()
-        e1.record(stream)
-        barrier()
-        ms = e0.elapsed_time(e1)
+        if need_flush:
+            # one event pair per step, an L2-sized write in between (outside the timed intervals)
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+            for a, b in evs:
+                flush_buf.fill_(1)
+                a.record(stream)
+                fn()
+                b.record(stream)
+            barrier()
+            ms = sum(a.elapsed_time(b) for a, b in evs)
+        else:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(steps):
+                fn()
+            e1.record(stream)
+            barrier()
+            ms = e0.elapsed_time(e1)
         if world > 1:
             t = torch.tensor([ms], device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -337,7 +418,8 @@ def run_b200(args, wl):
     wall0 = time.perf_counter()
     ms_e2e_dev = timed(step_e2e, args.steps)
     wall = (time.perf_counter() - wall0) * 1e3
-    ms_e2e = max(ms_e2e_dev, wall if world == 1 else ms_e2e_dev)  # N=1: the call is synchronous, wall clock bounds it
+    # N=1: the call is synchronous, so the wall clock bounds it (unless flushes sit between the steps)
+    ms_e2e = max(ms_e2e_dev, wall) if (world == 1 and not need_flush) else ms_e2e_dev
     clocks = sampler.stop() if rank == 0 else None
 
     launches = st1["kernel_launches"] - st0["kernel_launches"] + merge_launches[0]
@@ -364,12 +446,18 @@ def run_b200(args, wl):
             roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
                     "traffic": None, "kernel": "flat_gemm_kernel (tcgen05 bf16, HBM-bound batch)", "peak_source": peaks["source"]}
     elif prof["adc_scan_launches"] > 0:
-        roof = {"bound": "hbm", "achieved": None, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": None, "traffic": None,
-                "kernel": "adc_scan_kernel"}
+        t = prof["adc_scan_ms"] / prof["adc_scan_launches"] / 1e3
+        a = adc_bytes * B / t / 1e9
+        roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
+                "traffic": None, "kernel": "adc_scan_kernel (codes + row terms + ids of the probed lists + LUT)",
+                "peak_source": peaks["source"], "avg_launch_ms": t * 1e3, "bytes_per_query_scan": adc_bytes,
+                "bytes_per_query_whole_search": ivf_query_bytes,
+                "whole_search_gbs": ivf_query_bytes * B * args.steps / (ms / 1e3) / 1e9}
     elif prof["flat_scan_launches"] > 0:
         t = prof["flat_scan_ms"] / prof["flat_scan_launches"] / 1e3
         sel = wl.get("selectivity") or 1.0
-        bytes_ = n_local * dim * 4.0  # X read once per pass of <= 4 queries
+        # X read once per pass of <= 4 queries; masked rows are skipped before any load (s*N*D*4 + N/8)
+        bytes_ = n_local * dim * 4.0 * sel + (n_local / 8.0 if wl.get("selectivity") else 0.0)
         a = bytes_ / t / 1e9
         roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
                 "traffic": None, "kernel": "flat_scan_kernel (fp32, <=4 queries per pass)", "peak_source": peaks["source"],

@@ -323,6 +323,16 @@ class LanceHandle:
         return dict(metric=info.metric, dim=info.dim, P=info.P, M=info.M, n_indexed=info.n_indexed, centroids=cen,
                     codebook=cb, part_offsets=off, row_ids=ids, codes=codes)
 
+    def ivfpq_part_offsets(self) -> np.ndarray:
+        """part_offsets[P+1] only (no bulk export)."""
+        info = IvfPqInfo()
+        self._check(lib().lance_b200_get_ivfpq(self._h, C.byref(info), None, None, None, None, None, self._err, ERR_LEN),
+                    "get_ivfpq")
+        off = np.empty(info.P + 1, np.int64)
+        self._check(lib().lance_b200_get_ivfpq(self._h, C.byref(info), None, None, _ptr(off), None, None, self._err,
+                                               ERR_LEN), "get_ivfpq")
+        return off
+
     def ivfpq_search_debug(self, query, k, nprobes, refine_factor=1, allow=None):
         q = _f32(query)
         rf = max(int(refine_factor), 1)

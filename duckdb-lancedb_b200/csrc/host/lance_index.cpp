@@ -1,0 +1,248 @@
+// lance_index.cpp — throwing FFI wrappers, LanceIndex and the lance_search / lance_index_scan functions of the
+// host mirror (see lance_host.hpp for the reference lines each part follows).
+#include "lance_host.hpp"
+
+#include <algorithm>
+#include <cstdlib>
+
+#include "../../../include/lance_b200.h"
+
+namespace lance_host {
+
+static constexpr int ERR_BUF = 2048; // src/rust_ffi.cpp:46
+
+// ------------------------------------------------------------------ wrappers (src/rust_ffi.cpp:44-206)
+LanceHandle LanceCreateDetached(const std::string &db_path, int32_t dimension, const std::string &metric,
+                                const std::string &table_name) {
+	char err[ERR_BUF] = {0};
+	LanceHandle h = lance_create_detached(db_path.c_str(), dimension, metric.c_str(), table_name.c_str(), err, ERR_BUF);
+	if (!h) throw IOException(std::string("Lance create: ") + err);
+	return h;
+}
+LanceHandle LanceOpenDetached(const std::string &db_path, const std::string &table_name, const std::string &metric) {
+	char err[ERR_BUF] = {0};
+	LanceHandle h = lance_open_detached(db_path.c_str(), table_name.c_str(), metric.c_str(), err, ERR_BUF);
+	if (!h) throw IOException(std::string("Lance open: ") + err);
+	return h;
+}
+void LanceFreeDetached(LanceHandle handle) {
+	if (handle) lance_free_detached(handle);
+}
+int32_t LanceDetachedDimension(LanceHandle handle) { return lance_detached_dimension(handle); }
+int64_t LanceDetachedAdd(LanceHandle handle, const float *vector, int32_t dimension) {
+	char err[ERR_BUF] = {0};
+	int64_t label = lance_detached_add(handle, vector, dimension, err, ERR_BUF);
+	if (label < 0) throw IOException(std::string("Lance add: ") + err);
+	return label;
+}
+int32_t LanceDetachedAddBatch(LanceHandle handle, const float *vectors, int32_t num, int32_t dim, int64_t *out_labels) {
+	char err[ERR_BUF] = {0};
+	int32_t n = lance_detached_add_batch(handle, vectors, num, dim, out_labels, err, ERR_BUF);
+	if (n < 0) throw IOException(std::string("Lance add_batch: ") + err);
+	return n;
+}
+int32_t LanceDetachedSearch(LanceHandle handle, const float *query, int32_t dim, int32_t k, int32_t nprobes,
+                            int32_t refine_factor, const uint32_t *allow_bitmap, int64_t bitmap_bits,
+                            int64_t *out_labels, float *out_distances) {
+	char err[ERR_BUF] = {0};
+	int32_t n = allow_bitmap ? lance_detached_search_filtered(handle, query, dim, k, nprobes, refine_factor, allow_bitmap,
+	                                                          bitmap_bits, out_labels, out_distances, err, ERR_BUF)
+	                         : lance_detached_search(handle, query, dim, k, nprobes, refine_factor, out_labels,
+	                                                 out_distances, err, ERR_BUF);
+	if (n < 0) throw IOException(std::string("Lance search: ") + err);
+	return n;
+}
+int32_t LanceDetachedSearchBatch(LanceHandle handle, const float *queries, int32_t nq, int32_t dim, int32_t k,
+                                 int32_t nprobes, int32_t refine_factor, const uint32_t *allow_bitmap,
+                                 int64_t bitmap_bits, int64_t *out_labels, float *out_distances, int32_t *out_counts) {
+	char err[ERR_BUF] = {0};
+	int32_t n = lance_detached_search_batch(handle, queries, nq, dim, k, nprobes, refine_factor, allow_bitmap, bitmap_bits,
+	                                        out_labels, out_distances, out_counts, err, ERR_BUF);
+	if (n < 0) throw IOException(std::string("Lance search: ") + err);
+	return n;
+}
+int64_t LanceDetachedCount(LanceHandle handle) {
+	char err[ERR_BUF] = {0};
+	int64_t n = lance_detached_count(handle, err, ERR_BUF);
+	if (n < 0) throw IOException(std::string("Lance count: ") + err);
+	return n;
+}
+void LanceDetachedDelete(LanceHandle handle, int64_t label) {
+	char err[ERR_BUF] = {0};
+	if (lance_detached_delete(handle, label, err, ERR_BUF) != 0) throw IOException(std::string("Lance delete: ") + err);
+}
+void LanceDetachedDeleteBatch(LanceHandle handle, const int64_t *labels, int32_t count) {
+	char err[ERR_BUF] = {0};
+	if (lance_detached_delete_batch(handle, labels, count, err, ERR_BUF) != 0)
+		throw IOException(std::string("Lance delete_batch: ") + err);
+}
+void LanceDetachedCreateIndex(LanceHandle handle, int32_t num_partitions, int32_t num_sub_vectors) {
+	char err[ERR_BUF] = {0};
+	if (lance_detached_create_index(handle, num_partitions, num_sub_vectors, err, ERR_BUF) != 0)
+		throw IOException(std::string("Lance create_index: ") + err);
+}
+void LanceDetachedCreateHnswIndex(LanceHandle handle, int32_t m, int32_t ef_construction) {
+	char err[ERR_BUF] = {0};
+	if (lance_detached_create_hnsw_index(handle, m, ef_construction, err, ERR_BUF) != 0)
+		throw IOException(std::string("Lance create_hnsw_index: ") + err);
+}
+void LanceDetachedCompact(LanceHandle handle) {
+	char err[ERR_BUF] = {0};
+	if (lance_detached_compact(handle, err, ERR_BUF) != 0) throw IOException(std::string("Lance compact: ") + err);
+}
+int32_t LanceDetachedGetVector(LanceHandle handle, int64_t label, float *out_vec, int32_t capacity) {
+	char err[ERR_BUF] = {0};
+	int32_t n = lance_detached_get_vector(handle, label, out_vec, capacity, err, ERR_BUF);
+	if (n < 0) throw IOException(std::string("Lance get_vector: ") + err);
+	return n;
+}
+
+// ------------------------------------------------------------------ optimizer helpers (src/lance_optimizer.cpp:350-371)
+bool IsArrayDistanceFunction(const std::string &name) {
+	return name == "array_distance" || name == "array_cosine_distance" || name == "array_inner_product";
+}
+std::string DistanceFunctionToMetric(const std::string &name) {
+	if (name == "array_cosine_distance") return "cosine";
+	if (name == "array_inner_product") return "dot";
+	return "l2";
+}
+bool MetricMatchesIndex(const std::string &fm, const std::string &im) {
+	auto norm = [](const std::string &m) { return m == "ip" ? std::string("dot") : m; };
+	return norm(fm) == norm(im);
+}
+
+// ------------------------------------------------------------------ LanceIndex
+LanceIndex::LanceIndex(const std::string &name, int32_t dimension, const std::map<std::string, std::string> &options,
+                       const std::string &db_path, const std::string &table_name)
+    : name_(name), dimension_(dimension) {
+	for (auto &kv : options) { // src/lance_index.cpp:157-165
+		if (kv.first == "metric") metric_ = kv.second;
+		else if (kv.first == "nprobes") nprobes_ = std::atoi(kv.second.c_str());
+		else if (kv.first == "refine_factor") refine_factor_ = std::atoi(kv.second.c_str());
+	}
+	rust_handle_ = LanceCreateDetached(db_path, dimension_, metric_, table_name);
+}
+LanceIndex::~LanceIndex() { LanceFreeDetached(rust_handle_); }
+
+int64_t LanceIndex::GetVectorCount() const { return rust_handle_ ? LanceDetachedCount(rust_handle_) : 0; }
+
+void LanceIndex::Append(const float *vectors, int64_t count, const row_t *row_ids) {
+	// one FFI call per <= 2048-row chunk, as the sink does (src/lance_index.cpp:941-954)
+	std::vector<int64_t> labels;
+	for (int64_t off = 0; off < count; off += STANDARD_VECTOR_SIZE) {
+		const int32_t n = (int32_t)std::min<int64_t>(STANDARD_VECTOR_SIZE, count - off);
+		labels.resize(n);
+		LanceDetachedAddBatch(rust_handle_, vectors + (size_t)off * dimension_, n, dimension_, labels.data());
+		for (int32_t i = 0; i < n; i++) {
+			const int64_t label = labels[i];
+			if ((int64_t)label_to_rowid_.size() <= label) label_to_rowid_.resize((size_t)label + 1, -1);
+			label_to_rowid_[label] = row_ids[off + i];
+			rowid_to_label_[row_ids[off + i]] = label;
+		}
+	}
+}
+
+void LanceIndex::Delete(const row_t *row_ids, int64_t count) {
+	std::vector<int64_t> labels;
+	for (int64_t i = 0; i < count; i++) {
+		auto it = rowid_to_label_.find(row_ids[i]);
+		if (it == rowid_to_label_.end()) continue;
+		labels.push_back(it->second);
+		rowid_to_label_.erase(it);
+	}
+	if (!labels.empty()) LanceDetachedDeleteBatch(rust_handle_, labels.data(), (int32_t)labels.size());
+}
+
+std::vector<std::pair<row_t, float>> LanceIndex::Search(const float *query, int32_t dimension, int32_t k,
+                                                        const std::string &predicate) {
+	if (!rust_handle_ || dimension != dimension_) return {}; // :444-446
+	if (k <= 0) return {};
+	std::vector<int64_t> labels(k);
+	std::vector<float> distances(k);
+	std::vector<uint32_t> bitmap;
+	if (!predicate.empty()) bitmap = EvaluatePredicate(predicate, columns_, (int64_t)label_to_rowid_.size());
+	const int32_t n = LanceDetachedSearch(rust_handle_, query, dimension, k, nprobes_, refine_factor_,
+	                                      predicate.empty() ? nullptr : bitmap.data(), (int64_t)bitmap.size() * 32,
+	                                      labels.data(), distances.data());
+	std::vector<std::pair<row_t, float>> results;
+	results.reserve(n);
+	for (int32_t i = 0; i < n; i++) {
+		const int64_t label = labels[i];
+		if (label >= 0 && label < (int64_t)label_to_rowid_.size()) results.emplace_back(label_to_rowid_[label], distances[i]);
+	}
+	return results;
+}
+
+std::vector<std::vector<std::pair<row_t, float>>> LanceIndex::SearchBatch(const float *queries, int32_t nq,
+                                                                          int32_t dimension, int32_t k,
+                                                                          const std::string &predicate) {
+	std::vector<std::vector<std::pair<row_t, float>>> out((size_t)std::max(nq, 0));
+	if (!rust_handle_ || dimension != dimension_ || k <= 0 || nq <= 0) return out;
+	std::vector<int64_t> labels((size_t)nq * k);
+	std::vector<float> distances((size_t)nq * k);
+	std::vector<int32_t> counts(nq);
+	std::vector<uint32_t> bitmap;
+	if (!predicate.empty()) bitmap = EvaluatePredicate(predicate, columns_, (int64_t)label_to_rowid_.size());
+	LanceDetachedSearchBatch(rust_handle_, queries, nq, dimension, k, nprobes_, refine_factor_,
+	                         predicate.empty() ? nullptr : bitmap.data(), (int64_t)bitmap.size() * 32, labels.data(),
+	                         distances.data(), counts.data());
+	for (int32_t q = 0; q < nq; q++) {
+		out[q].reserve(counts[q]);
+		for (int32_t i = 0; i < counts[q]; i++) {
+			const int64_t label = labels[(size_t)q * k + i];
+			if (label >= 0 && label < (int64_t)label_to_rowid_.size())
+				out[q].emplace_back(label_to_rowid_[label], distances[(size_t)q * k + i]);
+		}
+	}
+	return out;
+}
+
+void LanceIndex::CreateAnnIndex(int32_t num_partitions, int32_t num_sub_vectors) {
+	if (!rust_handle_) throw IOException("Lance index not initialized");
+	LanceDetachedCreateIndex(rust_handle_, num_partitions, num_sub_vectors);
+}
+void LanceIndex::CreateHnswIndex(int32_t m, int32_t ef_construction) {
+	if (!rust_handle_) throw IOException("Lance index not initialized");
+	LanceDetachedCreateHnswIndex(rust_handle_, m, ef_construction);
+}
+
+// ------------------------------------------------------------------ lance_search (src/lance_search.cpp)
+std::unique_ptr<LanceSearchBindData> LanceSearchBind(LanceIndex *index, const std::vector<float> &query, int32_t k) {
+	if (!index) throw BinderException("lance_search: index not found");
+	auto bind = std::unique_ptr<LanceSearchBindData>(new LanceSearchBindData());
+	bind->index = index;
+	bind->query = query;
+	bind->k = k;
+	return bind;
+}
+std::unique_ptr<LanceSearchState> LanceSearchInit(const LanceSearchBindData &bind) {
+	auto state = std::unique_ptr<LanceSearchState>(new LanceSearchState());
+	auto results = bind.index->Search(bind.query.data(), (int32_t)bind.query.size(), bind.k);
+	state->row_ids.reserve(results.size());
+	state->distances.reserve(results.size());
+	for (auto &r : results) {
+		state->row_ids.push_back(r.first);
+		state->distances.push_back(r.second);
+	}
+	return state;
+}
+int64_t LanceSearchScan(LanceSearchState &state, int64_t *out_row_ids, float *out_distances) {
+	const size_t remaining = state.row_ids.size() - state.offset;
+	const size_t n = std::min<size_t>(remaining, (size_t)STANDARD_VECTOR_SIZE);
+	for (size_t i = 0; i < n; i++) {
+		out_row_ids[i] = state.row_ids[state.offset + i];
+		out_distances[i] = state.distances[state.offset + i];
+	}
+	state.offset += n;
+	return (int64_t)n;
+}
+
+std::vector<row_t> LanceIndexScanInit(const LanceIndexScanBindData &bind) {
+	auto results = bind.index->Search(bind.query_vector.data(), (int32_t)bind.query_vector.size(), bind.limit, bind.predicate);
+	std::vector<row_t> ids;
+	ids.reserve(results.size());
+	for (auto &r : results) ids.push_back(r.first);
+	return ids;
+}
+
+} // namespace lance_host

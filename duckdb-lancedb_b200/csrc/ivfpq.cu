@@ -119,13 +119,16 @@ __global__ void __launch_bounds__(256) adc_scan_kernel(
     const float *__restrict__ qn2, int metric, const long long *__restrict__ pad_offsets,
     const int32_t *__restrict__ slot_rows, const uint8_t *__restrict__ codes_il, const float *__restrict__ row_term,
     const uint32_t *__restrict__ allow, long long allow_bits, const uint32_t *__restrict__ deleted, int kc, int cap,
-    u64 *__restrict__ partials) {
+    int PS, u64 *__restrict__ partials) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	const int nwarps = blockDim.x >> 5;
 	const int warp = threadIdx.x >> 5;
 	const unsigned lane = lane_id();
 	const int q = blockIdx.y;
+	// slice s = (probe slot ps, sub-slice j): probes ps, ps+PS, .. and the j-th of J equal parts of each list,
+	// so that a single query still fills the machine (32 probed lists -> PS*J CTAs)
 	const int S = gridDim.x, s = blockIdx.x;
+	const int ps = s % PS, j = s / PS, J = S / PS;
 	float *lut = reinterpret_cast<float *>(smem_raw);                                 // [M][256]
 	int *cnts = reinterpret_cast<int *>(smem_raw + (size_t)M * 1024);                 // [nwarps]
 	u64 *bufs = reinterpret_cast<u64 *>(smem_raw + (size_t)M * 1024 + 64);            // [nwarps][cap]
@@ -143,12 +146,13 @@ __global__ void __launch_bounds__(256) adc_scan_kernel(
 	const int chunks = M / GRAN;
 	typedef typename CodeWord<GRAN>::T word_t;
 
-	for (int pi = s; pi < nprobes_eff; pi += S) {
+	for (int pi = ps; pi < nprobes_eff; pi += PS) {
 		const u64 pk = probe_keys[(size_t)q * probe_stride + pi];
 		if (pk == KEY_INVALID) continue;
 		const int p = (int)key_row(pk);
 		const float cst = (metric == METRIC_DOT) ? 1.0f : key_dist(pk) - qq;
-		const long long b0 = pad_offsets[p] >> 5, b1 = pad_offsets[p + 1] >> 5;
+		const long long pb0 = pad_offsets[p] >> 5, pnb = (pad_offsets[p + 1] >> 5) - pb0;
+		const long long b0 = pb0 + pnb * j / J, b1 = pb0 + pnb * (j + 1) / J;
 		for (long long b = b0 + warp; b < b1; b += nwarps) {
 			const long long slot = (b << 5) + lane;
 			const int row = __ldg(slot_rows + slot);

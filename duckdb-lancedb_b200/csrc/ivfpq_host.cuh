@@ -122,12 +122,12 @@ void Store::drop_index() {
 template <int GRAN>
 static void launch_adc(const IvfPqIndex &ix, const float *lut, const u64 *probe_keys, int np, const float *qn2,
                        const uint32_t *allow, long long allow_bits, const uint32_t *deleted, int kc, int cap, int nwarps,
-                       int S, int nq, size_t smem, u64 *partials, cudaStream_t s) {
+                       int S, int PS, int nq, size_t smem, u64 *partials, cudaStream_t s) {
 	auto kern = adc_scan_kernel<GRAN>;
 	if (smem > 48 * 1024) LB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 	kern<<<dim3(S, nq), nwarps * 32, smem, s>>>(lut, ix.M, probe_keys, np, np, qn2, ix.metric, ix.pad_offsets.as<long long>(),
 	                                            ix.slot_rows.as<int32_t>(), ix.codes_il.as<uint8_t>(), ix.row_term.as<float>(),
-	                                            allow, allow_bits, deleted, kc, cap, partials);
+	                                            allow, allow_bits, deleted, kc, cap, PS, partials);
 	LB_CUDA(cudaGetLastError());
 }
 
@@ -192,7 +192,10 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 	int per_sm = (int)((227 * 1024) / (smem + 1024));
 	if (per_sm < 1) per_sm = 1;
 	long long want = 2ll * num_sms_ * per_sm;
-	int S = (int)std::min<long long>(np, std::max<long long>(1, (want + nq - 1) / nq));
+	const long long want_q = std::max<long long>(1, (want + nq - 1) / nq); // CTAs wanted per query
+	const int PS = (int)std::min<long long>(np, want_q);                   // probe slots
+	const int J = (int)std::max<long long>(1, std::min<long long>(16, want_q / PS)); // sub-slices of every list
+	const int S = PS * J;
 	const int tail_k = (ix.n_indexed < n_rows_) ? k : 0;
 	const int fin_stride = kc + tail_k;
 	ws.work4.ensure(((size_t)nq * S * kc + (size_t)nq * kc + (size_t)nq * fin_stride + (size_t)nq * std::max(tail_k, 1)) * sizeof(u64));
@@ -203,9 +206,9 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 	{
 		int tix = timer_.begin(KC_ADC_SCAN, s);
 		switch (ix.gran) {
-		case 16: launch_adc<16>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, nq, smem, partials, s); break;
-		case 4: launch_adc<4>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, nq, smem, partials, s); break;
-		default: launch_adc<1>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, nq, smem, partials, s);
+		case 16: launch_adc<16>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, PS, nq, smem, partials, s); break;
+		case 4: launch_adc<4>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, PS, nq, smem, partials, s); break;
+		default: launch_adc<1>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, PS, nq, smem, partials, s);
 		}
 		timer_.end(tix, s);
 		launches++;

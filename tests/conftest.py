@@ -35,6 +35,14 @@ def pkg():
 
 
 @pytest.fixture(scope="session")
+def host(pkg):
+    """ctypes harness over the C++ host mirror (csrc/host/, include/lance_b200_host.h)."""
+    import importlib
+
+    return importlib.import_module("duckdb_lancedb_b200.host")
+
+
+@pytest.fixture(scope="session")
 def gpu(pkg):
     """A CUDA device must be present for -m gpu tests: fail loudly, never skip to a fallback."""
     n = pkg.device_count()

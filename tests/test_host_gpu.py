@@ -1,0 +1,118 @@
+"""The reference's SQL tests replayed through the C++ host mirror (csrc/host/): LanceIndex::Search
+(src/lance_index.cpp:442-465), the lance_search table function (src/lance_search.cpp:33-104) and the optimizer's
+replacement scan with predicate push-down (src/lance_optimizer.cpp:35-109, 204-344) — on the GPU, via the C ABI."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from parity import assert_topk_parity
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+FX = json.load(open(os.path.join(HERE, "golden", "reference_sql_fixtures.json")))
+
+
+def build_index(host, case, rowid_base=0):
+    X = np.array(case["rows"], np.float32)
+    ix = host.HostIndex(X.shape[1], case["metric"])
+    rowids = np.arange(len(X), dtype=np.int64) + rowid_base
+    ix.append(X, rowids)
+    for name, vals in case.get("columns", {}).items():
+        ix.columns.append(name, vals)
+    if "deleted_ids" in case:
+        ids = np.array(case["ids"])
+        ix.delete(rowids[np.isin(ids, case["deleted_ids"])])
+        assert ix.count() == len(X) - len(case["deleted_ids"])
+    return ix, X, rowids
+
+
+@pytest.mark.parametrize("case", FX["cases"], ids=[c["name"] for c in FX["cases"]])
+def test_reference_sql_fixture_through_host_mirror(gpu, host, case):
+    ix, X, rowids = build_index(host, case)
+    ids = np.array(case["ids"])
+    q = np.array(case["query"], np.float32)
+    with ix:
+        if "predicate" in case or "lance_optimizer" in case["name"]:
+            # SELECT id FROM t [WHERE p] ORDER BY array_distance(vec, q) LIMIT k, rewritten to lance_index_scan
+            got_rows = ix.lance_index_scan(q, case["k"], case.get("predicate", ""))
+            _, got_d = ix.search(q, case["k"], case.get("predicate", ""))
+        else:
+            # SELECT row_id, distance FROM lance_search('t', 'idx', q, k)
+            got_rows, got_d, chunks = ix.lance_search(q, case["k"])
+            assert chunks == (1 if len(got_rows) else 0)
+        if "expect_ids" in case:
+            assert [int(ids[r]) for r in got_rows] == case["expect_ids"]
+        if "expect_row_ids" in case:
+            assert list(got_rows) == case["expect_row_ids"]
+        if "expect_count" in case:
+            assert len(got_rows) == case["expect_count"]
+        if "expect_distances" in case:
+            assert ["%.6f" % v for v in got_d] == ["%.6f" % v for v in case["expect_distances"]]
+        if "expect_ids_sorted_by_distance_then_any" in case:
+            pos = 0
+            for group in case["expect_ids_sorted_by_distance_then_any"]:
+                assert sorted(ids[got_rows[pos:pos + len(group)]]) == sorted(group)
+                pos += len(group)
+
+
+def test_wrong_dimension_returns_no_rows(gpu, host):
+    """test/sql/lance_basic.test:55-59: a query of the wrong dimension yields 0 rows, not an error."""
+    with host.HostIndex(3, "l2") as ix:
+        ix.append(np.eye(3, dtype=np.float32), [0, 1, 2])
+        rows, d, chunks = ix.lance_search([1.0, 0.0], 1)
+        assert len(rows) == 0 and chunks == 0
+        assert len(ix.lance_index_scan([1.0, 0.0, 0.0, 0.0], 2)) == 0
+
+
+def test_rowid_mapping_append_delete_and_chunked_scan(gpu, host, oracle_mod):
+    """Row ids are DuckDB's, not labels: non-contiguous row ids, delete by row id, rows appended later, and a
+    k > 2048 result emitted in STANDARD_VECTOR_SIZE chunks (src/lance_search.cpp:84-104)."""
+    rng = np.random.default_rng(21)
+    n, d = 6000, 24
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    rowids = rng.permutation(10 * n)[:n].astype(np.int64)
+    q = rng.standard_normal(d, dtype=np.float32)
+    with host.HostIndex(d, "l2") as ix:
+        ix.append(X[:4000], rowids[:4000])
+        ix.append(X[4000:], rowids[4000:])  # appended after "index creation" (lance_basic.test:45-53)
+        dele = rng.choice(n, 300, replace=False)
+        ix.delete(rowids[dele])
+        ix.delete(np.array([10 ** 9]))  # unknown row id: ignored
+        assert ix.count() == n - 300
+        deleted = np.zeros(n, bool)
+        deleted[dele] = True
+        k = 3000
+        rows, dist, chunks = ix.lance_search(q, k)
+        assert len(rows) == k and chunks == 2
+        wl, wd32, wd64 = oracle_mod.flat_search(X, q, k, "l2", None, oracle_mod.make_bitmap(deleted))
+        label_of = {int(r): i for i, r in enumerate(rowids)}
+        got_labels = [label_of[int(r)] for r in rows]
+        assert_topk_parity(got_labels, dist, wl, wd64, lambda lab: oracle_mod.distance_f64("l2", q, X[lab]), what="host chunked")
+        assert (np.diff(dist) >= 0).all()  # result order = ascending distance (the ORDER BY node is gone)
+
+
+def test_host_index_options_batch_and_ann(gpu, host, oracle_mod):
+    """WITH (metric='cosine', nprobes=.., refine_factor=..) and lance_create_ann_index through the mirror."""
+    rng = np.random.default_rng(23)
+    n, d, k = 20000, 32, 10
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Q = rng.standard_normal((12, d), dtype=np.float32)
+    score = rng.integers(0, 100, n)
+    with host.HostIndex(d, "cosine", nprobes=64, refine_factor=4) as ix:
+        ix.append(X, np.arange(n))
+        ix.columns.append("score", score.tolist())
+        ids, dist, cnt = ix.search_batch(Q, k, "score > 20")
+        allow = oracle_mod.make_bitmap(score > 20)
+        for j in range(len(Q)):
+            wl, wd32, wd64 = oracle_mod.flat_search(X, Q[j], k, "cosine", allow, None)
+            assert_topk_parity(ids[j, :cnt[j]], dist[j, :cnt[j]], wl, wd64,
+                               lambda lab: oracle_mod.distance_f64("cosine", Q[j], X[lab]), what=f"host batch q{j}")
+        ix.create_ann_index(64, 8)  # SELECT * FROM lance_create_ann_index('t', 'idx', 64, 8)
+        rows, dist1 = ix.search(Q[0], k)
+        assert len(rows) == k and (np.diff(dist1) >= 0).all()
+        # all 64 partitions probed + refine -> the exact answer
+        wl, wd32, wd64 = oracle_mod.flat_search(X, Q[0], k, "cosine", None, None)
+        assert len(set(rows.tolist()) & set(wl.tolist())) >= k - 1
