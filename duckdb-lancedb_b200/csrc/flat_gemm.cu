@@ -26,6 +26,8 @@
 
 #include "flat_gemm_aux.cuh"
 #include "flat_gemm_kernel.cuh"
+#include "flat_gemm_ts_kernel.cuh"
+#include <cstdlib>
 
 namespace lb {
 
@@ -138,12 +140,37 @@ void FlatGemm::sync_rows(const float *X, long long n, long long cap_rows, cudaSt
 }
 
 struct GemmPlan {
-	int QT, KS, S, NG, R;
+	int QT, KS, S, NG, R, EB = 0;
 	size_t smem;
+	bool ts; // queries resident in tensor memory (flat_gemm_ts_kernel)
 };
+
+// 0 auto, 1 all-shared operands, 2 queries in TMEM (needs Kpad <= 256); LANCE_B200_GEMM=ss|ts
+static int gemm_variant_override() {
+	const char *e = getenv("LANCE_B200_GEMM");
+	if (!e) return 0;
+	return e[0] == 's' ? 1 : (e[0] == 't' ? 2 : 0);
+}
 
 static GemmPlan plan_gemm(int tilesQ, int nkb, int num_sms) {
 	GemmPlan best{};
+	const int variant = gemm_variant_override();
+	if (nkb <= 4 && variant != 1) {
+		// TMEM holds 256 columns of query tiles: K/2 columns each
+		int qt_max = std::min(8 / nkb, tilesQ);
+		int NG = (tilesQ + qt_max - 1) / qt_max;
+		best.ts = true;
+		best.NG = NG;
+		best.QT = (tilesQ + NG - 1) / NG;
+		best.KS = nkb;
+		best.EB = 8;
+		best.S = 2;
+		while (best.S < 4 && gemm_ts_smem_bytes(best.QT, nkb, best.S + 1, best.EB) <= TC_SMEM_MAX) best.S++;
+		best.R = std::max(1, num_sms / NG);
+		best.smem = gemm_ts_smem_bytes(best.QT, nkb, best.S, best.EB);
+		return best;
+	}
+	if (variant == 2) throw Error("LANCE_B200_GEMM=ts needs K <= 256");
 	// largest resident query block that still leaves two whole-tile stages
 	int qt_max = 1;
 	for (int qt = 2; qt <= 8; qt++)
@@ -178,6 +205,10 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	const int d = im.dim, Kpad = im.Kpad;
 	if (!im.attr_set) {
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(refresh_threshold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 		LB_CUDA(cudaFuncSetAttribute(rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 		im.attr_set = true;
@@ -187,7 +218,10 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	const long long ntiles = (n + GEMM_BN - 1) / GEMM_BN;
 	// segment growth: candidates per refresh ~ k * growth * (margin inflation); keep that well under TC_CAP
 	// total slow-path hits per query ~ (#segments) * growth * k: small k affords few, large segments
-	int growth = std::max(2, std::min(16, std::min(TC_CAP / (8 * k), 512 / k)));
+	int growth = std::max(2, std::min(4, std::min(TC_CAP / (8 * k), 512 / k)));
+	long long seed_tiles = TC_SEED_TILES;
+	if (const char *e = getenv("LANCE_B200_TC_GROWTH")) growth = std::max(2, atoi(e)); // tuning hooks
+	if (const char *e = getenv("LANCE_B200_TC_SEED")) seed_tiles = std::max(1, atoi(e));
 
 	for (int q0 = 0; q0 < nq_total; q0 += TC_QCHUNK) {
 		const int nq = std::min(TC_QCHUNK, nq_total - q0);
@@ -219,14 +253,24 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		p.nkb = im.nkb, p.ksteps_last = im.ksteps_last, p.QT = pl.QT, p.KS = pl.KS, p.S = pl.S, p.NG = pl.NG;
 		p.n_rows = n, p.thr = thr, p.cnt = cnt, p.cand = cand, p.CAP = TC_CAP;
 		p.deleted = deleted, p.allow = d_allow, p.allow_bits = allow_bits;
-		long long t0 = 0, seg = TC_SEED_TILES;
+		p.Qs = Qs, p.Kpad = Kpad, p.EB = pl.EB;
+		long long t0 = 0, seg = seed_tiles;
 		while (t0 < ntiles) {
 			long long t1 = std::min(ntiles, t0 + seg);
 			if (ntiles - t1 < seg) t1 = ntiles; // do not leave a short tail segment
 			p.tile_lo = t0, p.tile_hi = t1;
 			p.R = (int)std::min<long long>(pl.R, t1 - t0);
 			int tix = timer ? timer->begin(KC_FLAT_GEMM, s) : -1;
-			flat_gemm_kernel<<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(tmQ, im.tmX, p);
+			if (pl.ts) {
+				switch (im.nkb) {
+				case 1: flat_gemm_ts_kernel<1><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+				case 2: flat_gemm_ts_kernel<2><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+				case 3: flat_gemm_ts_kernel<3><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+				default: flat_gemm_ts_kernel<4><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+				}
+			} else {
+				flat_gemm_kernel<<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(tmQ, im.tmX, p);
+			}
 			LB_CUDA(cudaGetLastError());
 			if (timer) timer->end(tix, s);
 			refresh_threshold_kernel<<<nq, 256, sel_smem, s>>>(cand, TC_CAP, cnt, thr, margin, flag, k, cap);

@@ -35,6 +35,9 @@ struct GemmParams {
 	const uint32_t *deleted; // tombstones or null
 	const uint32_t *allow;   // prefilter bitmap or null
 	long long allow_bits;
+	const void *Qs;          // bf16 [NG*QT*128][Kpad] query tiles in global memory (TMEM-resident variant)
+	int Kpad;
+	int EB;                  // per-(epilogue group, query) shared-memory emit buffer entries (0 = append directly)
 };
 
 static constexpr int GEMM_BN = 128;
@@ -42,12 +45,40 @@ static constexpr int GEMM_NBUF = 4;
 static constexpr int GEMM_THREADS = 320;
 static constexpr int GEMM_KB_BYTES = 128 * 128; // one 64-wide k-block of a 128-row tile
 
-__device__ __noinline__ void gemm_emit(const GemmParams &p, int q, long long row, float score) {
+// Thread-private emit buffer in shared memory: slot-major ([slot][128 threads]) so that the lanes of a warp
+// never collide.  A hit costs one shared store; the global append (one atomicAdd for the whole buffer, whose
+// latency would otherwise stall the epilogue warp on every hit) happens when the buffer fills and at kernel end.
+struct EmitBuf {
+	uint2 *slots; // &buf[0][thread] or null
+	int *count;   // &cnt[thread]
+};
+
+__device__ __noinline__ void gemm_flush(const GemmParams &p, int q, const EmitBuf &eb) {
+	const int n = *eb.count;
+	if (n == 0) return;
+	const uint32_t pos = atomicAdd(p.cnt + q, (uint32_t)n);
+	for (int i = 0; i < n; i++)
+		if (pos + i < (uint32_t)p.CAP) p.cand[(size_t)q * p.CAP + pos + i] = eb.slots[i * 128];
+	*eb.count = 0;
+}
+
+__device__ __noinline__ void gemm_emit(const GemmParams &p, int q, long long row, float score, const EmitBuf &eb) {
 	if (row >= p.n_rows) return; // TMA zero-fill beyond the table
 	if (p.deleted && bit_test(p.deleted, row)) return;
 	if (p.allow && !(row < p.allow_bits && bit_test(p.allow, row))) return;
-	uint32_t pos = atomicAdd(p.cnt + q, 1u);
-	if (pos < (uint32_t)p.CAP) p.cand[(size_t)q * p.CAP + pos] = make_uint2(__float_as_uint(score), (uint32_t)row);
+	const uint2 e = make_uint2(__float_as_uint(score), (uint32_t)row);
+	if (!eb.slots) {
+		uint32_t pos = atomicAdd(p.cnt + q, 1u);
+		if (pos < (uint32_t)p.CAP) p.cand[(size_t)q * p.CAP + pos] = e;
+		return;
+	}
+	int n = *eb.count;
+	if (n == p.EB) {
+		gemm_flush(p, q, eb);
+		n = 0;
+	}
+	eb.slots[n * 128] = e;
+	*eb.count = n + 1;
 }
 
 __device__ __forceinline__ void tmem_wait_regs(uint32_t (&r)[32]) {
@@ -61,7 +92,7 @@ __device__ __forceinline__ void tmem_wait_regs(uint32_t (&r)[32]) {
 }
 
 __device__ __forceinline__ void gemm_process_chunk(const GemmParams &p, const uint32_t (&r)[32], float thr, int q,
-                                                   long long row0) {
+                                                   long long row0, const EmitBuf &eb) {
 	float a[10];
 #pragma unroll
 	for (int i = 0; i < 10; i++)
@@ -77,14 +108,14 @@ __device__ __forceinline__ void gemm_process_chunk(const GemmParams &p, const ui
 #pragma unroll
 				for (int j = 0; j < 3; j++) {
 					float v = __uint_as_float(r[3 * i + j]);
-					if (v >= thr) gemm_emit(p, q, row0 + 3 * i + j, v);
+					if (v >= thr) gemm_emit(p, q, row0 + 3 * i + j, v, eb);
 				}
 			}
 		}
 #pragma unroll
 		for (int i = 30; i < 32; i++) {
 			float v = __uint_as_float(r[i]);
-			if (v >= thr) gemm_emit(p, q, row0 + i, v);
+			if (v >= thr) gemm_emit(p, q, row0 + i, v, eb);
 		}
 	}
 }
@@ -134,30 +165,37 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 	__syncthreads();
 	tc::tc_fence_after();
 	const uint32_t tmem_base = *tmem_slot;
+	const bool has_work = p.tile_lo + r < p.tile_hi;
 
 	if (warp == 0) {
-		if (lane == 0) {
-			// ---------------- TMA producer
-			tc::mbar_expect_tx(bar_q, (uint32_t)p.QT * p.nkb * GEMM_KB_BYTES);
-			for (int t = 0; t < p.QT; t++)
-				for (int kb = 0; kb < p.nkb; kb++)
-					tc::tma_load_2d(Qs + (uint32_t)(t * p.nkb + kb) * GEMM_KB_BYTES, &tmQ, kb * 64, (g * p.QT + t) * 128,
-					                bar_q);
+		if (has_work) {
+			// ---------------- TMA producer (whole warp converged, one elected lane issues)
+			if (tc::elect_one()) {
+				tc::mbar_expect_tx(bar_q, (uint32_t)p.QT * p.nkb * GEMM_KB_BYTES);
+				for (int t = 0; t < p.QT; t++)
+					for (int kb = 0; kb < p.nkb; kb++)
+						tc::tma_load_2d(Qs + (uint32_t)(t * p.nkb + kb) * GEMM_KB_BYTES, &tmQ, kb * 64, (g * p.QT + t) * 128,
+						                bar_q);
+			}
+			__syncwarp();
 			uint32_t it = 0;
 			for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
 				for (int c = 0; c < nst; c++, it++) {
 					const uint32_t s = it % p.S, ph = (it / p.S) & 1u;
 					tc::mbar_wait(bar_empty + 8u * s, ph ^ 1u);
-					tc::mbar_expect_tx(bar_full + 8u * s, stage_bytes);
-					for (int kk = 0; kk < p.KS; kk++)
-						tc::tma_load_2d(Xs + s * stage_bytes + (uint32_t)kk * GEMM_KB_BYTES, &tmX, (c * p.KS + kk) * 64,
-						                (int)(tile * GEMM_BN), bar_full + 8u * s);
+					if (tc::elect_one()) {
+						tc::mbar_expect_tx(bar_full + 8u * s, stage_bytes);
+						for (int kk = 0; kk < p.KS; kk++)
+							tc::tma_load_2d(Xs + s * stage_bytes + (uint32_t)kk * GEMM_KB_BYTES, &tmX, (c * p.KS + kk) * 64,
+							                (int)(tile * GEMM_BN), bar_full + 8u * s);
+					}
+					__syncwarp();
 				}
 			}
 		}
 	} else if (warp == 1) {
-		if (lane == 0) {
-			// ---------------- MMA issuer (one thread)
+		if (has_work) {
+			// ---------------- MMA issuer: the warp stays converged, one elected lane issues the instructions
 			const uint32_t idesc = tc::umma_idesc_bf16(128, GEMM_BN);
 			tc::mbar_wait(bar_q, 0);
 			tc::tc_fence_after();
@@ -174,23 +212,29 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 							tc::mbar_wait(bar_full + 8u * s, ph);
 							tc::tc_fence_after();
 						}
-						for (int kk = 0; kk < p.KS; kk++) {
-							const int kb = c * p.KS + kk;
-							const int nk = (kb == p.nkb - 1) ? p.ksteps_last : 4;
-							const uint32_t a0 = Qs + (uint32_t)(t * p.nkb + kb) * GEMM_KB_BYTES;
-							const uint32_t b0 = Xs + s * stage_bytes + (uint32_t)kk * GEMM_KB_BYTES;
-							for (int k4 = 0; k4 < nk; k4++)
-								tc::umma_bf16(d, tc::umma_smem_desc(a0 + k4 * 32), tc::umma_smem_desc(b0 + k4 * 32), idesc,
-								              (uint32_t)((kb | k4) != 0));
+						if (tc::elect_one()) {
+							for (int kk = 0; kk < p.KS; kk++) {
+								const int kb = c * p.KS + kk;
+								const int nk = (kb == p.nkb - 1) ? p.ksteps_last : 4;
+								// descriptors built once per k-block; a 16-element K step adds 32 B = 2 to the address field
+								const uint64_t a0 = tc::umma_smem_desc(Qs + (uint32_t)(t * p.nkb + kb) * GEMM_KB_BYTES);
+								const uint64_t b0 = tc::umma_smem_desc(Xs + s * stage_bytes + (uint32_t)kk * GEMM_KB_BYTES);
+#pragma unroll
+								for (int k4 = 0; k4 < 4; k4++) {
+									if (k4 >= nk) break;
+									tc::umma_bf16(d, a0 + (uint64_t)(2 * k4), b0 + (uint64_t)(2 * k4), idesc,
+									              (uint32_t)((kb | k4) != 0));
+								}
+							}
+							if (t == p.QT - 1) tc::umma_commit(bar_empty + 8u * s);
+							if (c == nst - 1) tc::umma_commit(bar_tfull + 8u * b);
 						}
-						if (t == p.QT - 1) tc::umma_commit(bar_empty + 8u * s);
+						__syncwarp();
 					}
-					tc::umma_commit(bar_tfull + 8u * b);
 				}
 				it += nst;
 			}
 		}
-		__syncwarp();
 	} else {
 		// ---------------- epilogue: TMEM -> registers -> threshold filter -> candidate lists
 		const int e = (warp - 2) >> 2;
@@ -207,23 +251,24 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 				const int q = (g * p.QT + t) * 128 + lrow;
 				const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + b * GEMM_BN;
 				const long long row0 = tile * GEMM_BN;
+				const EmitBuf eb{nullptr, nullptr};
 				uint32_t va[32], vb[32];
 				tc::tmem_ld32(taddr, va);
 				tmem_wait_regs(va);
 				tc::tmem_ld32(taddr + 32, vb);
-				gemm_process_chunk(p, va, thr, q, row0);
+				gemm_process_chunk(p, va, thr, q, row0, eb);
 				tmem_wait_regs(vb);
 				tc::tmem_ld32(taddr + 64, va);
-				gemm_process_chunk(p, vb, thr, q, row0 + 32);
+				gemm_process_chunk(p, vb, thr, q, row0 + 32, eb);
 				tmem_wait_regs(va);
 				tc::tmem_ld32(taddr + 96, vb);
-				gemm_process_chunk(p, va, thr, q, row0 + 64);
+				gemm_process_chunk(p, va, thr, q, row0 + 64, eb);
 				tmem_wait_regs(vb);
 				// the accumulator is in registers: hand the TMEM buffer back before the last chunk is examined
 				tc::tc_fence_before();
 				__syncwarp();
 				if (lane == 0) tc::mbar_arrive(bar_tempty + 8u * b);
-				gemm_process_chunk(p, vb, thr, q, row0 + 96);
+				gemm_process_chunk(p, vb, thr, q, row0 + 96, eb);
 			}
 		}
 	}
