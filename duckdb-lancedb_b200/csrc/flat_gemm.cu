@@ -27,6 +27,7 @@
 #include "flat_gemm_aux.cuh"
 #include "flat_gemm_kernel.cuh"
 #include "flat_gemm_ts_kernel.cuh"
+#include "flat_gemm_tsk_kernel.cuh"
 #include <cstdlib>
 
 namespace lb {
@@ -47,10 +48,10 @@ static encode_tiled_fn get_encode_fn() {
 }
 
 // bf16 row-major [rows][Kpad] -> tiled map with a {64, 128} box and the 128-byte swizzle the UMMA descriptors expect
-static void encode_rows_map(CUtensorMap *m, const void *base, long long rows, int Kpad) {
+static void encode_rows_map(CUtensorMap *m, const void *base, long long rows, int Kpad, int box_rows = 128) {
 	cuuint64_t dims[2] = {(cuuint64_t)Kpad, (cuuint64_t)rows};
 	cuuint64_t strides[1] = {(cuuint64_t)Kpad * 2};
-	cuuint32_t box[2] = {64, 128};
+	cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
 	cuuint32_t estr[2] = {1, 1};
 	CUresult r = get_encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
 	                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -69,7 +70,7 @@ struct FlatGemm::Impl {
 	DevBuf shadow;   // bf16 [cap_rows][Kpad]
 	DevBuf max_norm; // one float (as bits)
 	long long rows_done = 0, cap_rows = 0;
-	CUtensorMap tmX;
+	CUtensorMap tmX, tmX64; // 128-row and 64-row boxes over the shadow
 	const void *tmX_base = nullptr;
 	long long tmX_rows = -1;
 	bool attr_set = false;
@@ -134,6 +135,7 @@ void FlatGemm::sync_rows(const float *X, long long n, long long cap_rows, cudaSt
 	}
 	if (im.tmX_base != im.shadow.p || im.tmX_rows != n) {
 		encode_rows_map(&im.tmX, im.shadow.p, n, im.Kpad); // rows beyond n read as zeros (TMA out-of-bounds fill)
+		encode_rows_map(&im.tmX64, im.shadow.p, n, im.Kpad, 64);
 		im.tmX_base = im.shadow.p;
 		im.tmX_rows = n;
 	}
@@ -142,7 +144,8 @@ void FlatGemm::sync_rows(const float *X, long long n, long long cap_rows, cudaSt
 struct GemmPlan {
 	int QT, KS, S, NG, R, EB = 0;
 	size_t smem;
-	bool ts; // queries resident in tensor memory (flat_gemm_ts_kernel)
+	bool ts;  // queries resident in tensor memory, whole-K X tiles (flat_gemm_ts_kernel, K <= 256)
+	bool tsk; // queries resident in tensor memory, K streamed (flat_gemm_tsk_kernel, K <= 768)
 };
 
 // 0 auto, 1 all-shared operands, 2 queries in TMEM (needs Kpad <= 256); LANCE_B200_GEMM=ss|ts
@@ -170,7 +173,20 @@ static GemmPlan plan_gemm(int tilesQ, int nkb, int num_sms) {
 		best.smem = gemm_ts_smem_bytes(best.QT, nkb, best.S, best.EB);
 		return best;
 	}
-	if (variant == 2) throw Error("LANCE_B200_GEMM=ts needs K <= 256");
+	if (nkb <= 12 && variant != 1) {
+		best.tsk = true;
+		best.QT = 1;
+		best.NG = tilesQ;
+		best.KS = std::min(4, nkb);
+		if (const char *e = getenv("LANCE_B200_TSK_KS")) best.KS = std::max(1, std::min(nkb, atoi(e)));
+		best.EB = 8;
+		best.S = 2;
+		while (best.S < 12 && gemm_tsk_smem_bytes(best.S + 1, best.KS, best.EB) <= TC_SMEM_MAX) best.S++;
+		best.R = std::max(1, num_sms / best.NG);
+		best.smem = gemm_tsk_smem_bytes(best.S, best.KS, best.EB);
+		return best;
+	}
+	if (variant == 2) throw Error("LANCE_B200_GEMM=ts needs K <= 768");
 	// largest resident query block that still leaves two whole-tile stages
 	int qt_max = 1;
 	for (int qt = 2; qt <= 8; qt++)
@@ -205,6 +221,7 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	const int d = im.dim, Kpad = im.Kpad;
 	if (!im.attr_set) {
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
@@ -223,8 +240,24 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	if (const char *e = getenv("LANCE_B200_TC_GROWTH")) growth = std::max(2, atoi(e)); // tuning hooks
 	if (const char *e = getenv("LANCE_B200_TC_SEED")) seed_tiles = std::max(1, atoi(e));
 
-	for (int q0 = 0; q0 < nq_total; q0 += TC_QCHUNK) {
-		const int nq = std::min(TC_QCHUNK, nq_total - q0);
+	for (int q0 = 0, nq = 0; q0 < nq_total; q0 += nq) {
+		// queries per pass: at most TC_QCHUNK; when every CTA holds a single query tile (large K), take a tile
+		// count c with c * floor(SMs / c) close to the SM count (32 tiles on 148 SMs would idle 20 of them)
+		int rem_tiles = (std::min(TC_QCHUNK, nq_total - q0) + 127) / 128;
+		int take = rem_tiles;
+		if (plan_gemm(rem_tiles, im.nkb, im.num_sms).QT == 1 && rem_tiles > 1) {
+			int best_used = 0;
+			for (int c = rem_tiles; c >= (rem_tiles + 1) / 2; c--) {
+				int used = c * std::max(1, im.num_sms / c);
+				if (used > im.num_sms) used = im.num_sms;
+				if (used * 100 >= im.num_sms * 95) {
+					take = c;
+					break;
+				}
+				if (used > best_used) best_used = used, take = c;
+			}
+		}
+		nq = std::min(take * 128, nq_total - q0);
 		const int tilesQ = (nq + 127) / 128;
 		GemmPlan pl = plan_gemm(tilesQ, im.nkb, im.num_sms);
 		const int nslots = pl.NG * pl.QT * 128;
@@ -261,7 +294,9 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 			p.tile_lo = t0, p.tile_hi = t1;
 			p.R = (int)std::min<long long>(pl.R, t1 - t0);
 			int tix = timer ? timer->begin(KC_FLAT_GEMM, s) : -1;
-			if (pl.ts) {
+			if (pl.tsk) {
+				flat_gemm_tsk_kernel<<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+			} else if (pl.ts) {
 				switch (im.nkb) {
 				case 1: flat_gemm_ts_kernel<1><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
 				case 2: flat_gemm_ts_kernel<2><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;

@@ -1,0 +1,181 @@
+// flat_gemm_tsk_kernel.cuh — large-K variant (256 < K <= 768) of the TMEM-resident candidate kernel.
+//
+// One query tile (128 queries x K bf16 = K/2 TMEM columns, up to 384) stays in tensor memory for the CTA's
+// life; X streams through shared memory in stages of 128 rows x KS 64-wide k-blocks (KS x 16 KB; the MMA warp
+// pays one barrier wait and one commit per stage, so a stage carries 4*KS MMAs), as many stages as fit.
+// TMEM map: [0,128) the ONE 128 x 128 accumulator | [128, 128 + K/2) the query tile.  With 384 columns taken
+// by the queries there is no room for a second N=128 accumulator (N=64 pairs were tried: dispatch-bound), so
+// the tile's MMAs (12 x 4 x 64 clk) and the drain alternate; the drain is kept short by having all 8 epilogue
+// warps pull their 64 columns into registers at once and release the accumulator BEFORE filtering.
+// UMMA M=128, N=128, A from TMEM.  Epilogue filter and emit buffers as in flat_gemm_ts_kernel.
+#pragma once
+#include "flat_gemm_kernel.cuh"
+
+namespace lb {
+
+static constexpr int TSK_KB_BYTES = GEMM_KB_BYTES; // 128 rows x 64 bf16
+
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p) {
+	extern __shared__ uint8_t smem_raw[];
+	const int warp = threadIdx.x >> 5;
+	const int lane = threadIdx.x & 31;
+	const int g = blockIdx.x % p.NG;
+	const int r = blockIdx.x / p.NG;
+	const int KC = p.nkb * 32; // TMEM columns of the query tile
+	const int nst = (p.nkb + p.KS - 1) / p.KS; // stages per half-tile (the last one may hold fewer k-blocks)
+	const uint32_t TSK_STAGE_BYTES = (uint32_t)p.KS * TSK_KB_BYTES;
+
+	const uint32_t sbase = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+	uint8_t *sgen = smem_raw + (sbase - tc::smem_u32(smem_raw));
+	const uint32_t Xs = sbase;
+	const uint32_t ctl_off = (uint32_t)p.S * TSK_STAGE_BYTES;
+	const uint32_t bars = sbase + ctl_off;
+	// barrier slots (8 B each): full[S] | empty[S] | qready | tfull | (unused) | tempty | (unused)
+	const uint32_t bar_full = bars, bar_empty = bars + 8u * p.S, bar_q = bars + 16u * p.S;
+	const uint32_t bar_tfull = bar_q + 8, bar_tempty = bar_tfull + 16;
+	uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(sgen + ctl_off + 16u * p.S + 8 + 32);
+	float *thr_s = reinterpret_cast<float *>(sgen + ctl_off + 16u * p.S + 8 + 32 + 16);
+	int *ecnt = reinterpret_cast<int *>(thr_s + 128);               // [2][128]
+	uint2 *eslots = reinterpret_cast<uint2 *>(ecnt + 2 * 128);      // [2][EB][128]
+	for (int i = threadIdx.x; i < 2 * 128; i += GEMM_THREADS) ecnt[i] = 0;
+	const bool has_work = p.tile_lo + r < p.tile_hi;
+
+	if (warp == 0 && lane == 0) {
+		tc::tma_prefetch_desc(&tmX);
+		for (int s = 0; s < p.S; s++) {
+			tc::mbar_init(bar_full + 8u * s, 1);
+			tc::mbar_init(bar_empty + 8u * s, 1);
+		}
+		tc::mbar_init(bar_q, 8);
+		tc::mbar_init(bar_tfull, 1);
+		tc::mbar_init(bar_tempty, 8);
+		tc::fence_barrier_init();
+	}
+	if (warp == 1) {
+		tc::tmem_alloc(tc::smem_u32(tmem_slot), 512);
+		tc::tmem_relinquish();
+	}
+	for (int i = threadIdx.x; i < 128; i += GEMM_THREADS) thr_s[i] = p.thr[(size_t)g * 128 + i];
+	tc::tc_fence_before();
+	__syncthreads();
+	tc::tc_fence_after();
+	const uint32_t tmem_base = *tmem_slot;
+	const uint32_t tmem_q = tmem_base + 128;
+
+	if (warp == 0) {
+		// ---------------- TMA producer: stages of KS boxes (128 rows x 64 columns each)
+		uint32_t it = 0;
+		for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
+			for (int c = 0; c < nst; c++, it++) {
+				const uint32_t s = it % p.S, ph = (it / p.S) & 1u;
+				const int kb0 = c * p.KS, nk = min(p.KS, p.nkb - kb0);
+				tc::mbar_wait(bar_empty + 8u * s, ph ^ 1u);
+				if (tc::elect_one()) {
+					tc::mbar_expect_tx(bar_full + 8u * s, (uint32_t)nk * TSK_KB_BYTES);
+					for (int kk = 0; kk < nk; kk++)
+						tc::tma_load_2d(Xs + s * TSK_STAGE_BYTES + (uint32_t)kk * TSK_KB_BYTES, &tmX, (kb0 + kk) * 64,
+						                (int)(tile * GEMM_BN), bar_full + 8u * s);
+				}
+				__syncwarp();
+			}
+		}
+	} else if (warp == 1) {
+		if (has_work) {
+			// ---------------- MMA issuer: D (128 x 128) = Q (TMEM) x Xtile^T (smem), K streamed
+			const uint32_t idesc = tc::umma_idesc_bf16(128, GEMM_BN);
+			tc::mbar_wait(bar_q, 0);
+			tc::tc_fence_after();
+			uint32_t it = 0, acc = 0;
+			for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
+				{
+					tc::mbar_wait(bar_tempty, (acc & 1u) ^ 1u);
+					tc::tc_fence_after();
+					const uint32_t d = tmem_base;
+					for (int c = 0; c < nst; c++, it++) {
+						const uint32_t s = it % p.S, ph = (it / p.S) & 1u;
+						const int kb0 = c * p.KS, nkk = min(p.KS, p.nkb - kb0);
+						tc::mbar_wait(bar_full + 8u * s, ph);
+						tc::tc_fence_after();
+						if (tc::elect_one()) {
+							for (int kk = 0; kk < nkk; kk++) {
+								const int kb = kb0 + kk;
+								const uint64_t bdesc = tc::umma_smem_desc(Xs + s * TSK_STAGE_BYTES + (uint32_t)kk * TSK_KB_BYTES);
+								const uint32_t qa = tmem_q + (uint32_t)(kb * 32);
+								const int nk = (kb == p.nkb - 1) ? p.ksteps_last : 4;
+#pragma unroll
+								for (int k4 = 0; k4 < 4; k4++) {
+									if (k4 >= nk) break;
+									tc::umma_bf16_ts(d, qa + k4 * 8, bdesc + (uint64_t)(2 * k4), idesc, (uint32_t)((kb | k4) != 0));
+								}
+							}
+							tc::umma_commit(bar_empty + 8u * s);
+							if (c == nst - 1) tc::umma_commit(bar_tfull);
+						}
+						__syncwarp();
+					}
+					acc++;
+				}
+			}
+		}
+	} else {
+		const int e = (warp - 2) >> 2;
+		const int quad = warp & 3;
+		const int lrow = quad * 32 + lane;
+		const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+		const int q = g * 128 + lrow;
+		if (has_work) {
+			// ---------------- queries: global bf16 -> registers -> TMEM; the two groups split the columns
+			const uint4 *src = reinterpret_cast<const uint4 *>(reinterpret_cast<const uint16_t *>(p.Qs) + (size_t)q * p.Kpad);
+			for (int c0 = e * 32; c0 < KC; c0 += 64) {
+				uint32_t v[32];
+#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					uint4 w = __ldg(src + (c0 >> 2) + j);
+					v[4 * j] = w.x, v[4 * j + 1] = w.y, v[4 * j + 2] = w.z, v[4 * j + 3] = w.w;
+				}
+				tc::tmem_st32(tmem_q + lane_base + (uint32_t)c0, v);
+			}
+			tc::tmem_st_wait();
+			tc::tc_fence_before();
+			__syncwarp();
+			if (lane == 0) tc::mbar_arrive(bar_q);
+		}
+		// ---------------- epilogue: every warp pulls 64 columns (group e: [64e, 64e+64)) of its lane quadrant
+		const float thr = thr_s[lrow];
+		const EmitBuf eb{p.EB ? eslots + (size_t)(e * p.EB) * 128 + lrow : nullptr, ecnt + e * 128 + lrow};
+		uint32_t acc = 0;
+		for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
+			{
+				tc::mbar_wait(bar_tfull, acc & 1u);
+				acc++;
+				tc::tc_fence_after();
+				const uint32_t taddr = tmem_base + lane_base + (uint32_t)e * 64;
+				const long long row0 = tile * GEMM_BN + e * 64;
+				uint32_t va[32], vb[32];
+				tc::tmem_ld32(taddr, va);
+				tc::tmem_ld32(taddr + 32, vb);
+				tmem_wait_regs(va);
+				tmem_wait_regs(vb);
+				tc::tc_fence_before();
+				__syncwarp();
+				if (lane == 0) tc::mbar_arrive(bar_tempty);
+				gemm_process_chunk(p, va, thr, q, row0, eb);
+				gemm_process_chunk(p, vb, thr, q, row0 + 32, eb);
+			}
+		}
+		if (p.EB) gemm_flush(p, q, eb);
+	}
+	tc::tc_fence_before();
+	__syncthreads();
+	if (warp == 1) {
+		tc::tc_fence_after();
+		tc::tmem_dealloc(tmem_base, 512);
+	}
+}
+
+static inline size_t gemm_tsk_smem_bytes(int S, int KS, int EB) {
+	return 1024 + (size_t)S * KS * TSK_KB_BYTES + 16u * S + 8 + 32 + 16 + 128 * 4 + 2 * 128 * 4 + (size_t)2 * EB * 128 * 8;
+}
+
+} // namespace lb
