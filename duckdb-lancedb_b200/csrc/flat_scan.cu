@@ -139,12 +139,62 @@ __device__ __forceinline__ unsigned live_mask8(long long row0, long long row_beg
 	return m & 0xFFu;
 }
 
+// Final select by a whole block: src[0..m) keys (KEY_INVALID entries ignored, read through L2 because other
+// SMs may have written them) -> sorted (label, distance) list of query slot `q`.  All threads of the block
+// call it; bufs = nwarps*cap keys and cnts = nwarps ints of shared memory.
+__device__ inline void block_final_select(const u64 *__restrict__ src, long long m, int k, int cap, u64 *bufs, int *cnts,
+                                          long long label_base, size_t q, int64_t *__restrict__ out_labels,
+                                          float *__restrict__ out_dist, int32_t *__restrict__ out_counts,
+                                          u64 *__restrict__ out_keys) {
+	const int nwarps = blockDim.x >> 5;
+	const int warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	WarpSelect sel;
+	sel.init(bufs + (size_t)warp * cap, cap, k);
+	for (long long i0 = (long long)warp * 128; i0 < m; i0 += (long long)nwarps * 128) {
+		u64 key[4];
+#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			long long i = i0 + u * 32 + lane;
+			key[u] = (i < m) ? __ldcg(src + i) : KEY_INVALID;
+		}
+#pragma unroll
+		for (int u = 0; u < 4; u++) sel.push(key[u] != KEY_INVALID, key[u]);
+	}
+	sel.finalize();
+	if (lane == 0) cnts[warp] = sel.cnt;
+	__syncthreads();
+	if (warp == 0) {
+		for (int w = 1; w < nwarps; w++) {
+			const u64 *s2 = bufs + (size_t)w * cap;
+			const int c = cnts[w];
+			for (int i0 = 0; i0 < c; i0 += 32) {
+				int i = i0 + lane;
+				u64 key = (i < c) ? s2[i] : KEY_INVALID;
+				sel.push(i < c, key);
+			}
+		}
+		sel.finalize();
+		for (int i = lane; i < k; i += 32) {
+			bool ok = i < sel.cnt;
+			u64 key = ok ? sel.buf[i] : KEY_INVALID;
+			if (out_labels) out_labels[q * k + i] = ok ? (int64_t)(label_base + (long long)key_row(key)) : -1;
+			if (out_dist) out_dist[q * k + i] = ok ? key_dist(key) : __int_as_float(0x7F800000);
+			if (out_keys) out_keys[q * k + i] = key;
+		}
+		if (lane == 0 && out_counts) out_counts[q] = sel.cnt;
+	}
+	__syncthreads();
+}
+
 template <int METRIC, int QB, int VEC>
 __global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_scan_kernel(const float *__restrict__ X, long long row_begin, long long n,
                                                          int d, const float *__restrict__ Q, int nq_valid, int k, int cap,
                                                          const uint32_t *__restrict__ allow, long long allow_bits,
                                                          const uint32_t *__restrict__ deleted,
-                                                         u64 *__restrict__ partials, u64 *g_tau) {
+                                                         u64 *__restrict__ partials, u64 *g_tau, long long label_base,
+                                                         int64_t *__restrict__ out_labels, float *__restrict__ out_dist,
+                                                         int32_t *__restrict__ out_counts, u64 *__restrict__ out_keys) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	const int nwarps = blockDim.x >> 5;
 	const int warp = threadIdx.x >> 5;
@@ -170,6 +220,7 @@ __global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_s
 	}
 	__syncthreads();
 
+	unsigned *ctl = reinterpret_cast<unsigned *>(g_tau + 8); // [0..3] list lengths - 1, [4] arrival ticket - 1
 	WarpSelect sel[QB];
 #pragma unroll
 	for (int j = 0; j < QB; j++) sel[j].init(bufs + ((size_t)warp * QB + j) * cap, cap, k);
@@ -266,12 +317,32 @@ __global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_s
 			if (lane == 0) atomicMin(g_tau + j, sel[j].tau);
 			__syncwarp();
 		}
+		// append only what can still make the global top-k (a sorted prefix) to query j's shared list
 		const u64 gt = *reinterpret_cast<volatile u64 *>(g_tau + j);
-		u64 *dst = partials + ((size_t)j * gridDim.x + blockIdx.x) * k;
-		for (int i = lane; i < k; i += 32) {
-			u64 key = (i < sel[j].cnt) ? sel[j].buf[i] : KEY_INVALID;
-			dst[i] = key <= gt ? key : KEY_INVALID;
+		int npass = 0;
+		for (int i0 = 0; i0 < sel[j].cnt; i0 += 32) {
+			int i = i0 + lane;
+			npass += __popc(__ballot_sync(0xFFFFFFFFu, i < sel[j].cnt && sel[j].buf[i] <= gt));
 		}
+		unsigned base = 0;
+		if (lane == 0 && npass > 0) base = atomicAdd(ctl + j, (unsigned)npass) + 1u; // counters start at 0xFFFFFFFF
+		base = __shfl_sync(0xFFFFFFFFu, base, 0);
+		u64 *dst = partials + (size_t)j * gridDim.x * k + base;
+		for (int i = lane; i < npass; i += 32) dst[i] = sel[j].buf[i];
+	}
+	// the last block to arrive runs the final select over the shared lists (no second launch)
+	__threadfence();
+	__syncthreads();
+	if (threadIdx.x == 0) cnts[0] = (atomicAdd(ctl + 4, 1u) + 1u == gridDim.x - 1u);
+	__syncthreads();
+	const bool last = cnts[0] != 0;
+	__syncthreads();
+	if (!last) return;
+	__threadfence();
+	for (int j = 0; j < QB && j < nq_valid; j++) {
+		const unsigned m = *reinterpret_cast<volatile unsigned *>(ctl + j) + 1u;
+		block_final_select(partials + (size_t)j * gridDim.x * k, (long long)m, k, cap, bufs, cnts, label_base, (size_t)j,
+		                   out_labels, out_dist, out_counts, out_keys);
 	}
 }
 
@@ -282,43 +353,11 @@ __global__ void __launch_bounds__(256) topk_merge_kernel(const u64 *__restrict__
                                                           float *__restrict__ out_dist, int32_t *__restrict__ out_counts,
                                                           u64 *__restrict__ out_keys) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
-	const int nwarps = blockDim.x >> 5;
-	const int warp = threadIdx.x >> 5;
-	const unsigned lane = lane_id();
 	int *cnts = reinterpret_cast<int *>(smem_raw);
 	u64 *bufs = reinterpret_cast<u64 *>(smem_raw + 64);
 	const int q = blockIdx.x;
-	const u64 *src = keys + (size_t)q * m;
-
-	WarpSelect sel;
-	sel.init(bufs + (size_t)warp * cap, cap, k);
-	for (long long i0 = (long long)warp * 32; i0 < m; i0 += (long long)nwarps * 32) {
-		long long i = i0 + lane;
-		u64 key = (i < m) ? src[i] : KEY_INVALID;
-		sel.push(key != KEY_INVALID, key);
-	}
-	sel.finalize();
-	if (lane == 0) cnts[warp] = sel.cnt;
-	__syncthreads();
-	if (warp != 0) return;
-	for (int w = 1; w < nwarps; w++) {
-		const u64 *s2 = bufs + (size_t)w * cap;
-		const int c = cnts[w];
-		for (int i0 = 0; i0 < c; i0 += 32) {
-			int i = i0 + lane;
-			u64 key = (i < c) ? s2[i] : KEY_INVALID;
-			sel.push(i < c, key);
-		}
-	}
-	sel.finalize();
-	for (int i = lane; i < k; i += 32) {
-		bool ok = i < sel.cnt;
-		u64 key = ok ? sel.buf[i] : KEY_INVALID;
-		if (out_labels) out_labels[(size_t)q * k + i] = ok ? (int64_t)(label_base + (long long)key_row(key)) : -1;
-		if (out_dist) out_dist[(size_t)q * k + i] = ok ? key_dist(key) : __int_as_float(0x7F800000);
-		if (out_keys) out_keys[(size_t)q * k + i] = key;
-	}
-	if (lane == 0 && out_counts) out_counts[q] = sel.cnt;
+	block_final_select(keys + (size_t)q * m, m, k, cap, bufs, cnts, label_base, (size_t)q, out_labels, out_dist,
+	                   out_counts, out_keys);
 }
 
 __global__ void fill_u64_kernel(u64 *p, long long n, u64 v) {
@@ -329,7 +368,7 @@ __global__ void fill_u64_kernel(u64 *p, long long n, u64 v) {
 // ------------------------------------------------------------------------------------------------ host
 
 typedef void (*scan_kernel_t)(const float *, long long, long long, int, const float *, int, int, int, const uint32_t *, long long,
-                              const uint32_t *, u64 *, u64 *);
+                              const uint32_t *, u64 *, u64 *, long long, int64_t *, float *, int32_t *, u64 *);
 
 template <int METRIC, int QB>
 static scan_kernel_t scan_kernel_vec(bool vec4) {
@@ -392,7 +431,7 @@ FlatScanPlan plan_flat_scan(const float *X, int metric, int d, int k, int nq, lo
 }
 
 size_t flat_scan_scratch_bytes(const FlatScanPlan &p, int k) {
-	return ((size_t)p.QB * p.grid * k + 8) * sizeof(u64);
+	return ((size_t)p.QB * p.grid * k + 16) * sizeof(u64);
 }
 
 static void merge_launch_params(long long m, int k, int &nwarps, int &cap, size_t &smem) {
@@ -427,26 +466,27 @@ void fill_u64(u64 *p, long long n, u64 v, cudaStream_t s, int64_t *launches) {
 
 // Runs the scan for a.nq queries (any count) in passes of plan.QB; results land in the out_* device buffers.
 void run_flat_scan(const FlatScanArgs &a, const FlatScanPlan &p, void *scratch, cudaStream_t s, int64_t *launches) {
+	// scratch header (16 words, all-ones at the start of a pass): g_tau[8] | list lengths - 1, arrival ticket - 1
 	u64 *g_tau = reinterpret_cast<u64 *>(scratch);
-	u64 *partials = g_tau + 8;
+	u64 *partials = g_tau + 16;
 	for (int q0 = 0; q0 < a.nq; q0 += p.QB) {
 		int nv = a.nq - q0 < p.QB ? a.nq - q0 : p.QB;
-		LB_CUDA(cudaMemsetAsync(g_tau, 0xFF, 8 * sizeof(u64), s)); // KEY_INVALID
+		LB_CUDA(cudaMemsetAsync(g_tau, 0xFF, 16 * sizeof(u64), s));
 		const float *dQ = a.dQ + (size_t)q0 * a.d;
 		const float *X = a.X;
-		long long n = a.n, allow_bits = a.allow_bits, row_begin = a.row_begin;
+		long long n = a.n, allow_bits = a.allow_bits, row_begin = a.row_begin, label_base = a.label_base;
 		int d = a.d, k = a.k, cap = p.cap;
 		const uint32_t *allow = a.allow, *deleted = a.deleted;
-		void *args[] = {&X, &row_begin, &n, &d, &dQ, &nv, &k, &cap, &allow, &allow_bits, &deleted, &partials, &g_tau};
+		int64_t *out_labels = a.out_labels ? a.out_labels + (size_t)q0 * a.k : nullptr;
+		float *out_dist = a.out_dist ? a.out_dist + (size_t)q0 * a.k : nullptr;
+		int32_t *out_counts = a.out_counts ? a.out_counts + q0 : nullptr;
+		u64 *out_keys = a.out_keys ? a.out_keys + (size_t)q0 * a.k : nullptr;
+		void *args[] = {&X,     &row_begin, &n,        &d,     &dQ,         &nv,         &k,        &cap,        &allow,
+		                &allow_bits, &deleted, &partials, &g_tau, &label_base, &out_labels, &out_dist, &out_counts, &out_keys};
 		int tix = a.timer ? a.timer->begin(KC_FLAT_SCAN, s) : -1;
 		LB_CUDA(cudaLaunchKernel(p.kernel, dim3(p.grid), dim3(p.nwarps * 32), args, p.smem, s));
 		if (a.timer) a.timer->end(tix, s);
 		if (launches) (*launches)++;
-		launch_topk_merge(partials, nv, (long long)p.grid * a.k, a.k, a.label_base,
-		                  a.out_labels ? a.out_labels + (size_t)q0 * a.k : nullptr,
-		                  a.out_dist ? a.out_dist + (size_t)q0 * a.k : nullptr,
-		                  a.out_counts ? a.out_counts + q0 : nullptr,
-		                  a.out_keys ? a.out_keys + (size_t)q0 * a.k : nullptr, s, launches);
 	}
 }
 
