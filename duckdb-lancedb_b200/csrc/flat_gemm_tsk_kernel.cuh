@@ -160,8 +160,8 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 				tc::tc_fence_before();
 				__syncwarp();
 				if (lane == 0) tc::mbar_arrive(bar_tempty);
-				gemm_process_chunk(p, va, thr, q, row0, eb);
-				gemm_process_chunk(p, vb, thr, q, row0 + 32, eb);
+				gemm_process_chunk_inline(p, va, thr, q, row0, eb);
+				gemm_process_chunk_inline(p, vb, thr, q, row0 + 32, eb);
 			}
 		}
 		if (p.EB) gemm_flush(p, q, eb);

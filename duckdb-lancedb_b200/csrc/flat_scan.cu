@@ -139,60 +139,15 @@ __device__ __forceinline__ unsigned live_mask8(long long row0, long long row_beg
 	return m & 0xFFu;
 }
 
-// Final select by a whole block: src[0..m) keys (KEY_INVALID entries ignored, read through L2 because other
-// SMs may have written them) -> sorted (label, distance) list of query slot `q`.  All threads of the block
-// call it; bufs = nwarps*cap keys and cnts = nwarps ints of shared memory.
-__device__ inline void block_final_select(const u64 *__restrict__ src, long long m, int k, int cap, u64 *bufs, int *cnts,
-                                          long long label_base, size_t q, int64_t *__restrict__ out_labels,
-                                          float *__restrict__ out_dist, int32_t *__restrict__ out_counts,
-                                          u64 *__restrict__ out_keys) {
-	const int nwarps = blockDim.x >> 5;
-	const int warp = threadIdx.x >> 5;
-	const unsigned lane = lane_id();
-	WarpSelect sel;
-	sel.init(bufs + (size_t)warp * cap, cap, k);
-	for (long long i0 = (long long)warp * 128; i0 < m; i0 += (long long)nwarps * 128) {
-		u64 key[4];
-#pragma unroll
-		for (int u = 0; u < 4; u++) {
-			long long i = i0 + u * 32 + lane;
-			key[u] = (i < m) ? __ldcg(src + i) : KEY_INVALID;
-		}
-#pragma unroll
-		for (int u = 0; u < 4; u++) sel.push(key[u] != KEY_INVALID, key[u]);
-	}
-	sel.finalize();
-	if (lane == 0) cnts[warp] = sel.cnt;
-	__syncthreads();
-	if (warp == 0) {
-		for (int w = 1; w < nwarps; w++) {
-			const u64 *s2 = bufs + (size_t)w * cap;
-			const int c = cnts[w];
-			for (int i0 = 0; i0 < c; i0 += 32) {
-				int i = i0 + lane;
-				u64 key = (i < c) ? s2[i] : KEY_INVALID;
-				sel.push(i < c, key);
-			}
-		}
-		sel.finalize();
-		for (int i = lane; i < k; i += 32) {
-			bool ok = i < sel.cnt;
-			u64 key = ok ? sel.buf[i] : KEY_INVALID;
-			if (out_labels) out_labels[q * k + i] = ok ? (int64_t)(label_base + (long long)key_row(key)) : -1;
-			if (out_dist) out_dist[q * k + i] = ok ? key_dist(key) : __int_as_float(0x7F800000);
-			if (out_keys) out_keys[q * k + i] = key;
-		}
-		if (lane == 0 && out_counts) out_counts[q] = sel.cnt;
-	}
-	__syncthreads();
-}
+static constexpr int SCAN_MAXG = 16;       // groups of the two-level final select
+static constexpr int SCAN_HDR_WORDS = 64;  // u64 words of control state in front of the lists
 
 template <int METRIC, int QB, int VEC>
 __global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_scan_kernel(const float *__restrict__ X, long long row_begin, long long n,
                                                          int d, const float *__restrict__ Q, int nq_valid, int k, int cap,
                                                          const uint32_t *__restrict__ allow, long long allow_bits,
                                                          const uint32_t *__restrict__ deleted,
-                                                         u64 *__restrict__ partials, u64 *g_tau, long long label_base,
+                                                         u64 *__restrict__ partials, u64 *g_tau, int G, long long label_base,
                                                          int64_t *__restrict__ out_labels, float *__restrict__ out_dist,
                                                          int32_t *__restrict__ out_counts, u64 *__restrict__ out_keys) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -220,7 +175,11 @@ __global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_s
 	}
 	__syncthreads();
 
-	unsigned *ctl = reinterpret_cast<unsigned *>(g_tau + 8); // [0..3] list lengths - 1, [4] arrival ticket - 1
+	// control words (all-ones at launch): list length - 1 per (query, group) | arrival ticket - 1 per group | final ticket - 1
+	unsigned *ctl = reinterpret_cast<unsigned *>(g_tau + 8);
+	const int grp = blockIdx.x % G;
+	const int gblocks = ((int)gridDim.x - grp + G - 1) / G;              // blocks in this group
+	const size_t gcap = (size_t)((gridDim.x + G - 1) / G) * k;           // key slots of a group list
 	WarpSelect sel[QB];
 #pragma unroll
 	for (int j = 0; j < QB; j++) sel[j].init(bufs + ((size_t)warp * QB + j) * cap, cap, k);
@@ -325,25 +284,38 @@ __global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_s
 			npass += __popc(__ballot_sync(0xFFFFFFFFu, i < sel[j].cnt && sel[j].buf[i] <= gt));
 		}
 		unsigned base = 0;
-		if (lane == 0 && npass > 0) base = atomicAdd(ctl + j, (unsigned)npass) + 1u; // counters start at 0xFFFFFFFF
+		if (lane == 0 && npass > 0) base = atomicAdd(ctl + j * SCAN_MAXG + grp, (unsigned)npass) + 1u; // counters start at 0xFFFFFFFF
 		base = __shfl_sync(0xFFFFFFFFu, base, 0);
-		u64 *dst = partials + (size_t)j * gridDim.x * k + base;
+		u64 *dst = partials + ((size_t)j * G + grp) * gcap + base;
 		for (int i = lane; i < npass; i += 32) dst[i] = sel[j].buf[i];
 	}
-	// the last block to arrive runs the final select over the shared lists (no second launch)
+	// Two-level final select without a second launch: the last block of each group reduces the group's list to k
+	// keys (the groups finish together, so these run in parallel on G SMs); the last group then selects the result.
 	__threadfence();
 	__syncthreads();
-	if (threadIdx.x == 0) cnts[0] = (atomicAdd(ctl + 4, 1u) + 1u == gridDim.x - 1u);
+	if (threadIdx.x == 0) cnts[0] = (atomicAdd(ctl + 4 * SCAN_MAXG + grp, 1u) + 1u == (unsigned)gblocks - 1u);
 	__syncthreads();
-	const bool last = cnts[0] != 0;
+	bool last = cnts[0] != 0;
 	__syncthreads();
 	if (!last) return;
 	__threadfence();
+	u64 *level2 = partials + (size_t)QB * G * gcap;
 	for (int j = 0; j < QB && j < nq_valid; j++) {
-		const unsigned m = *reinterpret_cast<volatile unsigned *>(ctl + j) + 1u;
-		block_final_select(partials + (size_t)j * gridDim.x * k, (long long)m, k, cap, bufs, cnts, label_base, (size_t)j,
-		                   out_labels, out_dist, out_counts, out_keys);
+		const unsigned m = *reinterpret_cast<volatile unsigned *>(ctl + j * SCAN_MAXG + grp) + 1u;
+		block_final_select(partials + ((size_t)j * G + grp) * gcap, (long long)m, k, cap, bufs, cnts, 0, 0, nullptr, nullptr,
+		                   nullptr, level2 + ((size_t)j * G + grp) * k);
 	}
+	__threadfence();
+	__syncthreads();
+	if (threadIdx.x == 0) cnts[0] = (atomicAdd(ctl + 5 * SCAN_MAXG, 1u) + 1u == (unsigned)G - 1u);
+	__syncthreads();
+	last = cnts[0] != 0;
+	__syncthreads();
+	if (!last) return;
+	__threadfence();
+	for (int j = 0; j < QB && j < nq_valid; j++)
+		block_final_select(level2 + (size_t)j * G * k, (long long)G * k, k, cap, bufs, cnts, label_base, (size_t)j, out_labels,
+		                   out_dist, out_counts, out_keys);
 }
 
 // Final select: keys[q][m] (KEY_INVALID entries ignored) -> sorted (label, distance) lists.
@@ -368,7 +340,7 @@ __global__ void fill_u64_kernel(u64 *p, long long n, u64 v) {
 // ------------------------------------------------------------------------------------------------ host
 
 typedef void (*scan_kernel_t)(const float *, long long, long long, int, const float *, int, int, int, const uint32_t *, long long,
-                              const uint32_t *, u64 *, u64 *, long long, int64_t *, float *, int32_t *, u64 *);
+                              const uint32_t *, u64 *, u64 *, int, long long, int64_t *, float *, int32_t *, u64 *);
 
 template <int METRIC, int QB>
 static scan_kernel_t scan_kernel_vec(bool vec4) {
@@ -430,8 +402,17 @@ FlatScanPlan plan_flat_scan(const float *X, int metric, int d, int k, int nq, lo
 	return p;
 }
 
+// groups of the two-level final select: about sqrt(grid), so both levels see equally short lists
+static int scan_groups(int grid, int k) {
+	if ((long long)grid * k <= 4096) return 1; // short lists: one level
+	int g = 1;
+	while (g < SCAN_MAXG && g * g < grid) g++;
+	return g;
+}
+
 size_t flat_scan_scratch_bytes(const FlatScanPlan &p, int k) {
-	return ((size_t)p.QB * p.grid * k + 16) * sizeof(u64);
+	const int G = scan_groups(p.grid, k);
+	return ((size_t)p.QB * G * ((p.grid + G - 1) / G) * k + (size_t)p.QB * G * k + SCAN_HDR_WORDS) * sizeof(u64);
 }
 
 static void merge_launch_params(long long m, int k, int &nwarps, int &cap, size_t &smem) {
@@ -466,12 +447,13 @@ void fill_u64(u64 *p, long long n, u64 v, cudaStream_t s, int64_t *launches) {
 
 // Runs the scan for a.nq queries (any count) in passes of plan.QB; results land in the out_* device buffers.
 void run_flat_scan(const FlatScanArgs &a, const FlatScanPlan &p, void *scratch, cudaStream_t s, int64_t *launches) {
-	// scratch header (16 words, all-ones at the start of a pass): g_tau[8] | list lengths - 1, arrival ticket - 1
+	// scratch header (all-ones at the start of a pass): g_tau[8] | control words of the final select
 	u64 *g_tau = reinterpret_cast<u64 *>(scratch);
-	u64 *partials = g_tau + 16;
+	u64 *partials = g_tau + SCAN_HDR_WORDS;
+	int G = scan_groups(p.grid, a.k);
 	for (int q0 = 0; q0 < a.nq; q0 += p.QB) {
 		int nv = a.nq - q0 < p.QB ? a.nq - q0 : p.QB;
-		LB_CUDA(cudaMemsetAsync(g_tau, 0xFF, 16 * sizeof(u64), s));
+		LB_CUDA(cudaMemsetAsync(g_tau, 0xFF, SCAN_HDR_WORDS * sizeof(u64), s));
 		const float *dQ = a.dQ + (size_t)q0 * a.d;
 		const float *X = a.X;
 		long long n = a.n, allow_bits = a.allow_bits, row_begin = a.row_begin, label_base = a.label_base;
@@ -482,7 +464,7 @@ void run_flat_scan(const FlatScanArgs &a, const FlatScanPlan &p, void *scratch, 
 		int32_t *out_counts = a.out_counts ? a.out_counts + q0 : nullptr;
 		u64 *out_keys = a.out_keys ? a.out_keys + (size_t)q0 * a.k : nullptr;
 		void *args[] = {&X,     &row_begin, &n,        &d,     &dQ,         &nv,         &k,        &cap,        &allow,
-		                &allow_bits, &deleted, &partials, &g_tau, &label_base, &out_labels, &out_dist, &out_counts, &out_keys};
+		                &allow_bits, &deleted, &partials, &g_tau, &G, &label_base, &out_labels, &out_dist, &out_counts, &out_keys};
 		int tix = a.timer ? a.timer->begin(KC_FLAT_SCAN, s) : -1;
 		LB_CUDA(cudaLaunchKernel(p.kernel, dim3(p.grid), dim3(p.nwarps * 32), args, p.smem, s));
 		if (a.timer) a.timer->end(tix, s);

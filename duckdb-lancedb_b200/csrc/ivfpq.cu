@@ -27,6 +27,7 @@
 #include <cmath>
 #include <cstring>
 
+#include "tc_ptx.cuh"
 #include "topk.cuh"
 
 namespace lb {
@@ -52,6 +53,63 @@ __global__ void prep_queries_kernel(const float *__restrict__ Q, int nq, int d, 
 	}
 	for (int o = 16; o; o >>= 1) s2 += __shfl_xor_sync(0xFFFFFFFFu, s2, o);
 	if (lane == 0) qn2[q] = s2;
+}
+
+// ------------------------------------------------------------------ batched probe (a12), nq >= 8
+// keys[q][p] = (d(q', c_p), p) for a 64 x 64 tile of (queries, centroids) per CTA, fp32, same per-element formula
+// as the streaming scan ((a-b)^2 summed, or 1 - a.b).  The centroid table is small (P x d, L2-resident), so this
+// is a register-tiled fp32 contraction (4 x 4 outputs per thread) rather than a pass of the table per 4 queries.
+template <int IS_DOT>
+__global__ void __launch_bounds__(256) probe_tile_kernel(const float *__restrict__ Qp, int nq, const float *__restrict__ C,
+                                                         int P, int d, u64 *__restrict__ keys) {
+	__shared__ __align__(16) float As[16][68];
+	__shared__ __align__(16) float Bs[16][68];
+	const int tq = threadIdx.x >> 4, tp = threadIdx.x & 15;
+	const int q0 = blockIdx.y * 64, p0 = blockIdx.x * 64;
+	float acc[4][4];
+#pragma unroll
+	for (int i = 0; i < 4; i++)
+#pragma unroll
+		for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+	for (int k0 = 0; k0 < d; k0 += 16) {
+#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			const int i = threadIdx.x + u * 256;
+			const int r = i >> 4, c = i & 15;
+			const bool kin = k0 + c < d;
+			As[c][r] = (kin && q0 + r < nq) ? __ldg(Qp + (size_t)(q0 + r) * d + k0 + c) : 0.f;
+			Bs[c][r] = (kin && p0 + r < P) ? __ldg(C + (size_t)(p0 + r) * d + k0 + c) : 0.f;
+		}
+		__syncthreads();
+#pragma unroll
+		for (int kk = 0; kk < 16; kk++) {
+			const float4 a4 = *reinterpret_cast<const float4 *>(&As[kk][tq * 4]);
+			const float4 b4 = *reinterpret_cast<const float4 *>(&Bs[kk][tp * 4]);
+			const float a[4] = {a4.x, a4.y, a4.z, a4.w}, b[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+			for (int i = 0; i < 4; i++)
+#pragma unroll
+				for (int j = 0; j < 4; j++) {
+					if (IS_DOT)
+						acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+					else {
+						const float e = a[i] - b[j];
+						acc[i][j] = fmaf(e, e, acc[i][j]);
+					}
+				}
+		}
+		__syncthreads();
+	}
+#pragma unroll
+	for (int i = 0; i < 4; i++) {
+		const int q = q0 + tq * 4 + i;
+		if (q >= nq) continue;
+#pragma unroll
+		for (int j = 0; j < 4; j++) {
+			const int pp = p0 + tp * 4 + j;
+			if (pp < P) keys[(size_t)q * P + pp] = make_key(IS_DOT ? 1.0f - acc[i][j] : acc[i][j], (uint32_t)pp);
+		}
+	}
 }
 
 // ------------------------------------------------------------------ per-query lookup table T1
@@ -113,50 +171,130 @@ __device__ __forceinline__ float lut4(const float *lut_m, uint32_t w) {
 	return lut_m[w & 0xFFu] + lut_m[256 + ((w >> 8) & 0xFFu)] + lut_m[512 + ((w >> 16) & 0xFFu)] + lut_m[768 + (w >> 24)];
 }
 
+// exact distance of (query qv, row of `key`) by one warp -> (distance, row) key on every lane (a14)
+__device__ __forceinline__ u64 warp_exact_key(const float *__restrict__ X, int d, const float *__restrict__ qv, int metric,
+                                              u64 key) {
+	if (key == KEY_INVALID) return KEY_INVALID;
+	const unsigned lane = lane_id();
+	const uint32_t row = key_row(key);
+	const float *x = X + (size_t)row * d;
+	float acc = 0.f, nx = 0.f, nq2 = 0.f;
+	for (int c = lane; c < d; c += 32) {
+		float a = __ldg(qv + c), b = __ldg(x + c);
+		if (metric == METRIC_L2) {
+			float e = a - b;
+			acc = fmaf(e, e, acc);
+		} else {
+			acc = fmaf(a, b, acc);
+			nx = fmaf(b, b, nx);
+			nq2 = fmaf(a, a, nq2);
+		}
+	}
+	for (int o = 16; o; o >>= 1) {
+		acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+		nx += __shfl_xor_sync(0xFFFFFFFFu, nx, o);
+		nq2 += __shfl_xor_sync(0xFFFFFFFFu, nq2, o);
+	}
+	float dist;
+	if (metric == METRIC_L2)
+		dist = acc;
+	else if (metric == METRIC_DOT)
+		dist = 1.0f - acc;
+	else {
+		float den = sqrtf(nq2) * sqrtf(nx);
+		if (!(den > 0.f))
+			dist = 1.0f;
+		else {
+			float sim = fminf(1.f, fmaxf(-1.f, acc / den));
+			dist = 1.0f - sim;
+		}
+	}
+	return make_key(dist, row);
+}
+
+struct AdcParams {
+	const float *lut_g; // [nq][M][256] per-query tables
+	int M;
+	const u64 *probe_keys; // [nq][probe_stride] (probe distance, partition) keys
+	int nprobes_eff, probe_stride;
+	const float *qn2;
+	int metric;
+	const long long *pad_offsets;
+	const int32_t *slot_rows;
+	const uint8_t *codes_il;
+	const float *row_term;
+	const uint32_t *allow;
+	long long allow_bits;
+	const uint32_t *deleted;
+	int kc, cap, PS;
+	u64 *partials;      // [nq][S][kc]
+	unsigned *tickets;  // [nq], zero before the launch
+	u64 *cand;          // [nq][kc] the kc best ADC keys (ascending)
+	// refine + final select, run by the last CTA of a query
+	const float *X;     // raw vectors
+	int d;
+	const float *Q;     // the caller's queries (not normalised)
+	int refine;         // 0: ADC distances are final
+	u64 *fin;           // [nq][fin_stride], first kc entries written here
+	int fin_stride;
+	int fuse_final;     // 1: also write the sorted top-k (no unindexed tail to merge)
+	int k;
+	long long label_base;
+	int64_t *out_labels;
+	float *out_dist;
+	int32_t *out_counts;
+};
+
 template <int GRAN>
-__global__ void __launch_bounds__(256) adc_scan_kernel(
-    const float *__restrict__ lut_g, int M, const u64 *__restrict__ probe_keys, int nprobes_eff, int probe_stride,
-    const float *__restrict__ qn2, int metric, const long long *__restrict__ pad_offsets,
-    const int32_t *__restrict__ slot_rows, const uint8_t *__restrict__ codes_il, const float *__restrict__ row_term,
-    const uint32_t *__restrict__ allow, long long allow_bits, const uint32_t *__restrict__ deleted, int kc, int cap,
-    int PS, u64 *__restrict__ partials) {
-	extern __shared__ __align__(16) unsigned char smem_raw[];
+__global__ void __launch_bounds__(256) adc_scan_kernel(const __grid_constant__ AdcParams p) {
+	extern __shared__ __align__(128) unsigned char smem_raw[];
 	const int nwarps = blockDim.x >> 5;
 	const int warp = threadIdx.x >> 5;
 	const unsigned lane = lane_id();
 	const int q = blockIdx.y;
+	const int M = p.M, kc = p.kc, cap = p.cap, PS = p.PS;
 	// slice s = (probe slot ps, sub-slice j): probes ps, ps+PS, .. and the j-th of J equal parts of each list,
 	// so that a single query still fills the machine (32 probed lists -> PS*J CTAs)
 	const int S = gridDim.x, s = blockIdx.x;
 	const int ps = s % PS, j = s / PS, J = S / PS;
 	float *lut = reinterpret_cast<float *>(smem_raw);                                 // [M][256]
-	int *cnts = reinterpret_cast<int *>(smem_raw + (size_t)M * 1024);                 // [nwarps]
+	int *cnts = reinterpret_cast<int *>(smem_raw + (size_t)M * 1024);                 // [nwarps] (+ flag at [8])
 	u64 *bufs = reinterpret_cast<u64 *>(smem_raw + (size_t)M * 1024 + 64);            // [nwarps][cap]
+	const uint32_t bar = tc::smem_u32(smem_raw + (size_t)M * 1024 + 48);
 
-	{
-		const float4 *src = reinterpret_cast<const float4 *>(lut_g + (size_t)q * M * 256);
-		float4 *dst = reinterpret_cast<float4 *>(lut);
-		for (int i = threadIdx.x; i < M * 64; i += blockDim.x) dst[i] = __ldg(src + i);
+	// the query's table comes in as one bulk copy (TMA engine), 32 KB pieces on one mbarrier
+	if (threadIdx.x == 0) {
+		tc::mbar_init(bar, 1);
+		tc::fence_barrier_init();
+		tc::mbar_expect_tx(bar, (uint32_t)M * 1024u);
+		const unsigned char *src = reinterpret_cast<const unsigned char *>(p.lut_g + (size_t)q * M * 256);
+		for (uint32_t off = 0; off < (uint32_t)M * 1024u; off += 32768u) {
+			uint32_t n = min(32768u, (uint32_t)M * 1024u - off);
+			tc::bulk_load(tc::smem_u32(lut) + off, src + off, n, bar);
+		}
 	}
 	__syncthreads();
 
 	WarpSelect sel;
 	sel.init(bufs + (size_t)warp * cap, cap, kc);
-	const float qq = qn2[q];
+	const float qq = p.qn2[q];
+	const int metric = p.metric;
 	const int chunks = M / GRAN;
 	typedef typename CodeWord<GRAN>::T word_t;
+	bool lut_ready = false;
 
-	for (int pi = ps; pi < nprobes_eff; pi += PS) {
-		const u64 pk = probe_keys[(size_t)q * probe_stride + pi];
+	for (int pi = ps; pi < p.nprobes_eff; pi += PS) {
+		const u64 pk = p.probe_keys[(size_t)q * p.probe_stride + pi];
 		if (pk == KEY_INVALID) continue;
-		const int p = (int)key_row(pk);
+		const int part = (int)key_row(pk);
 		const float cst = (metric == METRIC_DOT) ? 1.0f : key_dist(pk) - qq;
-		const long long pb0 = pad_offsets[p] >> 5, pnb = (pad_offsets[p + 1] >> 5) - pb0;
+		const long long pb0 = p.pad_offsets[part] >> 5, pnb = (p.pad_offsets[part + 1] >> 5) - pb0;
 		const long long b0 = pb0 + pnb * j / J, b1 = pb0 + pnb * (j + 1) / J;
 		for (long long b = b0 + warp; b < b1; b += nwarps) {
 			const long long slot = (b << 5) + lane;
-			const int row = __ldg(slot_rows + slot);
-			const word_t *cp = reinterpret_cast<const word_t *>(codes_il) + (size_t)b * chunks * 32 + lane;
+			const int row = __ldg(p.slot_rows + slot);
+			const float rterm = (metric == METRIC_DOT) ? 0.f : __ldg(p.row_term + slot);
+			const word_t *cp = reinterpret_cast<const word_t *>(p.codes_il) + (size_t)b * chunks * 32 + lane;
 			float acc = 0.f;
 			if (GRAN == 16) {
 				// issue all loads of the row first (M/16 independent 128-bit loads)
@@ -165,6 +303,10 @@ __global__ void __launch_bounds__(256) adc_scan_kernel(
 #pragma unroll
 					for (int u = 0; u < 6; u++)
 						if (c0 + u < chunks) w[u] = __ldg(reinterpret_cast<const uint4 *>(cp) + (size_t)(c0 + u) * 32);
+					if (!lut_ready) {
+						tc::mbar_wait(bar, 0);
+						lut_ready = true;
+					}
 #pragma unroll
 					for (int u = 0; u < 6; u++)
 						if (c0 + u < chunks) {
@@ -173,46 +315,74 @@ __global__ void __launch_bounds__(256) adc_scan_kernel(
 							       lut4(lm + 3072, w[u].w);
 						}
 				}
-			} else if (GRAN == 4) {
-				for (int c = 0; c < chunks; c++) {
-					uint32_t w = __ldg(reinterpret_cast<const uint32_t *>(cp) + (size_t)c * 32);
-					acc += lut4(lut + (size_t)c * 4 * 256, w);
-				}
 			} else {
-				for (int c = 0; c < chunks; c++) {
-					uint8_t w = __ldg(reinterpret_cast<const uint8_t *>(cp) + (size_t)c * 32);
-					acc += lut[c * 256 + w];
+				if (!lut_ready) {
+					tc::mbar_wait(bar, 0);
+					lut_ready = true;
+				}
+				if (GRAN == 4) {
+					for (int c = 0; c < chunks; c++) {
+						uint32_t w = __ldg(reinterpret_cast<const uint32_t *>(cp) + (size_t)c * 32);
+						acc += lut4(lut + (size_t)c * 4 * 256, w);
+					}
+				} else {
+					for (int c = 0; c < chunks; c++) {
+						uint8_t w = __ldg(reinterpret_cast<const uint8_t *>(cp) + (size_t)c * 32);
+						acc += lut[c * 256 + w];
+					}
 				}
 			}
 			float dist;
 			if (metric == METRIC_DOT)
 				dist = 1.0f + acc;
 			else {
-				dist = acc + __ldg(row_term + slot) + cst;
+				dist = acc + rterm + cst;
 				if (metric == METRIC_COSINE) dist *= 0.5f;
 			}
 			bool live = row >= 0;
-			if (live && deleted) live = !bit_test(deleted, row);
-			if (live && allow) live = (row < allow_bits) && bit_test(allow, row);
+			if (live && p.deleted) live = !bit_test(p.deleted, row);
+			if (live && p.allow) live = (row < p.allow_bits) && bit_test(p.allow, row);
 			sel.push(live, make_key(dist, (uint32_t)row));
 		}
 	}
+	if (!lut_ready) tc::mbar_wait(bar, 0); // the copy must land before the CTA may exit
 	sel.finalize();
 	if (lane == 0) cnts[warp] = sel.cnt;
 	__syncthreads();
-	if (warp != 0) return;
-	for (int w = 1; w < nwarps; w++) {
-		const u64 *src = bufs + (size_t)w * cap;
-		const int c = cnts[w];
-		for (int i0 = 0; i0 < c; i0 += 32) {
-			int i = i0 + lane;
-			u64 key = (i < c) ? src[i] : KEY_INVALID;
-			sel.push(i < c, key);
+	if (warp == 0) {
+		for (int w = 1; w < nwarps; w++) {
+			const u64 *src = bufs + (size_t)w * cap;
+			const int c = cnts[w];
+			for (int i0 = 0; i0 < c; i0 += 32) {
+				int i = i0 + lane;
+				u64 key = (i < c) ? src[i] : KEY_INVALID;
+				sel.push(i < c, key);
+			}
 		}
+		sel.finalize();
+		u64 *dst = p.partials + ((size_t)q * S + s) * kc;
+		for (int i = lane; i < kc; i += 32) dst[i] = (i < sel.cnt) ? sel.buf[i] : KEY_INVALID;
 	}
-	sel.finalize();
-	u64 *dst = partials + ((size_t)q * S + s) * kc;
-	for (int i = lane; i < kc; i += 32) dst[i] = (i < sel.cnt) ? sel.buf[i] : KEY_INVALID;
+	// the last CTA of the query selects its kc best ADC candidates, refines them and (no unindexed tail) sorts the
+	// final top-k: one launch instead of scan + merge + refine + merge
+	__threadfence();
+	__syncthreads();
+	if (threadIdx.x == 0) cnts[8] = (atomicAdd(p.tickets + q, 1u) == (unsigned)S - 1u);
+	__syncthreads();
+	if (!cnts[8]) return;
+	__threadfence();
+	block_final_select(p.partials + (size_t)q * S * kc, (long long)S * kc, kc, cap, bufs, cnts, 0, (size_t)q, nullptr, nullptr,
+	                   nullptr, p.cand);
+	u64 *fin = p.fin + (size_t)q * p.fin_stride;
+	for (int i = warp; i < kc; i += nwarps) {
+		const u64 key = p.cand[(size_t)q * kc + i];
+		const u64 res = p.refine ? warp_exact_key(p.X, p.d, p.Q + (size_t)q * p.d, metric, key) : key;
+		if (lane == 0) fin[i] = res;
+	}
+	__syncthreads();
+	if (p.fuse_final)
+		block_final_select(fin, kc, p.k, cap, bufs, cnts, p.label_base, (size_t)q, p.out_labels, p.out_dist, p.out_counts,
+		                   nullptr);
 }
 
 // ------------------------------------------------------------------ refine (a14): exact distance of the candidates
@@ -221,48 +391,9 @@ __global__ void refine_kernel(const float *__restrict__ X, int d, const float *_
                               const u64 *__restrict__ cand, int kc, int nq, u64 *__restrict__ out, int out_stride) {
 	long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if (w >= (long long)nq * kc) return;
-	const unsigned lane = lane_id();
 	const int q = (int)(w / kc), i = (int)(w % kc);
-	const u64 key = cand[(size_t)q * kc + i];
-	u64 res = KEY_INVALID;
-	if (key != KEY_INVALID) {
-		const uint32_t row = key_row(key);
-		const float *x = X + (size_t)row * d;
-		const float *qv = Q + (size_t)q * d;
-		float acc = 0.f, nx = 0.f, nq2 = 0.f;
-		for (int c = lane; c < d; c += 32) {
-			float a = __ldg(qv + c), b = __ldg(x + c);
-			if (metric == METRIC_L2) {
-				float e = a - b;
-				acc = fmaf(e, e, acc);
-			} else {
-				acc = fmaf(a, b, acc);
-				nx = fmaf(b, b, nx);
-				nq2 = fmaf(a, a, nq2);
-			}
-		}
-		for (int o = 16; o; o >>= 1) {
-			acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
-			nx += __shfl_xor_sync(0xFFFFFFFFu, nx, o);
-			nq2 += __shfl_xor_sync(0xFFFFFFFFu, nq2, o);
-		}
-		float dist;
-		if (metric == METRIC_L2)
-			dist = acc;
-		else if (metric == METRIC_DOT)
-			dist = 1.0f - acc;
-		else {
-			float den = sqrtf(nq2) * sqrtf(nx);
-			if (!(den > 0.f))
-				dist = 1.0f;
-			else {
-				float sim = fminf(1.f, fmaxf(-1.f, acc / den));
-				dist = 1.0f - sim;
-			}
-		}
-		res = make_key(dist, row);
-	}
-	if (lane == 0) out[(size_t)q * out_stride + i] = res;
+	const u64 res = warp_exact_key(X, d, Q + (size_t)q * d, metric, cand[(size_t)q * kc + i]);
+	if (lane_id() == 0) out[(size_t)q * out_stride + i] = res;
 }
 
 __global__ void copy_keys_strided_kernel(const u64 *__restrict__ src, int src_stride, int n_per, int nq,

@@ -120,14 +120,10 @@ void Store::drop_index() {
 
 // ------------------------------------------------------------------ search
 template <int GRAN>
-static void launch_adc(const IvfPqIndex &ix, const float *lut, const u64 *probe_keys, int np, const float *qn2,
-                       const uint32_t *allow, long long allow_bits, const uint32_t *deleted, int kc, int cap, int nwarps,
-                       int S, int PS, int nq, size_t smem, u64 *partials, cudaStream_t s) {
+static void launch_adc(const AdcParams &ap, int nwarps, int S, int nq, size_t smem, cudaStream_t s) {
 	auto kern = adc_scan_kernel<GRAN>;
 	if (smem > 48 * 1024) LB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	kern<<<dim3(S, nq), nwarps * 32, smem, s>>>(lut, ix.M, probe_keys, np, np, qn2, ix.metric, ix.pad_offsets.as<long long>(),
-	                                            ix.slot_rows.as<int32_t>(), ix.codes_il.as<uint8_t>(), ix.row_term.as<float>(),
-	                                            allow, allow_bits, deleted, kc, cap, PS, partials);
+	kern<<<dim3(S, nq), nwarps * 32, smem, s>>>(ap);
 	LB_CUDA(cudaGetLastError());
 }
 
@@ -156,7 +152,22 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 	// 2. probe: the nprobes nearest centroids = a flat scan over the centroid table (a12)
 	ws.work2.ensure((size_t)nq * np * sizeof(u64));
 	u64 *probe_keys = ws.work2.as<u64>();
-	{
+	if (nq >= 8) {
+		// batches: tiled fp32 contraction against the (L2-resident) centroid table, then one select per query
+		const int chunk = (int)std::max<long long>(64, std::min<long long>(nq, (256ll << 20) / ((long long)ix.P * 8)));
+		ws.probe_mat.ensure((size_t)std::min(nq, chunk) * ix.P * sizeof(u64));
+		for (int q0 = 0; q0 < nq; q0 += chunk) {
+			const int nc = std::min(chunk, nq - q0);
+			dim3 grid((ix.P + 63) / 64, (nc + 63) / 64);
+			if (metric_ == METRIC_DOT)
+				probe_tile_kernel<1><<<grid, 256, 0, s>>>(Qp + (size_t)q0 * d, nc, ix.centroids.as<float>(), ix.P, d, ws.probe_mat.as<u64>());
+			else
+				probe_tile_kernel<0><<<grid, 256, 0, s>>>(Qp + (size_t)q0 * d, nc, ix.centroids.as<float>(), ix.P, d, ws.probe_mat.as<u64>());
+			LB_CUDA(cudaGetLastError());
+			launches++;
+			launch_topk_merge(ws.probe_mat.as<u64>(), nc, ix.P, np, 0, nullptr, nullptr, nullptr, probe_keys + (size_t)q0 * np, s, &launches);
+		}
+	} else {
 		FlatScanArgs a;
 		a.X = ix.centroids.as<float>();
 		a.n = ix.P;
@@ -191,48 +202,49 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 	if (smem > 226 * 1024) throw Error("k * refine_factor too large for the ADC scan's shared memory");
 	int per_sm = (int)((227 * 1024) / (smem + 1024));
 	if (per_sm < 1) per_sm = 1;
-	long long want = 2ll * num_sms_ * per_sm;
+	// one resident wave for a lone query (every CTA pays a 96 KB table load), two for batches
+	long long want = (nq == 1 ? 1ll : 2ll) * num_sms_ * per_sm;
+	if (const char *e = getenv("LANCE_B200_ADC_CTAS")) want = std::max(1, atoi(e)); // tuning hook
 	const long long want_q = std::max<long long>(1, (want + nq - 1) / nq); // CTAs wanted per query
 	const int PS = (int)std::min<long long>(np, want_q);                   // probe slots
 	const int J = (int)std::max<long long>(1, std::min<long long>(16, want_q / PS)); // sub-slices of every list
 	const int S = PS * J;
 	const int tail_k = (ix.n_indexed < n_rows_) ? k : 0;
 	const int fin_stride = kc + tail_k;
-	ws.work4.ensure(((size_t)nq * S * kc + (size_t)nq * kc + (size_t)nq * fin_stride + (size_t)nq * std::max(tail_k, 1)) * sizeof(u64));
+	ws.work4.ensure(((size_t)nq * S * kc + (size_t)nq * kc + (size_t)nq * fin_stride + (size_t)nq * std::max(tail_k, 1)) * sizeof(u64) +
+	                (size_t)nq * sizeof(unsigned) + 64);
 	u64 *partials = ws.work4.as<u64>();
 	u64 *cand = partials + (size_t)nq * S * kc;
 	u64 *fin = cand + (size_t)nq * kc;
 	u64 *tailk = fin + (size_t)nq * fin_stride;
+	unsigned *tickets = reinterpret_cast<unsigned *>(tailk + (size_t)nq * std::max(tail_k, 1));
 	{
+		// 4-6 in one launch: the last CTA of a query merges the slices' lists (5), refines (6, a14) and, when there is no
+		// unindexed tail, writes the sorted top-k (8)
+		AdcParams ap;
+		ap.lut_g = lut, ap.M = M, ap.probe_keys = probe_keys, ap.nprobes_eff = np, ap.probe_stride = np, ap.qn2 = qn2;
+		ap.metric = ix.metric, ap.pad_offsets = ix.pad_offsets.as<long long>(), ap.slot_rows = ix.slot_rows.as<int32_t>();
+		ap.codes_il = ix.codes_il.as<uint8_t>(), ap.row_term = ix.row_term.as<float>();
+		ap.allow = d_allow, ap.allow_bits = allow_bits, ap.deleted = deleted, ap.kc = kc, ap.cap = cap, ap.PS = PS;
+		ap.partials = partials, ap.tickets = tickets, ap.cand = cand;
+		ap.X = X_.as<float>(), ap.d = d, ap.Q = d_queries, ap.refine = refine >= 1 ? 1 : 0, ap.fin = fin, ap.fin_stride = fin_stride;
+		ap.fuse_final = tail_k == 0 ? 1 : 0, ap.k = k, ap.label_base = label_base_;
+		ap.out_labels = d_out_labels, ap.out_dist = d_out_dist, ap.out_counts = d_out_counts;
+		LB_CUDA(cudaMemsetAsync(tickets, 0, (size_t)nq * sizeof(unsigned), s));
 		int tix = timer_.begin(KC_ADC_SCAN, s);
 		switch (ix.gran) {
-		case 16: launch_adc<16>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, PS, nq, smem, partials, s); break;
-		case 4: launch_adc<4>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, PS, nq, smem, partials, s); break;
-		default: launch_adc<1>(ix, lut, probe_keys, np, qn2, d_allow, allow_bits, deleted, kc, cap, nwarps, S, PS, nq, smem, partials, s);
+		case 16: launch_adc<16>(ap, nwarps, S, nq, smem, s); break;
+		case 4: launch_adc<4>(ap, nwarps, S, nq, smem, s); break;
+		default: launch_adc<1>(ap, nwarps, S, nq, smem, s);
 		}
 		timer_.end(tix, s);
 		launches++;
 	}
-	// 5. candidates = the kc best ADC keys per query
-	launch_topk_merge(partials, nq, (long long)S * kc, kc, 0, nullptr, nullptr, nullptr, cand, s, &launches);
 	if (d_dbg_cand) {
 		LB_CUDA(cudaMemcpyAsync(d_dbg_cand, cand, (size_t)nq * kc * sizeof(u64), cudaMemcpyDeviceToDevice, s));
 	}
 	(void)d_dbg_parts;
 	(void)d_dbg_ncand;
-
-	// 6. refine (a14): exact distances of the candidates (refine_factor >= 1), else ADC distances as they are
-	if (refine >= 1) {
-		int tix = timer_.begin(KC_RERANK, s);
-		refine_kernel<<<blocks_for((long long)nq * kc, 8), 256, 0, s>>>(X_.as<float>(), d, d_queries, metric_, cand, kc, nq,
-		                                                               fin, fin_stride);
-		LB_CUDA(cudaGetLastError());
-		timer_.end(tix, s);
-	} else {
-		copy_keys_strided_kernel<<<blocks_for((long long)nq * kc, 256), 256, 0, s>>>(cand, kc, kc, nq, fin, fin_stride, 0);
-		LB_CUDA(cudaGetLastError());
-	}
-	launches++;
 
 	// 7. rows appended after the index was built: exact scan of the tail, merged (Lance's unindexed fragments)
 	if (tail_k > 0) {
@@ -257,8 +269,9 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 		launches++;
 	}
 
-	// 8. final select
-	launch_topk_merge(fin, nq, fin_stride, k, label_base_, d_out_labels, d_out_dist, d_out_counts, nullptr, s, &launches);
+	// 8. final select (already done by the scan kernel when there is no tail)
+	if (tail_k > 0)
+		launch_topk_merge(fin, nq, fin_stride, k, label_base_, d_out_labels, d_out_dist, d_out_counts, nullptr, s, &launches);
 	std::lock_guard<std::mutex> g(stat_mu_);
 	ivfpq_batches_++;
 	launches_ += launches;

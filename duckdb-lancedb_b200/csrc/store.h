@@ -38,6 +38,7 @@ struct Workspace {
 	cudaStream_t stream = nullptr; // owned (io workspaces only)
 	std::mutex mu;                 // held while work that uses the buffers is being enqueued
 	DevBuf q, allow, out_labels, out_dist, out_counts, work, work2, work3, work4;
+	DevBuf probe_mat; // batched IVF probe: (distance, partition) keys [queries][P]
 	explicit Workspace(bool own_stream);
 	~Workspace();
 };

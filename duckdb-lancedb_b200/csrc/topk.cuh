@@ -96,4 +96,52 @@ struct WarpSelect {
 	__device__ inline void finalize() { compact(); }
 };
 
+// Final select by a whole block: src[0..m) keys (KEY_INVALID entries ignored, read through L2 because other
+// SMs may have written them) -> sorted (label, distance) list of query slot `q`.  All threads of the block
+// call it; bufs = nwarps*cap keys and cnts = nwarps ints of shared memory.
+__device__ inline void block_final_select(const u64 *__restrict__ src, long long m, int k, int cap, u64 *bufs, int *cnts,
+                                          long long label_base, size_t q, int64_t *__restrict__ out_labels,
+                                          float *__restrict__ out_dist, int32_t *__restrict__ out_counts,
+                                          u64 *__restrict__ out_keys) {
+	const int nwarps = blockDim.x >> 5;
+	const int warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	WarpSelect sel;
+	sel.init(bufs + (size_t)warp * cap, cap, k);
+	for (long long i0 = (long long)warp * 128; i0 < m; i0 += (long long)nwarps * 128) {
+		u64 key[4];
+#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			long long i = i0 + u * 32 + lane;
+			key[u] = (i < m) ? __ldcg(src + i) : KEY_INVALID;
+		}
+#pragma unroll
+		for (int u = 0; u < 4; u++) sel.push(key[u] != KEY_INVALID, key[u]);
+	}
+	sel.finalize();
+	if (lane == 0) cnts[warp] = sel.cnt;
+	__syncthreads();
+	if (warp == 0) {
+		for (int w = 1; w < nwarps; w++) {
+			const u64 *s2 = bufs + (size_t)w * cap;
+			const int c = cnts[w];
+			for (int i0 = 0; i0 < c; i0 += 32) {
+				int i = i0 + lane;
+				u64 key = (i < c) ? s2[i] : KEY_INVALID;
+				sel.push(i < c, key);
+			}
+		}
+		sel.finalize();
+		for (int i = lane; i < k; i += 32) {
+			bool ok = i < sel.cnt;
+			u64 key = ok ? sel.buf[i] : KEY_INVALID;
+			if (out_labels) out_labels[q * k + i] = ok ? (int64_t)(label_base + (long long)key_row(key)) : -1;
+			if (out_dist) out_dist[q * k + i] = ok ? key_dist(key) : __int_as_float(0x7F800000);
+			if (out_keys) out_keys[q * k + i] = key;
+		}
+		if (lane == 0 && out_counts) out_counts[q] = sel.cnt;
+	}
+	__syncthreads();
+}
+
 } // namespace lb
