@@ -325,28 +325,25 @@ def run_b200(args, wl):
     L = torch.empty((B, k), dtype=torch.int64, device=dev)
     D = torch.empty((B, k), dtype=torch.float32, device=dev)
     C = torch.empty(B, dtype=torch.int32, device=dev)
+    ss = None
     if world > 1:
         import importlib
 
         sharding = importlib.import_module("duckdb_lancedb_b200.sharding")
-        gatherer = sharding.ShardGather(world, B, k, dev)
-
-        def device_merge(GL, GD, GC, G, nq_, k_, ML, MD, MC):
-            pkg.merge_topk_device(local, GL.data_ptr(), GD.data_ptr(), GC.data_ptr(), G, nq_, k_, ML.data_ptr(),
-                                  MD.data_ptr(), MC.data_ptr(), stream=sp)
-            merge_launches[0] += 3
+        ss = sharding.ShardedSearch(pkg, h, world, B, k, dev, local)
     Lh = torch.empty((B, k), dtype=torch.int64).pin_memory()
     Dh = torch.empty((B, k), dtype=torch.float32).pin_memory()
     Ch = torch.empty(B, dtype=torch.int32).pin_memory()
     Qstage = torch.empty_like(Qd)
-    merge_launches = [0]
 
     def step_device(q_ptr):
-        """local top-k -> (N>1) NCCL all_gather of the lists -> final device select."""
+        """local top-k -> (N>1) one NCCL all_gather of the packed lists -> final device select -> settle."""
+        if world > 1:
+            out = ss.step(q_ptr, sp, nprobes=nprobes, refine_factor=1, d_allow=d_allow, allow_bits=allow_bits)
+            ss.settle()
+            return out
         h.search_device(q_ptr, B, k, L.data_ptr(), D.data_ptr(), C.data_ptr(), nprobes=nprobes, refine_factor=1,
                         d_allow=d_allow, allow_bits=allow_bits, stream=sp)
-        if world > 1:
-            return gatherer.gather_and_merge(L, D, C, device_merge)
         return L, D, C
 
     def step_e2e():
@@ -404,7 +401,8 @@ def run_b200(args, wl):
     st0 = h.stats()
     h.profile_enable(True)
     h.profile_read()
-    merge_launches[0] = 0
+    if ss:
+        ss.merges = 0
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -412,6 +410,7 @@ def run_b200(args, wl):
     prof = h.profile_read()
     h.profile_enable(False)
     st1 = h.stats()
+    merges_value = ss.merges if ss else 0
     # ---- end-to-end (host buffers) timed region
     for _ in range(2):
         step_e2e()
@@ -422,7 +421,7 @@ def run_b200(args, wl):
     ms_e2e = max(ms_e2e_dev, wall) if (world == 1 and not need_flush) else ms_e2e_dev
     clocks = sampler.stop() if rank == 0 else None
 
-    launches = st1["kernel_launches"] - st0["kernel_launches"] + merge_launches[0]
+    launches = st1["kernel_launches"] - st0["kernel_launches"] + merges_value
     qps = B * args.steps / (ms / 1e3)
     qps_e2e = B * args.steps / (ms_e2e / 1e3)
 

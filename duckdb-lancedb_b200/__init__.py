@@ -89,7 +89,10 @@ SIGNATURES = {
     "lance_detached_search_filtered": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _vp] + _ERR),
     "lance_detached_search_batch": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _vp, _vp] + _ERR),
     "lance_b200_search_device": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp] + _ERR),
+    "lance_b200_search_device_async": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp, _vp] + _ERR),
+    "lance_b200_search_finish": (_i32, [_vp, _vp] + _ERR),
     "lance_b200_merge_topk_device": (_i32, [_i32, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp] + _ERR),
+    "lance_b200_merge_topk_strided_device": (_i32, [_i32, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp, _vp, _vp, _vp] + _ERR),
     "lance_b200_set_label_base": (_i32, [_vp, _i64] + _ERR),
     "lance_b200_reserve": (_i32, [_vp, _i64] + _ERR),
     "lance_b200_add_batch_device": (_i64, [_vp, _vp, _i64, _i32, _vp] + _ERR),
@@ -287,6 +290,23 @@ class LanceHandle:
                                             _ptr(d_counts), _ptr(stream) if stream else None, self._err, ERR_LEN)
         self._check(rc, "search")
 
+    def search_device_async(self, d_queries: int, nq: int, k: int, d_labels: int, d_dist: int, d_counts: int,
+                            nprobes: int = 20, refine_factor: int = 1, d_allow: int = 0, allow_bits: int = 0, stream: int = 0,
+                            d_overflow: int = 0):
+        """search_device without its host synchronisation; pair with search_finish (include/lance_b200.h)."""
+        rc = lib().lance_b200_search_device_async(self._h, _ptr(d_queries), nq, k, nprobes, refine_factor,
+                                                  _ptr(d_allow) if d_allow else None, allow_bits, _ptr(d_labels),
+                                                  _ptr(d_dist), _ptr(d_counts), _ptr(d_overflow) if d_overflow else None,
+                                                  _ptr(stream) if stream else None, self._err, ERR_LEN)
+        self._check(rc, "search")
+
+    def search_finish(self, stream: int = 0) -> int:
+        """Waits for the stream and settles the pending overflow check; returns the number of re-run queries."""
+        rc = lib().lance_b200_search_finish(self._h, _ptr(stream) if stream else None, self._err, ERR_LEN)
+        if rc < 0:
+            self._check(rc, "search")
+        return int(rc)
+
     # ---- IVF_PQ
     def create_index(self, num_partitions: int = 0, num_sub_vectors: int = 0):
         self._check(lib().lance_detached_create_index(self._h, num_partitions, num_sub_vectors, self._err, ERR_LEN),
@@ -376,6 +396,17 @@ def merge_topk_device(device: int, d_labels: int, d_dists: int, d_counts: int, G
     rc = lib().lance_b200_merge_topk_device(device, _ptr(d_labels), _ptr(d_dists), _ptr(d_counts), G, nq, k,
                                             _ptr(d_out_labels), _ptr(d_out_dists), _ptr(d_out_counts),
                                             _ptr(stream) if stream else None, err, ERR_LEN)
+    if rc != 0:
+        raise LanceError("Lance merge: " + err.value.decode())
+
+
+def merge_topk_strided_device(device: int, d_labels: int, d_dists: int, d_counts: int, ls: int, ds: int, cs: int, G: int,
+                              nq: int, k: int, d_out_labels: int, d_out_dists: int, d_out_counts: int, stream: int = 0):
+    """Final select over per-rank packed records (element strides ls/ds/cs between ranks); one launch."""
+    err = C.create_string_buffer(ERR_LEN)
+    rc = lib().lance_b200_merge_topk_strided_device(device, _ptr(d_labels), _ptr(d_dists), _ptr(d_counts), ls, ds, cs, G,
+                                                    nq, k, _ptr(d_out_labels), _ptr(d_out_dists), _ptr(d_out_counts),
+                                                    _ptr(stream) if stream else None, err, ERR_LEN)
     if rc != 0:
         raise LanceError("Lance merge: " + err.value.decode())
 

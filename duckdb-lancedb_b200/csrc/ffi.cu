@@ -221,29 +221,44 @@ int32_t lance_b200_search_device(void *handle, const float *d_queries, int32_t n
 	})
 }
 
-int32_t lance_b200_merge_topk_device(int32_t device, const int64_t *d_labels, const float *d_dists,
-                                     const int32_t *d_counts, int32_t G, int32_t nq, int32_t k,
-                                     int64_t *d_out_labels, float *d_out_dists, int32_t *d_out_counts, void *stream,
-                                     char *err_buf, int err_buf_len) {
+int32_t lance_b200_search_device_async(void *handle, const float *d_queries, int32_t nq, int32_t k, int32_t nprobes,
+                                       int32_t refine_factor, const uint32_t *d_allow, int64_t bitmap_bits,
+                                       int64_t *d_out_labels, float *d_out_distances, int32_t *d_out_counts,
+                                       uint32_t *d_overflow, void *stream, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("search failed: ", -1, {
+		h->search_device(d_queries, nq, k, nprobes, refine_factor, d_allow, bitmap_bits, d_out_labels, d_out_distances,
+		                 d_out_counts, static_cast<cudaStream_t>(stream), true, d_overflow);
+		return 0;
+	})
+}
+
+int32_t lance_b200_search_finish(void *handle, void *stream, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("search failed: ", -1, { return h->search_finish(static_cast<cudaStream_t>(stream)); })
+}
+
+int32_t lance_b200_merge_topk_strided_device(int32_t device, const int64_t *d_labels, const float *d_dists,
+                                             const int32_t *d_counts, int64_t labels_stride, int64_t dists_stride,
+                                             int64_t counts_stride, int32_t G, int32_t nq, int32_t k,
+                                             int64_t *d_out_labels, float *d_out_dists, int32_t *d_out_counts,
+                                             void *stream, char *err_buf, int err_buf_len) {
 	LB_TRY("merge failed: ", -1, {
 		if (G <= 0 || nq < 0 || k < 0) throw lb::Error("bad shape");
 		if (nq == 0 || k == 0) return 0;
 		LB_CUDA(cudaSetDevice(device));
-		cudaStream_t s = static_cast<cudaStream_t>(stream);
-		size_t nkeys = (size_t)nq * G * k + (size_t)nq * k;
-		void *scratch = nullptr;
-		LB_CUDA(cudaMallocAsync(&scratch, nkeys * sizeof(lb::u64), s));
-		lb::u64 *keys = static_cast<lb::u64 *>(scratch);
-		try {
-			lb::launch_merge_lists(d_labels, d_dists, d_counts, G, nq, k, keys, keys + (size_t)nq * G * k, d_out_labels,
-			                       d_out_dists, d_out_counts, s, nullptr);
-		} catch (...) {
-			cudaFreeAsync(scratch, s);
-			throw;
-		}
-		LB_CUDA(cudaFreeAsync(scratch, s));
+		lb::launch_merge_lists(d_labels, d_dists, d_counts, labels_stride, dists_stride, counts_stride, G, nq, k, d_out_labels,
+		                       d_out_dists, d_out_counts, static_cast<cudaStream_t>(stream), nullptr);
 		return 0;
 	})
+}
+
+int32_t lance_b200_merge_topk_device(int32_t device, const int64_t *d_labels, const float *d_dists,
+                                     const int32_t *d_counts, int32_t G, int32_t nq, int32_t k,
+                                     int64_t *d_out_labels, float *d_out_dists, int32_t *d_out_counts, void *stream,
+                                     char *err_buf, int err_buf_len) {
+	return lance_b200_merge_topk_strided_device(device, d_labels, d_dists, d_counts, (int64_t)nq * k, (int64_t)nq * k, nq, G, nq,
+	                                            k, d_out_labels, d_out_dists, d_out_counts, stream, err_buf, err_buf_len);
 }
 
 int32_t lance_b200_set_label_base(void *handle, int64_t base, char *err_buf, int err_buf_len) {

@@ -22,6 +22,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "flat_gemm_aux.cuh"
@@ -74,6 +75,24 @@ struct FlatGemm::Impl {
 	const void *tmX_base = nullptr;
 	long long tmX_rows = -1;
 	bool attr_set = false;
+	// deferred overflow check of the last search (FlatGemm::search with defer = true)
+	struct Pending {
+		bool active = false;
+		cudaStream_t s = nullptr;
+		const float *X = nullptr, *Q = nullptr;
+		long long n = 0, allow_bits = 0, label_base = 0;
+		const uint32_t *deleted = nullptr, *allow = nullptr;
+		const uint32_t *flag_out = nullptr, *total = nullptr;
+		int nq = 0, k = 0;
+		int64_t *out_labels = nullptr;
+		float *out_dist = nullptr;
+		int32_t *out_counts = nullptr;
+	} pend;
+	uint32_t *h_total = nullptr; // pinned
+	std::mutex pend_mu;
+	~Impl() {
+		if (h_total) cudaFreeHost(h_total);
+	}
 };
 
 static void shape_for(int dim, int metric, int &Kreal16, int &Kpad, int &nkb, int &ksteps_last) {
@@ -216,8 +235,9 @@ static GemmPlan plan_gemm(int tilesQ, int nkb, int num_sms) {
 void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, const float *d_queries, int nq_total, int k,
                       const uint32_t *d_allow, long long allow_bits, long long label_base, int64_t *d_out_labels,
                       float *d_out_dist, int32_t *d_out_counts, Workspace &ws, cudaStream_t s, int64_t *launches,
-                      int64_t *fallback_queries, KernelTimer *timer) {
+                      int64_t *fallback_queries, KernelTimer *timer, bool defer) {
 	Impl &im = *impl_;
+	finish(ws, launches, fallback_queries); // a previous deferred check still uses the scratch buffers
 	const int d = im.dim, Kpad = im.Kpad;
 	if (!im.attr_set) {
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
@@ -325,31 +345,86 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		LB_CUDA(cudaGetLastError());
 		(*launches) += 2;
 
-		// overflowed lists (degenerate data) -> exact fp32 scan for those queries.  One small read-back per pass.
+		// overflowed lists (degenerate data) -> exact fp32 scan for those queries.  One small read-back per pass,
+		// which the caller may defer to finish() when the whole batch is a single pass.
+		const bool last_pass = q0 + nq >= nq_total;
+		if (defer && q0 == 0 && last_pass) {
+			std::lock_guard<std::mutex> g(im.pend_mu);
+			if (!im.pend.active) {
+				if (!im.h_total) LB_CUDA(cudaMallocHost(&im.h_total, 16));
+				*im.h_total = 0;
+				LB_CUDA(cudaMemcpyAsync(im.h_total, total, 4, cudaMemcpyDeviceToHost, s));
+				Impl::Pending &pd = im.pend;
+				pd.active = true, pd.s = s, pd.X = X, pd.Q = Qchunk, pd.n = n, pd.allow_bits = allow_bits, pd.label_base = label_base;
+				pd.deleted = deleted, pd.allow = d_allow, pd.flag_out = flag_out, pd.total = total, pd.nq = nq, pd.k = k;
+				pd.out_labels = d_out_labels, pd.out_dist = d_out_dist, pd.out_counts = d_out_counts;
+				return;
+			}
+		}
 		uint32_t h_total = 0;
 		LB_CUDA(cudaMemcpyAsync(&h_total, total, 4, cudaMemcpyDeviceToHost, s));
 		LB_CUDA(cudaStreamSynchronize(s));
-		if (h_total > 0) {
-			std::vector<uint32_t> hf(nq);
-			LB_CUDA(cudaMemcpyAsync(hf.data(), flag_out, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
-			LB_CUDA(cudaStreamSynchronize(s));
-			for (int q = 0; q < nq; q++) {
-				if (!hf[q]) continue;
-				FlatScanArgs a;
-				a.X = X, a.n = n, a.d = d, a.metric = im.metric;
-				a.dQ = Qchunk + (size_t)q * d;
-				a.nq = 1, a.k = k;
-				a.allow = d_allow, a.allow_bits = allow_bits, a.deleted = deleted, a.label_base = label_base;
-				a.out_labels = d_out_labels + (size_t)(q0 + q) * k;
-				a.out_dist = d_out_dist + (size_t)(q0 + q) * k;
-				a.out_counts = d_out_counts + q0 + q;
-				FlatScanPlan fp = plan_flat_scan(X, im.metric, d, k, 1, n, im.num_sms);
-				ws.work4.ensure(flat_scan_scratch_bytes(fp, k));
-				run_flat_scan(a, fp, ws.work4.p, s, launches);
-				(*fallback_queries)++;
-			}
-		}
+		if (h_total > 0)
+			rerun_flagged(X, n, deleted, Qchunk, nq, k, d_allow, allow_bits, label_base, d_out_labels + (size_t)q0 * k,
+			              d_out_dist + (size_t)q0 * k, d_out_counts + q0, flag_out, ws, s, launches, fallback_queries);
 	}
+}
+
+void FlatGemm::rerun_flagged(const float *X, long long n, const uint32_t *deleted, const float *Qchunk, int nq, int k,
+                             const uint32_t *d_allow, long long allow_bits, long long label_base, int64_t *d_out_labels,
+                             float *d_out_dist, int32_t *d_out_counts, const uint32_t *flag_out, Workspace &ws,
+                             cudaStream_t s, int64_t *launches, int64_t *fallback_queries) {
+	Impl &im = *impl_;
+	const int d = im.dim;
+	std::vector<uint32_t> hf(nq);
+	LB_CUDA(cudaMemcpyAsync(hf.data(), flag_out, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+	LB_CUDA(cudaStreamSynchronize(s));
+	for (int q = 0; q < nq; q++) {
+		if (!hf[q]) continue;
+		FlatScanArgs a;
+		a.X = X, a.n = n, a.d = d, a.metric = im.metric;
+		a.dQ = Qchunk + (size_t)q * d;
+		a.nq = 1, a.k = k;
+		a.allow = d_allow, a.allow_bits = allow_bits, a.deleted = deleted, a.label_base = label_base;
+		a.out_labels = d_out_labels + (size_t)q * k;
+		a.out_dist = d_out_dist + (size_t)q * k;
+		a.out_counts = d_out_counts + q;
+		FlatScanPlan fp = plan_flat_scan(X, im.metric, d, k, 1, n, im.num_sms);
+		ws.work4.ensure(flat_scan_scratch_bytes(fp, k));
+		run_flat_scan(a, fp, ws.work4.p, s, launches);
+		(*fallback_queries)++;
+	}
+}
+
+// Completes a deferred overflow check: waits for the stream, and if some candidate list overflowed re-runs those
+// queries with the exact scan (and waits again).  Returns the number of re-run queries; 0 and no wait when nothing
+// is pending.
+int FlatGemm::finish(Workspace &ws, int64_t *launches, int64_t *fallback_queries) {
+	Impl &im = *impl_;
+	Impl::Pending pd;
+	{
+		std::lock_guard<std::mutex> g(im.pend_mu);
+		if (!im.pend.active) return 0;
+		pd = im.pend;
+		im.pend.active = false;
+	}
+	LB_CUDA(cudaStreamSynchronize(pd.s));
+	if (*im.h_total == 0) return 0;
+	int64_t before = *fallback_queries;
+	rerun_flagged(pd.X, pd.n, pd.deleted, pd.Q, pd.nq, pd.k, pd.allow, pd.allow_bits, pd.label_base, pd.out_labels, pd.out_dist,
+	              pd.out_counts, pd.flag_out, ws, pd.s, launches, fallback_queries);
+	LB_CUDA(cudaStreamSynchronize(pd.s));
+	return (int)(*fallback_queries - before);
+}
+
+const uint32_t *FlatGemm::pending_total() const {
+	std::lock_guard<std::mutex> g(impl_->pend_mu);
+	return impl_->pend.active ? impl_->pend.total : nullptr;
+}
+
+bool FlatGemm::has_pending() const {
+	std::lock_guard<std::mutex> g(impl_->pend_mu);
+	return impl_->pend.active;
 }
 
 } // namespace lb

@@ -22,9 +22,19 @@ public:
 	void search(const float *X, long long n, const uint32_t *deleted, const float *d_queries, int nq, int k,
 	            const uint32_t *d_allow, long long allow_bits, long long label_base, int64_t *d_out_labels,
 	            float *d_out_dist, int32_t *d_out_counts, Workspace &ws, cudaStream_t s, int64_t *launches,
-	            int64_t *fallback_queries, KernelTimer *timer);
+	            int64_t *fallback_queries, KernelTimer *timer, bool defer = false);
+	// defer = true: when the batch is a single pass, the candidate-list overflow check (one 4-byte read-back and a
+	// stream synchronise) is left to finish(); until then the results of overflowed queries (degenerate data only)
+	// are not final and the caller's buffers must stay valid.
+	int finish(Workspace &ws, int64_t *launches, int64_t *fallback_queries);
+	bool has_pending() const;
+	const uint32_t *pending_total() const; // device word: number of overflowed queries of the pending search
 
 private:
+	void rerun_flagged(const float *X, long long n, const uint32_t *deleted, const float *Qchunk, int nq, int k,
+	                   const uint32_t *d_allow, long long allow_bits, long long label_base, int64_t *d_out_labels,
+	                   float *d_out_dist, int32_t *d_out_counts, const uint32_t *flag_out, Workspace &ws, cudaStream_t s,
+	                   int64_t *launches, int64_t *fallback_queries);
 	struct Impl;
 	Impl *impl_;
 };

@@ -117,6 +117,28 @@ __device__ __noinline__ void gemm_emit_chunk(const GemmParams &p, const uint32_t
 		}
 }
 
+// One hit of one lane (the sparse case: a warm threshold passes a few scores per query and segment).
+__device__ __noinline__ void gemm_emit(const GemmParams &p, int q, long long row, float score, uint2 *slots, int *count) {
+	if (row >= p.n_rows) return; // TMA zero-fill beyond the table
+	if (p.deleted && bit_test(p.deleted, row)) return;
+	if (p.allow && !(row < p.allow_bits && bit_test(p.allow, row))) return;
+	const uint2 e = make_uint2(__float_as_uint(score), (uint32_t)row);
+	if (!slots) {
+		uint32_t pos = atomicAdd(p.cnt + q, 1u);
+		if (pos < (uint32_t)p.CAP) p.cand[(size_t)q * p.CAP + pos] = e;
+		return;
+	}
+	int n = *count;
+	if (n == p.EB) {
+		const uint32_t pos = atomicAdd(p.cnt + q, (uint32_t)n);
+		for (int i = 0; i < n; i++)
+			if (pos + i < (uint32_t)p.CAP) p.cand[(size_t)q * p.CAP + pos + i] = slots[i * 128];
+		n = 0;
+	}
+	slots[n * 128] = e;
+	*count = n + 1;
+}
+
 __device__ __forceinline__ void tmem_wait_regs(uint32_t (&r)[32]) {
 	// tcgen05.wait::ld with the destination registers as in/out operands, so that no use is scheduled above it
 	asm volatile("tcgen05.wait::ld.sync.aligned;"
@@ -137,11 +159,31 @@ __device__ __forceinline__ void gemm_process_chunk(const GemmParams &p, const ui
 	float m4 = tc::fmax3(a[9], __uint_as_float(r[30]), __uint_as_float(r[31]));
 	float m = fmaxf(tc::fmax3(m1, m2, m3), m4);
 	if (m >= thr) {
-		// rare once the threshold is warm
-		uint32_t tmp[32];
+		// rare once the threshold is warm.  Few lanes here (the steady state: one query, one score): walk the triple
+		// maxima, a handful of instructions, because this epilogue is the kernel's critical path.  Many lanes (cold
+		// threshold, seed segment): the branch-free bulk routine, whose cost does not grow with the number of hits.
+		if (__popc(__activemask()) <= 4) {
 #pragma unroll
-		for (int c = 0; c < 32; c++) tmp[c] = r[c];
-		gemm_emit_chunk(p, tmp, thr, q, row0, eb.slots, eb.count);
+			for (int i = 0; i < 10; i++) {
+				if (a[i] >= thr) {
+#pragma unroll
+					for (int j = 0; j < 3; j++) {
+						const float v = __uint_as_float(r[3 * i + j]);
+						if (v >= thr) gemm_emit(p, q, row0 + 3 * i + j, v, eb.slots, eb.count);
+					}
+				}
+			}
+#pragma unroll
+			for (int i = 30; i < 32; i++) {
+				const float v = __uint_as_float(r[i]);
+				if (v >= thr) gemm_emit(p, q, row0 + i, v, eb.slots, eb.count);
+			}
+		} else {
+			uint32_t tmp[32];
+#pragma unroll
+			for (int c = 0; c < 32; c++) tmp[c] = r[c];
+			gemm_emit_chunk(p, tmp, thr, q, row0, eb.slots, eb.count);
+		}
 	}
 }
 

@@ -2,6 +2,8 @@
 #pragma once
 #include "common.cuh"
 
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -46,12 +48,14 @@ struct KernelTimer {
 	// sums and clears; the caller has synchronised the device
 	void read(double ms[KC_COUNT], int64_t n[KC_COUNT]) {
 		std::lock_guard<std::mutex> g(mu);
+		const bool dump = getenv("LANCE_B200_TIMER_DUMP") != nullptr; // per-launch durations on stderr (tuning aid)
 		for (int i = 0; i < KC_COUNT; i++) ms[i] = 0, n[i] = 0;
 		for (auto &r : recs) {
 			float t = 0.f;
 			if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) {
 				ms[r.cls] += t;
 				n[r.cls]++;
+				if (dump) fprintf(stderr, "[lance_b200 timer] class %d  %.3f us\n", r.cls, t * 1e3);
 			}
 			free_events.push_back(r.a);
 			free_events.push_back(r.b);
@@ -110,11 +114,12 @@ void fill_u64(u64 *p, long long n, u64 v, cudaStream_t s, int64_t *launches);
 // ------------------------------------------------------------------ store_kernels.cu
 void launch_set_bits(uint32_t *bitmap, const int64_t *d_rows, int count, long long nrows, cudaStream_t s,
                      int64_t *launches);
-// Final select over G gathered per-shard lists (labels, dists)[G][nq][k], counts[G][nq].  Keys carry the
-// index g*k+i, which orders ties like the label does because shard g holds a lower label range than
-// shard g+1 and every list is already (distance, label)-sorted.  scratch: (nq*G*k + nq*k) u64.
-void launch_merge_lists(const int64_t *labels, const float *dists, const int32_t *counts, int G, int nq, int k,
-                        u64 *scratch_keys, u64 *scratch_sel, int64_t *out_labels, float *out_dists,
-                        int32_t *out_counts, cudaStream_t s, int64_t *launches);
+// Final select over G gathered per-shard lists in one launch.  Shard g's labels / dists / counts start at
+// labels + g*ls, dists + g*ds, counts + g*cs (element strides): [G][nq][k] arrays (ls = ds = nq*k, cs = nq) or a
+// gathered buffer of per-rank packed records.  Keys carry the index g*k+i, which orders ties like the label does
+// because shard g holds a lower label range than shard g+1 and every list is already (distance, label)-sorted.
+void launch_merge_lists(const int64_t *labels, const float *dists, const int32_t *counts, long long ls, long long ds,
+                        long long cs, int G, int nq, int k, int64_t *out_labels, float *out_dists, int32_t *out_counts,
+                        cudaStream_t s, int64_t *launches);
 
 } // namespace lb

@@ -245,7 +245,7 @@ int64_t Store::get_all(int64_t *out_labels, float *out_vectors) {
 // ------------------------------------------------------------------ search
 void Store::search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
                           int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
-                          cudaStream_t s) {
+                          cudaStream_t s, bool defer, uint32_t *d_overflow) {
 	std::shared_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));
 	if (nq <= 0) return;
@@ -261,9 +261,37 @@ void Store::search_device(const float *d_queries, int nq, int k, int nprobes, in
 		ivfpq_search_locked(d_queries, nq, k, nprobes, refine, d_allow, allow_bits, d_out_labels, d_out_dist,
 		                    d_out_counts, *ws, s, nullptr, nullptr, nullptr);
 	else
-		flat_search_locked(d_queries, nq, k, d_allow, allow_bits, d_out_labels, d_out_dist, d_out_counts, *ws, s);
+		flat_search_locked(d_queries, nq, k, d_allow, allow_bits, d_out_labels, d_out_dist, d_out_counts, *ws, s, defer);
+	if (d_overflow) {
+		// number of queries whose result is not final until search_finish (0 on every path but a pending tcgen05 batch)
+		const uint32_t *t = (defer && flat_gemm_) ? flat_gemm_->pending_total() : nullptr;
+		if (t)
+			LB_CUDA(cudaMemcpyAsync(d_overflow, t, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+		else
+			LB_CUDA(cudaMemsetAsync(d_overflow, 0, sizeof(uint32_t), s));
+	}
 	std::lock_guard<std::mutex> g(stat_mu_);
 	searches_++;
+}
+
+// Completes an asynchronous device search (search_device with defer = true): waits for its stream and settles the
+// candidate-list overflow check.  Returns how many queries had to be re-run by the exact scan.
+int Store::search_finish(cudaStream_t s) {
+	std::shared_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	int rerun = 0;
+	if (flat_gemm_ && flat_gemm_->has_pending()) {
+		Workspace *ws = scratch_for(s);
+		std::lock_guard<std::mutex> wg(ws->mu);
+		int64_t launches = 0, fallback = 0;
+		rerun = flat_gemm_->finish(*ws, &launches, &fallback);
+		std::lock_guard<std::mutex> g(stat_mu_);
+		tc_fallback_ += fallback;
+		launches_ += launches;
+	} else {
+		LB_CUDA(cudaStreamSynchronize(s));
+	}
+	return rerun;
 }
 
 void Store::search_host(const float *queries, int nq, int k, int nprobes, int refine, const uint32_t *allow,
@@ -304,7 +332,7 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 
 void Store::flat_search_locked(const float *d_queries, int nq, int k, const uint32_t *d_allow, int64_t allow_bits,
                                int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts, Workspace &ws,
-                               cudaStream_t s) {
+                               cudaStream_t s, bool defer) {
 	int64_t launches = 0;
 	const int mode = flat_path_.load();
 	bool use_tc = false;
@@ -324,7 +352,7 @@ void Store::flat_search_locked(const float *d_queries, int nq, int k, const uint
 		}
 		int64_t fallback = 0;
 		flat_gemm_->search(X_.as<float>(), n_rows_, n_deleted_ > 0 ? deleted_.as<uint32_t>() : nullptr, d_queries, nq, k, d_allow, allow_bits,
-		                   label_base_, d_out_labels, d_out_dist, d_out_counts, ws, s, &launches, &fallback, &timer_);
+		                   label_base_, d_out_labels, d_out_dist, d_out_counts, ws, s, &launches, &fallback, &timer_, defer);
 		std::lock_guard<std::mutex> g(stat_mu_);
 		tc_batches_++;
 		tc_fallback_ += fallback;

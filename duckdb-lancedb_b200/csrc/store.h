@@ -72,7 +72,8 @@ public:
 	// everything on the device, enqueued on s
 	void search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
 	                   int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
-	                   cudaStream_t s);
+	                   cudaStream_t s, bool defer = false, uint32_t *d_overflow = nullptr);
+	int search_finish(cudaStream_t s);
 
 	// IVF_PQ (ivfpq.cu)
 	void create_index(int num_partitions, int num_sub_vectors);
@@ -101,7 +102,7 @@ private:
 	Workspace *scratch_for(cudaStream_t s); // work issued on one stream is ordered, so it can share scratch
 	void flat_search_locked(const float *d_queries, int nq, int k, const uint32_t *d_allow, int64_t allow_bits,
 	                        int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts, Workspace &ws,
-	                        cudaStream_t s);
+	                        cudaStream_t s, bool defer = false);
 	void ivfpq_search_locked(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
 	                         int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
 	                         Workspace &ws, cudaStream_t s, int32_t *d_dbg_parts, u64 *d_dbg_cand, int32_t *d_dbg_ncand);

@@ -1,5 +1,6 @@
 // store_kernels.cu — small bookkeeping kernels of the device store: tombstones, list merge plumbing.
 #include "kernels.h"
+#include "topk.cuh"
 
 namespace lb {
 
@@ -21,43 +22,77 @@ void launch_set_bits(uint32_t *bitmap, const int64_t *d_rows, int count, long lo
 	if (launches) (*launches)++;
 }
 
-__global__ void lists_to_keys_kernel(const float *dists, const int32_t *counts, int G, int nq, int k, u64 *keys) {
-	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-	long long total = (long long)nq * G * k;
-	if (t >= total) return;
-	int i = (int)(t % k);
-	int g = (int)((t / k) % G);
-	int q = (int)(t / ((long long)k * G));
-	bool ok = i < counts[(size_t)g * nq + q];
-	float d = dists[((size_t)g * nq + q) * k + i];
-	keys[t] = ok ? make_key(d, (uint32_t)(g * k + i)) : KEY_INVALID;
-}
-
-__global__ void gather_labels_kernel(const u64 *sel, const int64_t *labels, int G, int nq, int k, int64_t *out_labels) {
-	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= (long long)nq * k) return;
-	int q = (int)(t / k);
-	u64 key = sel[t];
-	if (key == KEY_INVALID) {
-		out_labels[t] = -1;
-		return;
+// Final select over G per-shard lists in ONE launch, one block per query.  labels/dists/counts of shard g start
+// at labels + g*ls, dists + g*ds, counts + g*cs (element strides), so both the [G][nq][k] layout and a gathered
+// buffer of per-rank packed records work.  Keys carry the index g*k+i in their low word.
+__global__ void __launch_bounds__(256) merge_lists_kernel(const int64_t *__restrict__ labels, const float *__restrict__ dists,
+                                                           const int32_t *__restrict__ counts, long long ls, long long ds,
+                                                           long long cs, int G, int nq, int k, int cap,
+                                                           int64_t *__restrict__ out_labels, float *__restrict__ out_dists,
+                                                           int32_t *__restrict__ out_counts) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	int *cnts = reinterpret_cast<int *>(smem_raw);
+	u64 *bufs = reinterpret_cast<u64 *>(smem_raw + 64);
+	const int nwarps = blockDim.x >> 5, warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	const int q = blockIdx.x;
+	const int m = G * k;
+	WarpSelect sel;
+	sel.init(bufs + (size_t)warp * cap, cap, k);
+	for (int i0 = warp * 32; i0 < m; i0 += nwarps * 32) {
+		const int i = i0 + lane;
+		bool ok = false;
+		u64 key = KEY_INVALID;
+		if (i < m) {
+			const int g = i / k, j = i - g * k;
+			ok = j < counts[(size_t)g * cs + q];
+			if (ok) key = make_key(dists[(size_t)g * ds + (size_t)q * k + j], (uint32_t)i);
+		}
+		sel.push(ok, key);
 	}
-	uint32_t idx = key_row(key);
-	int g = idx / k, i = idx % k;
-	out_labels[t] = labels[((size_t)g * nq + q) * k + i];
+	sel.finalize();
+	if (lane == 0) cnts[warp] = sel.cnt;
+	__syncthreads();
+	if (warp != 0) return;
+	for (int w = 1; w < nwarps; w++) {
+		const u64 *s2 = bufs + (size_t)w * cap;
+		const int c = cnts[w];
+		for (int i0 = 0; i0 < c; i0 += 32) {
+			const int i = i0 + lane;
+			sel.push(i < c, i < c ? s2[i] : KEY_INVALID);
+		}
+	}
+	sel.finalize();
+	for (int i = lane; i < k; i += 32) {
+		const bool ok = i < sel.cnt;
+		int64_t lab = -1;
+		float dd = __int_as_float(0x7F800000);
+		if (ok) {
+			const u64 key = sel.buf[i];
+			const int idx = (int)key_row(key), g = idx / k, j = idx - g * k;
+			lab = labels[(size_t)g * ls + (size_t)q * k + j];
+			dd = key_dist(key);
+		}
+		out_labels[(size_t)q * k + i] = lab;
+		out_dists[(size_t)q * k + i] = dd;
+	}
+	if (lane == 0) out_counts[q] = sel.cnt;
 }
 
-void launch_merge_lists(const int64_t *labels, const float *dists, const int32_t *counts, int G, int nq, int k,
-                        u64 *scratch_keys, u64 *scratch_sel, int64_t *out_labels, float *out_dists,
-                        int32_t *out_counts, cudaStream_t s, int64_t *launches) {
+void launch_merge_lists(const int64_t *labels, const float *dists, const int32_t *counts, long long ls, long long ds,
+                        long long cs, int G, int nq, int k, int64_t *out_labels, float *out_dists, int32_t *out_counts,
+                        cudaStream_t s, int64_t *launches) {
 	if (nq <= 0 || k <= 0) return;
-	long long total = (long long)nq * G * k;
-	lists_to_keys_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(dists, counts, G, nq, k, scratch_keys);
-	LB_CUDA(cudaGetLastError());
-	if (launches) (*launches)++;
-	launch_topk_merge(scratch_keys, nq, (long long)G * k, k, 0, nullptr, out_dists, out_counts, scratch_sel, s, launches);
-	long long outn = (long long)nq * k;
-	gather_labels_kernel<<<(unsigned)((outn + 255) / 256), 256, 0, s>>>(scratch_sel, labels, G, nq, k, out_labels);
+	const int cap = warpsel_cap(k);
+	int nwarps = 8;
+	while (nwarps > 1 && (nwarps / 2) * 32 >= G * k) nwarps >>= 1;
+	while (nwarps > 1 && 64 + (size_t)nwarps * cap * 8 > 200 * 1024) nwarps >>= 1;
+	const size_t smem = 64 + (size_t)nwarps * cap * 8;
+	if (smem > 200 * 1024) throw Error("k too large for the device merge");
+	if (smem > 48 * 1024)
+		LB_CUDA(cudaFuncSetAttribute(merge_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	merge_lists_kernel<<<nq, nwarps * 32, smem, s>>>(labels, dists, counts, ls, ds, cs, G, nq, k, cap, out_labels, out_dists,
+	                                                  out_counts);
 	LB_CUDA(cudaGetLastError());
 	if (launches) (*launches)++;
 }

@@ -20,29 +20,41 @@ def shard_range(rows: int, rank: int, world: int):
 
 
 class ShardGather:
-    """Preallocated gather buffers for one (nq, k) shape."""
+    """Preallocated gather buffers for one (nq, k) shape.
+
+    Every rank's result is ONE packed record [labels int64 nq*k | dists f32 nq*k | counts i32 nq | overflow i32]
+    (padded to 16 B); `L`, `D`, `C`, `O` are views into it, so the search writes its output straight into the record
+    and a single all_gather moves it.  `GL`, `GD`, `GC`, `GO` are strided views [world, ...] over the gathered records."""
 
     def __init__(self, world: int, nq: int, k: int, device, group=None):
         self.world, self.nq, self.k, self.group = world, nq, k, group
-        self.GL = torch.empty((world, nq, k), dtype=torch.int64, device=device)
-        self.GD = torch.empty((world, nq, k), dtype=torch.float32, device=device)
-        self.GC = torch.empty((world, nq), dtype=torch.int32, device=device)
+        lb, db, cb = nq * k * 8, nq * k * 4, nq * 4
+        self.rec_bytes = (lb + db + cb + 4 + 15) // 16 * 16
+        self.rec = torch.zeros(self.rec_bytes, dtype=torch.uint8, device=device)
+        self.L = self.rec[:lb].view(torch.int64).view(nq, k)
+        self.D = self.rec[lb:lb + db].view(torch.float32).view(nq, k)
+        self.C = self.rec[lb + db:lb + db + cb].view(torch.int32)
+        self.O = self.rec[lb + db + cb:lb + db + cb + 4].view(torch.int32)
+        self.all = torch.zeros((world, self.rec_bytes), dtype=torch.uint8, device=device)
+        self.GL = self.all[:, :lb].view(torch.int64).view(world, nq, k)
+        self.GD = self.all[:, lb:lb + db].view(torch.float32).view(world, nq, k)
+        self.GC = self.all[:, lb + db:lb + db + cb].view(torch.int32)
+        self.GO = self.all[:, lb + db + cb:lb + db + cb + 4].view(torch.int32)
         self.ML = torch.empty((nq, k), dtype=torch.int64, device=device)
         self.MD = torch.empty((nq, k), dtype=torch.float32, device=device)
         self.MC = torch.empty(nq, dtype=torch.int32, device=device)
 
-    def gather(self, labels: torch.Tensor, dists: torch.Tensor, counts: torch.Tensor):
-        """labels/dists [nq, k], counts [nq] of this rank -> (GL, GD, GC) with the rank as leading dimension."""
+    def gather(self, labels: torch.Tensor = None, dists: torch.Tensor = None, counts: torch.Tensor = None):
+        """This rank's lists (or, with no arguments, whatever was written into self.L/D/C) -> (GL, GD, GC), strided
+        views with the rank as leading dimension."""
+        if labels is not None and labels.data_ptr() != self.L.data_ptr():
+            self.L.copy_(labels)
+            self.D.copy_(dists)
+            self.C.copy_(counts)
         if self.world == 1:
-            self.GL[0].copy_(labels)
-            self.GD[0].copy_(dists)
-            self.GC[0].copy_(counts)
+            self.all[0].copy_(self.rec)
         else:
-            # output viewed as the concatenation along dim 0 (the form both NCCL and gloo accept)
-            w, nq, k = self.world, self.nq, self.k
-            dist.all_gather_into_tensor(self.GL.view(w * nq, k), labels.contiguous(), group=self.group)
-            dist.all_gather_into_tensor(self.GD.view(w * nq, k), dists.contiguous(), group=self.group)
-            dist.all_gather_into_tensor(self.GC.view(w * nq), counts.contiguous(), group=self.group)
+            dist.all_gather_into_tensor(self.all.view(-1), self.rec, group=self.group)
         return self.GL, self.GD, self.GC
 
     def gather_and_merge(self, labels, dists, counts, merge):
@@ -50,3 +62,45 @@ class ShardGather:
         GL, GD, GC = self.gather(labels, dists, counts)
         merge(GL, GD, GC, self.world, self.nq, self.k, self.ML, self.MD, self.MC)
         return self.ML, self.MD, self.MC
+
+
+class ShardedSearch:
+    """One rank's side of a sharded search step: local top-k on this rank's shard -> one all_gather of
+    the packed records -> device-side final select, all enqueued on one stream without a host synchronisation
+    (lance_b200_search_device_async).  `settle()` then waits for the stream and, if any shard reported an
+    overflowed candidate list (degenerate data), has every rank finish its search and repeats gather + select, so
+    the merged lists are exact on every rank."""
+
+    def __init__(self, pkg, handle, world: int, nq: int, k: int, device, device_index: int, group=None, merge=None):
+        self.pkg, self.h, self.world, self.nq, self.k, self.dev_index = pkg, handle, world, nq, k, device_index
+        self.g = ShardGather(world, nq, k, device, group)
+        self.merges = 0
+        self.stream = 0
+        if merge is not None:  # host-side select (CPU tests over gloo)
+            self._merge = merge
+
+    def _merge(self, GL, GD, GC, G, nq, k, ML, MD, MC):
+        self.pkg.merge_topk_strided_device(self.dev_index, GL.data_ptr(), GD.data_ptr(), GC.data_ptr(), GL.stride(0),
+                                           GD.stride(0), GC.stride(0), G, nq, k, ML.data_ptr(), MD.data_ptr(),
+                                           MC.data_ptr(), stream=self.stream)
+        self.merges += 1
+
+    def step(self, d_queries: int, stream: int, **search_kw):
+        g = self.g
+        self.stream = stream
+        self.h.search_device_async(d_queries, self.nq, self.k, g.L.data_ptr(), g.D.data_ptr(), g.C.data_ptr(),
+                                   stream=stream, d_overflow=g.O.data_ptr(), **search_kw)
+        return g.gather_and_merge(None, None, None, self._merge)
+
+    def settle(self) -> int:
+        """Host-side end of a step; returns how many queries any shard had to re-run (0 on non-degenerate data)."""
+        g = self.g
+        pending = int(g.GO.sum().item())  # waits for the stream
+        if pending == 0:
+            return 0
+        self.h.search_finish(self.stream)
+        g.O.zero_()
+        g.gather_and_merge(None, None, None, self._merge)
+        if g.rec.is_cuda:
+            torch.cuda.current_stream().synchronize()
+        return pending

@@ -116,6 +116,30 @@ int32_t lance_b200_search_device(void *handle, const float *d_queries, int32_t n
                                  int64_t *d_out_labels, float *d_out_distances, int32_t *d_out_counts, void *stream,
                                  char *err_buf, int err_buf_len);
 
+/* Same final select over a gathered buffer of per-rank packed records: shard g's lists start at
+ * d_labels + g*labels_stride, d_dists + g*dists_stride, d_counts + g*counts_stride (strides in elements), so one
+ * all_gather of [labels | dists | counts] per rank feeds it directly.  One kernel launch on `stream`. */
+int32_t lance_b200_merge_topk_strided_device(int32_t device, const int64_t *d_labels, const float *d_dists,
+                                             const int32_t *d_counts, int64_t labels_stride, int64_t dists_stride,
+                                             int64_t counts_stride, int32_t G, int32_t nq, int32_t k,
+                                             int64_t *d_out_labels, float *d_out_dists, int32_t *d_out_counts,
+                                             void *stream, char *err_buf, int err_buf_len);
+
+/* lance_b200_search_device without its one host synchronisation.  The batched flat path ends with a 4-byte
+ * read-back ("did any candidate list overflow?", degenerate data only) that lance_b200_search_device waits for;
+ * the _async form leaves it pending so that the caller can enqueue the multi-GPU gather and merge behind the
+ * search without a gap.  lance_b200_search_finish waits for `stream`, settles the check (re-running overflowed
+ * queries with the exact scan into the same output buffers, which must still be valid) and returns the number
+ * of re-run queries (0 = the results that were already consumed are final), or -1.  d_overflow (nullable, device)
+ * receives, in stream order, the number of queries whose result is not final yet, so a multi-GPU step can carry
+ * it through its gather and learn on every rank whether any shard has to be settled.  One pending search per
+ * handle; the next search on the handle settles a pending one first. */
+int32_t lance_b200_search_device_async(void *handle, const float *d_queries, int32_t nq, int32_t k, int32_t nprobes,
+                                       int32_t refine_factor, const uint32_t *d_allow, int64_t bitmap_bits,
+                                       int64_t *d_out_labels, float *d_out_distances, int32_t *d_out_counts,
+                                       uint32_t *d_overflow, void *stream, char *err_buf, int err_buf_len);
+int32_t lance_b200_search_finish(void *handle, void *stream, char *err_buf, int err_buf_len);
+
 /* Final select of the multi-GPU merge: G gathered per-shard lists
  * d_labels/d_dists [G][nq][k], d_counts [G][nq] -> one [nq][k] list.  Device buffers, on `stream`. */
 int32_t lance_b200_merge_topk_device(int32_t device, const int64_t *d_labels, const float *d_dists,

@@ -156,3 +156,51 @@ def test_tc_auto_mode_picks_tensor_path_for_batches(gpu):
         s1 = h.stats()
         assert s1["flat_tc_batches"] == s0["flat_tc_batches"] + 1
         assert s1["flat_simt_batches"] == s0["flat_simt_batches"] + 1
+
+
+def _async_search(h, Q, k):
+    """lance_b200_search_device_async + lance_b200_search_finish with device buffers; returns host arrays, the
+    overflow word the search wrote on-stream, and the number of queries finish re-ran."""
+    import torch
+
+    dev = torch.device("cuda", 0)
+    nq = Q.shape[0]
+    Qd = torch.from_numpy(Q).to(dev)
+    L = torch.full((nq, k), -7, dtype=torch.int64, device=dev)
+    D = torch.zeros((nq, k), dtype=torch.float32, device=dev)
+    C = torch.zeros(nq, dtype=torch.int32, device=dev)
+    O = torch.full((1,), 99, dtype=torch.int32, device=dev)
+    sp = torch.cuda.current_stream().cuda_stream
+    h.set_flat_path(2)
+    h.search_device_async(Qd.data_ptr(), nq, k, L.data_ptr(), D.data_ptr(), C.data_ptr(), stream=sp, d_overflow=O.data_ptr())
+    rerun = h.search_finish(sp)
+    h.set_flat_path(0)
+    return L.cpu().numpy(), D.cpu().numpy(), C.cpu().numpy(), int(O.item()), rerun
+
+
+def test_tc_async_search_and_finish_match_the_synchronous_call(gpu, oracle_mod):
+    n, d, k, nq = 70_000, 128, 10, 96
+    rng = np.random.default_rng(21)
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Q = rng.standard_normal((nq, d), dtype=np.float32)
+    with gpu.LanceHandle(d, "dot") as h:
+        h.add_batch(X)
+        L0, D0, C0, _ = tc_search(h, Q, k)
+        L, D, C, ovf, rerun = _async_search(h, Q, k)
+        assert ovf == 0 and rerun == 0
+        assert (L == L0).all() and (C == C0).all() and np.array_equal(D, D0)
+        assert h.search_finish(0) == 0  # nothing pending any more
+
+
+def test_tc_async_overflow_is_reported_and_settled_by_finish(gpu, oracle_mod):
+    n, d, k, nq = 70_000, 32, 5, 8
+    rng = np.random.default_rng(9)
+    base = rng.standard_normal((1, d), dtype=np.float32)
+    X = np.repeat(base, n, axis=0)
+    X[:100] = rng.standard_normal((100, d), dtype=np.float32) * 8.0 + 20.0
+    Q = base + 0.1 * rng.standard_normal((nq, d), dtype=np.float32)
+    with gpu.LanceHandle(d, "l2") as h:
+        h.add_batch(X)
+        L, D, C, ovf, rerun = _async_search(h, Q, k)
+        assert ovf > 0 and rerun == ovf
+        check_oracle(oracle_mod, X, Q, L, D, C, k, "l2", what="tc async ties")

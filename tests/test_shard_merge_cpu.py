@@ -73,6 +73,73 @@ def _worker(rank, world, port, n, d, nq, k, metric, outdir):
     dist.destroy_process_group()
 
 
+class _StubHandle:
+    """Stands in for LanceHandle on CPU: the asynchronous search of rank `bad_rank` reports an overflowed query and
+    leaves a wrong list for it until search_finish repairs it (what FlatGemm::finish does on the device)."""
+
+    def __init__(self, rank, bad_rank, L, D, C, sg):
+        self.rank, self.bad, self.Lt, self.Dt, self.Ct, self.sg = rank, bad_rank, L, D, C, sg
+        self.finished = 0
+
+    def search_device_async(self, d_queries, nq, k, d_labels, d_dist, d_counts, stream=0, d_overflow=0, **kw):
+        self.sg.L.copy_(self.Lt)
+        self.sg.D.copy_(self.Dt)
+        self.sg.C.copy_(self.Ct)
+        self.sg.O.zero_()
+        if self.rank == self.bad:
+            self.sg.C[1] = 0  # query 1 not final yet
+            self.sg.O[0] = 1
+
+    def search_finish(self, stream=0):
+        self.finished += 1
+        if self.rank == self.bad:
+            self.sg.C[1] = self.Ct[1]
+            return 1
+        return 0
+
+
+def _settle_worker(rank, world, port, outdir):
+    import importlib
+    import torch
+    import torch.distributed as dist
+
+    sys.path.insert(0, ROOT)
+    from __graft_entry__ import load_package
+
+    load_package()
+    sharding = importlib.import_module("duckdb_lancedb_b200.sharding")
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    nq, k = 3, 4
+    # shard r holds distances r + 0.1*i, labels 100*r + i
+    L = torch.tensor([[100 * rank + i for i in range(k)]] * nq, dtype=torch.int64)
+    D = torch.tensor([[rank + 0.1 * i for i in range(k)]] * nq, dtype=torch.float32)
+    C = torch.full((nq,), k, dtype=torch.int32)
+
+    def merge(GL, GD, GC, G, nq_, k_, ML, MD, MC):
+        for j in range(nq_):
+            ents = sorted((float(GD[g, j, i]), int(GL[g, j, i])) for g in range(G) for i in range(int(GC[g, j])))[:k_]
+            MC[j] = len(ents)
+            for i, (dd, ll) in enumerate(ents):
+                ML[j, i], MD[j, i] = ll, dd
+
+    ss = sharding.ShardedSearch(None, None, world, nq, k, torch.device("cpu"), 0, merge=merge)
+    ss.h = _StubHandle(rank, 0, L, D, C, ss.g)
+    ML, MD, MC = ss.step(0, 0)
+    stale = ML.clone()
+    n = ss.settle()
+    assert n == 1 and ss.h.finished == 1  # every rank settles, also the ones without an overflow of their own
+    assert stale[1].tolist() == [100, 101, 102, 103]  # before: shard 0's list for query 1 was missing
+    assert ML[1].tolist() == [0, 1, 2, 3] and ML[0].tolist() == [0, 1, 2, 3]
+    assert ss.settle() == 0
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_step_settles_overflowed_shard(pkg, tmp_path):
+    port = _free_port()
+    mp.spawn(_settle_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+
+
 @pytest.mark.parametrize("world,metric", [(2, "l2"), (2, "dot"), (3, "cosine")])
 def test_sharded_search_equals_single_shard(oracle_mod, tmp_path, world, metric):
     n, d, nq, k = 3001, 16, 6, 10
