@@ -266,8 +266,14 @@ def run_b200(args, wl):
             raise SystemExit("launch N>1 with torchrun: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    saved_stdout = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL writes its version banner to stdout; stdout must carry exactly one JSON line, so point fd 1 at
+        # stderr until that line is printed
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     pkg.set_default_device(local)
     peaks = load_peaks()
@@ -478,7 +484,10 @@ def run_b200(args, wl):
                           "tc_fallback_queries": st1["tc_fallback_queries"] - st0["tc_fallback_queries"],
                           "ivfpq_batches": st1["ivfpq_batches"] - st0["ivfpq_batches"]},
                 "profile_ms": {kk: vv for kk, vv in prof.items()}}
-        print(json.dumps(line))
+        if saved_stdout is not None:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+        print(json.dumps(line), flush=True)
     h.close()
     if world > 1:
         dist.destroy_process_group()

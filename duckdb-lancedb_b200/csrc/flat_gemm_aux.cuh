@@ -111,31 +111,47 @@ __global__ void __launch_bounds__(256) refresh_threshold_kernel(uint2 *__restric
 	if (c < k) return; // fewer than k live candidates so far: keep everything, threshold stays
 	uint2 *list = cand + (size_t)q * CAP;
 	u64 *bufs = reinterpret_cast<u64 *>(smem_raw);
-	WarpSelect sel;
-	sel.init(bufs + (size_t)warp * cap, cap, k);
-	for (int i0 = warp * 32; i0 < c; i0 += 256) {
-		int i = i0 + lane;
-		float sc = i < c ? __uint_as_float(list[i].x) : 0.f;
-		sel.push(i < c, make_key(-sc, (uint32_t)i));
-	}
-	sel.finalize();
-	if (lane == 0) cnts[warp] = sel.cnt;
-	__syncthreads();
-	if (warp == 0) {
-		for (int w = 1; w < 8; w++) {
-			const u64 *s2 = bufs + (size_t)w * cap;
-			const int cw = cnts[w];
-			for (int i0 = 0; i0 < cw; i0 += 32) {
-				int i = i0 + lane;
-				sel.push(i < cw, i < cw ? s2[i] : KEY_INVALID);
-			}
-		}
-		sel.finalize();
-		if (lane == 0) {
-			float ak = -key_dist(sel.buf[k - 1]);
+	if (c <= 8 * cap) {
+		// short list (every refresh but the one after the seed segment): one block-wide sort instead of per-warp
+		// selection plus a serial fold — this kernel runs once per segment and its latency is pure overhead
+		int n = 64;
+		while (n < c) n <<= 1;
+		for (int i = threadIdx.x; i < n; i += 256)
+			bufs[i] = i < c ? make_key(-__uint_as_float(list[i].x), (uint32_t)i) : KEY_INVALID;
+		block_bitonic_sort(bufs, n, IdentityMap());
+		if (threadIdx.x == 0) {
+			float ak = -key_dist(bufs[k - 1]);
 			float t = ak - margin[q];
 			s_thr = fmaxf(t, thr[q]);
 			s_base = 0;
+		}
+	} else {
+		WarpSelect sel;
+		sel.init(bufs + (size_t)warp * cap, cap, k);
+		for (int i0 = warp * 32; i0 < c; i0 += 256) {
+			int i = i0 + lane;
+			float sc = i < c ? __uint_as_float(list[i].x) : 0.f;
+			sel.push(i < c, make_key(-sc, (uint32_t)i));
+		}
+		sel.finalize();
+		if (lane == 0) cnts[warp] = sel.cnt;
+		__syncthreads();
+		if (warp == 0) {
+			for (int w = 1; w < 8; w++) {
+				const u64 *s2 = bufs + (size_t)w * cap;
+				const int cw = cnts[w];
+				for (int i0 = 0; i0 < cw; i0 += 32) {
+					int i = i0 + lane;
+					sel.push(i < cw, i < cw ? s2[i] : KEY_INVALID);
+				}
+			}
+			sel.finalize();
+			if (lane == 0) {
+				float ak = -key_dist(sel.buf[k - 1]);
+				float t = ak - margin[q];
+				s_thr = fmaxf(t, thr[q]);
+				s_base = 0;
+			}
 		}
 	}
 	__syncthreads();

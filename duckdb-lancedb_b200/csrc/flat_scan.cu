@@ -139,8 +139,8 @@ __device__ __forceinline__ unsigned live_mask8(long long row0, long long row_beg
 	return m & 0xFFu;
 }
 
-static constexpr int SCAN_MAXG = 16;       // groups of the two-level final select
-static constexpr int SCAN_HDR_WORDS = 64;  // u64 words of control state in front of the lists
+static constexpr int SCAN_MAXG = 32;       // groups of the two-level final select
+static constexpr int SCAN_HDR_WORDS = 128; // u64 words of control state in front of the lists
 
 template <int METRIC, int QB, int VEC>
 __global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_scan_kernel(const float *__restrict__ X, long long row_begin, long long n,
@@ -250,44 +250,36 @@ __global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_s
 	}
 
 #pragma unroll
+	for (int j = 0; j < QB; j++) sel[j].pad();
+	// block merge: one block-wide sort per query over the warps' buffers (query j's buffers are QB*cap apart);
+	// afterwards the block's k best keys of query j are the first k entries of warp 0's buffer j
+#pragma unroll
 	for (int j = 0; j < QB; j++) {
-		sel[j].finalize();
-		if (lane == 0) cnts[warp * QB + j] = sel[j].cnt;
+		const int lc = 31 - __clz(cap);
+		block_bitonic_sort(bufs, nwarps * cap, [=](int i) { return (((i >> lc) * QB + j) << lc) + (i & (cap - 1)); });
 	}
-	__syncthreads();
-	// block merge: warp (j % nwarps) folds the other warps' lists of query j into its own
 #pragma unroll
 	for (int j = 0; j < QB; j++) {
 		if (warp != (j % nwarps)) continue;
-		for (int w = 0; w < nwarps; w++) {
-			if (w == warp) continue;
-			const u64 *src = bufs + ((size_t)w * QB + j) * cap;
-			const int c = cnts[w * QB + j];
-			for (int i0 = 0; i0 < c; i0 += 32) {
-				int i = i0 + lane;
-				u64 key = (i < c) ? src[i] : KEY_INVALID;
-				sel[j].push(i < c, key);
-			}
-		}
-		sel[j].finalize();
+		const u64 *mine = bufs + (size_t)j * cap;
 		// publish this block's k-th best, then write only what can still make the global top-k: every
 		// block's k-th best bounds the global k-th best from above, so keys beyond g_tau are dead already
-		if (sel[j].cnt == k) {
-			if (lane == 0) atomicMin(g_tau + j, sel[j].tau);
+		if (mine[k - 1] != KEY_INVALID) {
+			if (lane == 0) atomicMin(g_tau + j, mine[k - 1]);
 			__syncwarp();
 		}
 		// append only what can still make the global top-k (a sorted prefix) to query j's shared list
 		const u64 gt = *reinterpret_cast<volatile u64 *>(g_tau + j);
 		int npass = 0;
-		for (int i0 = 0; i0 < sel[j].cnt; i0 += 32) {
+		for (int i0 = 0; i0 < k; i0 += 32) {
 			int i = i0 + lane;
-			npass += __popc(__ballot_sync(0xFFFFFFFFu, i < sel[j].cnt && sel[j].buf[i] <= gt));
+			npass += __popc(__ballot_sync(0xFFFFFFFFu, i < k && mine[i] != KEY_INVALID && mine[i] <= gt));
 		}
 		unsigned base = 0;
 		if (lane == 0 && npass > 0) base = atomicAdd(ctl + j * SCAN_MAXG + grp, (unsigned)npass) + 1u; // counters start at 0xFFFFFFFF
 		base = __shfl_sync(0xFFFFFFFFu, base, 0);
 		u64 *dst = partials + ((size_t)j * G + grp) * gcap + base;
-		for (int i = lane; i < npass; i += 32) dst[i] = sel[j].buf[i];
+		for (int i = lane; i < npass; i += 32) dst[i] = mine[i];
 	}
 	// Two-level final select without a second launch: the last block of each group reduces the group's list to k
 	// keys (the groups finish together, so these run in parallel on G SMs); the last group then selects the result.
@@ -384,6 +376,11 @@ FlatScanPlan plan_flat_scan(const float *X, int metric, int d, int k, int nq, lo
 			            " is too large for the device scan");
 		QB >>= 1;
 		nwarps = 8;
+	}
+	// small tables (the IVF centroid table, C1-sized shards): narrower blocks, so that every SM gets work
+	{
+		const long long ngroups_all = (n + 7) / 8;
+		while (nwarps > 2 && ngroups_all / nwarps < 2ll * num_sms) nwarps >>= 1;
 	}
 	p.QB = QB;
 	p.nwarps = nwarps;

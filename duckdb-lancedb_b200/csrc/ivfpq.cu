@@ -346,22 +346,11 @@ __global__ void __launch_bounds__(256) adc_scan_kernel(const __grid_constant__ A
 		}
 	}
 	if (!lut_ready) tc::mbar_wait(bar, 0); // the copy must land before the CTA may exit
-	sel.finalize();
-	if (lane == 0) cnts[warp] = sel.cnt;
-	__syncthreads();
+	sel.pad();
+	block_bitonic_sort(bufs, nwarps * cap, IdentityMap()); // the CTA's kc best = the first kc keys
 	if (warp == 0) {
-		for (int w = 1; w < nwarps; w++) {
-			const u64 *src = bufs + (size_t)w * cap;
-			const int c = cnts[w];
-			for (int i0 = 0; i0 < c; i0 += 32) {
-				int i = i0 + lane;
-				u64 key = (i < c) ? src[i] : KEY_INVALID;
-				sel.push(i < c, key);
-			}
-		}
-		sel.finalize();
 		u64 *dst = p.partials + ((size_t)q * S + s) * kc;
-		for (int i = lane; i < kc; i += 32) dst[i] = (i < sel.cnt) ? sel.buf[i] : KEY_INVALID;
+		for (int i = lane; i < kc; i += 32) dst[i] = bufs[i];
 	}
 	// the last CTA of the query selects its kc best ADC candidates, refines them and (no unindexed tail) sorts the
 	// final top-k: one launch instead of scan + merge + refine + merge

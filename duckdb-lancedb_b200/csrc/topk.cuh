@@ -94,52 +94,89 @@ struct WarpSelect {
 	}
 
 	__device__ inline void finalize() { compact(); }
+
+	// Leaves the buffered keys as they are (unsorted, possibly more than k) and fills the rest of the buffer with
+	// KEY_INVALID, so that a block-wide sort over all the warps' buffers can take over.
+	__device__ inline void pad() {
+		__syncwarp();
+		for (int i = cnt + lane_id(); i < cap; i += 32) buf[i] = KEY_INVALID;
+		__syncwarp();
+	}
 };
+
+// Ascending bitonic sort of n keys (n = power of two) by the whole block; key i lives at base[map(i)].  All threads
+// call it.  Replaces "one warp folds the other warps' lists in" at the end of every scan: with 8 warps x cap keys
+// that fold was the longest serial stretch of the small-table scans (ncu: 1/3 of the C1 kernel spent at its barrier).
+struct IdentityMap {
+	__device__ __forceinline__ int operator()(int i) const { return i; }
+};
+template <class Map>
+__device__ inline void block_bitonic_sort(u64 *base, int n, Map map) {
+	__syncthreads();
+	for (int size = 2; size <= n; size <<= 1) {
+		for (int stride = size >> 1; stride > 0; stride >>= 1) {
+			for (int i = threadIdx.x; i < (n >> 1); i += blockDim.x) {
+				const int pos = 2 * i - (i & (stride - 1));
+				const int pa = map(pos), pb = map(pos + stride);
+				const bool up = ((pos & size) == 0);
+				const u64 a = base[pa], b = base[pb];
+				if ((a > b) == up) {
+					base[pa] = b;
+					base[pb] = a;
+				}
+			}
+			__syncthreads();
+		}
+	}
+}
 
 // Final select by a whole block: src[0..m) keys (KEY_INVALID entries ignored, read through L2 because other
 // SMs may have written them) -> sorted (label, distance) list of query slot `q`.  All threads of the block
-// call it; bufs = nwarps*cap keys and cnts = nwarps ints of shared memory.
+// call it; bufs = nwarps*cap keys of shared memory (cnts is unused, kept for the callers' layouts).
 __device__ inline void block_final_select(const u64 *__restrict__ src, long long m, int k, int cap, u64 *bufs, int *cnts,
                                           long long label_base, size_t q, int64_t *__restrict__ out_labels,
                                           float *__restrict__ out_dist, int32_t *__restrict__ out_counts,
                                           u64 *__restrict__ out_keys) {
+	(void)cnts;
 	const int nwarps = blockDim.x >> 5;
 	const int warp = threadIdx.x >> 5;
 	const unsigned lane = lane_id();
-	WarpSelect sel;
-	sel.init(bufs + (size_t)warp * cap, cap, k);
-	for (long long i0 = (long long)warp * 128; i0 < m; i0 += (long long)nwarps * 128) {
-		u64 key[4];
+	if (m <= (long long)nwarps * cap) {
+		// short list (the usual case for the in-kernel two-level selects): straight into shared memory, one sort
+		int n = 64;
+		while (n < (int)m || n < k) n <<= 1;
+		for (int i = threadIdx.x; i < n; i += blockDim.x) bufs[i] = i < (int)m ? __ldcg(src + i) : KEY_INVALID;
+		block_bitonic_sort(bufs, n, IdentityMap());
+	} else {
+		WarpSelect sel;
+		sel.init(bufs + (size_t)warp * cap, cap, k);
+		for (long long i0 = (long long)warp * 128; i0 < m; i0 += (long long)nwarps * 128) {
+			u64 key[4];
 #pragma unroll
-		for (int u = 0; u < 4; u++) {
-			long long i = i0 + u * 32 + lane;
-			key[u] = (i < m) ? __ldcg(src + i) : KEY_INVALID;
+			for (int u = 0; u < 4; u++) {
+				long long i = i0 + u * 32 + lane;
+				key[u] = (i < m) ? __ldcg(src + i) : KEY_INVALID;
+			}
+#pragma unroll
+			for (int u = 0; u < 4; u++) sel.push(key[u] != KEY_INVALID, key[u]);
 		}
-#pragma unroll
-		for (int u = 0; u < 4; u++) sel.push(key[u] != KEY_INVALID, key[u]);
+		sel.pad();
+		block_bitonic_sort(bufs, nwarps * cap, IdentityMap());
 	}
-	sel.finalize();
-	if (lane == 0) cnts[warp] = sel.cnt;
-	__syncthreads();
 	if (warp == 0) {
-		for (int w = 1; w < nwarps; w++) {
-			const u64 *s2 = bufs + (size_t)w * cap;
-			const int c = cnts[w];
-			for (int i0 = 0; i0 < c; i0 += 32) {
-				int i = i0 + lane;
-				u64 key = (i < c) ? s2[i] : KEY_INVALID;
-				sel.push(i < c, key);
+		int cnt = 0;
+		for (int i0 = 0; i0 < k; i0 += 32) {
+			const int i = i0 + lane;
+			const bool ok = i < k && bufs[i] != KEY_INVALID;
+			const u64 key = ok ? bufs[i] : KEY_INVALID;
+			cnt += __popc(__ballot_sync(0xFFFFFFFFu, ok));
+			if (i < k) {
+				if (out_labels) out_labels[q * k + i] = ok ? (int64_t)(label_base + (long long)key_row(key)) : -1;
+				if (out_dist) out_dist[q * k + i] = ok ? key_dist(key) : __int_as_float(0x7F800000);
+				if (out_keys) out_keys[q * k + i] = key;
 			}
 		}
-		sel.finalize();
-		for (int i = lane; i < k; i += 32) {
-			bool ok = i < sel.cnt;
-			u64 key = ok ? sel.buf[i] : KEY_INVALID;
-			if (out_labels) out_labels[q * k + i] = ok ? (int64_t)(label_base + (long long)key_row(key)) : -1;
-			if (out_dist) out_dist[q * k + i] = ok ? key_dist(key) : __int_as_float(0x7F800000);
-			if (out_keys) out_keys[q * k + i] = key;
-		}
-		if (lane == 0 && out_counts) out_counts[q] = sel.cnt;
+		if (lane == 0 && out_counts) out_counts[q] = cnt;
 	}
 	__syncthreads();
 }
