@@ -248,6 +248,7 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(refresh_threshold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 		LB_CUDA(cudaFuncSetAttribute(rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
+		LB_CUDA(cudaFuncSetAttribute(rerank_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 		im.attr_set = true;
 	}
 	const int cap = warpsel_cap(k);
@@ -335,9 +336,19 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 			seg *= growth;
 		}
 		int tix = timer ? timer->begin(KC_RERANK, s) : -1;
-		rerank_kernel<<<nq, 256, sel_smem, s>>>(X, d, im.metric, Qchunk, cand, TC_CAP, cnt, flag, k, cap, label_base,
-		                                        d_out_labels + (size_t)q0 * k, d_out_dist + (size_t)q0 * k,
-		                                        d_out_counts + q0);
+		if (nq >= 2 * im.num_sms) {
+			rerank_kernel<<<nq, 256, sel_smem, s>>>(X, d, im.metric, Qchunk, cand, TC_CAP, cnt, flag, k, cap, label_base,
+			                                        d_out_labels + (size_t)q0 * k, d_out_dist + (size_t)q0 * k,
+			                                        d_out_counts + q0);
+		} else {
+			const int T = std::min(32, (2 * im.num_sms + nq - 1) / nq);
+			rerank_dist_kernel<<<dim3(nq, T), 256, 0, s>>>(X, d, im.metric, Qchunk, cand, TC_CAP, cnt, flag);
+			LB_CUDA(cudaGetLastError());
+			rerank_select_kernel<<<nq, 256, sel_smem, s>>>(cand, TC_CAP, cnt, flag, k, cap, label_base,
+			                                               d_out_labels + (size_t)q0 * k, d_out_dist + (size_t)q0 * k,
+			                                               d_out_counts + q0);
+			(*launches)++;
+		}
 		LB_CUDA(cudaGetLastError());
 		if (timer) timer->end(tix, s);
 		LB_CUDA(cudaMemsetAsync(total, 0, 4, s));

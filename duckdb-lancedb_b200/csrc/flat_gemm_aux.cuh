@@ -2,6 +2,7 @@
 // bf16 shadow of the table, bf16 query tiles + error margins, threshold refresh / list compaction between
 // row segments, and the exact fp32 re-rank that produces the returned (label, distance) lists.
 #pragma once
+#include "exact.cuh"
 #include <cuda_bf16.h>
 
 #include "topk.cuh"
@@ -13,10 +14,6 @@ namespace lb {
 // the tensor core; 2^-8 = 0.00390625, the rest is slack.
 static constexpr float GEMM_ERR_C = 0.0041f;
 
-__device__ __forceinline__ float warp_sum(float v) {
-	for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
-	return v;
-}
 
 // ------------------------------------------------------------------ shadow rows
 // One warp per row: Xs[row] = bf16 of  x (dot) | x/|x| (cosine) | [x, -|x|^2/2 as three bf16 terms] (l2),
@@ -185,51 +182,7 @@ __global__ void __launch_bounds__(256) refresh_threshold_kernel(uint2 *__restric
 	}
 }
 
-// ------------------------------------------------------------------ exact re-rank
-// exact distance of (q, x) by one warp, in the reference's reported units (same formulas as flat_scan.cu)
-__device__ __forceinline__ float warp_exact_distance(int metric, const float *__restrict__ q, const float *__restrict__ x,
-                                                     int d, bool vec4) {
-	const unsigned lane = lane_id();
-	float acc = 0.f, nx = 0.f, nq = 0.f;
-	if (vec4) {
-		const float4 *q4 = reinterpret_cast<const float4 *>(q), *x4 = reinterpret_cast<const float4 *>(x);
-		for (int c = lane; c < (d >> 2); c += 32) {
-			float4 a = __ldg(q4 + c), b = __ldg(x4 + c);
-			if (metric == METRIC_L2) {
-				float e0 = a.x - b.x, e1 = a.y - b.y, e2 = a.z - b.z, e3 = a.w - b.w;
-				acc = fmaf(e0, e0, acc), acc = fmaf(e1, e1, acc), acc = fmaf(e2, e2, acc), acc = fmaf(e3, e3, acc);
-			} else {
-				acc = fmaf(a.x, b.x, acc), acc = fmaf(a.y, b.y, acc), acc = fmaf(a.z, b.z, acc), acc = fmaf(a.w, b.w, acc);
-				if (metric == METRIC_COSINE) {
-					nx = fmaf(b.x, b.x, nx), nx = fmaf(b.y, b.y, nx), nx = fmaf(b.z, b.z, nx), nx = fmaf(b.w, b.w, nx);
-					nq = fmaf(a.x, a.x, nq), nq = fmaf(a.y, a.y, nq), nq = fmaf(a.z, a.z, nq), nq = fmaf(a.w, a.w, nq);
-				}
-			}
-		}
-	} else {
-		for (int c = lane; c < d; c += 32) {
-			float a = __ldg(q + c), b = __ldg(x + c);
-			if (metric == METRIC_L2) {
-				float e = a - b;
-				acc = fmaf(e, e, acc);
-			} else {
-				acc = fmaf(a, b, acc);
-				nx = fmaf(b, b, nx);
-				nq = fmaf(a, a, nq);
-			}
-		}
-	}
-	acc = warp_sum(acc);
-	if (metric == METRIC_L2) return acc;
-	if (metric == METRIC_DOT) return 1.0f - acc;
-	nx = warp_sum(nx);
-	nq = warp_sum(nq);
-	float den = sqrtf(nq) * sqrtf(nx);
-	if (!(den > 0.f)) return 1.0f;
-	float sim = fminf(1.f, fmaxf(-1.f, acc / den));
-	return 1.0f - sim;
-}
-
+// ------------------------------------------------------------------ exact re-rank (warp_exact_distance: exact.cuh)
 // One block per query: exact fp32 distance of every surviving candidate, fused top-k, sorted output.
 __global__ void __launch_bounds__(256) rerank_kernel(const float *__restrict__ X, int d, int metric,
                                                      const float *__restrict__ Q, const uint2 *__restrict__ cand, int CAP,
@@ -281,6 +234,39 @@ __global__ void __launch_bounds__(256) rerank_kernel(const float *__restrict__ X
 		out_dist[(size_t)q * k + i] = ok ? key_dist(key) : __int_as_float(0x7F800000);
 	}
 	if (lane == 0) out_counts[q] = sel.cnt;
+}
+
+// Small batches: the same re-rank in two launches, so that the exact distances of one query's candidates are
+// spread over T blocks instead of being computed by a single one (64 queries would use 64 of the 148 SMs).
+// Phase 1, grid (nq, T): candidate i of query q -> (exact distance, row) key, written over the candidate in place.
+__global__ void __launch_bounds__(256) rerank_dist_kernel(const float *__restrict__ X, int d, int metric,
+                                                          const float *__restrict__ Q, uint2 *__restrict__ cand, int CAP,
+                                                          const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ flag) {
+	const int q = blockIdx.x;
+	const int warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	if (flag[q] != 0 || cnt[q] > (uint32_t)CAP) return;
+	const int c = (int)cnt[q];
+	uint2 *list = cand + (size_t)q * CAP;
+	const float *qv = Q + (size_t)q * d;
+	const bool vec4 = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0) && ((reinterpret_cast<uintptr_t>(Q) & 15) == 0);
+	for (int i = blockIdx.y * 8 + warp; i < c; i += gridDim.y * 8) {
+		const uint32_t row = list[i].y;
+		const float dist = warp_exact_distance(metric, qv, X + (size_t)row * d, d, vec4);
+		if (lane == 0) reinterpret_cast<u64 *>(list)[i] = make_key(dist, row);
+	}
+}
+// Phase 2, one block per query: top-k of the keys.
+__global__ void __launch_bounds__(256) rerank_select_kernel(const uint2 *__restrict__ cand, int CAP, const uint32_t *__restrict__ cnt,
+                                                            const uint32_t *__restrict__ flag, int k, int cap, long long label_base,
+                                                            int64_t *__restrict__ out_labels, float *__restrict__ out_dist,
+                                                            int32_t *__restrict__ out_counts) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	const int q = blockIdx.x;
+	const bool bad = flag[q] != 0 || cnt[q] > (uint32_t)CAP;
+	const int c = bad ? 0 : (int)cnt[q];
+	block_final_select(reinterpret_cast<const u64 *>(cand + (size_t)q * CAP), c, k, cap, reinterpret_cast<u64 *>(smem_raw), nullptr,
+	                   label_base, (size_t)q, out_labels, out_dist, out_counts, nullptr);
 }
 
 // number of flagged queries -> *out (read by the host to run the exact scan for them)

@@ -27,6 +27,7 @@
 #include <cmath>
 #include <cstring>
 
+#include "exact.cuh"
 #include "tc_ptx.cuh"
 #include "topk.cuh"
 
@@ -175,40 +176,9 @@ __device__ __forceinline__ float lut4(const float *lut_m, uint32_t w) {
 __device__ __forceinline__ u64 warp_exact_key(const float *__restrict__ X, int d, const float *__restrict__ qv, int metric,
                                               u64 key) {
 	if (key == KEY_INVALID) return KEY_INVALID;
-	const unsigned lane = lane_id();
 	const uint32_t row = key_row(key);
-	const float *x = X + (size_t)row * d;
-	float acc = 0.f, nx = 0.f, nq2 = 0.f;
-	for (int c = lane; c < d; c += 32) {
-		float a = __ldg(qv + c), b = __ldg(x + c);
-		if (metric == METRIC_L2) {
-			float e = a - b;
-			acc = fmaf(e, e, acc);
-		} else {
-			acc = fmaf(a, b, acc);
-			nx = fmaf(b, b, nx);
-			nq2 = fmaf(a, a, nq2);
-		}
-	}
-	for (int o = 16; o; o >>= 1) {
-		acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
-		nx += __shfl_xor_sync(0xFFFFFFFFu, nx, o);
-		nq2 += __shfl_xor_sync(0xFFFFFFFFu, nq2, o);
-	}
-	float dist;
-	if (metric == METRIC_L2)
-		dist = acc;
-	else if (metric == METRIC_DOT)
-		dist = 1.0f - acc;
-	else {
-		float den = sqrtf(nq2) * sqrtf(nx);
-		if (!(den > 0.f))
-			dist = 1.0f;
-		else {
-			float sim = fminf(1.f, fmaxf(-1.f, acc / den));
-			dist = 1.0f - sim;
-		}
-	}
+	const bool vec4 = (d % 4 == 0) && (((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(qv)) & 15) == 0);
+	const float dist = warp_exact_distance(metric, qv, X + (size_t)row * d, d, vec4);
 	return make_key(dist, row);
 }
 
@@ -246,7 +216,7 @@ struct AdcParams {
 };
 
 template <int GRAN>
-__global__ void __launch_bounds__(256) adc_scan_kernel(const __grid_constant__ AdcParams p) {
+__global__ void __launch_bounds__(512) adc_scan_kernel(const __grid_constant__ AdcParams p) {
 	extern __shared__ __align__(128) unsigned char smem_raw[];
 	const int nwarps = blockDim.x >> 5;
 	const int warp = threadIdx.x >> 5;

@@ -196,7 +196,8 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 
 	// 4. ADC scan (a13) -> per (query, slice) candidate lists
 	const int cap = warpsel_cap(kc);
-	int nwarps = 8;
+	int nwarps = nq >= 64 ? 16 : 8; // batches: more warps per table copy to hide the code-load latency
+	if (const char *e = getenv("LANCE_B200_ADC_WARPS")) nwarps = std::max(1, std::min(16, atoi(e))); // tuning hook
 	while (nwarps > 1 && (size_t)M * 1024 + 64 + (size_t)nwarps * cap * 8 > 220 * 1024) nwarps >>= 1;
 	const size_t smem = (size_t)M * 1024 + 64 + (size_t)nwarps * cap * 8;
 	if (smem > 226 * 1024) throw Error("k * refine_factor too large for the ADC scan's shared memory");

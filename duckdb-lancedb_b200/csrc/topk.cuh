@@ -113,6 +113,9 @@ struct IdentityMap {
 template <class Map>
 __device__ inline void block_bitonic_sort(u64 *base, int n, Map map) {
 	__syncthreads();
+	// Pair i of a stage touches positions 2i - (i & (stride-1)) and + stride: for stride <= 32 the 32 pairs of a warp
+	// stay inside the warp's own 64 positions, so those stages need a warp barrier only; a block barrier is needed
+	// after a stage with stride > 32 and before the next one that has (45 stages of a 512-key sort: 10 block barriers).
 	for (int size = 2; size <= n; size <<= 1) {
 		for (int stride = size >> 1; stride > 0; stride >>= 1) {
 			for (int i = threadIdx.x; i < (n >> 1); i += blockDim.x) {
@@ -125,9 +128,14 @@ __device__ inline void block_bitonic_sort(u64 *base, int n, Map map) {
 					base[pb] = a;
 				}
 			}
-			__syncthreads();
+			const int next_stride = stride > 1 ? (stride >> 1) : size; // first stride of the next size
+			if (stride > 32 || next_stride > 32)
+				__syncthreads();
+			else
+				__syncwarp();
 		}
 	}
+	__syncthreads();
 }
 
 // Final select by a whole block: src[0..m) keys (KEY_INVALID entries ignored, read through L2 because other
