@@ -260,6 +260,10 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	long long seed_tiles = TC_SEED_TILES;
 	if (const char *e = getenv("LANCE_B200_TC_GROWTH")) growth = std::max(2, atoi(e)); // tuning hooks
 	if (const char *e = getenv("LANCE_B200_TC_SEED")) seed_tiles = std::max(1, atoi(e));
+	// growth of the second segment (tuning hook): the seed's threshold passes ~k/seed_rows of the rows, so a jump of j
+	// costs ~j*k emits per query and saves log4(j) launches + refreshes
+	int jump = growth; // measured on B200: larger jumps lose more to emission than they save in launches
+	if (const char *e = getenv("LANCE_B200_TC_JUMP")) jump = std::max(2, atoi(e));
 
 	for (int q0 = 0, nq = 0; q0 < nq_total; q0 += nq) {
 		// queries per pass: at most TC_QCHUNK; when every CTA holds a single query tile (large K), take a tile
@@ -333,7 +337,7 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 			LB_CUDA(cudaGetLastError());
 			(*launches) += 2;
 			t0 = t1;
-			seg *= growth;
+			seg *= (t0 == seed_tiles ? jump : growth);
 		}
 		int tix = timer ? timer->begin(KC_RERANK, s) : -1;
 		if (nq >= 2 * im.num_sms) {

@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(256) refresh_threshold_kernel(uint2 *__restric
 	if (c < k) return; // fewer than k live candidates so far: keep everything, threshold stays
 	uint2 *list = cand + (size_t)q * CAP;
 	u64 *bufs = reinterpret_cast<u64 *>(smem_raw);
-	if (c <= 8 * cap) {
+	if (c <= 8 * cap && c <= 1024) {
 		// short list (every refresh but the one after the seed segment): one block-wide sort instead of per-warp
 		// selection plus a serial fold — this kernel runs once per segment and its latency is pure overhead
 		int n = 64;
@@ -123,32 +123,23 @@ __global__ void __launch_bounds__(256) refresh_threshold_kernel(uint2 *__restric
 			s_base = 0;
 		}
 	} else {
-		WarpSelect sel;
-		sel.init(bufs + (size_t)warp * cap, cap, k);
-		for (int i0 = warp * 32; i0 < c; i0 += 256) {
-			int i = i0 + lane;
-			float sc = i < c ? __uint_as_float(list[i].x) : 0.f;
-			sel.push(i < c, make_key(-sc, (uint32_t)i));
+		// long list (after the seed segment, or large k): radix-select the k best scores; A_k is the worst of them
+		__shared__ u64 s_max;
+		if (threadIdx.x == 0) s_max = 0;
+		block_radix_select([=](int i) { return make_key(-__uint_as_float(list[i].x), (uint32_t)i); }, c, k, bufs);
+		u64 mx = 0;
+		for (int i = threadIdx.x; i < k; i += 256) mx = bufs[i] > mx ? bufs[i] : mx;
+		for (int o = 16; o; o >>= 1) {
+			const u64 v = __shfl_xor_sync(0xFFFFFFFFu, mx, o);
+			mx = v > mx ? v : mx;
 		}
-		sel.finalize();
-		if (lane == 0) cnts[warp] = sel.cnt;
+		if (lane == 0) atomicMax(&s_max, mx);
 		__syncthreads();
-		if (warp == 0) {
-			for (int w = 1; w < 8; w++) {
-				const u64 *s2 = bufs + (size_t)w * cap;
-				const int cw = cnts[w];
-				for (int i0 = 0; i0 < cw; i0 += 32) {
-					int i = i0 + lane;
-					sel.push(i < cw, i < cw ? s2[i] : KEY_INVALID);
-				}
-			}
-			sel.finalize();
-			if (lane == 0) {
-				float ak = -key_dist(sel.buf[k - 1]);
-				float t = ak - margin[q];
-				s_thr = fmaxf(t, thr[q]);
-				s_base = 0;
-			}
+		if (threadIdx.x == 0) {
+			float ak = -key_dist(s_max);
+			float t = ak - margin[q];
+			s_thr = fmaxf(t, thr[q]);
+			s_base = 0;
 		}
 	}
 	__syncthreads();
@@ -207,10 +198,13 @@ __global__ void __launch_bounds__(256) rerank_kernel(const float *__restrict__ X
 		const uint32_t myrow = mine < c ? list[mine].y : 0u;
 		float mydist = 0.f;
 		const int nb = min(32, c - i0);
-		for (int j = 0; j < nb; j++) {
-			const uint32_t row = __shfl_sync(0xFFFFFFFFu, myrow, j);
-			float dist = warp_exact_distance(metric, qv, X + (size_t)row * d, d, vec4);
-			if ((int)lane == j) mydist = dist;
+		for (int j = 0; j < nb; j += 2) {
+			const uint32_t r0 = __shfl_sync(0xFFFFFFFFu, myrow, j);
+			const uint32_t r1 = __shfl_sync(0xFFFFFFFFu, myrow, min(j + 1, nb - 1));
+			float d0, d1;
+			warp_exact_distance_x2(metric, qv, X + (size_t)r0 * d, X + (size_t)r1 * d, d, vec4, d0, d1);
+			if ((int)lane == j) mydist = d0;
+			if ((int)lane == j + 1) mydist = d1;
 		}
 		sel.push(mine < c, make_key(mydist, myrow));
 	}

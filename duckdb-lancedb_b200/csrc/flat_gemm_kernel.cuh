@@ -80,27 +80,22 @@ __device__ __forceinline__ uint32_t gemm_chunk_valid(const GemmParams &p, long l
 	return m;
 }
 
-// Slow path of a 32-column chunk for the lanes (queries) that have a score at or above their threshold.  Out of
-// line and fed through a local-memory copy of the chunk, so that the hot loop keeps its registers; inside there is
-// no per-hit branch or call that could serialise the lanes: hits go to the thread's shared-memory buffer while it
-// has room, otherwise the buffered and the new hits go to the query's list with ONE atomicAdd.
-__device__ __noinline__ void gemm_emit_chunk(const GemmParams &p, const uint32_t *r, float thr, int q, long long row0,
+// Bulk emit of one 32-column chunk for the lanes (queries) that have hits (`hits` = passing columns, already
+// masked by gemm_chunk_valid).  Out of line and fed through a local-memory copy of the chunk, so that the hot
+// loop keeps its registers; the work per lane is proportional to its own hits (a loop over the set bits), and the
+// buffered + new hits go to the query's list with ONE atomicAdd when the thread's shared-memory buffer is full.
+__device__ __noinline__ void gemm_emit_chunk(const GemmParams &p, const uint32_t *r, uint32_t hits, int q, long long row0,
                                              uint2 *slots, int *count) {
-	uint32_t hits = 0u;
-#pragma unroll
-	for (int c = 0; c < 32; c++) hits |= (__uint_as_float(r[c]) >= thr ? 1u : 0u) << c;
-	hits &= gemm_chunk_valid(p, row0);
 	const int h = __popc(hits);
-	if (h == 0) return;
 	const uint32_t rbase = (uint32_t)row0;
 	int n = slots ? *count : 0;
 	if (slots && n + h <= p.EB) {
-#pragma unroll
-		for (int c = 0; c < 32; c++)
-			if ((hits >> c) & 1u) {
-				slots[n * 128] = make_uint2(r[c], rbase + c);
-				n++;
-			}
+		while (hits) {
+			const int c = __ffs(hits) - 1;
+			hits &= hits - 1;
+			slots[n * 128] = make_uint2(r[c], rbase + c);
+			n++;
+		}
 		*count = n;
 		return;
 	}
@@ -109,12 +104,12 @@ __device__ __noinline__ void gemm_emit_chunk(const GemmParams &p, const uint32_t
 	for (int i = 0; i < n; i++, pos++)
 		if (pos < (uint32_t)p.CAP) dst[pos] = slots[i * 128];
 	if (slots) *count = 0;
-#pragma unroll
-	for (int c = 0; c < 32; c++)
-		if ((hits >> c) & 1u) {
-			if (pos < (uint32_t)p.CAP) dst[pos] = make_uint2(r[c], rbase + c);
-			pos++;
-		}
+	while (hits) {
+		const int c = __ffs(hits) - 1;
+		hits &= hits - 1;
+		if (pos < (uint32_t)p.CAP) dst[pos] = make_uint2(r[c], rbase + c);
+		pos++;
+	}
 }
 
 // One hit of one lane (the sparse case: a warm threshold passes a few scores per query and segment).
@@ -179,10 +174,16 @@ __device__ __forceinline__ void gemm_process_chunk(const GemmParams &p, const ui
 				if (v >= thr) gemm_emit(p, q, row0 + i, v, eb.slots, eb.count);
 			}
 		} else {
-			uint32_t tmp[32];
+			uint32_t hits = 0u;
 #pragma unroll
-			for (int c = 0; c < 32; c++) tmp[c] = r[c];
-			gemm_emit_chunk(p, tmp, thr, q, row0, eb.slots, eb.count);
+			for (int c = 0; c < 32; c++) hits |= (__uint_as_float(r[c]) >= thr ? 1u : 0u) << c;
+			hits &= gemm_chunk_valid(p, row0);
+			if (hits) {
+				uint32_t tmp[32];
+#pragma unroll
+				for (int c = 0; c < 32; c++) tmp[c] = r[c];
+				gemm_emit_chunk(p, tmp, hits, q, row0, eb.slots, eb.count);
+			}
 		}
 	}
 }

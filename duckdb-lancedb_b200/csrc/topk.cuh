@@ -138,6 +138,96 @@ __device__ inline void block_bitonic_sort(u64 *base, int n, Map map) {
 	__syncthreads();
 }
 
+// k smallest of m keys by the whole block with an MSB-first radix select (8-bit digits, shared-memory histogram):
+// O(m / blockDim) independent loads per pass and 2-4 passes for distance keys, instead of streaming every key through
+// the warp selectors (whose compaction sorts serialise) — the tails of the single-query kernels and the threshold
+// refresh of large-k batches are latency-bound on exactly this step.  key_at(i) returns key i (i < m); the winners
+// land UNSORTED in out[0..k) (KEY_INVALID-padded when fewer than k valid keys exist), `out` must hold k + 32 keys.
+// All threads call it; m >= k.
+template <class KeyAt>
+__device__ inline void block_radix_select(KeyAt key_at, int m, int k, u64 *out) {
+	__shared__ int hist[256];
+	__shared__ int s_need, s_digit, s_bin, s_nout, s_nbin;
+	u64 prefix = 0;
+	int bits = 0, need = k;
+	__syncthreads();
+	while (true) {
+		for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+		__syncthreads();
+		for (int i0 = 0; i0 < m; i0 += blockDim.x) {
+			const int i = i0 + threadIdx.x;
+			int digit = -1 - (int)(threadIdx.x & 31); // lanes without a key match nobody
+			if (i < m) {
+				const u64 key = key_at(i);
+				if (bits == 0 || (key >> (64 - bits)) == prefix) digit = (int)((key >> (56 - bits)) & 255u);
+			}
+			// distance keys share their leading digits: one shared-memory atomic per distinct digit of the warp
+			const unsigned peers = __match_any_sync(0xFFFFFFFFu, digit);
+			if (digit >= 0 && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&hist[digit], __popc(peers));
+		}
+		__syncthreads();
+		if (threadIdx.x < 32) {
+			// warp 0: smallest digit whose cumulative count reaches `need`
+			const int lane = threadIdx.x;
+			int c[8], sum = 0;
+#pragma unroll
+			for (int j = 0; j < 8; j++) c[j] = hist[lane * 8 + j], sum += c[j];
+			int incl = sum;
+			for (int o = 1; o < 32; o <<= 1) {
+				int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+				if (lane >= o) incl += v;
+			}
+			int before = incl - sum; // keys in digits below this lane's 8
+			const bool mine = before < need && incl >= need;
+			if (mine) {
+				int j = 0;
+				while (before + c[j] < need) before += c[j], j++;
+				s_digit = lane * 8 + j;
+				s_need = need - before;
+				s_bin = c[j];
+			}
+		}
+		__syncthreads();
+		prefix = (prefix << 8) | (u64)s_digit;
+		bits += 8;
+		need = s_need;
+		const int bin = s_bin;
+		__syncthreads();
+		if (bin <= 32 || bits == 64) break;
+	}
+	// winners: every key below the prefix, plus the `need` smallest of the (<= 32, or all-equal) keys on it
+	if (threadIdx.x == 0) s_nout = 0, s_nbin = 0;
+	for (int i = threadIdx.x; i < k; i += blockDim.x) out[i] = KEY_INVALID; // fewer than k valid keys: padding
+	__syncthreads();
+	u64 *binl = out + k;
+	for (int i = threadIdx.x; i < m; i += blockDim.x) {
+		const u64 key = key_at(i);
+		const u64 top = key >> (64 - bits);
+		if (top < prefix)
+			out[atomicAdd(&s_nout, 1)] = key;
+		else if (top == prefix) {
+			const int pos = atomicAdd(&s_nbin, 1);
+			if (pos < 32) binl[pos] = key;
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x < 32) {
+		// one warp: sort the bin (<= 32 keys) in registers, append its `need` smallest
+		const int lane = threadIdx.x, nb = min(s_nbin, 32);
+		u64 v = lane < nb ? binl[lane] : KEY_INVALID;
+		for (int size = 2; size <= 32; size <<= 1)
+			for (int stride = size >> 1; stride > 0; stride >>= 1) {
+				const u64 o = __shfl_xor_sync(0xFFFFFFFFu, v, stride);
+				const bool up = (lane & size) == 0, lower = (lane & stride) == 0;
+				v = (lower == up) ? (v < o ? v : o) : (v < o ? o : v);
+			}
+		const int base = s_nout;
+		__syncwarp();
+		if (lane < need) out[base + lane] = v;
+	}
+	__syncthreads();
+}
+
 // Final select by a whole block: src[0..m) keys (KEY_INVALID entries ignored, read through L2 because other
 // SMs may have written them) -> sorted (label, distance) list of query slot `q`.  All threads of the block
 // call it; bufs = nwarps*cap keys of shared memory (cnts is unused, kept for the callers' layouts).
@@ -156,20 +246,12 @@ __device__ inline void block_final_select(const u64 *__restrict__ src, long long
 		for (int i = threadIdx.x; i < n; i += blockDim.x) bufs[i] = i < (int)m ? __ldcg(src + i) : KEY_INVALID;
 		block_bitonic_sort(bufs, n, IdentityMap());
 	} else {
-		WarpSelect sel;
-		sel.init(bufs + (size_t)warp * cap, cap, k);
-		for (long long i0 = (long long)warp * 128; i0 < m; i0 += (long long)nwarps * 128) {
-			u64 key[4];
-#pragma unroll
-			for (int u = 0; u < 4; u++) {
-				long long i = i0 + u * 32 + lane;
-				key[u] = (i < m) ? __ldcg(src + i) : KEY_INVALID;
-			}
-#pragma unroll
-			for (int u = 0; u < 4; u++) sel.push(key[u] != KEY_INVALID, key[u]);
-		}
-		sel.pad();
-		block_bitonic_sort(bufs, nwarps * cap, IdentityMap());
+		// long list: radix-select the k smallest, then sort just those
+		block_radix_select([=](int i) { return __ldcg(src + i); }, (int)m, k, bufs);
+		int n = 64;
+		while (n < k) n <<= 1;
+		for (int i = k + threadIdx.x; i < n; i += blockDim.x) bufs[i] = KEY_INVALID;
+		block_bitonic_sort(bufs, n, IdentityMap());
 	}
 	if (warp == 0) {
 		int cnt = 0;

@@ -1,0 +1,11 @@
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_flat_tc_gpu.py -x -q 2>&1 | tail -2
+run() { name=$1; shift; timeout 600 python bench.py "$@" --no-cpu-baseline > gpurun_out/bench_$name.json 2> gpurun_out/bench_$name.err; tail -c 300 gpurun_out/bench_$name.err; }
+for j in 4 16 64; do
+LANCE_B200_TC_JUMP=$j run j${j}_r12 --workload c4 --rows 12500000 --steps 10
+done
+for j in 4 6 16; do
+LANCE_B200_TC_JUMP=$j run j${j}_c2 --workload c2
+done
+LANCE_B200_TC_JUMP=64 run j64_r100 --workload c4
+LANCE_B200_TC_JUMP=4 run j4_r100 --workload c4

@@ -169,3 +169,26 @@ def test_batch_equals_singles_and_defaults(gpu, oracle_mod):
     with gpu.LanceHandle(d, "l2") as h:
         with pytest.raises(gpu.LanceError, match="empty table"):
             h.create_index(4, 4)
+
+
+@pytest.mark.parametrize("metric", ["cosine", "dot", "l2"])
+def test_batched_probe_equals_single_query_probe(gpu, oracle_mod, metric):
+    """Batches (>= 8 queries) probe with the tiled contraction, single queries with the streaming scan: the probed
+    partitions, and with them the final lists, must agree (and agree with the oracle for a sample of queries)."""
+    rng = np.random.default_rng(77)
+    n, d, P, M = 30_000, 64, 64, 16
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Q = rng.standard_normal((41, d), dtype=np.float32)
+    with gpu.LanceHandle(d, metric) as h:
+        h.add_batch(X)
+        h.create_index(P, M)
+        g = h.get_ivfpq()
+        ix = oracle_mod.IvfPqIndex(metric, d, g["P"], g["M"], g["centroids"], g["codebook"], g["part_offsets"], g["row_ids"],
+                                   g["codes"], n_indexed=g["n_indexed"])
+        L, D, C = h.search_batch(Q, 10, nprobes=8, refine_factor=1)
+        for j in range(41):
+            l, dd = h.search(Q[j], 10, nprobes=8, refine_factor=1)
+            assert list(l) == list(L[j, :C[j]]), f"{metric} q{j}"
+            np.testing.assert_allclose(dd, D[j, :C[j]], rtol=1e-6)
+        for j in (0, 13, 40):
+            compare_with_oracle(oracle_mod, h, ix, X, Q[j], 10, 8, 1, metric, what=f"{metric} batched-probe q{j}")
