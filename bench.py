@@ -188,6 +188,16 @@ def cpu_ivfpq_sample(wl, nq, threads, seed=SEED):
     return time.perf_counter() - t0, nq
 
 
+def host_threads(oracle):
+    """All the host threads the CPU arm can use.  torchrun exports OMP_NUM_THREADS=1 to its workers, which would
+    make the reference arm single-threaded at N > 1; the affinity mask of the process is what really bounds it."""
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    return max(oracle.num_threads(), avail)
+
+
 def cpu_sample_shape(wl, budget_pairs):
     """Pick (rows, queries) of the sample so that rows*queries*dim ~ budget, keeping the batch shape when possible."""
     q = min(wl["batch"], 64)
@@ -199,7 +209,7 @@ def cpu_baseline(wl, seconds_target=12.0):
     import oracle
 
     oracle.build()
-    threads = oracle.num_threads()
+    threads = host_threads(oracle)
     if wl["kind"] == "ivfpq":
         dt, nq = cpu_ivfpq_sample(wl, 4 * threads, threads)
         nq = int(max(4 * threads, min(4096, nq * seconds_target / max(dt, 1e-3))))
@@ -233,7 +243,7 @@ def run_reference(args, wl):
     import oracle
 
     oracle.build()
-    threads = oracle.num_threads()
+    threads = host_threads(oracle)
     if wl["kind"] == "ivfpq":
         times = []
         nq = 8 * threads
@@ -405,26 +415,42 @@ def run_b200(args, wl):
     shard_bytes = n_local * dim * 4 if wl["kind"] == "flat" else 1 << 40
     need_flush = shard_bytes <= 200e6  # the 126 MB L2 would otherwise serve the table on every step after the first
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if need_flush else None
+    flush_rd = torch.zeros(64 << 20, dtype=torch.float32, device=dev) if need_flush else None  # 256 MB, read-only pass
+
+    wall_ms = [0.0]
 
     def timed(fn, steps):
+        """K steps bracketed by barrier + synchronize; device time from CUDA events on the launching stream (max over
+        ranks), host wall-clock of the same steps in wall_ms[0]."""
         barrier()
         if need_flush:
-            # one event pair per step, an L2-sized write in between (outside the timed intervals)
+            # one event pair per step.  Between steps (outside the timed intervals): write a buffer larger than L2, read
+            # another one — the table is evicted AND the dirty lines of the write are already back in DRAM — and wait,
+            # so that a step that runs on the library's own stream cannot overlap the flush
             evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+            wall = 0.0
             for a, b in evs:
                 flush_buf.fill_(1)
+                flush_rd.sum()
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
                 a.record(stream)
                 fn()
                 b.record(stream)
+                b.synchronize()
+                wall += time.perf_counter() - t0
             barrier()
             ms = sum(a.elapsed_time(b) for a, b in evs)
+            wall_ms[0] = wall * 1e3
         else:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
             e0.record(stream)
             for _ in range(steps):
                 fn()
             e1.record(stream)
             barrier()
+            wall_ms[0] = (time.perf_counter() - t0) * 1e3
             ms = e0.elapsed_time(e1)
         if world > 1:
             t = torch.tensor([ms], device=dev, dtype=torch.float64)
@@ -452,11 +478,10 @@ def run_b200(args, wl):
     # ---- end-to-end (host buffers) timed region
     for _ in range(2):
         step_e2e()
-    wall0 = time.perf_counter()
     ms_e2e_dev = timed(step_e2e, args.steps)
-    wall = (time.perf_counter() - wall0) * 1e3
-    # N=1: the call is synchronous, so the wall clock bounds it (unless flushes sit between the steps)
-    ms_e2e = max(ms_e2e_dev, wall) if (world == 1 and not need_flush) else ms_e2e_dev
+    # N=1: the reference-facing call is synchronous and runs on the library's own stream, so the host wall-clock of
+    # the steps is the end-to-end time (the events on torch's stream only bound it from below)
+    ms_e2e = max(ms_e2e_dev, wall_ms[0]) if world == 1 else ms_e2e_dev
     clocks = sampler.stop() if rank == 0 else None
 
     launches = st1["kernel_launches"] - st0["kernel_launches"] + merges_value
