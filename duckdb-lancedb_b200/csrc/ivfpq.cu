@@ -113,6 +113,74 @@ __global__ void __launch_bounds__(256) probe_tile_kernel(const float *__restrict
 	}
 }
 
+// ------------------------------------------------------------------ probe of a few queries (a12), nq < 8
+// One warp per centroid: the row is read once (128-bit loads when d % 4 == 0) and scored against all nq queries held
+// in shared memory; keys[q][p] = (d(q', c_p), p).  The select (launch_topk_merge) follows.  A lone query used to go
+// through the streaming scan, whose two-level in-kernel select of k = nprobes keys over hundreds of tiny blocks cost
+// more than reading the 12 MB table.
+template <int IS_DOT>
+__global__ void __launch_bounds__(256) probe_rows_kernel(const float *__restrict__ Qp, int nq, const float *__restrict__ C,
+                                                         int P, int d, u64 *__restrict__ keys) {
+	extern __shared__ __align__(16) float probe_qs[]; // [nq][d]
+	for (int i = threadIdx.x; i < nq * d; i += blockDim.x) probe_qs[i] = Qp[i];
+	__syncthreads();
+	const int warp = threadIdx.x >> 5;
+	const unsigned lane = lane_id();
+	const int row = blockIdx.x * (blockDim.x >> 5) + warp;
+	if (row >= P) return;
+	float acc[8];
+#pragma unroll
+	for (int j = 0; j < 8; j++) acc[j] = 0.f;
+	const float *x = C + (size_t)row * d;
+	if ((d & 3) == 0 && ((reinterpret_cast<uintptr_t>(C) & 15) == 0)) {
+		const float4 *x4 = reinterpret_cast<const float4 *>(x);
+		const float4 *q4 = reinterpret_cast<const float4 *>(probe_qs);
+		const int n4 = d >> 2;
+#pragma unroll 4
+		for (int c = lane; c < n4; c += 32) {
+			const float4 b = __ldg(x4 + c);
+#pragma unroll
+			for (int j = 0; j < 8; j++) {
+				if (j < nq) {
+					const float4 a = q4[j * n4 + c];
+					if (IS_DOT) {
+						acc[j] = fmaf(a.x, b.x, acc[j]), acc[j] = fmaf(a.y, b.y, acc[j]), acc[j] = fmaf(a.z, b.z, acc[j]),
+						acc[j] = fmaf(a.w, b.w, acc[j]);
+					} else {
+						const float e0 = a.x - b.x, e1 = a.y - b.y, e2 = a.z - b.z, e3 = a.w - b.w;
+						acc[j] = fmaf(e0, e0, acc[j]), acc[j] = fmaf(e1, e1, acc[j]), acc[j] = fmaf(e2, e2, acc[j]),
+						acc[j] = fmaf(e3, e3, acc[j]);
+					}
+				}
+			}
+		}
+	} else {
+		for (int c = lane; c < d; c += 32) {
+			const float b = __ldg(x + c);
+#pragma unroll
+			for (int j = 0; j < 8; j++) {
+				if (j < nq) {
+					const float a = probe_qs[j * d + c];
+					if (IS_DOT)
+						acc[j] = fmaf(a, b, acc[j]);
+					else {
+						const float e = a - b;
+						acc[j] = fmaf(e, e, acc[j]);
+					}
+				}
+			}
+		}
+	}
+#pragma unroll
+	for (int j = 0; j < 8; j++) {
+		if (j < nq) {
+			float v = acc[j];
+			for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+			if (lane == 0) keys[(size_t)j * P + row] = make_key(IS_DOT ? 1.0f - v : v, (uint32_t)row);
+		}
+	}
+}
+
 // ------------------------------------------------------------------ per-query lookup table T1
 // lut[q][m][c] = |q'_m - cb[m][c]|^2 (l2/cosine) or -(q'_m . cb[m][c]) (dot).
 // grid (M, ceil(nq / QPB)); 256 threads = one codeword each; the codebook slice of sub-quantizer m is

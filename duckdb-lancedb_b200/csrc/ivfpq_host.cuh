@@ -168,18 +168,21 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 			launch_topk_merge(ws.probe_mat.as<u64>(), nc, ix.P, np, 0, nullptr, nullptr, nullptr, probe_keys + (size_t)q0 * np, s, &launches);
 		}
 	} else {
-		FlatScanArgs a;
-		a.X = ix.centroids.as<float>();
-		a.n = ix.P;
-		a.d = d;
-		a.metric = metric_ == METRIC_DOT ? METRIC_DOT : METRIC_L2;
-		a.dQ = Qp;
-		a.nq = nq;
-		a.k = np;
-		a.out_keys = probe_keys;
-		FlatScanPlan p = plan_flat_scan(a.X, a.metric, d, np, nq, ix.P, num_sms_);
-		ws.work.ensure(flat_scan_scratch_bytes(p, np));
-		run_flat_scan(a, p, ws.work.p, s, &launches);
+		// a few queries: one warp per centroid scores all of them, then one select per query
+		ws.probe_mat.ensure((size_t)nq * ix.P * sizeof(u64));
+		const size_t qsm = (size_t)nq * d * sizeof(float);
+		if (qsm > 200 * 1024) throw Error("dimension too large for the IVF probe");
+		const int blocks = (ix.P + 7) / 8;
+		if (metric_ == METRIC_DOT) {
+			if (qsm > 48 * 1024) LB_CUDA(cudaFuncSetAttribute(probe_rows_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qsm));
+			probe_rows_kernel<1><<<blocks, 256, qsm, s>>>(Qp, nq, ix.centroids.as<float>(), ix.P, d, ws.probe_mat.as<u64>());
+		} else {
+			if (qsm > 48 * 1024) LB_CUDA(cudaFuncSetAttribute(probe_rows_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qsm));
+			probe_rows_kernel<0><<<blocks, 256, qsm, s>>>(Qp, nq, ix.centroids.as<float>(), ix.P, d, ws.probe_mat.as<u64>());
+		}
+		LB_CUDA(cudaGetLastError());
+		launches++;
+		launch_topk_merge(ws.probe_mat.as<u64>(), nq, ix.P, np, 0, nullptr, nullptr, nullptr, probe_keys, s, &launches);
 	}
 
 	// 3. per-query lookup table T1
