@@ -572,6 +572,7 @@ def main():
     ap.add_argument("--batch", type=int, default=None, help="override the workload's query batch")
     ap.add_argument("--rows", type=int, default=None, help="override the workload's row count (experiments only)")
     ap.add_argument("--k", type=int, default=None)
+    ap.add_argument("--selectivity", type=float, default=None, help="c5: fraction of rows the prefilter keeps (0.8 / 0.01)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
@@ -581,6 +582,9 @@ def main():
         wl["rows"] = args.rows
     if args.k:
         wl["k"] = args.k
+    if args.selectivity is not None and wl.get("selectivity"):
+        wl["selectivity"] = args.selectivity
+        wl["desc"] = wl["desc"].replace("80% selectivity", f"{100 * args.selectivity:g}% selectivity")
     if args.impl == "reference":
         run_reference(args, wl)
     else:
