@@ -202,6 +202,9 @@ def cpu_sample_shape(wl, budget_pairs):
     """Pick (rows, queries) of the sample so that rows*queries*dim ~ budget, keeping the batch shape when possible."""
     q = min(wl["batch"], 64)
     rows = int(min(wl["rows"], max(10_000, budget_pairs // (q * wl["dim"]))))
+    # bound the host memory of the sample (<= 2 GiB of fp32 rows, larger than any host cache); the time budget is
+    # filled by repeating the sample instead
+    rows = min(rows, (2 << 30) // (4 * wl["dim"]))
     return rows, q
 
 

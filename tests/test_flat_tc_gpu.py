@@ -235,3 +235,44 @@ def test_full_size_c2_tensor_path_equals_scan(gpu):
             if list(l1) != list(L[j]):
                 assert sorted(l1) == sorted(L[j]) or np.allclose(np.sort(d1), np.sort(D[j]), rtol=1e-5), f"q{j}"
             np.testing.assert_allclose(D[j], d1, rtol=1e-4, atol=1e-6)
+
+
+def test_sharded_step_on_one_gpu_packed_record_and_strided_merge(gpu, oracle_mod):
+    """The multi-GPU step (sharding.ShardedSearch: async search into the packed record -> gather -> strided device
+    merge -> settle) with world = 1, and the strided merge over two hand-made shards of the same table."""
+    import importlib
+
+    import torch
+
+    sharding = importlib.import_module("duckdb_lancedb_b200.sharding")
+    n, d, k, nq = 70_000, 64, 10, 40
+    rng = np.random.default_rng(31)
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Q = rng.standard_normal((nq, d), dtype=np.float32)
+    dev = torch.device("cuda", 0)
+    Qd = torch.from_numpy(Q).to(dev)
+    sp = torch.cuda.current_stream().cuda_stream
+    with gpu.LanceHandle(d, "l2") as h:
+        h.add_batch(X)
+        ss = sharding.ShardedSearch(gpu, h, 1, nq, k, dev, 0)
+        ML, MD, MC = ss.step(Qd.data_ptr(), sp)
+        assert ss.settle() == 0
+        L, D, C = ML.cpu().numpy(), MD.cpu().numpy(), MC.cpu().numpy()
+        check_oracle(oracle_mod, X, Q[:6], L[:6], D[:6], C[:6], k, "l2", what="sharded world=1")
+        L1, D1, C1 = h.search_batch(Q, k)
+        assert (L == L1).all() and (C == C1).all()
+    # two shards (label ranges) searched one after the other into a 2-rank record buffer, merged by the strided kernel
+    half = n // 2
+    g2 = sharding.ShardGather(2, nq, k, dev)
+    for r, (lo, hi) in enumerate(((0, half), (half, n))):
+        with gpu.LanceHandle(d, "l2") as h:
+            h.set_label_base(lo)
+            h.add_batch(X[lo:hi])
+            h.search_device(Qd.data_ptr(), nq, k, g2.L.data_ptr(), g2.D.data_ptr(), g2.C.data_ptr(), stream=sp)
+            torch.cuda.synchronize()
+            g2.all[r].copy_(g2.rec)
+    gpu.merge_topk_strided_device(0, g2.GL.data_ptr(), g2.GD.data_ptr(), g2.GC.data_ptr(), g2.GL.stride(0), g2.GD.stride(0),
+                                  g2.GC.stride(0), 2, nq, k, g2.ML.data_ptr(), g2.MD.data_ptr(), g2.MC.data_ptr(), stream=sp)
+    torch.cuda.synchronize()
+    assert (g2.ML.cpu().numpy() == L1).all() and (g2.MC.cpu().numpy() == C1).all()
+    np.testing.assert_allclose(g2.MD.cpu().numpy(), D1, rtol=1e-5)
