@@ -11,6 +11,7 @@
 #include <cstdint>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <unordered_map>
@@ -120,6 +121,15 @@ private:
 	std::vector<row_t> label_to_rowid_;
 	std::unordered_map<row_t, int64_t> rowid_to_label_;
 	ColumnSet columns_;
+	// predicate string -> allow bitmap, reused while the labels and the extra columns are unchanged: the WHERE of the
+	// rewritten query is constant across a workload, evaluating it over N rows on the host is not
+	struct CachedBitmap {
+		uint64_t signature = 0;
+		std::shared_ptr<const std::vector<uint32_t>> bitmap;
+	};
+	std::map<std::string, CachedBitmap> predicate_cache_;
+	std::mutex predicate_mu_;
+	std::shared_ptr<const std::vector<uint32_t>> PredicateBitmap(const std::string &predicate);
 };
 
 // ------------------------------------------------------------------ lance_search table function (src/lance_search.cpp)

@@ -153,16 +153,33 @@ void LanceIndex::Delete(const row_t *row_ids, int64_t count) {
 	if (!labels.empty()) LanceDetachedDeleteBatch(rust_handle_, labels.data(), (int32_t)labels.size());
 }
 
+std::shared_ptr<const std::vector<uint32_t>> LanceIndex::PredicateBitmap(const std::string &predicate) {
+	// signature of what the bitmap depends on: the number of labels and the length of every extra column (append-only)
+	uint64_t sig = 1469598103934665603ull ^ (uint64_t)label_to_rowid_.size();
+	for (const auto &kv : columns_) sig = (sig * 1099511628211ull) ^ (uint64_t)kv.second.size() ^ ((uint64_t)kv.first.size() << 48);
+	{
+		std::lock_guard<std::mutex> g(predicate_mu_);
+		auto it = predicate_cache_.find(predicate);
+		if (it != predicate_cache_.end() && it->second.signature == sig) return it->second.bitmap;
+	}
+	auto bm = std::make_shared<const std::vector<uint32_t>>(
+	    EvaluatePredicate(predicate, columns_, (int64_t)label_to_rowid_.size()));
+	std::lock_guard<std::mutex> g(predicate_mu_);
+	if (predicate_cache_.size() >= 16) predicate_cache_.clear();
+	predicate_cache_[predicate] = CachedBitmap{sig, bm};
+	return bm;
+}
+
 std::vector<std::pair<row_t, float>> LanceIndex::Search(const float *query, int32_t dimension, int32_t k,
                                                         const std::string &predicate) {
 	if (!rust_handle_ || dimension != dimension_) return {}; // :444-446
 	if (k <= 0) return {};
 	std::vector<int64_t> labels(k);
 	std::vector<float> distances(k);
-	std::vector<uint32_t> bitmap;
-	if (!predicate.empty()) bitmap = EvaluatePredicate(predicate, columns_, (int64_t)label_to_rowid_.size());
+	std::shared_ptr<const std::vector<uint32_t>> bitmap;
+	if (!predicate.empty()) bitmap = PredicateBitmap(predicate);
 	const int32_t n = LanceDetachedSearch(rust_handle_, query, dimension, k, nprobes_, refine_factor_,
-	                                      predicate.empty() ? nullptr : bitmap.data(), (int64_t)bitmap.size() * 32,
+	                                      bitmap ? bitmap->data() : nullptr, bitmap ? (int64_t)bitmap->size() * 32 : 0,
 	                                      labels.data(), distances.data());
 	std::vector<std::pair<row_t, float>> results;
 	results.reserve(n);
@@ -181,10 +198,10 @@ std::vector<std::vector<std::pair<row_t, float>>> LanceIndex::SearchBatch(const 
 	std::vector<int64_t> labels((size_t)nq * k);
 	std::vector<float> distances((size_t)nq * k);
 	std::vector<int32_t> counts(nq);
-	std::vector<uint32_t> bitmap;
-	if (!predicate.empty()) bitmap = EvaluatePredicate(predicate, columns_, (int64_t)label_to_rowid_.size());
+	std::shared_ptr<const std::vector<uint32_t>> bitmap;
+	if (!predicate.empty()) bitmap = PredicateBitmap(predicate);
 	LanceDetachedSearchBatch(rust_handle_, queries, nq, dimension, k, nprobes_, refine_factor_,
-	                         predicate.empty() ? nullptr : bitmap.data(), (int64_t)bitmap.size() * 32, labels.data(),
+	                         bitmap ? bitmap->data() : nullptr, bitmap ? (int64_t)bitmap->size() * 32 : 0, labels.data(),
 	                         distances.data(), counts.data());
 	for (int32_t q = 0; q < nq; q++) {
 		out[q].reserve(counts[q]);

@@ -123,3 +123,29 @@ def test_host_index_options_batch_and_ann(gpu, host, oracle_mod):
             assert abs(oracle_mod.distance_f64("cosine", Q[0], X[r]) - dd) <= 1e-4 * max(dd, 1e-3)
         wl, wd32, wd64 = oracle_mod.flat_search(X, Q[0], k, "cosine", None, None)
         assert len(set(rows.tolist()) & set(wl.tolist())) >= 3  # coarse PQ (8 x 4-d sub-vectors): recall, not parity
+
+
+def test_predicate_bitmap_cache_follows_appends(gpu, host, oracle_mod):
+    """LanceIndex keeps predicate -> bitmap while labels and columns are unchanged; an append must invalidate it."""
+    rng = np.random.default_rng(29)
+    n, d, k = 3000, 16, 5
+    X = rng.standard_normal((2 * n, d), dtype=np.float32)
+    q = rng.standard_normal(d, dtype=np.float32)
+    score = rng.integers(0, 100, 2 * n)
+    with host.HostIndex(d, "l2") as ix:
+        ix.append(X[:n], np.arange(n))
+        ix.columns.append("score", score[:n].tolist())
+        for _ in range(2):  # second call is served from the cache
+            rows, dist = ix.search(q, k, "score < 30")
+            wl, _, wd64 = oracle_mod.flat_search(X[:n], q, k, "l2", oracle_mod.make_bitmap(score[:n] < 30), None)
+            assert list(rows) == list(wl)
+        # a very near neighbour that passes the predicate arrives with the next append
+        X[n + 5] = q + 1e-3
+        score[n + 5] = 7
+        ix.append(X[n:], np.arange(n, 2 * n))
+        ix.columns.append("score", score[n:].tolist())
+        rows, dist = ix.search(q, k, "score < 30")
+        wl, _, wd64 = oracle_mod.flat_search(X, q, k, "l2", oracle_mod.make_bitmap(score < 30), None)
+        assert rows[0] == n + 5 and list(rows) == list(wl)
+        rows2, _ = ix.search(q, k, "score >= 30")  # another predicate, same index
+        assert n + 5 not in rows2.tolist()
