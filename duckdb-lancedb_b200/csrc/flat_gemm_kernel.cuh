@@ -188,6 +188,71 @@ __device__ __forceinline__ void gemm_process_chunk(const GemmParams &p, const ui
 	}
 }
 
+// Deferred form for the kernel whose accumulator release sits on the critical path (flat_gemm_ts_kernel: one
+// accumulator's MMAs take 512 clocks, about what its drain takes, so whatever a hit costs BEFORE the release stalls
+// the tensor pipe — measured: emission cost 0.6 ms of a 3.1 ms batch on a 12.5 M-row shard).  A chunk with a hit is
+// only parked: the hitting lanes copy their 32 scores into one of the warp's GEMM_NPEND shared-memory slots
+// ([33 words]: scores + (lane | chunk << 8)); gemm_drain_pending emits them after the accumulator has been released.
+// Returns false when the slots are full (the caller falls back to gemm_process_chunk).
+static constexpr int GEMM_NPEND = 4;
+static constexpr int GEMM_PEND_WORDS = GEMM_NPEND * 33 + 1; // per epilogue warp, last word = count
+
+__device__ __forceinline__ float gemm_chunk_max(const uint32_t (&r)[32]) {
+	float a[10];
+#pragma unroll
+	for (int i = 0; i < 10; i++)
+		a[i] = tc::fmax3(__uint_as_float(r[3 * i]), __uint_as_float(r[3 * i + 1]), __uint_as_float(r[3 * i + 2]));
+	float m1 = tc::fmax3(a[0], a[1], a[2]), m2 = tc::fmax3(a[3], a[4], a[5]), m3 = tc::fmax3(a[6], a[7], a[8]);
+	float m4 = tc::fmax3(a[9], __uint_as_float(r[30]), __uint_as_float(r[31]));
+	return fmaxf(tc::fmax3(m1, m2, m3), m4);
+}
+
+__device__ __forceinline__ void gemm_park_chunk(const GemmParams &p, const uint32_t (&r)[32], float thr, int q, long long row0,
+                                                const EmitBuf &eb, uint32_t *pend, int chunk) {
+	const bool hit = gemm_chunk_max(r) >= thr;
+	const unsigned hm = __ballot_sync(0xFFFFFFFFu, hit);
+	if (hm == 0u) return; // the common case: one vote
+	const int lane = threadIdx.x & 31;
+	const int base = (int)pend[GEMM_NPEND * 33];
+	const int nh = __popc(hm);
+	if (base + nh <= GEMM_NPEND) {
+		if (hit) {
+			uint32_t *dst = pend + (base + __popc(hm & ((1u << lane) - 1u))) * 33;
+#pragma unroll
+			for (int c = 0; c < 32; c++) dst[c] = r[c];
+			dst[32] = (uint32_t)lane | ((uint32_t)chunk << 8);
+		}
+		__syncwarp();
+		if (lane == 0) pend[GEMM_NPEND * 33] = (uint32_t)(base + nh);
+		__syncwarp();
+	} else {
+		gemm_process_chunk(p, r, thr, q, row0, eb); // slots full (cold threshold): emit now
+	}
+}
+
+// after the accumulator's release: every parked chunk is emitted by the lane that owns it
+__device__ __forceinline__ void gemm_drain_pending(const GemmParams &p, float thr, int q, long long tile_row0,
+                                                   const EmitBuf &eb, uint32_t *pend) {
+	const int np = (int)pend[GEMM_NPEND * 33];
+	if (np == 0) return;
+	const int lane = threadIdx.x & 31;
+	for (int s = 0; s < np; s++) {
+		const uint32_t *v = pend + s * 33;
+		const uint32_t meta = v[32];
+		if ((int)(meta & 0xFFu) == lane) {
+			const long long row0 = tile_row0 + 32 * (int)(meta >> 8);
+			uint32_t hits = 0u;
+#pragma unroll
+			for (int c = 0; c < 32; c++) hits |= (__uint_as_float(v[c]) >= thr ? 1u : 0u) << c;
+			hits &= gemm_chunk_valid(p, row0);
+			if (hits) gemm_emit_chunk(p, v, hits, q, row0, eb.slots, eb.count);
+		}
+	}
+	__syncwarp();
+	if (lane == 0) pend[GEMM_NPEND * 33] = 0u;
+	__syncwarp();
+}
+
 // Variant for the K-streamed kernel (flat_gemm_tsk_kernel), whose epilogue has registers to spare and whose
 // workloads (large k) emit two orders of magnitude more candidates: the slow path is taken by the whole warp
 // together and stays in registers (measured on C2, B=4096: 8.9 ms per batch against 13.2 ms with the call).

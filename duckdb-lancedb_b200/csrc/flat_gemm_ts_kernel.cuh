@@ -38,6 +38,9 @@ flat_gemm_ts_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p)
 	// emit buffers: counters [2][QT][128] then slots [2][QT][EB][128]
 	int *ecnt = reinterpret_cast<int *>(thr_s + p.QT * 128);
 	uint2 *eslots = reinterpret_cast<uint2 *>(ecnt + 2 * p.QT * 128);
+	// parked-chunk slots of the 8 epilogue warps (gemm_park_chunk), behind the emit buffers
+	uint32_t *pend_all = reinterpret_cast<uint32_t *>(eslots + (size_t)2 * p.QT * p.EB * 128);
+	for (int i = threadIdx.x; i < 8 * GEMM_PEND_WORDS; i += GEMM_THREADS) pend_all[i] = 0u;
 	for (int i = threadIdx.x; i < 2 * p.QT * 128; i += GEMM_THREADS) ecnt[i] = 0;
 	const bool has_work = p.tile_lo + r < p.tile_hi;
 
@@ -155,22 +158,25 @@ flat_gemm_ts_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p)
 				const long long row0 = tile * GEMM_BN;
 				const EmitBuf eb{p.EB ? eslots + (size_t)((e * p.QT + t) * p.EB) * 128 + lrow : nullptr,
 				                 ecnt + (e * p.QT + t) * 128 + lrow};
+				uint32_t *pend = pend_all + (warp - 2) * GEMM_PEND_WORDS;
 				uint32_t va[32], vb[32];
 				tc::tmem_ld32(taddr, va);
 				tmem_wait_regs(va);
 				tc::tmem_ld32(taddr + 32, vb);
-				gemm_process_chunk(p, va, thr, q, row0, eb);
+				gemm_park_chunk(p, va, thr, q, row0, eb, pend, 0);
 				tmem_wait_regs(vb);
 				tc::tmem_ld32(taddr + 64, va);
-				gemm_process_chunk(p, vb, thr, q, row0 + 32, eb);
+				gemm_park_chunk(p, vb, thr, q, row0 + 32, eb, pend, 1);
 				tmem_wait_regs(va);
 				tc::tmem_ld32(taddr + 96, vb);
-				gemm_process_chunk(p, va, thr, q, row0 + 64, eb);
+				gemm_park_chunk(p, va, thr, q, row0 + 64, eb, pend, 2);
 				tmem_wait_regs(vb);
 				tc::tc_fence_before();
 				__syncwarp();
 				if (lane == 0) tc::mbar_arrive(bar_tempty + 8u * e);
+				// the accumulator is free again: everything below overlaps the next MMAs
 				gemm_process_chunk(p, vb, thr, q, row0 + 96, eb);
+				gemm_drain_pending(p, thr, q, row0, eb, pend);
 			}
 		}
 		if (p.EB) {
@@ -190,7 +196,7 @@ flat_gemm_ts_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p)
 
 static inline size_t gemm_ts_smem_bytes(int QT, int nkb, int S, int EB) {
 	return 1024 + (size_t)S * nkb * GEMM_KB_BYTES + 16u * S + 8 + 32 + 16 + (size_t)QT * 128 * 4 +
-	       (size_t)2 * QT * 128 * 4 + (size_t)2 * QT * EB * 128 * 8;
+	       (size_t)2 * QT * 128 * 4 + (size_t)2 * QT * EB * 128 * 8 + (size_t)8 * GEMM_PEND_WORDS * 4;
 }
 
 } // namespace lb
