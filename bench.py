@@ -538,7 +538,9 @@ def run_b200(args, wl):
             # scan can exceed it) and the nominal 8 TB/s
             roof["peak_nominal"] = 8000.0
             roof["frac_nominal"] = roof["achieved"] / 8000.0
-        roof["traffic"], note = load_traffic(args.workload, B)
+        # the committed capture is of the default shape of the workload; an overridden shape has no measured traffic
+        stock = not args.rows and (args.selectivity is None or args.selectivity == WORKLOADS[args.workload].get("selectivity"))
+        roof["traffic"], note = load_traffic(args.workload, B) if stock else (None, None)
         if note:
             roof["traffic_note"] = note
     if rank == 0:
