@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(256) probe_rows_kernel(const float *__restrict
 // read once per block and reused for QPB queries.
 static const int LUT_QPB = 16;
 __global__ void __launch_bounds__(256) lut_kernel(const float *__restrict__ Qp, int nq, int d, int M, int dsub,
-                                                  const float *__restrict__ codebook, int is_dot,
+                                                  const float *__restrict__ codebook, int is_dot, int transposed,
                                                   float *__restrict__ lut) {
 	extern __shared__ float lut_sm[]; // cb slice [256][dsub+1] + q sub-vectors [QPB][dsub]
 	const int m = blockIdx.x;
@@ -213,7 +213,11 @@ __global__ void __launch_bounds__(256) lut_kernel(const float *__restrict__ Qp, 
 				acc = fmaf(e, e, acc);
 			}
 		}
-		lut[((size_t)(q0 + j) * M + m) * 256 + c] = acc;
+		// transposed ([q][256][M]): the layout of the bank-conflict-free scan (adc_scan_kernel<32>)
+		if (transposed)
+			lut[((size_t)(q0 + j) * 256 + c) * M + m] = acc;
+		else
+			lut[((size_t)(q0 + j) * M + m) * 256 + c] = acc;
 	}
 }
 
@@ -224,6 +228,10 @@ template <int GRAN>
 struct CodeWord;
 template <>
 struct CodeWord<16> {
+	typedef uint4 T;
+};
+template <>
+struct CodeWord<32> { // 16-byte granule, sub-quantizers XOR-rotated by the lane inside every block of 32
 	typedef uint4 T;
 };
 template <>
@@ -238,6 +246,20 @@ struct CodeWord<1> {
 __device__ __forceinline__ float lut4(const float *lut_m, uint32_t w) {
 	// four consecutive sub-quantizers packed in one 32-bit word (little endian)
 	return lut_m[w & 0xFFu] + lut_m[256 + ((w >> 8) & 0xFFu)] + lut_m[512 + ((w >> 16) & 0xFFu)] + lut_m[768 + (w >> 24)];
+}
+
+// Rotated layout (M % 32 == 0): stored position i of a 32-wide sub-quantizer block holds, for the row of lane l, the
+// code of sub-quantizer (i ^ l), and the table is transposed ([256][M]).  The 32 lanes of a lookup then read the 32
+// different sub-quantizers of the block: word index c*M + 32*jj + (i ^ l) = bank (i ^ l), whatever the codes are.
+// `base` = table + 128*jj bytes, `i0` = first stored position of the four bytes of w, M4 = 4*M, lane4 = 4*lane.
+template <uint32_t M4>
+__device__ __forceinline__ float lut4_rot(const unsigned char *base, uint32_t w, int i0, uint32_t lane4) {
+	const uint32_t c0 = w & 0xFFu, c1 = __byte_perm(w, 0, 0x4441), c2 = __byte_perm(w, 0, 0x4442), c3 = w >> 24;
+	const float a = *reinterpret_cast<const float *>(base + c0 * M4 + ((uint32_t)((i0 + 0) << 2) ^ lane4));
+	const float b = *reinterpret_cast<const float *>(base + c1 * M4 + ((uint32_t)((i0 + 1) << 2) ^ lane4));
+	const float c = *reinterpret_cast<const float *>(base + c2 * M4 + ((uint32_t)((i0 + 2) << 2) ^ lane4));
+	const float d = *reinterpret_cast<const float *>(base + c3 * M4 + ((uint32_t)((i0 + 3) << 2) ^ lane4));
+	return (a + b) + (c + d);
 }
 
 // exact distance of (query qv, row of `key`) by one warp -> (distance, row) key on every lane (a14)
@@ -283,7 +305,8 @@ struct AdcParams {
 	int32_t *out_counts;
 };
 
-template <int GRAN>
+// NB = M / 32 for the rotated layout (GRAN 32; compile-time so that every table offset is an immediate), else 0
+template <int GRAN, int NB>
 __global__ void __launch_bounds__(512) adc_scan_kernel(const __grid_constant__ AdcParams p) {
 	extern __shared__ __align__(128) unsigned char smem_raw[];
 	const int nwarps = blockDim.x >> 5;
@@ -317,10 +340,82 @@ __global__ void __launch_bounds__(512) adc_scan_kernel(const __grid_constant__ A
 	sel.init(bufs + (size_t)warp * cap, cap, kc);
 	const float qq = p.qn2[q];
 	const int metric = p.metric;
-	const int chunks = M / GRAN;
+	constexpr int GBYTES = GRAN == 32 ? 16 : GRAN;
+	const int chunks = M / GBYTES;
+	const uint32_t lane4 = lane << 2;
 	typedef typename CodeWord<GRAN>::T word_t;
 	bool lut_ready = false;
 
+	if constexpr (GRAN == 32 && NB <= 3) {
+		// Software-pipelined form of the loop below: a warp walks its blocks of all its lists as one sequence and
+		// loads the code words of block i+1 before it looks up block i, so the HBM latency overlaps the lookups.
+		constexpr int CH = NB * 2;
+		int pi = ps - PS;
+		long long b = 0, b1 = 0; // next block of the current list, end of the list
+		float cst_list = 0.f;
+		// advance to the warp's next block; false when the lists are exhausted
+		auto next_block = [&](long long &blk, float &cst) -> bool {
+			while (b >= b1) {
+				pi += PS;
+				if (pi >= p.nprobes_eff) return false;
+				const u64 pk = p.probe_keys[(size_t)q * p.probe_stride + pi];
+				if (pk == KEY_INVALID) continue;
+				const int part = (int)key_row(pk);
+				cst_list = (metric == METRIC_DOT) ? 1.0f : key_dist(pk) - qq;
+				const long long pb0 = p.pad_offsets[part] >> 5, pnb = (p.pad_offsets[part + 1] >> 5) - pb0;
+				b = pb0 + pnb * j / J + warp;
+				b1 = pb0 + pnb * (j + 1) / J;
+			}
+			blk = b, cst = cst_list;
+			b += nwarps;
+			return true;
+		};
+		uint4 wn[CH];
+		int row_n = -1;
+		float rterm_n = 0.f, cst_n = 0.f;
+		auto fetch = [&](long long blk) {
+			const long long slot = (blk << 5) + lane;
+			row_n = __ldg(p.slot_rows + slot);
+			rterm_n = (metric == METRIC_DOT) ? 0.f : __ldg(p.row_term + slot);
+			const uint4 *cp = reinterpret_cast<const uint4 *>(p.codes_il) + (size_t)blk * CH * 32 + lane;
+#pragma unroll
+			for (int u = 0; u < CH; u++) wn[u] = __ldg(cp + (size_t)u * 32);
+		};
+		long long blk;
+		bool more = next_block(blk, cst_n);
+		if (more) fetch(blk);
+		tc::mbar_wait(bar, 0);
+		lut_ready = true;
+		while (more) {
+			uint4 w[CH];
+#pragma unroll
+			for (int u = 0; u < CH; u++) w[u] = wn[u];
+			const int row = row_n;
+			const float rterm = rterm_n, cst = cst_n;
+			more = next_block(blk, cst_n);
+			if (more) fetch(blk);
+			float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+			for (int u = 0; u < CH; u++) {
+				const unsigned char *lb = reinterpret_cast<const unsigned char *>(lut) + (u >> 1) * 128;
+				const int i0 = (u & 1) * 16;
+				a0 += lut4_rot<NB * 128u>(lb, w[u].x, i0, lane4) + lut4_rot<NB * 128u>(lb, w[u].y, i0 + 4, lane4);
+				a1 += lut4_rot<NB * 128u>(lb, w[u].z, i0 + 8, lane4) + lut4_rot<NB * 128u>(lb, w[u].w, i0 + 12, lane4);
+			}
+			const float acc = a0 + a1;
+			float dist;
+			if (metric == METRIC_DOT)
+				dist = 1.0f + acc;
+			else {
+				dist = acc + rterm + cst;
+				if (metric == METRIC_COSINE) dist *= 0.5f;
+			}
+			bool live = row >= 0;
+			if (live && p.deleted) live = !bit_test(p.deleted, row);
+			if (live && p.allow) live = (row < p.allow_bits) && bit_test(p.allow, row);
+			sel.push(live, make_key(dist, (uint32_t)row));
+		}
+	} else
 	for (int pi = ps; pi < p.nprobes_eff; pi += PS) {
 		const u64 pk = p.probe_keys[(size_t)q * p.probe_stride + pi];
 		if (pk == KEY_INVALID) continue;
@@ -334,7 +429,31 @@ __global__ void __launch_bounds__(512) adc_scan_kernel(const __grid_constant__ A
 			const float rterm = (metric == METRIC_DOT) ? 0.f : __ldg(p.row_term + slot);
 			const word_t *cp = reinterpret_cast<const word_t *>(p.codes_il) + (size_t)b * chunks * 32 + lane;
 			float acc = 0.f;
-			if (GRAN == 16) {
+			if (GRAN == 32) {
+				// chunk ch = stored positions 16*(ch&1) .. +15 of sub-quantizer block ch/2
+				constexpr int CH = NB * 2;
+				float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+				for (int c0 = 0; c0 < CH; c0 += 6) {
+					uint4 w[6];
+#pragma unroll
+					for (int u = 0; u < 6; u++)
+						if (c0 + u < CH) w[u] = __ldg(reinterpret_cast<const uint4 *>(cp) + (size_t)(c0 + u) * 32);
+					if (!lut_ready) {
+						tc::mbar_wait(bar, 0);
+						lut_ready = true;
+					}
+#pragma unroll
+					for (int u = 0; u < 6; u++)
+						if (c0 + u < CH) {
+							const unsigned char *lb = reinterpret_cast<const unsigned char *>(lut) + ((c0 + u) >> 1) * 128;
+							const int i0 = ((c0 + u) & 1) * 16;
+							a0 += lut4_rot<NB * 128u>(lb, w[u].x, i0, lane4) + lut4_rot<NB * 128u>(lb, w[u].y, i0 + 4, lane4);
+							a1 += lut4_rot<NB * 128u>(lb, w[u].z, i0 + 8, lane4) + lut4_rot<NB * 128u>(lb, w[u].w, i0 + 12, lane4);
+						}
+				}
+				acc = a0 + a1;
+			} else if (GRAN == 16) {
 				// issue all loads of the row first (M/16 independent 128-bit loads)
 				for (int c0 = 0; c0 < chunks; c0 += 6) {
 					uint4 w[6];
@@ -467,7 +586,8 @@ __global__ void build_slots_kernel(const long long *__restrict__ part_offsets, c
 	}
 }
 
-// codes[n][M] (exchange) -> interleaved [n_pad/32][M/gran][32][gran]
+// codes[n][M] (exchange) -> interleaved [n_pad/32][M/gran][32][gran]; gran 32 = 16-byte granules with the
+// sub-quantizers of every block of 32 XOR-rotated by the row's lane (lut4_rot)
 __global__ void interleave_codes_kernel(const uint8_t *__restrict__ codes, const long long *__restrict__ slot_src, int M,
                                         int gran, long long n_pad, uint8_t *__restrict__ codes_il) {
 	long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -478,6 +598,10 @@ __global__ void interleave_codes_kernel(const uint8_t *__restrict__ codes, const
 	uint8_t v = src >= 0 ? codes[(size_t)src * M + m] : 0;
 	long long b = s >> 5;
 	int r = (int)(s & 31);
+	if (gran == 32) {
+		m = (m & ~31) | ((m & 31) ^ r);
+		gran = 16;
+	}
 	codes_il[(((size_t)b * (M / gran) + m / gran) * 32 + r) * gran + (m % gran)] = v;
 }
 

@@ -13,7 +13,7 @@ struct IvfPqIndex {
 	int metric = METRIC_L2;
 	int dim = 0, P = 0, M = 0, dsub = 0;
 	int64_t n_indexed = 0; // rows [0, n_indexed) are covered; later rows are scanned exactly
-	int gran = 16;         // interleave granule in bytes (16, 4 or 1)
+	int gran = 16;         // interleave granule in bytes (16, 4 or 1); 32 = 16-byte granules, lane-rotated (M % 32 == 0)
 	int64_t n_pad = 0;     // padded slots (every partition rounded up to 32 rows)
 	int64_t max_part_rows = 0;
 

@@ -15,6 +15,9 @@ struct IvfPqExchange {
 static void finalize_index(IvfPqIndex &ix, IvfPqExchange &ex, long long label_base, cudaStream_t s, int64_t *launches) {
 	const int P = ix.P, M = ix.M;
 	ix.gran = (M % 16 == 0) ? 16 : (M % 4 == 0 ? 4 : 1);
+	if (M % 32 == 0) ix.gran = 32; // rotated granules + transposed table: no shared-memory bank conflicts in the scan
+	if (const char *e = getenv("LANCE_B200_ADC_ROT")) // tuning hook (A/B of the two layouts)
+		if (atoi(e) == 0 && ix.gran == 32) ix.gran = 16;
 	std::vector<long long> pad(P + 1, 0);
 	ix.max_part_rows = 0;
 	for (int p = 0; p < P; p++) {
@@ -119,9 +122,9 @@ void Store::drop_index() {
 }
 
 // ------------------------------------------------------------------ search
-template <int GRAN>
+template <int GRAN, int NB = 0>
 static void launch_adc(const AdcParams &ap, int nwarps, int S, int nq, size_t smem, cudaStream_t s) {
-	auto kern = adc_scan_kernel<GRAN>;
+	auto kern = adc_scan_kernel<GRAN, NB>;
 	if (smem > 48 * 1024) LB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 	kern<<<dim3(S, nq), nwarps * 32, smem, s>>>(ap);
 	LB_CUDA(cudaGetLastError());
@@ -192,7 +195,7 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 		size_t smem = ((size_t)256 * (ix.dsub + 1) + (size_t)LUT_QPB * ix.dsub) * sizeof(float);
 		if (smem > 48 * 1024) LB_CUDA(cudaFuncSetAttribute(lut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 		lut_kernel<<<dim3(M, blocks_for(nq, LUT_QPB)), 256, smem, s>>>(Qp, nq, d, M, ix.dsub, ix.codebook.as<float>(),
-		                                                               metric_ == METRIC_DOT ? 1 : 0, lut);
+		                                                               metric_ == METRIC_DOT ? 1 : 0, ix.gran == 32 ? 1 : 0, lut);
 		LB_CUDA(cudaGetLastError());
 		launches++;
 	}
@@ -237,6 +240,17 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 		LB_CUDA(cudaMemsetAsync(tickets, 0, (size_t)nq * sizeof(unsigned), s));
 		int tix = timer_.begin(KC_ADC_SCAN, s);
 		switch (ix.gran) {
+		case 32: // the table must fit in shared memory, so M <= 192
+			switch (M / 32) {
+			case 1: launch_adc<32, 1>(ap, nwarps, S, nq, smem, s); break;
+			case 2: launch_adc<32, 2>(ap, nwarps, S, nq, smem, s); break;
+			case 3: launch_adc<32, 3>(ap, nwarps, S, nq, smem, s); break;
+			case 4: launch_adc<32, 4>(ap, nwarps, S, nq, smem, s); break;
+			case 5: launch_adc<32, 5>(ap, nwarps, S, nq, smem, s); break;
+			case 6: launch_adc<32, 6>(ap, nwarps, S, nq, smem, s); break;
+			default: throw Error("IVF_PQ: sub-vector count too large for the ADC scan's shared memory");
+			}
+			break;
 		case 16: launch_adc<16>(ap, nwarps, S, nq, smem, s); break;
 		case 4: launch_adc<4>(ap, nwarps, S, nq, smem, s); break;
 		default: launch_adc<1>(ap, nwarps, S, nq, smem, s);
