@@ -154,16 +154,24 @@ __device__ inline void block_radix_select(KeyAt key_at, int m, int k, u64 *out) 
 	while (true) {
 		for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
 		__syncthreads();
-		for (int i0 = 0; i0 < m; i0 += blockDim.x) {
-			const int i = i0 + threadIdx.x;
-			int digit = -1 - (int)(threadIdx.x & 31); // lanes without a key match nobody
-			if (i < m) {
-				const u64 key = key_at(i);
-				if (bits == 0 || (key >> (64 - bits)) == prefix) digit = (int)((key >> (56 - bits)) & 255u);
+		// four keys per thread and round: the loads (L2 round trips when key_at reads global memory) overlap
+		for (int i0 = 0; i0 < m; i0 += 4 * (int)blockDim.x) {
+			u64 key[4];
+#pragma unroll
+			for (int u = 0; u < 4; u++) {
+				const int i = i0 + u * (int)blockDim.x + (int)threadIdx.x;
+				key[u] = i < m ? key_at(i) : 0ull;
 			}
-			// distance keys share their leading digits: one shared-memory atomic per distinct digit of the warp
-			const unsigned peers = __match_any_sync(0xFFFFFFFFu, digit);
-			if (digit >= 0 && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&hist[digit], __popc(peers));
+#pragma unroll
+			for (int u = 0; u < 4; u++) {
+				const int i = i0 + u * (int)blockDim.x + (int)threadIdx.x;
+				if (i0 + u * (int)blockDim.x >= m) break; // uniform
+				int digit = -1 - (int)(threadIdx.x & 31); // lanes without a key match nobody
+				if (i < m && (bits == 0 || (key[u] >> (64 - bits)) == prefix)) digit = (int)((key[u] >> (56 - bits)) & 255u);
+				// distance keys share their leading digits: one shared-memory atomic per distinct digit of the warp
+				const unsigned peers = __match_any_sync(0xFFFFFFFFu, digit);
+				if (digit >= 0 && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&hist[digit], __popc(peers));
+			}
 		}
 		__syncthreads();
 		if (threadIdx.x < 32) {
@@ -200,14 +208,24 @@ __device__ inline void block_radix_select(KeyAt key_at, int m, int k, u64 *out) 
 	for (int i = threadIdx.x; i < k; i += blockDim.x) out[i] = KEY_INVALID; // fewer than k valid keys: padding
 	__syncthreads();
 	u64 *binl = out + k;
-	for (int i = threadIdx.x; i < m; i += blockDim.x) {
-		const u64 key = key_at(i);
-		const u64 top = key >> (64 - bits);
-		if (top < prefix)
-			out[atomicAdd(&s_nout, 1)] = key;
-		else if (top == prefix) {
-			const int pos = atomicAdd(&s_nbin, 1);
-			if (pos < 32) binl[pos] = key;
+	for (int i0 = 0; i0 < m; i0 += 4 * (int)blockDim.x) {
+		u64 key[4];
+#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			const int i = i0 + u * (int)blockDim.x + (int)threadIdx.x;
+			key[u] = i < m ? key_at(i) : KEY_INVALID;
+		}
+#pragma unroll
+		for (int u = 0; u < 4; u++) {
+			const int i = i0 + u * (int)blockDim.x + (int)threadIdx.x;
+			if (i >= m) continue;
+			const u64 top = key[u] >> (64 - bits);
+			if (top < prefix)
+				out[atomicAdd(&s_nout, 1)] = key[u];
+			else if (top == prefix) {
+				const int pos = atomicAdd(&s_nbin, 1);
+				if (pos < 32) binl[pos] = key[u];
+			}
 		}
 	}
 	__syncthreads();

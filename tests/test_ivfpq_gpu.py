@@ -87,6 +87,39 @@ def test_checker_trained_index_on_gpu(gpu, oracle_mod, metric, d, P, M):
         assert list(l) == list(wl)
 
 
+@pytest.mark.parametrize("d,M", [(64, 32), (128, 64), (96, 96), (128, 128), (160, 160), (192, 192)])
+def test_rotated_scan_layout_all_widths(gpu, oracle_mod, d, M):
+    """M % 32 == 0 selects the lane-rotated code layout with the transposed table (adc_scan_kernel<32, M/32>:
+    software-pipelined for M <= 96, plain loop above); every width must give the oracle's candidates, with ragged
+    lists (sizes not multiples of 32), deletes and a prefilter."""
+    rng = np.random.default_rng(900 + M)
+    n, P = 5000, 7
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Q = rng.standard_normal((2, d), dtype=np.float32)
+    for metric in ("l2", "dot"):
+        ix = oracle_mod.IvfPqIndex.train(X, metric, P, M, iters=3)
+        with gpu.LanceHandle(d, metric) as h:
+            h.add_batch(X)
+            h.set_ivfpq(ix.centroids, ix.codebook, ix.part_offsets, ix.row_ids, ix.codes)
+            dead = rng.choice(n, 300, replace=False)
+            h.delete_batch(dead)
+            deleted = oracle_mod.make_bitmap(np.isin(np.arange(n), dead))
+            allow = gpu.make_bitmap(rng.random(n) < 0.3)
+            for j in range(2):
+                compare_with_oracle(oracle_mod, h, ix, X, Q[j], 10, 3, 1, metric, None, deleted, what=f"rot {metric} M={M} q{j}")
+                compare_with_oracle(oracle_mod, h, ix, X, Q[j], 25, P, 2, metric, allow, deleted, what=f"rot {metric} M={M} q{j} allow")
+            # a batch (one CTA per query walks all its lists) equals the single-query launches (lists split over CTAs)
+            Qb = rng.standard_normal((70, d), dtype=np.float32)
+            L, D, C = h.search_batch(Qb, 10, nprobes=4, refine_factor=0)
+            for j in (0, 33, 69):
+                l, dd = h.search(Qb[j], 10, nprobes=4, refine_factor=0)
+                assert list(l) == list(L[j, :C[j]])
+                # the (query, partition) term comes from the tiled probe in a batch, from the streaming one otherwise
+                np.testing.assert_allclose(dd, D[j, :C[j]], rtol=1e-5)
+            back = h.get_ivfpq()
+            np.testing.assert_array_equal(back["codes"], ix.codes)  # the exchange layout is not rotated
+
+
 @pytest.mark.parametrize("metric", ["l2", "cosine", "dot"])
 def test_gpu_trained_index_exported_to_checker(gpu, oracle_mod, metric):
     rng = np.random.default_rng(77)
