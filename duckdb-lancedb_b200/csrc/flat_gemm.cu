@@ -256,7 +256,11 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	const long long ntiles = (n + GEMM_BN - 1) / GEMM_BN;
 	// segment growth: candidates per refresh ~ k * growth * (margin inflation); keep that well under TC_CAP
 	// total slow-path hits per query ~ (#segments) * growth * k: small k affords few, large segments
-	int growth = std::max(2, std::min(4, std::min(TC_CAP / (8 * k), 512 / k)));
+	// A single query tile (<= 128 queries) emits little, so its launches + refreshes dominate: grow faster
+	// (B200, B=64: C2 0.535 -> 0.49 ms, C5 shape 1.53 -> 1.44 ms per batch); full batches are emission-bound at 4.
+	const bool one_tile = nq_total <= 128; // query tile rows (the MMA M dimension)
+	const int growth_hi = one_tile ? (k <= 32 ? 16 : 8) : 4;
+	int growth = std::max(2, std::min(growth_hi, std::min(TC_CAP / (8 * k), (one_tile ? 2048 : 512) / k)));
 	long long seed_tiles = TC_SEED_TILES;
 	if (const char *e = getenv("LANCE_B200_TC_GROWTH")) growth = std::max(2, atoi(e)); // tuning hooks
 	if (const char *e = getenv("LANCE_B200_TC_SEED")) seed_tiles = std::max(1, atoi(e));
