@@ -323,6 +323,9 @@ __global__ void __launch_bounds__(256, (QB == 1 ? 3 : (QB == 2 ? 2 : 1))) flat_s
 	for (int j = 0; j < QB && j < nq_valid; j++)
 		block_final_select(level2 + (size_t)j * G * k, (long long)G * k, k, cap, bufs, cnts, label_base, (size_t)j, out_labels,
 		                   out_dist, out_counts, out_keys);
+	// Every other block took its tickets after its last access to the header, so the header can be handed back
+	// all-ones: the next pass over a persistent header needs no memset launch.
+	for (int i = threadIdx.x; i < SCAN_HDR_WORDS; i += blockDim.x) g_tau[i] = ~0ull;
 }
 
 // Final select: keys[q][m] (KEY_INVALID entries ignored) -> sorted (label, distance) lists.
@@ -460,12 +463,15 @@ void fill_u64(u64 *p, long long n, u64 v, cudaStream_t s, int64_t *launches) {
 // Runs the scan for a.nq queries (any count) in passes of plan.QB; results land in the out_* device buffers.
 void run_flat_scan(const FlatScanArgs &a, const FlatScanPlan &p, void *scratch, cudaStream_t s, int64_t *launches) {
 	// scratch header (all-ones at the start of a pass): g_tau[8] | control words of the final select
-	u64 *g_tau = reinterpret_cast<u64 *>(scratch);
-	u64 *partials = g_tau + SCAN_HDR_WORDS;
+	static_assert(SCAN_HDR_BYTES == SCAN_HDR_WORDS * sizeof(u64), "header size");
+	const bool persistent = a.hdr && a.hdr_clean;
+	u64 *g_tau = persistent ? a.hdr : reinterpret_cast<u64 *>(scratch);
+	u64 *partials = reinterpret_cast<u64 *>(scratch) + SCAN_HDR_WORDS;
 	int G = scan_groups(p.grid, a.k);
 	for (int q0 = 0; q0 < a.nq; q0 += p.QB) {
 		int nv = a.nq - q0 < p.QB ? a.nq - q0 : p.QB;
-		LB_CUDA(cudaMemsetAsync(g_tau, 0xFF, SCAN_HDR_WORDS * sizeof(u64), s));
+		if (!persistent || !*a.hdr_clean) LB_CUDA(cudaMemsetAsync(g_tau, 0xFF, SCAN_HDR_WORDS * sizeof(u64), s));
+		if (persistent) *a.hdr_clean = false; // until the launch below is in the stream
 		const float *dQ = a.dQ + (size_t)q0 * a.d;
 		const float *X = a.X;
 		long long n = a.n, allow_bits = a.allow_bits, row_begin = a.row_begin, label_base = a.label_base;
@@ -481,6 +487,7 @@ void run_flat_scan(const FlatScanArgs &a, const FlatScanPlan &p, void *scratch, 
 		LB_CUDA(cudaLaunchKernel(p.kernel, dim3(p.grid), dim3(p.nwarps * 32), args, p.smem, s));
 		if (a.timer) a.timer->end(tix, s);
 		if (launches) (*launches)++;
+		if (persistent) *a.hdr_clean = true; // the pass's last block restores the header
 	}
 }
 

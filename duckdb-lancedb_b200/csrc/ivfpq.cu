@@ -288,7 +288,7 @@ struct AdcParams {
 	const uint32_t *deleted;
 	int kc, cap, PS;
 	u64 *partials;      // [nq][S][kc]
-	unsigned *tickets;  // [nq], zero before the launch
+	unsigned *tickets;  // [nq], zero before the launch; the last CTA of a query zeroes its ticket again
 	u64 *cand;          // [nq][kc] the kc best ADC keys (ascending)
 	// refine + final select, run by the last CTA of a query
 	const float *X;     // raw vectors
@@ -516,6 +516,7 @@ __global__ void __launch_bounds__(512) adc_scan_kernel(const __grid_constant__ A
 	if (threadIdx.x == 0) cnts[8] = (atomicAdd(p.tickets + q, 1u) == (unsigned)S - 1u);
 	__syncthreads();
 	if (!cnts[8]) return;
+	if (threadIdx.x == 0) p.tickets[q] = 0u; // every other CTA of the query has arrived: ready for the next launch
 	__threadfence();
 	block_final_select(p.partials + (size_t)q * S * kc, (long long)S * kc, kc, cap, bufs, cnts, 0, (size_t)q, nullptr, nullptr,
 	                   nullptr, p.cand);

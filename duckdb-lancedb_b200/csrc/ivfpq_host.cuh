@@ -224,7 +224,13 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 	u64 *cand = partials + (size_t)nq * S * kc;
 	u64 *fin = cand + (size_t)nq * kc;
 	u64 *tailk = fin + (size_t)nq * fin_stride;
-	unsigned *tickets = reinterpret_cast<unsigned *>(tailk + (size_t)nq * std::max(tail_k, 1));
+	// arrival tickets: persistent and zero between launches (the last CTA of a query hands its ticket back), so the
+	// scan is one launch; zeroed here only when the buffer is new
+	if (ws.adc_tickets.bytes < (size_t)nq * sizeof(unsigned)) {
+		ws.adc_tickets.ensure(std::max<size_t>((size_t)nq * sizeof(unsigned), 4096));
+		LB_CUDA(cudaMemsetAsync(ws.adc_tickets.p, 0, ws.adc_tickets.bytes, s));
+	}
+	unsigned *tickets = ws.adc_tickets.as<unsigned>();
 	{
 		// 4-6 in one launch: the last CTA of a query merges the slices' lists (5), refines (6, a14) and, when there is no
 		// unindexed tail, writes the sorted top-k (8)
@@ -237,7 +243,6 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 		ap.X = X_.as<float>(), ap.d = d, ap.Q = d_queries, ap.refine = refine >= 1 ? 1 : 0, ap.fin = fin, ap.fin_stride = fin_stride;
 		ap.fuse_final = tail_k == 0 ? 1 : 0, ap.k = k, ap.label_base = label_base_;
 		ap.out_labels = d_out_labels, ap.out_dist = d_out_dist, ap.out_counts = d_out_counts;
-		LB_CUDA(cudaMemsetAsync(tickets, 0, (size_t)nq * sizeof(unsigned), s));
 		int tix = timer_.begin(KC_ADC_SCAN, s);
 		switch (ix.gran) {
 		case 32: // the table must fit in shared memory, so M <= 192

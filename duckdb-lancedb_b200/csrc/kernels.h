@@ -90,7 +90,12 @@ struct FlatScanArgs {
 	u64 *out_keys = nullptr;       // [nq][k] device (nullable): raw keys, row-relative
 	long long row_begin = 0;       // only rows >= row_begin are scanned (IVF_PQ's unindexed tail)
 	KernelTimer *timer = nullptr;
+	// Optional persistent scan header (SCAN_HDR_BYTES, device) + its host-side "is all-ones" flag: the last block of a
+	// pass leaves the header as the next pass needs it, so a pass is one launch instead of memset + launch.
+	u64 *hdr = nullptr;
+	bool *hdr_clean = nullptr;
 };
+static constexpr size_t SCAN_HDR_BYTES = 128 * sizeof(u64);
 
 struct FlatScanPlan {
 	int QB = 1;     // queries per pass (1, 2 or 4)

@@ -377,6 +377,12 @@ void Store::flat_search_locked(const float *d_queries, int nq, int k, const uint
 	a.timer = &timer_;
 	FlatScanPlan p = plan_flat_scan(a.X, metric_, dim_, k, nq, n_rows_, num_sms_);
 	ws.work.ensure(flat_scan_scratch_bytes(p, k));
+	if (!ws.scan_hdr.p) {
+		ws.scan_hdr.alloc(SCAN_HDR_BYTES);
+		ws.scan_hdr_clean = false;
+	}
+	a.hdr = ws.scan_hdr.as<u64>();
+	a.hdr_clean = &ws.scan_hdr_clean;
 	run_flat_scan(a, p, ws.work.p, s, &launches);
 	std::lock_guard<std::mutex> g(stat_mu_);
 	simt_batches_++;

@@ -39,6 +39,9 @@ struct Workspace {
 	std::mutex mu;                 // held while work that uses the buffers is being enqueued
 	DevBuf q, allow, out_labels, out_dist, out_counts, work, work2, work3, work4;
 	DevBuf probe_mat; // batched IVF probe: (distance, partition) keys [queries][P]
+	DevBuf scan_hdr;  // persistent header of the flat scan (kernels.h SCAN_HDR_BYTES), all-ones between passes
+	bool scan_hdr_clean = false;
+	DevBuf adc_tickets; // persistent arrival tickets of the ADC scan (one per query), zero between launches
 	explicit Workspace(bool own_stream);
 	~Workspace();
 };
