@@ -338,8 +338,8 @@ __global__ void __launch_bounds__(256) topk_merge_kernel(const u64 *__restrict__
 	int *cnts = reinterpret_cast<int *>(smem_raw);
 	u64 *bufs = reinterpret_cast<u64 *>(smem_raw + 64);
 	const int q = blockIdx.x;
-	block_final_select(keys + (size_t)q * m, m, k, cap, bufs, cnts, label_base, (size_t)q, out_labels, out_dist,
-	                   out_counts, out_keys);
+	block_final_select<true>(keys + (size_t)q * m, m, k, cap, bufs, cnts, label_base, (size_t)q, out_labels, out_dist,
+	                         out_counts, out_keys);
 }
 
 __global__ void fill_u64_kernel(u64 *p, long long n, u64 v) {

@@ -246,9 +246,98 @@ __device__ inline void block_radix_select(KeyAt key_at, int m, int k, u64 *out) 
 	__syncthreads();
 }
 
+// Same selection for m <= 16 * blockDim.x with the keys held in registers: every key is loaded ONCE (16 independent
+// loads per thread) instead of once per radix pass — the passes of a one-block select over a few thousand keys in
+// global memory are otherwise a chain of L2 round trips (IVF probe select: 4 096 centroid keys -> nprobes).
+template <class KeyAt>
+__device__ inline void block_radix_select_regs(KeyAt key_at, int m, int k, u64 *out) {
+	__shared__ int hist[256];
+	__shared__ int s_need, s_digit, s_bin, s_nout, s_nbin;
+	const int nt = (int)blockDim.x, tid = (int)threadIdx.x;
+	u64 key[16];
+#pragma unroll
+	for (int u = 0; u < 16; u++) key[u] = (u * nt + tid < m) ? key_at(u * nt + tid) : 0ull;
+	u64 prefix = 0;
+	int bits = 0, need = k;
+	__syncthreads();
+	while (true) {
+		for (int i = tid; i < 256; i += nt) hist[i] = 0;
+		__syncthreads();
+#pragma unroll
+		for (int u = 0; u < 16; u++) {
+			if (u * nt >= m) break; // uniform
+			int digit = -1 - (tid & 31); // lanes without a key match nobody
+			if (u * nt + tid < m && (bits == 0 || (key[u] >> (64 - bits)) == prefix)) digit = (int)((key[u] >> (56 - bits)) & 255u);
+			const unsigned peers = __match_any_sync(0xFFFFFFFFu, digit);
+			if (digit >= 0 && (tid & 31) == __ffs(peers) - 1) atomicAdd(&hist[digit], __popc(peers));
+		}
+		__syncthreads();
+		if (tid < 32) {
+			const int lane = tid;
+			int c[8], sum = 0;
+#pragma unroll
+			for (int j = 0; j < 8; j++) c[j] = hist[lane * 8 + j], sum += c[j];
+			int incl = sum;
+			for (int o = 1; o < 32; o <<= 1) {
+				int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+				if (lane >= o) incl += v;
+			}
+			int before = incl - sum;
+			const bool mine = before < need && incl >= need;
+			if (mine) {
+				int j = 0;
+				while (before + c[j] < need) before += c[j], j++;
+				s_digit = lane * 8 + j;
+				s_need = need - before;
+				s_bin = c[j];
+			}
+		}
+		__syncthreads();
+		prefix = (prefix << 8) | (u64)s_digit;
+		bits += 8;
+		need = s_need;
+		const int bin = s_bin;
+		__syncthreads();
+		if (bin <= 32 || bits == 64) break;
+	}
+	if (tid == 0) s_nout = 0, s_nbin = 0;
+	for (int i = tid; i < k; i += nt) out[i] = KEY_INVALID;
+	__syncthreads();
+	u64 *binl = out + k;
+#pragma unroll
+	for (int u = 0; u < 16; u++) {
+		if (u * nt + tid >= m) continue;
+		const u64 top = key[u] >> (64 - bits);
+		if (top < prefix)
+			out[atomicAdd(&s_nout, 1)] = key[u];
+		else if (top == prefix) {
+			const int pos = atomicAdd(&s_nbin, 1);
+			if (pos < 32) binl[pos] = key[u];
+		}
+	}
+	__syncthreads();
+	if (tid < 32) {
+		const int lane = tid, nb = min(s_nbin, 32);
+		u64 v = lane < nb ? binl[lane] : KEY_INVALID;
+		for (int size = 2; size <= 32; size <<= 1)
+			for (int stride = size >> 1; stride > 0; stride >>= 1) {
+				const u64 o = __shfl_xor_sync(0xFFFFFFFFu, v, stride);
+				const bool up = (lane & size) == 0, lower = (lane & stride) == 0;
+				v = (lower == up) ? (v < o ? v : o) : (v < o ? o : v);
+			}
+		const int base = s_nout;
+		__syncwarp();
+		if (lane < need) out[base + lane] = v;
+	}
+	__syncthreads();
+}
+
 // Final select by a whole block: src[0..m) keys (KEY_INVALID entries ignored, read through L2 because other
 // SMs may have written them) -> sorted (label, distance) list of query slot `q`.  All threads of the block
 // call it; bufs = nwarps*cap keys of shared memory (cnts is unused, kept for the callers' layouts).
+// REGS: lists of up to 16 keys per thread go through block_radix_select_regs (standalone select kernels only: the
+// 32 extra live registers would cost the scan kernels occupancy).
+template <bool REGS = false>
 __device__ inline void block_final_select(const u64 *__restrict__ src, long long m, int k, int cap, u64 *bufs, int *cnts,
                                           long long label_base, size_t q, int64_t *__restrict__ out_labels,
                                           float *__restrict__ out_dist, int32_t *__restrict__ out_counts,
@@ -265,7 +354,10 @@ __device__ inline void block_final_select(const u64 *__restrict__ src, long long
 		block_bitonic_sort(bufs, n, IdentityMap());
 	} else {
 		// long list: radix-select the k smallest, then sort just those
-		block_radix_select([=](int i) { return __ldcg(src + i); }, (int)m, k, bufs);
+		if (REGS && m <= 16ll * (long long)blockDim.x)
+			block_radix_select_regs([=](int i) { return __ldcg(src + i); }, (int)m, k, bufs);
+		else
+			block_radix_select([=](int i) { return __ldcg(src + i); }, (int)m, k, bufs);
 		int n = 64;
 		while (n < k) n <<= 1;
 		for (int i = k + threadIdx.x; i < n; i += blockDim.x) bufs[i] = KEY_INVALID;
