@@ -56,6 +56,16 @@ Workspace::Workspace(bool own_stream) {
 }
 Workspace::~Workspace() {
 	if (stream) cudaStreamDestroy(stream);
+	if (h_stage) cudaFreeHost(h_stage);
+}
+void *Workspace::stage(size_t bytes) {
+	if (bytes > h_stage_bytes) {
+		if (h_stage) cudaFreeHost(h_stage);
+		h_stage = nullptr, h_stage_bytes = 0;
+		LB_CUDA(cudaMallocHost(&h_stage, bytes + bytes / 2 + 4096));
+		h_stage_bytes = bytes + bytes / 2 + 4096;
+	}
+	return h_stage;
 }
 
 // ------------------------------------------------------------------ Store
@@ -305,11 +315,22 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 	auto io = acquire_io();
 	try {
 		cudaStream_t s = io->stream;
-		io->q.ensure((size_t)nq * dim_ * sizeof(float));
-		io->out_labels.ensure((size_t)nq * k * sizeof(int64_t));
-		io->out_dist.ensure((size_t)nq * k * sizeof(float));
-		io->out_counts.ensure((size_t)nq * sizeof(int32_t));
-		LB_CUDA(cudaMemcpyAsync(io->q.p, queries, (size_t)nq * dim_ * sizeof(float), cudaMemcpyHostToDevice, s));
+		const size_t qb = (size_t)nq * dim_ * sizeof(float);
+		const size_t lb = (size_t)nq * k * sizeof(int64_t), db = (size_t)nq * k * sizeof(float), cb = (size_t)nq * sizeof(int32_t);
+		// small calls (single queries, modest batches) go through pinned staging and one packed result buffer
+		const bool staged = qb + lb + db + cb <= (1u << 20);
+		io->q.ensure(qb);
+		io->out_labels.ensure(lb + db + cb);
+		int64_t *d_labels = io->out_labels.as<int64_t>();
+		float *d_dist = reinterpret_cast<float *>(reinterpret_cast<char *>(io->out_labels.p) + lb);
+		int32_t *d_counts = reinterpret_cast<int32_t *>(reinterpret_cast<char *>(io->out_labels.p) + lb + db);
+		char *hs = staged ? static_cast<char *>(io->stage(qb + lb + db + cb)) : nullptr;
+		if (staged) {
+			std::memcpy(hs, queries, qb);
+			LB_CUDA(cudaMemcpyAsync(io->q.p, hs, qb, cudaMemcpyHostToDevice, s));
+		} else {
+			LB_CUDA(cudaMemcpyAsync(io->q.p, queries, qb, cudaMemcpyHostToDevice, s));
+		}
 		const uint32_t *d_allow = nullptr;
 		if (allow) {
 			size_t words = (size_t)((allow_bits + 31) / 32);
@@ -317,12 +338,19 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 			LB_CUDA(cudaMemcpyAsync(io->allow.p, allow, words * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
 			d_allow = io->allow.as<uint32_t>();
 		}
-		search_device(io->q.as<float>(), nq, k, nprobes, refine, d_allow, allow_bits, io->out_labels.as<int64_t>(),
-		              io->out_dist.as<float>(), io->out_counts.as<int32_t>(), s);
-		LB_CUDA(cudaMemcpyAsync(out_labels, io->out_labels.p, (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
-		LB_CUDA(cudaMemcpyAsync(out_dist, io->out_dist.p, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, s));
-		LB_CUDA(cudaMemcpyAsync(out_counts, io->out_counts.p, (size_t)nq * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-		LB_CUDA(cudaStreamSynchronize(s));
+		search_device(io->q.as<float>(), nq, k, nprobes, refine, d_allow, allow_bits, d_labels, d_dist, d_counts, s);
+		if (staged) {
+			LB_CUDA(cudaMemcpyAsync(hs + qb, d_labels, lb + db + cb, cudaMemcpyDeviceToHost, s));
+			LB_CUDA(cudaStreamSynchronize(s));
+			std::memcpy(out_labels, hs + qb, lb);
+			std::memcpy(out_dist, hs + qb + lb, db);
+			std::memcpy(out_counts, hs + qb + lb + db, cb);
+		} else {
+			LB_CUDA(cudaMemcpyAsync(out_labels, d_labels, lb, cudaMemcpyDeviceToHost, s));
+			LB_CUDA(cudaMemcpyAsync(out_dist, d_dist, db, cudaMemcpyDeviceToHost, s));
+			LB_CUDA(cudaMemcpyAsync(out_counts, d_counts, cb, cudaMemcpyDeviceToHost, s));
+			LB_CUDA(cudaStreamSynchronize(s));
+		}
 	} catch (...) {
 		release_io(std::move(io));
 		throw;

@@ -42,6 +42,11 @@ struct Workspace {
 	DevBuf scan_hdr;  // persistent header of the flat scan (kernels.h SCAN_HDR_BYTES), all-ones between passes
 	bool scan_hdr_clean = false;
 	DevBuf adc_tickets; // persistent arrival tickets of the ADC scan (one per query), zero between launches
+	// small host-buffer calls: pinned staging (query in, packed [labels | distances | counts] out) so that the
+	// call is one async H2D + one D2H instead of four pageable copies that each block the host
+	void *h_stage = nullptr;
+	size_t h_stage_bytes = 0;
+	void *stage(size_t bytes);
 	explicit Workspace(bool own_stream);
 	~Workspace();
 };
