@@ -224,6 +224,16 @@ class LanceHandle:
     def delete(self, label: int):
         self._check(lib().lance_detached_delete(self._h, int(label), self._err, ERR_LEN), "delete")
 
+    def merge(self, source: "LanceHandle", live_source_labels):
+        """lance_detached_merge (src/rust_ffi.cpp:119-128): append the listed live rows of `source` under fresh labels;
+        returns (old_labels, new_labels)."""
+        l = np.ascontiguousarray(live_source_labels, np.int64)
+        old = np.empty(max(l.shape[0], 1), np.int64)
+        new = np.empty(max(l.shape[0], 1), np.int64)
+        n = self._check(lib().lance_detached_merge(self._h, source._h, _ptr(l), l.shape[0], _ptr(old), _ptr(new),
+                                                   self._err, ERR_LEN), "merge")
+        return old[:n], new[:n]
+
     def get_vector(self, label: int) -> np.ndarray:
         out = np.empty(self.dim, np.float32)
         self._check(lib().lance_detached_get_vector(self._h, int(label), _ptr(out), self.dim, self._err, ERR_LEN),

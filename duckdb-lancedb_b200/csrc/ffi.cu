@@ -99,10 +99,20 @@ int32_t lance_detached_add_batch_arrow(void *, void *, void *, int64_t *, char *
 	return -1;
 }
 
-int32_t lance_detached_merge(void *, void *, const int64_t *, int32_t, int64_t *, int64_t *, char *err_buf,
+int32_t lance_detached_merge(void *target_handle, void *source_handle, const int64_t *live_source_labels,
+                             int32_t live_count, int64_t *out_old_labels, int64_t *out_new_labels, char *err_buf,
                              int err_buf_len) {
-	write_err(err_buf, err_buf_len, "merge failed: not supported by the B200 backend");
-	return -1;
+	// rust_lib/src/ffi.rs:187-228
+	if (!target_handle || !source_handle) {
+		write_err(err_buf, err_buf_len, "null handle");
+		return -1;
+	}
+	void *handle = target_handle;
+	LB_HANDLE(-1)
+	LB_TRY("merge failed: ", -1, {
+		Store *src = static_cast<Store *>(source_handle);
+		return h->merge_from(*src, live_source_labels, live_count, out_old_labels, out_new_labels);
+	})
 }
 
 int32_t lance_detached_search_batch(void *handle, const float *queries, int32_t nq, int32_t dim, int32_t k,

@@ -252,6 +252,58 @@ int64_t Store::get_all(int64_t *out_labels, float *out_vectors) {
 	return live;
 }
 
+// rust_lib/src/lance_manager.rs:307-393 (merge_from): the rows of `src` whose label is listed, exists and is not
+// tombstoned are appended here in the source's storage order (what its `label IN (...)` query returns) under
+// fresh sequential labels.  Rows move device to device; only the label lists touch the host.
+int Store::merge_from(Store &src, const int64_t *live_labels, int count, int64_t *out_old, int64_t *out_new) {
+	if (&src == this) throw Error("cannot merge an index into itself");
+	if (src.dim_ != dim_)
+		throw Error("dimension mismatch: target " + std::to_string(dim_) + ", source " + std::to_string(src.dim_));
+	if (count <= 0 || !live_labels) return 0;
+	if (!out_old || !out_new) throw Error("null buffer");
+	std::vector<int64_t> rows;
+	rows.reserve(count);
+	DevBuf tmp; // [m][dim] on the source's device
+	int64_t src_base = 0, l = 0;
+	{
+		std::shared_lock<std::shared_mutex> lk(src.mu_);
+		LB_CUDA(cudaSetDevice(src.device_));
+		src_base = src.label_base_;
+		for (int i = 0; i < count; i++) {
+			const int64_t r = live_labels[i] - src_base;
+			if (r < 0 || r >= src.n_rows_ || ((src.deleted_host_[(size_t)(r >> 5)] >> (r & 31)) & 1u)) continue;
+			rows.push_back(r);
+		}
+		std::sort(rows.begin(), rows.end());
+		rows.erase(std::unique(rows.begin(), rows.end()), rows.end());
+		if (rows.empty()) return 0;
+		DevBuf d_rows;
+		d_rows.alloc(rows.size() * sizeof(int64_t));
+		tmp.alloc(rows.size() * (size_t)dim_ * sizeof(float));
+		LB_CUDA(cudaMemcpyAsync(d_rows.p, rows.data(), rows.size() * sizeof(int64_t), cudaMemcpyHostToDevice, src.copy_stream_));
+		launch_gather_rows(src.X_.as<float>(), d_rows.as<int64_t>(), (long long)rows.size(), dim_, tmp.as<float>(),
+		                   src.copy_stream_, &l);
+		LB_CUDA(cudaStreamSynchronize(src.copy_stream_));
+		src.add_launches(l);
+	}
+	const int64_t m = (int64_t)rows.size();
+	int64_t first;
+	if (src.device_ == device_) {
+		first = add_device(tmp.as<float>(), m, copy_stream_);
+	} else {
+		LB_CUDA(cudaSetDevice(device_));
+		DevBuf here;
+		here.alloc((size_t)m * dim_ * sizeof(float));
+		LB_CUDA(cudaMemcpyPeer(here.p, device_, tmp.p, src.device_, (size_t)m * dim_ * sizeof(float)));
+		first = add_device(here.as<float>(), m, copy_stream_);
+	}
+	for (int64_t i = 0; i < m; i++) {
+		out_old[i] = src_base + rows[(size_t)i];
+		out_new[i] = first + i;
+	}
+	return (int)m;
+}
+
 // ------------------------------------------------------------------ search
 void Store::search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
                           int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,

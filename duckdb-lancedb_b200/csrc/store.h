@@ -73,6 +73,8 @@ public:
 	int64_t rows();
 	void get_vector(int64_t label, float *out);
 	int64_t get_all(int64_t *out_labels, float *out_vectors); // returns live count
+	// appends the listed live rows of `src` (storage order) with fresh labels; fills the old -> new mapping
+	int merge_from(Store &src, const int64_t *live_labels, int count, int64_t *out_old, int64_t *out_new);
 
 	// host buffers in, host buffers out (the reference-facing call)
 	void search_host(const float *queries, int nq, int k, int nprobes, int refine, const uint32_t *allow,

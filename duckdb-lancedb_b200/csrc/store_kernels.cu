@@ -22,6 +22,24 @@ void launch_set_bits(uint32_t *bitmap, const int64_t *d_rows, int count, long lo
 	if (launches) (*launches)++;
 }
 
+// dst[i][:] = X[rows[i]][:] — one warp per row (index merge: live rows of the source handle, lance_manager.rs:307-345)
+__global__ void gather_rows_kernel(const float *__restrict__ X, const int64_t *__restrict__ rows, long long m, int d,
+                                   float *__restrict__ dst) {
+	const long long i = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (i >= m) return;
+	const float *src = X + (size_t)rows[i] * d;
+	float *out = dst + (size_t)i * d;
+	for (int c = threadIdx.x & 31; c < d; c += 32) out[c] = src[c];
+}
+
+void launch_gather_rows(const float *X, const int64_t *d_rows, long long m, int d, float *dst, cudaStream_t s,
+                        int64_t *launches) {
+	if (m <= 0) return;
+	gather_rows_kernel<<<(unsigned)((m + 7) / 8), 256, 0, s>>>(X, d_rows, m, d, dst);
+	LB_CUDA(cudaGetLastError());
+	if (launches) (*launches)++;
+}
+
 // Final select over G per-shard lists in ONE launch, one block per query.  labels/dists/counts of shard g start
 // at labels + g*ls, dists + g*ds, counts + g*cs (element strides), so both the [G][nq][k] layout and a gathered
 // buffer of per-rank packed records work.  Keys carry the index g*k+i in their low word.

@@ -56,7 +56,10 @@ int32_t lance_detached_add_batch(void *handle, const float *vectors, int32_t num
 /* rust_ffi.cpp:21-22: not on the kNN path, returns -1 */
 int32_t lance_detached_add_batch_arrow(void *handle, void *arrow_schema, void *arrow_array, int64_t *out_labels,
                                        char *err_buf, int err_buf_len);
-/* rust_ffi.cpp:23-25: not on the kNN path, returns -1 */
+/* rust_ffi.cpp:23-25 / ffi.rs:187-228 / lance_manager.rs:307-393: the listed labels of the source that exist and are
+ * not deleted are appended to the target (device-to-device row gather, source storage order) under fresh
+ * sequential labels; out_old/out_new (capacity live_count) receive the mapping.  Returns the merged count, -1 on error
+ * (null handle, dimension mismatch, source == target). */
 int32_t lance_detached_merge(void *target_handle, void *source_handle, const int64_t *live_source_labels,
                              int32_t live_count, int64_t *out_old_labels, int64_t *out_new_labels, char *err_buf,
                              int err_buf_len);

@@ -311,3 +311,39 @@ def test_concurrent_searches_one_handle(gpu, oracle_mod):
         [t.join() for t in ts]
         assert not errors, errors
         assert h.count() == 20_000 + 4096
+
+
+def test_merge_moves_live_rows_between_handles(gpu, oracle_mod):
+    """lance_detached_merge (rust_lib/src/ffi.rs:187-228, lance_manager.rs:307-393): the listed live rows of the source
+    land in the target under fresh sequential labels, in the source's storage order; unknown and deleted labels are
+    skipped; searching the target equals searching the concatenated table."""
+    rng = np.random.default_rng(808)
+    d = 24
+    A = rng.standard_normal((700, d), dtype=np.float32)
+    B = rng.standard_normal((500, d), dtype=np.float32)
+    with gpu.LanceHandle(d, "l2") as ta, gpu.LanceHandle(d, "l2") as sb:
+        ta.add_batch(A)
+        sb.add_batch(B)
+        sb.delete_batch([3, 77, 499])
+        want = [498, 5, 3, 10_000, -4, 77, 250, 5, 0]  # unsorted, a duplicate, deleted and unknown labels
+        old, new = ta.merge(sb, want)
+        assert old.tolist() == [0, 5, 250, 498]
+        assert new.tolist() == [700, 701, 702, 703]
+        assert ta.count() == 704
+        for o, n in zip(old, new):
+            np.testing.assert_array_equal(ta.get_vector(int(n)), B[o])
+        X = np.concatenate([A, B[old]])
+        for q in (B[250], A[13], rng.standard_normal(d).astype(np.float32)):
+            l, dd = ta.search(q, 7)
+            wl, wd32, wd64 = oracle_mod.flat_search(X, q, 7, "l2")
+            assert list(l) == list(wl)
+            np.testing.assert_allclose(dd, wd64, rtol=1e-4, atol=1e-6)
+        # nothing to merge, and the error contract
+        o2, n2 = ta.merge(sb, [])
+        assert len(o2) == 0 and ta.count() == 704
+        with pytest.raises(gpu.LanceError, match="merge"):
+            ta.merge(ta, [1])
+        with gpu.LanceHandle(d + 1, "l2") as other:
+            other.add_batch(rng.standard_normal((4, d + 1), dtype=np.float32))
+            with pytest.raises(gpu.LanceError, match="dimension mismatch"):
+                ta.merge(other, [0])
