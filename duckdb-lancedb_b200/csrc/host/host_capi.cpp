@@ -111,6 +111,9 @@ int32_t lbh_index_delete(void *index, const int64_t *row_ids, int64_t count, cha
 		return 0;
 	})
 }
+int32_t lbh_index_merge(void *index, void *other, char *err_buf, int err_buf_len) {
+	HTRY(-1, { return static_cast<LanceIndex *>(index)->MergeIndexes(*static_cast<LanceIndex *>(other)); })
+}
 int64_t lbh_index_count(void *index, char *err_buf, int err_buf_len) {
 	HTRY(-1, { return static_cast<LanceIndex *>(index)->GetVectorCount(); })
 }

@@ -50,6 +50,9 @@ int32_t LanceDetachedSearchBatch(LanceHandle handle, const float *queries, int32
 int64_t LanceDetachedCount(LanceHandle handle);
 void LanceDetachedDelete(LanceHandle handle, int64_t label);
 void LanceDetachedDeleteBatch(LanceHandle handle, const int64_t *labels, int32_t count);
+// src/rust_ffi.cpp:119-128
+int32_t LanceDetachedMerge(LanceHandle target, LanceHandle source, const int64_t *live_source_labels, int32_t live_count,
+                           int64_t *out_old_labels, int64_t *out_new_labels);
 void LanceDetachedCreateIndex(LanceHandle handle, int32_t num_partitions, int32_t num_sub_vectors);
 void LanceDetachedCreateHnswIndex(LanceHandle handle, int32_t m, int32_t ef_construction);
 void LanceDetachedCompact(LanceHandle handle);
@@ -102,6 +105,11 @@ public:
 	// query batch (north_star); out[q] as Search()
 	std::vector<std::vector<std::pair<row_t, float>>> SearchBatch(const float *queries, int32_t nq, int32_t dimension,
 	                                                             int32_t k, const std::string &predicate = "");
+	// MergeIndexes (src/lance_index.cpp:624-668): the live rows of `other` move into this index on the device
+	// (lance_detached_merge), label <-> row id maps follow the returned old -> new mapping, and the rows' extra
+	// column values (kept on the host here) are carried over under the new labels.
+	// Returns the number of merged rows.
+	int32_t MergeIndexes(LanceIndex &other);
 	void CreateAnnIndex(int32_t num_partitions, int32_t num_sub_vectors); // :467-472
 	void CreateHnswIndex(int32_t m, int32_t ef_construction);              // :474-479
 

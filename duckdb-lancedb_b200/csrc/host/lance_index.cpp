@@ -76,6 +76,14 @@ void LanceDetachedDeleteBatch(LanceHandle handle, const int64_t *labels, int32_t
 	if (lance_detached_delete_batch(handle, labels, count, err, ERR_BUF) != 0)
 		throw IOException(std::string("Lance delete_batch: ") + err);
 }
+int32_t LanceDetachedMerge(LanceHandle target, LanceHandle source, const int64_t *live_source_labels, int32_t live_count,
+                           int64_t *out_old_labels, int64_t *out_new_labels) {
+	char err[ERR_BUF] = {0};
+	const int32_t n = lance_detached_merge(target, source, live_source_labels, live_count, out_old_labels, out_new_labels,
+	                                       err, ERR_BUF);
+	if (n < 0) throw IOException(std::string("Lance merge: ") + err);
+	return n;
+}
 void LanceDetachedCreateIndex(LanceHandle handle, int32_t num_partitions, int32_t num_sub_vectors) {
 	char err[ERR_BUF] = {0};
 	if (lance_detached_create_index(handle, num_partitions, num_sub_vectors, err, ERR_BUF) != 0)
@@ -148,9 +156,57 @@ void LanceIndex::Delete(const row_t *row_ids, int64_t count) {
 		auto it = rowid_to_label_.find(row_ids[i]);
 		if (it == rowid_to_label_.end()) continue;
 		labels.push_back(it->second);
+		// the slot is dead in the forward mapping too (:410-413)
+		if (it->second >= 0 && (size_t)it->second < label_to_rowid_.size()) label_to_rowid_[(size_t)it->second] = (row_t)-1;
 		rowid_to_label_.erase(it);
 	}
 	if (!labels.empty()) LanceDetachedDeleteBatch(rust_handle_, labels.data(), (int32_t)labels.size());
+}
+
+static void AppendColumnValue(Column &dst, const Column *src, size_t at) {
+	// NULL when the source index does not have the column or the value is NULL
+	const bool ok = src && at < src->size() && src->valid[at];
+	dst.valid.push_back(ok ? 1 : 0);
+	switch (dst.type) {
+	case ColumnType::VARCHAR: dst.s.push_back(ok && at < src->s.size() ? src->s[at] : std::string()); break;
+	case ColumnType::DOUBLE: dst.d.push_back(ok && at < src->d.size() ? src->d[at] : 0.0); break;
+	default: dst.i.push_back(ok && at < src->i.size() ? src->i[at] : 0); break;
+	}
+}
+
+int32_t LanceIndex::MergeIndexes(LanceIndex &other) {
+	if (!rust_handle_ || !other.rust_handle_) return 0; // :626-629
+	std::vector<int64_t> live_labels;
+	std::vector<row_t> live_rowids;
+	for (size_t i = 0; i < other.label_to_rowid_.size(); i++) {
+		if (other.label_to_rowid_[i] == (row_t)-1) continue;
+		live_labels.push_back((int64_t)i);
+		live_rowids.push_back(other.label_to_rowid_[i]);
+	}
+	if (live_labels.empty()) return 0;
+	const int32_t count = (int32_t)live_labels.size();
+	std::vector<int64_t> out_old(count), out_new(count);
+	const int32_t n = LanceDetachedMerge(rust_handle_, other.rust_handle_, live_labels.data(), count, out_old.data(),
+	                                     out_new.data());
+	std::unordered_map<int64_t, row_t> old_label_to_rowid;
+	for (size_t i = 0; i < live_labels.size(); i++) old_label_to_rowid[live_labels[i]] = live_rowids[i];
+	for (int32_t i = 0; i < n; i++) {
+		auto it = old_label_to_rowid.find(out_old[i]);
+		if (it == old_label_to_rowid.end()) continue;
+		const int64_t new_label = out_new[i];
+		if ((int64_t)label_to_rowid_.size() <= new_label) label_to_rowid_.resize((size_t)new_label + 1, (row_t)-1);
+		label_to_rowid_[(size_t)new_label] = it->second;
+		rowid_to_label_[it->second] = new_label;
+		// extra columns are indexed by label: pad to the new label, then take the source row's values
+		for (auto &kv : columns_) {
+			Column &c = kv.second;
+			while ((int64_t)c.size() < new_label) AppendColumnValue(c, nullptr, 0);
+			auto oc = other.columns_.find(kv.first);
+			const Column *src = (oc != other.columns_.end() && oc->second.type == c.type) ? &oc->second : nullptr;
+			if ((int64_t)c.size() == new_label) AppendColumnValue(c, src, (size_t)out_old[i]);
+		}
+	}
+	return n;
 }
 
 std::shared_ptr<const std::vector<uint32_t>> LanceIndex::PredicateBitmap(const std::string &predicate) {

@@ -149,3 +149,42 @@ def test_predicate_bitmap_cache_follows_appends(gpu, host, oracle_mod):
         assert rows[0] == n + 5 and list(rows) == list(wl)
         rows2, _ = ix.search(q, k, "score >= 30")  # another predicate, same index
         assert n + 5 not in rows2.tolist()
+
+
+def test_merge_indexes_moves_live_rows_and_their_columns(gpu, host, oracle_mod):
+    """LanceIndex::MergeIndexes (src/lance_index.cpp:624-668): the live rows of the other index land in this one
+    (device-side lance_detached_merge), keep their DuckDB row ids and their extra column values; rows deleted from
+    the other index stay out.  Searching afterwards equals the oracle over the union."""
+    rng = np.random.default_rng(41)
+    na, nb, d, k = 900, 600, 16, 6
+    A = rng.standard_normal((na, d), dtype=np.float32)
+    B = rng.standard_normal((nb, d), dtype=np.float32)
+    sa = rng.integers(0, 100, na)
+    sb = rng.integers(0, 100, nb)
+    rows_a = np.arange(na)                 # DuckDB row ids of A
+    rows_b = 10_000 + np.arange(nb)        # ... and of B (disjoint)
+    dead_b = np.array([10_003, 10_250, 10_599])
+    with host.HostIndex(d, "l2") as ia, host.HostIndex(d, "l2") as ib:
+        ia.append(A, rows_a)
+        ia.columns.append("score", sa.tolist())
+        ib.append(B, rows_b)
+        ib.columns.append("score", sb.tolist())
+        ib.delete(dead_b)
+        assert ia.merge_indexes(ib) == nb - 3
+        assert ia.count() == na + nb - 3
+        keep = ~np.isin(rows_b, dead_b)
+        X = np.concatenate([A, B[keep]])
+        rowids = np.concatenate([rows_a, rows_b[keep]])
+        score = np.concatenate([sa, sb[keep]])
+        for q in (B[250], B[7], A[11], rng.standard_normal(d).astype(np.float32)):
+            rows, dist = ia.search(q, k)
+            wl, _, wd64 = oracle_mod.flat_search(X, q, k, "l2")
+            assert list(rows) == rowids[wl].tolist()
+            np.testing.assert_allclose(dist, wd64, rtol=1e-4, atol=1e-6)
+            rows, dist = ia.search(q, k, "score < 40")
+            wl, _, wd64 = oracle_mod.flat_search(X, q, k, "l2", oracle_mod.make_bitmap(score < 40), None)
+            assert list(rows) == rowids[wl].tolist()
+        assert 10_250 not in ia.search(B[250], k)[0].tolist()  # deleted before the merge
+        # merging an index without live rows is a no-op
+        with host.HostIndex(d, "l2") as ie:
+            assert ia.merge_indexes(ie) == 0
