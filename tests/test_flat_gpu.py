@@ -124,6 +124,24 @@ def test_query_batch_sizes(gpu, oracle_mod, nq):
         check_against_oracle(oracle_mod, h, X, Q, 10, "l2", what=f"nq={nq}")
 
 
+@pytest.mark.parametrize("d,nq,k", [(3, 1, 3), (5, 3, 7), (7, 5, 1), (33, 2, 11), (129, 9, 5)])
+def test_host_buffer_results_with_odd_dimensions(gpu, oracle_mod, d, nq, k):
+    """Small host-buffer calls get their packed [labels | distances | counts] result written in place into the
+    mapped staging buffer behind the queries (store.cu search_host): the int64 labels must stay aligned whatever
+    nq * d * 4 is, and the caller's buffers must hold exactly what the device path returns."""
+    rng = np.random.default_rng(100 * d + nq)
+    X = rng.standard_normal((4000, d), dtype=np.float32)
+    Q = rng.standard_normal((nq, d), dtype=np.float32)
+    for metric in ("l2", "cosine", "dot"):
+        with gpu.LanceHandle(d, metric) as h:
+            h.add_batch(X)
+            check_against_oracle(oracle_mod, h, X, Q, k, metric, what=f"d={d} nq={nq} k={k} {metric}")
+            # repeated calls reuse the staging buffer: same answer every time
+            a = h.search(Q[0], k)
+            b = h.search(Q[0], k)
+            assert list(a[0]) == list(b[0]) and np.array_equal(a[1], b[1])
+
+
 def test_edge_cases(gpu, oracle_mod):
     rng = np.random.default_rng(5)
     d = 16
