@@ -72,6 +72,11 @@ def lib():
         _lib.oracle_ivfpq_search.restype = C.c_int
         _lib.oracle_adc_distance.restype = C.c_float
         _lib.oracle_metric_from_string.restype = C.c_int
+        _lib.oracle_ivfpq_search_parts.restype = C.c_int
+        _lib.oracle_flat_search_batch_blocked.restype = C.c_int
+        _lib.oracle_acc_new.restype = C.c_void_p
+        _lib.oracle_acc_add.restype = None
+        _lib.oracle_acc_finish.restype = None
     return _lib
 
 
@@ -151,6 +156,54 @@ def flat_search_batch_f32(X, Q, k, metric="l2", allow=None, deleted=None, nthrea
                                        C.c_int(nq), C.c_int(k), _ptr(allow), _ptr(deleted), _ptr(labels),
                                        _ptr(dist), _ptr(counts), C.c_int(nthreads))
     return labels, dist, counts
+
+
+def flat_search_batch_blocked(X, Q, k, metric="l2", allow=None, deleted=None, nthreads=0):
+    """Cache-blocked SGEMM-style fp32 batch search (the timed CPU baseline)."""
+    X, Q = _f32(X), _f32(Q)
+    n, d = X.shape
+    nq = Q.shape[0]
+    allow, deleted = _bitmap(allow), _bitmap(deleted)
+    labels = np.full((nq, max(k, 1)), -1, np.int64)
+    dist = np.full((nq, max(k, 1)), np.inf, np.float32)
+    counts = np.zeros(nq, np.int32)
+    lib().oracle_flat_search_batch_blocked(_ptr(X), C.c_int64(n), C.c_int(d), C.c_int(metric_id(metric)), _ptr(Q),
+                                           C.c_int(nq), C.c_int(k), _ptr(allow), _ptr(deleted), _ptr(labels),
+                                           _ptr(dist), _ptr(counts), C.c_int(nthreads))
+    return labels, dist, counts
+
+
+class FlatAccumulator:
+    """oracle_flat_search for several queries over a table that arrives in row chunks (fp64 truth, OpenMP)."""
+
+    def __init__(self, Q, k, metric="l2", label_base=0):
+        Q = _f32(Q)
+        if Q.ndim == 1:
+            Q = Q.reshape(1, -1)
+        self.nq, self.d = Q.shape
+        self.k, self.label_base = int(k), int(label_base)
+        lib().oracle_acc_new.restype = C.c_void_p
+        self._a = lib().oracle_acc_new(C.c_int(metric_id(metric)), _ptr(Q), C.c_int(self.nq), C.c_int(self.d),
+                                       C.c_int(self.k))
+
+    def add(self, X, row0=0, allow=None, deleted=None, allow_bits=None, nthreads=0):
+        X = _f32(X)
+        assert X.ndim == 2 and X.shape[1] == self.d and self._a
+        allow, deleted = _bitmap(allow), _bitmap(deleted)
+        if allow_bits is None:
+            allow_bits = 0 if allow is None else allow.shape[0] * 32
+        lib().oracle_acc_add(C.c_void_p(self._a), _ptr(X), C.c_int64(X.shape[0]), C.c_int64(int(row0)), _ptr(allow),
+                             C.c_int64(int(allow_bits)), _ptr(deleted), C.c_int64(self.label_base), C.c_int(nthreads))
+
+    def finish(self):
+        """-> list of (labels int64[c], dist64 float64[c]) per query."""
+        kk = max(self.k, 1)
+        labels = np.empty((self.nq, kk), np.int64)
+        d64 = np.empty((self.nq, kk), np.float64)
+        counts = np.zeros(self.nq, np.int32)
+        lib().oracle_acc_finish(C.c_void_p(self._a), _ptr(labels), _ptr(d64), _ptr(counts))
+        self._a = None
+        return [(labels[j, :counts[j]].copy(), d64[j, :counts[j]].copy()) for j in range(self.nq)]
 
 
 def num_threads() -> int:
@@ -234,6 +287,28 @@ class IvfPqIndex:
         c = lib().oracle_ivfpq_search(C.byref(s), _ptr(X), C.c_int64(n), _ptr(q), C.c_int(k), C.c_int(nprobes),
                                       C.c_int(int(refine_factor)), _ptr(allow), _ptr(deleted), _ptr(parts),
                                       _ptr(cl), _ptr(ca), C.byref(nc), _ptr(ol), _ptr(od))
+        return dict(parts=parts, cand_labels=cl[: nc.value].copy(), cand_adc=ca[: nc.value].copy(),
+                    labels=ol[:c].copy(), dist=od[:c].copy())
+
+    def search_parts(self, X, q, k, parts, refine_factor=1, allow=None, deleted=None):
+        """The same pipeline over a GIVEN list of partitions (oracle_ivfpq_search_parts).  X may be None when
+        refine_factor == 0 and the index covers every row (no row is then read)."""
+        q = _f32(q)
+        Xc = None if X is None else _f32(X)
+        n = self.n_indexed if Xc is None else Xc.shape[0]
+        allow, deleted = _bitmap(allow), _bitmap(deleted)
+        parts = np.ascontiguousarray(parts, np.int32)
+        rf = max(int(refine_factor), 1)
+        cl = np.empty(k * rf, np.int64)
+        ca = np.empty(k * rf, np.float32)
+        nc = C.c_int32(0)
+        ol = np.empty(k, np.int64)
+        od = np.empty(k, np.float32)
+        s = self._c()
+        c = lib().oracle_ivfpq_search_parts(C.byref(s), _ptr(Xc), C.c_int64(n), _ptr(q), C.c_int(k), _ptr(parts),
+                                            C.c_int(parts.shape[0]), C.c_int(int(refine_factor)), _ptr(allow),
+                                            _ptr(deleted), _ptr(cl), _ptr(ca), C.byref(nc), _ptr(ol), _ptr(od))
+        assert c >= 0
         return dict(parts=parts, cand_labels=cl[: nc.value].copy(), cand_adc=ca[: nc.value].copy(),
                     labels=ol[:c].copy(), dist=od[:c].copy())
 

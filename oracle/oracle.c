@@ -418,11 +418,11 @@ float oracle_adc_distance(const oracle_ivfpq_t *ix, const float *lut, const uint
 	return (float)adc_sum(ix, lut, code);
 }
 
-int oracle_ivfpq_search(const oracle_ivfpq_t *ix, const float *X, int64_t n, const float *q, int k,
-                        int nprobes, int refine_factor, const uint32_t *allow,
-                        const uint32_t *deleted, int32_t *out_parts, int64_t *out_cand_labels,
-                        float *out_cand_adc, int32_t *out_ncand, int64_t *out_labels,
-                        float *out_dist) {
+static int ivfpq_search_impl(const oracle_ivfpq_t *ix, const float *X, int64_t n, const float *q, int k,
+                             int nprobes, int refine_factor, const uint32_t *allow,
+                             const uint32_t *deleted, const int32_t *forced_parts, int32_t *out_parts,
+                             int64_t *out_cand_labels, float *out_cand_adc, int32_t *out_ncand,
+                             int64_t *out_labels, float *out_dist) {
 	int d = ix->dim;
 	if (k <= 0) return 0;
 	if (nprobes < 1) nprobes = 1;
@@ -430,7 +430,11 @@ int oracle_ivfpq_search(const oracle_ivfpq_t *ix, const float *X, int64_t n, con
 	int rf = refine_factor < 1 ? 1 : refine_factor;
 	int64_t ncand_cap = (int64_t)k * rf;
 	int32_t *parts = (int32_t *)malloc(sizeof(int32_t) * (size_t)nprobes);
-	int np = oracle_ivf_probe(ix, q, nprobes, parts, NULL);
+	int np = nprobes;
+	if (forced_parts)
+		memcpy(parts, forced_parts, sizeof(int32_t) * (size_t)nprobes);
+	else
+		np = oracle_ivf_probe(ix, q, nprobes, parts, NULL);
 	if (out_parts) memcpy(out_parts, parts, sizeof(int32_t) * (size_t)np);
 
 	float *lut = (float *)malloc(sizeof(float) * (size_t)ix->M * 256);
@@ -477,6 +481,25 @@ int oracle_ivfpq_search(const oracle_ivfpq_t *ix, const float *X, int64_t n, con
 	free(lut);
 	free(parts);
 	return cnt;
+}
+
+int oracle_ivfpq_search(const oracle_ivfpq_t *ix, const float *X, int64_t n, const float *q, int k,
+                        int nprobes, int refine_factor, const uint32_t *allow,
+                        const uint32_t *deleted, int32_t *out_parts, int64_t *out_cand_labels,
+                        float *out_cand_adc, int32_t *out_ncand, int64_t *out_labels,
+                        float *out_dist) {
+	return ivfpq_search_impl(ix, X, n, q, k, nprobes, refine_factor, allow, deleted, NULL, out_parts,
+	                         out_cand_labels, out_cand_adc, out_ncand, out_labels, out_dist);
+}
+
+int oracle_ivfpq_search_parts(const oracle_ivfpq_t *ix, const float *X, int64_t n, const float *q, int k,
+                              const int32_t *parts, int nparts, int refine_factor,
+                              const uint32_t *allow, const uint32_t *deleted, int64_t *out_cand_labels,
+                              float *out_cand_adc, int32_t *out_ncand, int64_t *out_labels,
+                              float *out_dist) {
+	if (nparts < 1 || nparts > ix->P) return -1;
+	return ivfpq_search_impl(ix, X, n, q, k, nparts, refine_factor, allow, deleted, parts, NULL,
+	                         out_cand_labels, out_cand_adc, out_ncand, out_labels, out_dist);
 }
 
 /* ------------------------------------------------------------------ training */
@@ -576,4 +599,287 @@ void oracle_ivfpq_train(const float *X, int64_t n, int d, int metric, int P, int
 	free(R);
 	free(assign);
 	free(Xn);
+}
+
+/* ------------------------------------------------------------------ chunked fp64 accumulator
+ * Same ranking truth as oracle_flat_search (fp64 distance, ties by label), but the table arrives in
+ * row chunks and several queries share one pass over each chunk, OpenMP over the rows of a chunk.
+ * This is what lets the full-size configurations of BASELINE.json (100 M x 128, 10 M x 384 ...) be
+ * checked against the oracle without ever holding the table on the host. */
+struct oracle_acc {
+	int metric, nq, d, k;
+	double *Qd;  /* [nq][d] */
+	double *qn;  /* [nq] |q|^2 */
+	heap_t *heaps; /* [nq] */
+};
+
+oracle_acc_t *oracle_acc_new(int metric, const float *Q, int nq, int d, int k) {
+	oracle_acc_t *a = (oracle_acc_t *)calloc(1, sizeof(oracle_acc_t));
+	a->metric = metric, a->nq = nq, a->d = d, a->k = k;
+	a->Qd = (double *)malloc(sizeof(double) * (size_t)nq * (size_t)d);
+	a->qn = (double *)calloc((size_t)nq, sizeof(double));
+	a->heaps = (heap_t *)malloc(sizeof(heap_t) * (size_t)nq);
+	for (int j = 0; j < nq; j++) {
+		heap_init(&a->heaps[j], k);
+		for (int i = 0; i < d; i++) {
+			double v = (double)Q[(int64_t)j * d + i];
+			a->Qd[(int64_t)j * d + i] = v;
+			a->qn[j] += v * v;
+		}
+	}
+	return a;
+}
+
+void oracle_acc_add(oracle_acc_t *a, const float *X, int64_t n, int64_t row0, const uint32_t *allow,
+                    int64_t allow_bits, const uint32_t *deleted, int64_t label_base, int nthreads) {
+	if (n <= 0 || a->k <= 0) return;
+#ifdef _OPENMP
+	if (nthreads <= 0) nthreads = omp_get_max_threads();
+#else
+	nthreads = 1;
+#endif
+	if ((int64_t)nthreads > n) nthreads = (int)n;
+	const int nq = a->nq, d = a->d, metric = a->metric;
+	heap_t *heaps = (heap_t *)malloc(sizeof(heap_t) * (size_t)nthreads * (size_t)nq);
+	for (int64_t i = 0; i < (int64_t)nthreads * nq; i++) heap_init(&heaps[i], a->k);
+#pragma omp parallel num_threads(nthreads)
+	{
+#ifdef _OPENMP
+		int t = omp_get_thread_num(), T = omp_get_num_threads();
+#else
+		int t = 0, T = 1;
+#endif
+		int64_t lo = n * t / T, hi = n * (t + 1) / T;
+		heap_t *mine = heaps + (int64_t)t * nq;
+		double *xd = (double *)malloc(sizeof(double) * (size_t)d);
+		for (int64_t i = lo; i < hi; i++) {
+			const int64_t row = row0 + i;
+			if (deleted && bit_test(deleted, row)) continue;
+			if (allow && !(row < allow_bits && bit_test(allow, row))) continue;
+			const float *x = X + i * (int64_t)d;
+			double nx = 0.0;
+			for (int c = 0; c < d; c++) {
+				xd[c] = (double)x[c];
+				nx += xd[c] * xd[c];
+			}
+			for (int j = 0; j < nq; j++) {
+				const double *q = a->Qd + (int64_t)j * d;
+				double acc = 0.0, dist;
+				if (metric == ORACLE_L2) {
+#pragma omp simd reduction(+ : acc)
+					for (int c = 0; c < d; c++) {
+						double e = q[c] - xd[c];
+						acc += e * e;
+					}
+					dist = acc;
+				} else {
+#pragma omp simd reduction(+ : acc)
+					for (int c = 0; c < d; c++) acc += q[c] * xd[c];
+					if (metric == ORACLE_DOT)
+						dist = 1.0 - acc;
+					else {
+						double den = sqrt(a->qn[j]) * sqrt(nx);
+						if (!(den > 0.0))
+							dist = 1.0;
+						else {
+							double sim = acc / den;
+							if (sim > 1.0) sim = 1.0;
+							if (sim < -1.0) sim = -1.0;
+							dist = 1.0 - sim;
+						}
+					}
+				}
+				ent_t e = {dist, label_base + row};
+				heap_push(&mine[j], e);
+			}
+		}
+		free(xd);
+	}
+	for (int j = 0; j < nq; j++)
+		for (int t = 0; t < nthreads; t++) {
+			heap_t *h = &heaps[(int64_t)t * nq + j];
+			for (int i = 0; i < h->n; i++) heap_push(&a->heaps[j], h->h[i]);
+		}
+	for (int64_t i = 0; i < (int64_t)nthreads * nq; i++) heap_free(&heaps[i]);
+	free(heaps);
+}
+
+void oracle_acc_finish(oracle_acc_t *a, int64_t *out_labels, double *out_dist64, int32_t *out_counts) {
+	for (int j = 0; j < a->nq; j++) {
+		heap_t *h = &a->heaps[j];
+		heap_sort_asc(h);
+		for (int i = 0; i < h->n; i++) {
+			out_labels[(int64_t)j * a->k + i] = h->h[i].id;
+			out_dist64[(int64_t)j * a->k + i] = h->h[i].d;
+		}
+		out_counts[j] = h->n;
+		heap_free(h);
+	}
+	free(a->heaps);
+	free(a->Qd);
+	free(a->qn);
+	free(a);
+}
+
+/* ------------------------------------------------------------------ blocked fp32 batch search
+ * The timed CPU baseline SURVEY.md 8(d) asks for: "blocked SGEMM-style flat search + heap top-k, all
+ * host cores".  Queries are packed into panels of 16 (k-major, so one AVX2 register pair holds the 16
+ * queries' element i), rows are taken 6 at a time: a 6 x 16 register tile (12 accumulators), every
+ * row element broadcast once per panel.  L2 uses |q|^2 + |x|^2 - 2 q.x, cosine the same dot product.
+ * Row blocks are sized to stay cache resident while all the panels pass over them.  Ranking rule as
+ * everywhere: ascending (distance, label). */
+typedef float v8f __attribute__((vector_size(32), aligned(4)));
+#define OB_QP 16
+#define OB_RT 6
+
+static inline void micro_6x16(const float *const x[OB_RT], const float *qt, int d, float out[OB_RT][OB_QP]) {
+	v8f a00 = {0}, a01 = {0}, a10 = {0}, a11 = {0}, a20 = {0}, a21 = {0};
+	v8f a30 = {0}, a31 = {0}, a40 = {0}, a41 = {0}, a50 = {0}, a51 = {0};
+	const float *x0 = x[0], *x1 = x[1], *x2 = x[2], *x3 = x[3], *x4 = x[4], *x5 = x[5];
+	for (int i = 0; i < d; i++) {
+		const v8f q0 = *(const v8f *)(qt + (int64_t)i * OB_QP), q1 = *(const v8f *)(qt + (int64_t)i * OB_QP + 8);
+		a00 += x0[i] * q0, a01 += x0[i] * q1;
+		a10 += x1[i] * q0, a11 += x1[i] * q1;
+		a20 += x2[i] * q0, a21 += x2[i] * q1;
+		a30 += x3[i] * q0, a31 += x3[i] * q1;
+		a40 += x4[i] * q0, a41 += x4[i] * q1;
+		a50 += x5[i] * q0, a51 += x5[i] * q1;
+	}
+	*(v8f *)&out[0][0] = a00, *(v8f *)&out[0][8] = a01;
+	*(v8f *)&out[1][0] = a10, *(v8f *)&out[1][8] = a11;
+	*(v8f *)&out[2][0] = a20, *(v8f *)&out[2][8] = a21;
+	*(v8f *)&out[3][0] = a30, *(v8f *)&out[3][8] = a31;
+	*(v8f *)&out[4][0] = a40, *(v8f *)&out[4][8] = a41;
+	*(v8f *)&out[5][0] = a50, *(v8f *)&out[5][8] = a51;
+}
+
+int oracle_flat_search_batch_blocked(const float *X, int64_t n, int d, int metric, const float *Q, int nq,
+                                     int k, const uint32_t *allow, const uint32_t *deleted,
+                                     int64_t *out_labels, float *out_dist, int32_t *out_counts,
+                                     int nthreads) {
+	if (nq <= 0) return 0;
+	if (k <= 0 || n <= 0) {
+		for (int j = 0; j < nq; j++)
+			if (out_counts) out_counts[j] = 0;
+		return 0;
+	}
+#ifdef _OPENMP
+	if (nthreads <= 0) nthreads = omp_get_max_threads();
+#else
+	nthreads = 1;
+#endif
+	if ((int64_t)nthreads > n) nthreads = (int)n;
+	const int npan = (nq + OB_QP - 1) / OB_QP;
+	const int nqp = npan * OB_QP;
+	/* panels: Qt[p][i][16] */
+	float *Qt = (float *)aligned_alloc(64, sizeof(float) * (size_t)npan * (size_t)d * OB_QP);
+	float *qn = (float *)calloc((size_t)nqp, sizeof(float));
+	for (int p = 0; p < npan; p++)
+		for (int i = 0; i < d; i++)
+			for (int u = 0; u < OB_QP; u++) {
+				int j = p * OB_QP + u;
+				Qt[((int64_t)p * d + i) * OB_QP + u] = j < nq ? Q[(int64_t)j * d + i] : 0.f;
+			}
+	for (int j = 0; j < nq; j++) {
+		float s = 0.f;
+		for (int i = 0; i < d; i++) s += Q[(int64_t)j * d + i] * Q[(int64_t)j * d + i];
+		qn[j] = s;
+	}
+	int RB = (int)(262144 / ((int64_t)d * 4)); /* ~256 KB of rows per block */
+	if (RB < 2 * OB_RT) RB = 2 * OB_RT;
+	if (RB > 1024) RB = 1024;
+	heap_t *heaps = (heap_t *)malloc(sizeof(heap_t) * (size_t)nthreads * (size_t)nq);
+	for (int64_t i = 0; i < (int64_t)nthreads * nq; i++) heap_init(&heaps[i], k);
+
+#pragma omp parallel num_threads(nthreads)
+	{
+#ifdef _OPENMP
+		int t = omp_get_thread_num(), T = omp_get_num_threads();
+#else
+		int t = 0, T = 1;
+#endif
+		int64_t lo = n * t / T, hi = n * (t + 1) / T;
+		heap_t *mine = heaps + (int64_t)t * nq;
+		float *thr = (float *)malloc(sizeof(float) * (size_t)nqp);
+		for (int j = 0; j < nqp; j++) thr[j] = j < nq ? INFINITY : -INFINITY;
+		const float **rows = (const float **)malloc(sizeof(float *) * (size_t)(RB + OB_RT));
+		int64_t *ids = (int64_t *)malloc(sizeof(int64_t) * (size_t)(RB + OB_RT));
+		float *xn = (float *)malloc(sizeof(float) * (size_t)(RB + OB_RT));
+		float out[OB_RT][OB_QP] __attribute__((aligned(32)));
+		for (int64_t b0 = lo; b0 < hi; b0 += RB) {
+			int64_t b1 = b0 + RB < hi ? b0 + RB : hi;
+			int m = 0;
+			for (int64_t i = b0; i < b1; i++) {
+				if (!row_live(allow, deleted, i)) continue;
+				rows[m] = X + i * (int64_t)d;
+				ids[m] = i;
+				m++;
+			}
+			if (m == 0) continue;
+			if (metric != ORACLE_DOT)
+				for (int r = 0; r < m; r++) {
+					float s = 0.f;
+					const float *x = rows[r];
+#pragma omp simd reduction(+ : s)
+					for (int i = 0; i < d; i++) s += x[i] * x[i];
+					xn[r] = s;
+				}
+			for (int r = m; r < m + OB_RT; r++) rows[r] = rows[m - 1]; /* padding of the last tile */
+			for (int p = 0; p < npan; p++) {
+				const float *qt = Qt + (int64_t)p * d * OB_QP;
+				const float *tp = thr + p * OB_QP;
+				for (int r0 = 0; r0 < m; r0 += OB_RT) {
+					micro_6x16(rows + r0, qt, d, out);
+					const int rr = m - r0 < OB_RT ? m - r0 : OB_RT;
+					for (int r = 0; r < rr; r++) {
+						for (int u = 0; u < OB_QP; u++) {
+							float dot = out[r][u], dist;
+							const int j = p * OB_QP + u;
+							if (metric == ORACLE_DOT)
+								dist = 1.0f - dot;
+							else if (metric == ORACLE_L2) {
+								dist = qn[j] + xn[r0 + r] - 2.0f * dot;
+								if (dist < 0.f) dist = 0.f;
+							} else {
+								float den = sqrtf(qn[j]) * sqrtf(xn[r0 + r]);
+								float sim = den > 0.f ? dot / den : 0.f;
+								if (sim > 1.f) sim = 1.f;
+								if (sim < -1.f) sim = -1.f;
+								dist = 1.0f - sim;
+							}
+							if (dist <= tp[u]) {
+								ent_t e = {(double)dist, ids[r0 + r]};
+								heap_push(&mine[j], e);
+								if (mine[j].n == mine[j].cap) thr[j] = (float)mine[j].h[0].d;
+							}
+						}
+					}
+				}
+			}
+		}
+		free(xn);
+		free(ids);
+		free(rows);
+		free(thr);
+	}
+	for (int j = 0; j < nq; j++) {
+		heap_t fin;
+		heap_init(&fin, k);
+		for (int t = 0; t < nthreads; t++) {
+			heap_t *h = &heaps[(int64_t)t * nq + j];
+			for (int i = 0; i < h->n; i++) heap_push(&fin, h->h[i]);
+		}
+		heap_sort_asc(&fin);
+		for (int i = 0; i < fin.n; i++) {
+			out_labels[(int64_t)j * k + i] = fin.h[i].id;
+			out_dist[(int64_t)j * k + i] = (float)fin.h[i].d;
+		}
+		if (out_counts) out_counts[j] = fin.n;
+		heap_free(&fin);
+	}
+	for (int64_t i = 0; i < (int64_t)nthreads * nq; i++) heap_free(&heaps[i]);
+	free(heaps);
+	free(qn);
+	free(Qt);
+	return nq;
 }

@@ -105,6 +105,35 @@ int oracle_ivfpq_search(const oracle_ivfpq_t *ix, const float *X, int64_t n, con
                         float *out_cand_adc, int32_t *out_ncand, int64_t *out_labels,
                         float *out_dist);
 
+/* Same search over a GIVEN list of partitions (no probe).  Used when the device's probe and the fp64
+ * probe legally differ at a tie (two centroids within 1e-5 relative): the rest of the pipeline is then
+ * still compared on identical lists. */
+int oracle_ivfpq_search_parts(const oracle_ivfpq_t *ix, const float *X, int64_t n, const float *q, int k,
+                              const int32_t *parts, int nparts, int refine_factor,
+                              const uint32_t *allow, const uint32_t *deleted, int64_t *out_cand_labels,
+                              float *out_cand_adc, int32_t *out_ncand, int64_t *out_labels,
+                              float *out_dist);
+
+/* ---------------- chunked truth accumulator (full-size parity tests) ----------------
+ * oracle_flat_search for several queries over a table that arrives in row chunks: fp64 distances,
+ * ranking by (distance, label), OpenMP over the rows of a chunk.  Chunk rows are table rows
+ * [row0, row0 + n); bitmaps are indexed by table row; label = label_base + table row; rows at or
+ * beyond allow_bits are filtered out when `allow` is given (the C ABI's bitmap_bits rule). */
+typedef struct oracle_acc oracle_acc_t;
+oracle_acc_t *oracle_acc_new(int metric, const float *Q, int nq, int d, int k);
+void oracle_acc_add(oracle_acc_t *a, const float *X, int64_t n, int64_t row0, const uint32_t *allow,
+                    int64_t allow_bits, const uint32_t *deleted, int64_t label_base, int nthreads);
+/* out_labels / out_dist64 are [nq][k], out_counts [nq]; frees the accumulator */
+void oracle_acc_finish(oracle_acc_t *a, int64_t *out_labels, double *out_dist64, int32_t *out_counts);
+
+/* Cache-blocked SGEMM-style fp32 batch search (6 x 16 register tiles over query panels), the timed
+ * CPU baseline of SURVEY.md 8(d).  Same outputs as oracle_flat_search_batch_f32; L2 distances come
+ * from |q|^2 + |x|^2 - 2 q.x (so they carry the cancellation error of that form: ~1e-6 of |q|^2+|x|^2). */
+int oracle_flat_search_batch_blocked(const float *X, int64_t n, int d, int metric, const float *Q, int nq,
+                                     int k, const uint32_t *allow, const uint32_t *deleted,
+                                     int64_t *out_labels, float *out_dist, int32_t *out_counts,
+                                     int nthreads);
+
 /* ---------------- training (so that small indexes can be built on the CPU) ---------------- */
 /* Lloyd k-means, deterministic: initial centres = rows floor(i*n/k); `iters` full passes;
  * an empty cluster keeps its previous centre.  metric selects the assignment distance
