@@ -130,6 +130,44 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+GEN_CHUNK = 1 << 22
+
+
+def table_chunks(dim, lo, hi, dev):
+    """The synthetic table, rows [lo, hi): yields (first_row, tensor[rows, dim]) pieces generated on the device.
+    Chunk c of 2^22 rows is seeded with SEED + 7919*c, so every sharding (and tests/test_baseline_shapes_gpu.py)
+    sees the same table."""
+    import torch
+
+    g = torch.Generator(device=dev)
+    pos = lo
+    while pos < hi:
+        cidx = pos // GEN_CHUNK
+        g.manual_seed(SEED + 7919 * cidx)
+        blk = torch.randn((GEN_CHUNK, dim), generator=g, device=dev, dtype=torch.float32)
+        a, b = pos - cidx * GEN_CHUNK, min(hi, (cidx + 1) * GEN_CHUNK) - cidx * GEN_CHUNK
+        yield pos, blk[a:b]
+        pos += b - a
+        del blk
+
+
+def bench_queries(B, dim, dev):
+    import torch
+
+    g = torch.Generator(device=dev)
+    g.manual_seed(SEED + 1)
+    return torch.randn((B, dim), generator=g, device=dev, dtype=torch.float32)
+
+
+def bench_mask(rows, selectivity, dev):
+    """Prefilter of the C5 workload: bool[rows], True = the row may be returned."""
+    import torch
+
+    g = torch.Generator(device=dev)
+    g.manual_seed(SEED + 2)
+    return torch.rand(rows, generator=g, device=dev) < selectivity
+
+
 def shard_range(rows, rank, world):
     """Contiguous row ranges (duckdb-lancedb_b200/sharding.py)."""
     return rows * rank // world, rows * (rank + 1) // world
@@ -340,27 +378,15 @@ def run_b200(args, wl):
     h = pkg.LanceHandle(dim, metric)
     h.set_label_base(lo)
     h.reserve(n_local)
-    chunk = 1 << 22
-    g = torch.Generator(device=dev)
-    c0 = lo // chunk
-    pos = lo
-    while pos < hi:
-        cidx = pos // chunk
-        g.manual_seed(SEED + 7919 * cidx)
-        blk = torch.randn((chunk, dim), generator=g, device=dev, dtype=torch.float32)
-        a, b = pos - cidx * chunk, min(hi, (cidx + 1) * chunk) - cidx * chunk
-        h.add_batch_device(blk[a:b].data_ptr(), b - a, dim, sp)
-        pos += b - a
-        del blk
+    for pos, blk in table_chunks(dim, lo, hi, dev):
+        h.add_batch_device(blk.data_ptr(), blk.shape[0], dim, sp)
     assert h.count() == n_local
-    g.manual_seed(SEED + 1)
-    Qd = torch.randn((B, dim), generator=g, device=dev, dtype=torch.float32)
+    Qd = bench_queries(B, dim, dev)
     Qh = Qd.cpu().pin_memory()
 
     d_allow, allow_bits, allow_host = 0, 0, None
     if wl.get("selectivity"):
-        g.manual_seed(SEED + 2)
-        mask = (torch.rand(rows, generator=g, device=dev) < wl["selectivity"])[lo:hi]
+        mask = bench_mask(rows, wl["selectivity"], dev)[lo:hi]
         allow_host = pkg.make_bitmap(mask.cpu().numpy())
         allow_t = torch.from_numpy(allow_host.view(np.int32)).to(dev)
         d_allow, allow_bits = allow_t.data_ptr(), allow_host.shape[0] * 32

@@ -74,8 +74,12 @@ struct FlatGemm::Impl {
 	CUtensorMap tmX, tmX64; // 128-row and 64-row boxes over the shadow
 	const void *tmX_base = nullptr;
 	long long tmX_rows = -1;
-	bool attr_set = false;
-	// deferred overflow check of the last search (FlatGemm::search with defer = true)
+	std::once_flag attr_once;
+	// the shadow / max_norm work of sync_rows is enqueued on the first caller's stream: every search waits for this
+	// event on ITS stream before it reads the shadow (two concurrent callers use two streams)
+	cudaEvent_t shadow_ev = nullptr;
+	bool shadow_ev_set = false;
+	// deferred overflow check of a search (FlatGemm::search with defer = true), one per stream
 	struct Pending {
 		bool active = false;
 		cudaStream_t s = nullptr;
@@ -87,11 +91,23 @@ struct FlatGemm::Impl {
 		int64_t *out_labels = nullptr;
 		float *out_dist = nullptr;
 		int32_t *out_counts = nullptr;
-	} pend;
-	uint32_t *h_total = nullptr; // pinned
+		uint32_t *h_total = nullptr; // pinned, owned by this slot
+	};
+	std::vector<Pending> pend; // one slot per stream that ever deferred (a handful)
 	std::mutex pend_mu;
+	Pending *slot_for(cudaStream_t s, bool create) { // pend_mu held
+		for (auto &p : pend)
+			if (p.s == s) return &p;
+		if (!create) return nullptr;
+		pend.emplace_back();
+		pend.back().s = s;
+		LB_CUDA(cudaMallocHost(&pend.back().h_total, 16));
+		return &pend.back();
+	}
 	~Impl() {
-		if (h_total) cudaFreeHost(h_total);
+		for (auto &p : pend)
+			if (p.h_total) cudaFreeHost(p.h_total);
+		if (shadow_ev) cudaEventDestroy(shadow_ev);
 	}
 };
 
@@ -109,8 +125,9 @@ FlatGemm::FlatGemm(int device, int num_sms, int dim, int metric) : impl_(new Imp
 	impl_->dim = dim;
 	impl_->metric = metric;
 	shape_for(dim, metric, impl_->Kreal16, impl_->Kpad, impl_->nkb, impl_->ksteps_last);
-	impl_->max_norm.alloc(16);
+	impl_->max_norm.alloc(16); // [0] max |x| (float bits), [1] "a row with a non-finite norm exists"
 	LB_CUDA(cudaMemset(impl_->max_norm.p, 0, 16));
+	LB_CUDA(cudaEventCreateWithFlags(&impl_->shadow_ev, cudaEventDisableTiming));
 }
 FlatGemm::~FlatGemm() { delete impl_; }
 
@@ -151,7 +168,11 @@ void FlatGemm::sync_rows(const float *X, long long n, long long cap_rows, cudaSt
 		LB_CUDA(cudaGetLastError());
 		if (launches) (*launches)++;
 		im.rows_done = n;
+		LB_CUDA(cudaEventRecord(im.shadow_ev, s));
+		im.shadow_ev_set = true;
 	}
+	// called under the store's gemm mutex: whoever comes next (any stream) orders itself behind the shadow work
+	if (im.shadow_ev_set) LB_CUDA(cudaStreamWaitEvent(s, im.shadow_ev, 0));
 	if (im.tmX_base != im.shadow.p || im.tmX_rows != n) {
 		encode_rows_map(&im.tmX, im.shadow.p, n, im.Kpad); // rows beyond n read as zeros (TMA out-of-bounds fill)
 		encode_rows_map(&im.tmX64, im.shadow.p, n, im.Kpad, 64);
@@ -237,9 +258,9 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
                       float *d_out_dist, int32_t *d_out_counts, Workspace &ws, cudaStream_t s, int64_t *launches,
                       int64_t *fallback_queries, KernelTimer *timer, bool defer) {
 	Impl &im = *impl_;
-	finish(ws, launches, fallback_queries); // a previous deferred check still uses the scratch buffers
+	finish(ws, s, launches, fallback_queries); // a previous deferred check on this stream still uses the scratch buffers
 	const int d = im.dim, Kpad = im.Kpad;
-	if (!im.attr_set) {
+	std::call_once(im.attr_once, [] {
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
@@ -249,8 +270,7 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		LB_CUDA(cudaFuncSetAttribute(refresh_threshold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 		LB_CUDA(cudaFuncSetAttribute(rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 		LB_CUDA(cudaFuncSetAttribute(rerank_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
-		im.attr_set = true;
-	}
+	});
 	const int cap = warpsel_cap(k);
 	const size_t sel_smem = (size_t)8 * cap * sizeof(u64);
 	const long long ntiles = (n + GEMM_BN - 1) / GEMM_BN;
@@ -360,7 +380,8 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		LB_CUDA(cudaGetLastError());
 		if (timer) timer->end(tix, s);
 		LB_CUDA(cudaMemsetAsync(total, 0, 4, s));
-		count_flags_kernel<<<(nq + 255) / 256, 256, 0, s>>>(flag, cnt, TC_CAP, nq, flag_out, total);
+		count_flags_kernel<<<(nq + 255) / 256, 256, 0, s>>>(flag, cnt, TC_CAP, nq, d_out_counts + q0, k,
+		                                                    im.max_norm.as<uint32_t>() + 1, flag_out, total);
 		LB_CUDA(cudaGetLastError());
 		(*launches) += 2;
 
@@ -369,16 +390,13 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		const bool last_pass = q0 + nq >= nq_total;
 		if (defer && q0 == 0 && last_pass) {
 			std::lock_guard<std::mutex> g(im.pend_mu);
-			if (!im.pend.active) {
-				if (!im.h_total) LB_CUDA(cudaMallocHost(&im.h_total, 16));
-				*im.h_total = 0;
-				LB_CUDA(cudaMemcpyAsync(im.h_total, total, 4, cudaMemcpyDeviceToHost, s));
-				Impl::Pending &pd = im.pend;
-				pd.active = true, pd.s = s, pd.X = X, pd.Q = Qchunk, pd.n = n, pd.allow_bits = allow_bits, pd.label_base = label_base;
-				pd.deleted = deleted, pd.allow = d_allow, pd.flag_out = flag_out, pd.total = total, pd.nq = nq, pd.k = k;
-				pd.out_labels = d_out_labels, pd.out_dist = d_out_dist, pd.out_counts = d_out_counts;
-				return;
-			}
+			Impl::Pending &pd = *im.slot_for(s, true);
+			*pd.h_total = 0;
+			LB_CUDA(cudaMemcpyAsync(pd.h_total, total, 4, cudaMemcpyDeviceToHost, s));
+			pd.active = true, pd.X = X, pd.Q = Qchunk, pd.n = n, pd.allow_bits = allow_bits, pd.label_base = label_base;
+			pd.deleted = deleted, pd.allow = d_allow, pd.flag_out = flag_out, pd.total = total, pd.nq = nq, pd.k = k;
+			pd.out_labels = d_out_labels, pd.out_dist = d_out_dist, pd.out_counts = d_out_counts;
+			return;
 		}
 		uint32_t h_total = 0;
 		LB_CUDA(cudaMemcpyAsync(&h_total, total, 4, cudaMemcpyDeviceToHost, s));
@@ -415,20 +433,21 @@ void FlatGemm::rerun_flagged(const float *X, long long n, const uint32_t *delete
 	}
 }
 
-// Completes a deferred overflow check: waits for the stream, and if some candidate list overflowed re-runs those
-// queries with the exact scan (and waits again).  Returns the number of re-run queries; 0 and no wait when nothing
-// is pending.
-int FlatGemm::finish(Workspace &ws, int64_t *launches, int64_t *fallback_queries) {
+// Completes the deferred overflow check of stream s: waits for the stream, and if some candidate list overflowed
+// re-runs those queries with the exact scan (and waits again).  Returns the number of re-run queries; 0 and no wait
+// when nothing is pending on that stream.  Other streams' pending searches are not touched.
+int FlatGemm::finish(Workspace &ws, cudaStream_t s, int64_t *launches, int64_t *fallback_queries) {
 	Impl &im = *impl_;
 	Impl::Pending pd;
 	{
 		std::lock_guard<std::mutex> g(im.pend_mu);
-		if (!im.pend.active) return 0;
-		pd = im.pend;
-		im.pend.active = false;
+		Impl::Pending *slot = im.slot_for(s, false);
+		if (!slot || !slot->active) return 0;
+		pd = *slot;
+		slot->active = false;
 	}
 	LB_CUDA(cudaStreamSynchronize(pd.s));
-	if (*im.h_total == 0) return 0;
+	if (*pd.h_total == 0) return 0;
 	int64_t before = *fallback_queries;
 	rerun_flagged(pd.X, pd.n, pd.deleted, pd.Q, pd.nq, pd.k, pd.allow, pd.allow_bits, pd.label_base, pd.out_labels, pd.out_dist,
 	              pd.out_counts, pd.flag_out, ws, pd.s, launches, fallback_queries);
@@ -436,14 +455,16 @@ int FlatGemm::finish(Workspace &ws, int64_t *launches, int64_t *fallback_queries
 	return (int)(*fallback_queries - before);
 }
 
-const uint32_t *FlatGemm::pending_total() const {
+const uint32_t *FlatGemm::pending_total(cudaStream_t s) const {
 	std::lock_guard<std::mutex> g(impl_->pend_mu);
-	return impl_->pend.active ? impl_->pend.total : nullptr;
+	Impl::Pending *slot = impl_->slot_for(s, false);
+	return slot && slot->active ? slot->total : nullptr;
 }
 
-bool FlatGemm::has_pending() const {
+bool FlatGemm::has_pending(cudaStream_t s) const {
 	std::lock_guard<std::mutex> g(impl_->pend_mu);
-	return impl_->pend.active;
+	Impl::Pending *slot = impl_->slot_for(s, false);
+	return slot && slot->active;
 }
 
 } // namespace lb

@@ -26,9 +26,10 @@ public:
 	// defer = true: when the batch is a single pass, the candidate-list overflow check (one 4-byte read-back and a
 	// stream synchronise) is left to finish(); until then the results of overflowed queries (degenerate data only)
 	// are not final and the caller's buffers must stay valid.
-	int finish(Workspace &ws, int64_t *launches, int64_t *fallback_queries);
-	bool has_pending() const;
-	const uint32_t *pending_total() const; // device word: number of overflowed queries of the pending search
+	// One pending search per STREAM; finish settles the caller's stream only.
+	int finish(Workspace &ws, cudaStream_t s, int64_t *launches, int64_t *fallback_queries);
+	bool has_pending(cudaStream_t s) const;
+	const uint32_t *pending_total(cudaStream_t s) const; // device word: number of overflowed queries of the pending search
 
 private:
 	void rerun_flagged(const float *X, long long n, const uint32_t *deleted, const float *Qchunk, int nq, int k,

@@ -49,7 +49,15 @@ __global__ void __launch_bounds__(256) shadow_rows_kernel(const float *__restric
 		__nv_bfloat16 h3 = __float2bfloat16_rn(r2);
 		o[d] = h1, o[d + 1] = h2, o[d + 2] = h3;
 	}
-	if (lane == 0 && metric != METRIC_COSINE) atomicMax(max_norm_bits, __float_as_uint(nrm));
+	// A row with a NaN / Inf component must not poison the margin of every query (max over the finite rows only);
+	// its own scores are NaN / Inf and never pass a threshold, so it can only matter when fewer than k finite rows
+	// survive — count_flags_kernel sends exactly those queries to the exact scan, which ranks such rows last.
+	if (lane == 0) {
+		if (!(nrm <= 3.0e38f))
+			atomicOr(max_norm_bits + 1, 1u);
+		else if (metric != METRIC_COSINE)
+			atomicMax(max_norm_bits, __float_as_uint(nrm));
+	}
 }
 
 // ------------------------------------------------------------------ query tiles
@@ -77,10 +85,13 @@ __global__ void __launch_bounds__(256) prep_query_tiles_kernel(const float *__re
 		float xn = metric == METRIC_COSINE ? 1.01f : __uint_as_float(*max_norm_bits);
 		float qn = sqrtf(s);
 		// l2: the folded -|x|^2/2 term is exact to ~2^-24 relative; covered by the absolute slack below
-		margin[q] = 2.0f * (GEMM_ERR_C * qn * xn + 1e-6f * (1.0f + xn * xn));
-		thr[q] = real ? -__int_as_float(0x7F800000) : __int_as_float(0x7F800000);
+		const float mg = 2.0f * (GEMM_ERR_C * qn * xn + 1e-6f * (1.0f + xn * xn));
+		// a query (or table) whose bound is not finite cannot be certified: straight to the exact scan, emit nothing
+		const bool certifiable = mg <= 3.0e38f;
+		margin[q] = mg;
+		thr[q] = (real && certifiable) ? -__int_as_float(0x7F800000) : __int_as_float(0x7F800000);
 		cnt[q] = 0;
-		flag[q] = 0;
+		flag[q] = (real && !certifiable) ? 1u : 0u;
 	}
 }
 
@@ -263,12 +274,16 @@ __global__ void __launch_bounds__(256) rerank_select_kernel(const uint2 *__restr
 	                   label_base, (size_t)q, out_labels, out_dist, out_counts, nullptr);
 }
 
-// number of flagged queries -> *out (read by the host to run the exact scan for them)
+// number of flagged queries -> *total (read by the host to run the exact scan for them).  Flagged: the list
+// overflowed, the bound was not finite, or the table holds rows with non-finite components and the query came back
+// with fewer than k results (the exact scan ranks such rows last instead of dropping them).
 __global__ void count_flags_kernel(const uint32_t *__restrict__ flag, const uint32_t *__restrict__ cnt, int CAP, int nq,
+                                   const int32_t *__restrict__ out_counts, int k, const uint32_t *__restrict__ nonfinite,
                                    uint32_t *__restrict__ flag_out, uint32_t *__restrict__ total) {
 	int q = blockIdx.x * blockDim.x + threadIdx.x;
 	if (q >= nq) return;
 	uint32_t f = (flag[q] != 0 || cnt[q] > (uint32_t)CAP) ? 1u : 0u;
+	if (!f && *nonfinite != 0u && out_counts[q] < k) f = 1u;
 	flag_out[q] = f;
 	if (f) atomicAdd(total, 1u);
 }

@@ -66,6 +66,25 @@ static void check_shape(int dim, int P, int M) {
 	if (P <= 0 || M <= 0) throw Error("num_partitions and num_sub_vectors must be positive");
 	if (dim % M != 0) throw Error("dimension " + std::to_string(dim) + " is not divisible by num_sub_vectors " + std::to_string(M));
 	if ((size_t)M * 1024 + 8192 > 200 * 1024) throw Error("num_sub_vectors > 192 does not fit the shared-memory lookup table");
+	// lut_kernel keeps one sub-quantizer's codebook slice [256][dsub + 1] and LUT_QPB query sub-vectors in shared memory
+	const int dsub = dim / M;
+	if (((size_t)256 * (dsub + 1) + (size_t)LUT_QPB * dsub) * sizeof(float) > 220 * 1024)
+		throw Error("sub-vector dimension " + std::to_string(dsub) + " (dimension / num_sub_vectors) is too large: use at least " +
+		            std::to_string((dim + 199) / 200) + " sub-vectors");
+}
+
+// num_sub_vectors = 0: lancedb's rule (dim/16, else dim/8, else 1: lance_manager.rs:483-515) when the device scan
+// supports the result, else the largest sub-vector width >= 16 that divides the dimension and fits
+static int default_sub_vectors(int d) {
+	int M = d % 16 == 0 ? d / 16 : (d % 8 == 0 ? d / 8 : 1);
+	auto fits = [&](int m) {
+		const int dsub = d / m;
+		return (size_t)m * 1024 + 8192 <= 200 * 1024 && ((size_t)256 * (dsub + 1) + (size_t)LUT_QPB * dsub) * sizeof(float) <= 220 * 1024;
+	};
+	if (fits(M)) return M;
+	for (int dsub = 200; dsub >= 1; dsub--)
+		if (d % dsub == 0 && fits(d / dsub)) return d / dsub;
+	return M; // check_shape reports why
 }
 
 void Store::set_index(int P, int M, int64_t n_indexed, const float *centroids, const float *codebook,
@@ -75,8 +94,18 @@ void Store::set_index(int P, int M, int64_t n_indexed, const float *centroids, c
 	check_shape(dim_, P, M);
 	if (n_indexed < 0 || n_indexed > n_rows_) throw Error("index covers more rows than the table holds");
 	if (part_offsets[0] != 0 || part_offsets[P] != n_indexed) throw Error("part_offsets must span [0, n_indexed]");
-	for (int64_t i = 0; i < n_indexed; i++)
-		if (row_ids[i] < label_base_ || row_ids[i] >= label_base_ + n_rows_) throw Error("row id outside the table");
+	{
+		// the tail scan assumes the indexed rows are exactly [0, n_indexed): row_ids must be a permutation of
+		// [label_base, label_base + n_indexed)
+		std::vector<bool> seen((size_t)n_indexed, false);
+		for (int64_t i = 0; i < n_indexed; i++) {
+			const int64_t r = row_ids[i] - label_base_;
+			if (r < 0 || r >= n_rows_) throw Error("row id outside the table");
+			if (r >= n_indexed || seen[(size_t)r])
+				throw Error("row_ids must be a permutation of the first n_indexed labels of the table");
+			seen[(size_t)r] = true;
+		}
+	}
 	std::unique_ptr<IvfPqIndexFull> ix(new IvfPqIndexFull());
 	ix->metric = metric_;
 	ix->dim = dim_, ix->P = P, ix->M = M, ix->dsub = dim_ / M, ix->n_indexed = n_indexed;

@@ -51,7 +51,8 @@ void Store::create_index(int num_partitions, int num_sub_vectors) {
 	if (n <= 0) throw Error("cannot train an IVF_PQ index on an empty table");
 	int P = num_partitions > 0 ? num_partitions : (int)std::max(1.0, std::floor(std::sqrt((double)n) + 0.5));
 	if (P > n) P = (int)n;
-	int M = num_sub_vectors > 0 ? num_sub_vectors : (d % 16 == 0 ? d / 16 : (d % 8 == 0 ? d / 8 : 1));
+	if (n >= (1ll << 31) - 64) throw Error("IVF_PQ training supports fewer than 2^31 rows per device store");
+	int M = num_sub_vectors > 0 ? num_sub_vectors : default_sub_vectors(d);
 	check_shape(d, P, M);
 	const int dsub = d / M;
 	const bool is_dot = metric_ == METRIC_DOT;

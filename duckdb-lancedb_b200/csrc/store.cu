@@ -326,7 +326,7 @@ void Store::search_device(const float *d_queries, int nq, int k, int nprobes, in
 		flat_search_locked(d_queries, nq, k, d_allow, allow_bits, d_out_labels, d_out_dist, d_out_counts, *ws, s, defer);
 	if (d_overflow) {
 		// number of queries whose result is not final until search_finish (0 on every path but a pending tcgen05 batch)
-		const uint32_t *t = (defer && flat_gemm_) ? flat_gemm_->pending_total() : nullptr;
+		const uint32_t *t = (defer && flat_gemm_) ? flat_gemm_->pending_total(s) : nullptr;
 		if (t)
 			LB_CUDA(cudaMemcpyAsync(d_overflow, t, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
 		else
@@ -342,11 +342,11 @@ int Store::search_finish(cudaStream_t s) {
 	std::shared_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));
 	int rerun = 0;
-	if (flat_gemm_ && flat_gemm_->has_pending()) {
+	if (flat_gemm_ && flat_gemm_->has_pending(s)) {
 		Workspace *ws = scratch_for(s);
 		std::lock_guard<std::mutex> wg(ws->mu);
 		int64_t launches = 0, fallback = 0;
-		rerun = flat_gemm_->finish(*ws, &launches, &fallback);
+		rerun = flat_gemm_->finish(*ws, s, &launches, &fallback);
 		std::lock_guard<std::mutex> g(stat_mu_);
 		tc_fallback_ += fallback;
 		launches_ += launches;

@@ -136,7 +136,8 @@ int32_t lance_b200_merge_topk_strided_device(int32_t device, const int64_t *d_la
  * of re-run queries (0 = the results that were already consumed are final), or -1.  d_overflow (nullable, device)
  * receives, in stream order, the number of queries whose result is not final yet, so a multi-GPU step can carry
  * it through its gather and learn on every rank whether any shard has to be settled.  One pending search per
- * handle; the next search on the handle settles a pending one first. */
+ * (handle, stream); the next search on the same stream settles that stream's pending one first, other streams'
+ * pending searches are not touched. */
 int32_t lance_b200_search_device_async(void *handle, const float *d_queries, int32_t nq, int32_t k, int32_t nprobes,
                                        int32_t refine_factor, const uint32_t *d_allow, int64_t bitmap_bits,
                                        int64_t *d_out_labels, float *d_out_distances, int32_t *d_out_counts,

@@ -276,3 +276,79 @@ def test_sharded_step_on_one_gpu_packed_record_and_strided_merge(gpu, oracle_mod
     torch.cuda.synchronize()
     assert (g2.ML.cpu().numpy() == L1).all() and (g2.MC.cpu().numpy() == C1).all()
     np.testing.assert_allclose(g2.MD.cpu().numpy(), D1, rtol=1e-5)
+
+
+def test_tc_concurrent_batched_searches_right_after_an_append(gpu, oracle_mod):
+    """Two threads issue their first batched searches (each on its own library stream) right after add_batch: the
+    bf16 shadow and max|x| are built on ONE of the streams, the other must wait for them (cudaEvent) instead of
+    reading an unwritten shadow."""
+    import threading
+
+    n, d, k, nq = 300_000, 128, 10, 64
+    rng = np.random.default_rng(41)
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Qs = [rng.standard_normal((nq, d), dtype=np.float32) for _ in range(4)]
+    for rep in range(3):
+        with gpu.LanceHandle(d, "dot") as h:
+            h.add_batch(X)
+            out = [None] * len(Qs)
+            start = threading.Barrier(len(Qs))
+
+            def work(i):
+                start.wait()
+                out[i] = h.search_batch(Qs[i], k)
+
+            ts = [threading.Thread(target=work, args=(i,)) for i in range(len(Qs))]
+            [t.start() for t in ts]
+            [t.join() for t in ts]
+            assert h.stats()["flat_tc_batches"] == len(Qs)
+            for i, (L, D, C) in enumerate(out):
+                check_oracle(oracle_mod, X, Qs[i][:3], L[:3], D[:3], C[:3], k, "dot", what=f"concurrent rep{rep} t{i}")
+            # all threads' full batches equal a quiet re-run
+            for i, (L, D, C) in enumerate(out):
+                L2, D2, C2 = h.search_batch(Qs[i], k)
+                assert (L == L2).all() and (C == C2).all()
+
+
+@pytest.mark.parametrize("metric", ["l2", "cosine", "dot"])
+def test_tc_nan_and_inf_rows_do_not_poison_the_batch(gpu, oracle_mod, metric):
+    """A NaN row (and, for l2, an Inf row): max|x| (the error bound of every query) must stay finite; with enough finite rows
+    the results are those of the table without the two rows, and the batched path equals the single-query scan."""
+    n, d, k, nq = 70_000, 64, 10, 16
+    rng = np.random.default_rng(43)
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    X[1234, 5] = np.nan
+    if metric == "l2":  # an infinite component is infinitely FAR under l2 (under dot it would be infinitely near)
+        X[4321, 7] = np.inf
+    Q = rng.standard_normal((nq, d), dtype=np.float32)
+    with gpu.LanceHandle(d, metric) as h:
+        h.add_batch(X)
+        L, D, C, fb = tc_search(h, Q, k)
+        assert (C == k).all() and np.isfinite(D).all()
+        assert not np.isin(L, [1234, 4321]).any()
+        dele = oracle_mod.make_bitmap(np.isin(np.arange(n), [1234, 4321]))
+        check_oracle(oracle_mod, X, Q[:4], L[:4], D[:4], C[:4], k, metric, None, dele, what=f"nan rows {metric}")
+        # fewer finite survivors than k: the exact scan takes over for those queries and ranks the NaN row last
+        mask = np.zeros(n, bool)
+        mask[[10, 20, 30, 1234]] = True
+        L2, D2, C2, fb2 = tc_search(h, Q, k, allow=gpu.make_bitmap(mask))
+        assert fb2 == nq and (C2 == 4).all()
+        for j in range(nq):
+            l1, d1 = h.search(Q[j], k, allow=gpu.make_bitmap(mask))
+            assert list(l1) == list(L2[j, :4]) and sorted(l1[:3]) == [10, 20, 30] and l1[3] == 1234
+
+
+def test_tc_nonfinite_query_goes_to_the_exact_scan(gpu, oracle_mod):
+    n, d, k, nq = 70_000, 32, 5, 9
+    rng = np.random.default_rng(47)
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Q = rng.standard_normal((nq, d), dtype=np.float32)
+    Q[3, 0] = np.inf
+    with gpu.LanceHandle(d, "dot") as h:
+        h.add_batch(X)
+        L, D, C, fb = tc_search(h, Q, k)
+        assert fb == 1
+        ok = [j for j in range(nq) if j != 3]
+        check_oracle(oracle_mod, X, Q[ok][:4], L[ok][:4], D[ok][:4], C[ok][:4], k, "dot", what="inf query batch")
+        l1, d1 = h.search(Q[3], k)
+        assert list(l1) == list(L[3, :C[3]])

@@ -225,3 +225,32 @@ def test_batched_probe_equals_single_query_probe(gpu, oracle_mod, metric):
             np.testing.assert_allclose(dd, D[j, :C[j]], rtol=1e-6)
         for j in (0, 13, 40):
             compare_with_oracle(oracle_mod, h, ix, X, Q[j], 10, 8, 1, metric, what=f"{metric} batched-probe q{j}")
+
+
+def test_default_sub_vectors_for_awkward_dimensions_and_bad_exchange_rows(gpu, oracle_mod):
+    """dim % 8 != 0: lancedb's default would be ONE sub-vector of `dim` floats, which the device scan's lookup-table
+    kernel cannot hold for large dims; the default then falls to the widest sub-vector that fits, and an explicit
+    infeasible request is rejected at create time (not at the first search)."""
+    rng = np.random.default_rng(3)
+    n, d = 3000, 300
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    with gpu.LanceHandle(d, "l2") as h:
+        h.add_batch(X)
+        h.create_index(8, 0)
+        g = h.get_ivfpq()
+        assert d % g["M"] == 0 and d // g["M"] <= 200 and g["M"] > 1
+        l, dd = h.search(X[17], 5, nprobes=8, refine_factor=4)
+        assert l[0] == 17 and dd[0] < 1e-6
+        with pytest.raises(gpu.LanceError, match="too large"):
+            h.create_index(8, 1)
+    # set_ivfpq: row ids that are not a permutation of the indexed prefix are rejected
+    n, d, P, M = 2000, 16, 4, 4
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    ix = oracle_mod.IvfPqIndex.train(X, "l2", P, M, iters=2)
+    with gpu.LanceHandle(d, "l2") as h:
+        h.add_batch(X)
+        bad = ix.row_ids.copy()
+        bad[5] = bad[6]
+        with pytest.raises(gpu.LanceError, match="permutation"):
+            h.set_ivfpq(ix.centroids, ix.codebook, ix.part_offsets, bad, ix.codes)
+        h.set_ivfpq(ix.centroids, ix.codebook, ix.part_offsets, ix.row_ids, ix.codes)
