@@ -1,21 +1,27 @@
 #!/usr/bin/env python
-"""bench.py — kNN queries/sec of the B200 flat-search hot path (BASELINE.json metric), one JSON line.
+"""bench.py — kNN queries/sec of the B200 search hot path (BASELINE.json metric), one JSON line.
 
   python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
   python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle port), rank 0 only
   torchrun --nproc-per-node N bench.py --gpus N ...          # N > 1: one process per GPU, NCCL gather + device merge
 
-Workload (default `c4`, the configuration BASELINE.json's metric "queries/sec (k=10) at 1/2/4/8 B200" is quoted on,
-and it fits one GPU): flat dot-product search, 100M x 128 fp32 rows sharded by contiguous row ranges over the
-N GPUs, batch of 1024 queries replicated to every GPU, k=10.  A "step" = one batch through the hot path:
-local top-k on every shard, all_gather of the per-shard lists, final device-side select.  Strong scaling
-(total rows fixed).  Other workloads (`--workload c1|c2|c3|c5`) are BASELINE.json's remaining configs.
+Headline workload (default `c4`, the configuration BASELINE.json's metric "queries/sec (k=10) at 1/2/4/8 B200" is
+quoted on, and it fits one GPU): flat dot-product search, 100M x 128 fp32 rows sharded by contiguous row ranges over
+the N GPUs, batch of 1024 queries replicated to every GPU, k=10.  A "step" = one batch through the hot path: local
+top-k on every shard, all_gather of the per-shard lists, final device-side select.  Strong scaling (total rows fixed).
+
+At N=1 the default run then times BASELINE.json's other configurations as well (c1; c2 at batch 1 / 64 / 4096; c3 at
+batch 1 / 4096; c5 with the 80 % and the 1 % prefilter) and reports them under `configs` in the same JSON line, each
+with value, ms_per_step, e2e, BOTH roofline fractions (step level = algorithmic work / ms_per_step, kernel level =
+algorithmic work / CUDA-event time of the dominant kernel) and a CPU figure.  `--workload cN` times one of them as the
+headline instead (no `configs`), `--no-configs` skips them.
 
 `value`   : queries/s with queries, rows and results resident in HBM (CUDA events, max over ranks).
 `e2e`     : same metric through the reference-facing C-ABI call with HOST buffers: pinned host queries are
             copied H2D and the final (label, distance) lists D2H inside the timed region, every step.
 `roofline`: the dominant kernel's algorithmic bytes (or flops) / its CUDA-event duration, vs MEASURED_PEAKS.json.
-`cpu_baseline`: the oracle's OpenMP fp32 batch search timed on this box's host cores on a bounded sample.
+`cpu_baseline`: the oracle's OpenMP fp32 search (cache-blocked SGEMM-style kernel for batches) timed on this box's
+            host cores, on the full table where that takes seconds, else on a bounded sample (said in `sample`).
 """
 from __future__ import annotations
 
@@ -48,7 +54,15 @@ WORKLOADS = {
     "c5": dict(rows=10_000_000, dim=384, metric="l2", batch=1, k=10, kind="flat", selectivity=0.8,
                desc="ORDER BY array_distance LIMIT 10 with WHERE prefilter (80% selectivity bitmap), 10Mx384"),
 }
+# the configurations the default N=1 run reports under `configs`, grouped by table: (name, workload, overrides)
+SUBCONFIGS = [
+    ("c1", "c1", {}),
+    ("c2b1", "c2", {"batch": 1}), ("c2b64", "c2", {"batch": 64}), ("c2b4096", "c2", {"batch": 4096}),
+    ("c5", "c5", {"selectivity": 0.8}), ("c5s01", "c5", {"selectivity": 0.01}),
+    ("c3b1", "c3", {"batch": 1}), ("c3b4096", "c3", {"batch": 4096}),
+]
 SEED = 0xC0FFEE
+GEN_CHUNK = 1 << 22
 
 
 def load_peaks():
@@ -60,16 +74,76 @@ def load_peaks():
     return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, source="fallback")
 
 
-def load_traffic(workload, batch):
+def load_traffic(name):
     """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of the dominant kernel from the committed
-    `ncu --set full` capture of this workload (profiles/traffic.json, written from profiles/*_ncu_full.txt)."""
+    `ncu --set full` capture of this configuration (profiles/traffic.json, written from profiles/*_ncu_full.txt)."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if not os.path.exists(p):
         return None, None
-    ent = json.load(open(p)).get(f"{workload}_b{batch}")
+    ent = json.load(open(p)).get(name)
     if not ent:
         return None, None
     return ent.get("bytes"), ent.get("note")
+
+
+# ------------------------------------------------------------------------------------------------ synthetic data
+def _mixture_centres(dim, dev):
+    """--data clustered: 1 000 unit-norm centres (unit-norm mixture of 1 000 Gaussians, sigma 0.05)."""
+    import torch
+
+    g = torch.Generator(device=dev)
+    g.manual_seed(SEED + 3)
+    c = torch.randn((1000, dim), generator=g, device=dev, dtype=torch.float32)
+    return c / c.norm(dim=1, keepdim=True)
+
+
+def _clustered(n, dim, g, dev):
+    import torch
+
+    cen = _mixture_centres(dim, dev)
+    idx = torch.randint(0, cen.shape[0], (n,), generator=g, device=dev)
+    x = cen[idx] + 0.05 * torch.randn((n, dim), generator=g, device=dev, dtype=torch.float32)
+    return x / x.norm(dim=1, keepdim=True)
+
+
+def table_chunks(dim, lo, hi, dev, data="gaussian"):
+    """The synthetic table, rows [lo, hi): yields (first_row, tensor[rows, dim]) pieces generated on the device.
+    Chunk c of 2^22 rows is seeded with SEED + 7919*c, so every sharding (and tests/test_baseline_shapes_gpu.py)
+    sees the same table."""
+    import torch
+
+    g = torch.Generator(device=dev)
+    pos = lo
+    while pos < hi:
+        cidx = pos // GEN_CHUNK
+        g.manual_seed(SEED + 7919 * cidx)
+        if data == "clustered":
+            blk = _clustered(GEN_CHUNK, dim, g, dev)
+        else:
+            blk = torch.randn((GEN_CHUNK, dim), generator=g, device=dev, dtype=torch.float32)
+        a, b = pos - cidx * GEN_CHUNK, min(hi, (cidx + 1) * GEN_CHUNK) - cidx * GEN_CHUNK
+        yield pos, blk[a:b]
+        pos += b - a
+        del blk
+
+
+def bench_queries(B, dim, dev, data="gaussian"):
+    import torch
+
+    g = torch.Generator(device=dev)
+    g.manual_seed(SEED + 1)
+    if data == "clustered":
+        return _clustered(B, dim, g, dev)
+    return torch.randn((B, dim), generator=g, device=dev, dtype=torch.float32)
+
+
+def bench_mask(rows, selectivity, dev):
+    """Prefilter of the C5 workload: bool[rows], True = the row may be returned."""
+    import torch
+
+    g = torch.Generator(device=dev)
+    g.manual_seed(SEED + 2)
+    return torch.rand(rows, generator=g, device=dev) < selectivity
 
 
 class ClockSampler:
@@ -98,22 +172,14 @@ class ClockSampler:
         for ln in self.proc.stdout:
             self.lines.append((time.perf_counter(), ln.strip()))
 
-    def count_since(self, t0):
-        return sum(1 for t, _ in self.lines if t >= t0)
-
-    def stop(self, t0=0.0):
-        """Samples that arrived at or after t0 (the start of the timed region) are the ones reported."""
+    def summary(self, t0=0.0, t1=float("inf")):
+        """Samples that arrived in [t0, t1] (a timed region) are the ones reported."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for t, ln in self.lines:
-            if t < t0:
+        for t, ln in list(self.lines):
+            if t < t0 or t > t1:
                 continue
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
@@ -129,43 +195,14 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
 
-
-GEN_CHUNK = 1 << 22
-
-
-def table_chunks(dim, lo, hi, dev):
-    """The synthetic table, rows [lo, hi): yields (first_row, tensor[rows, dim]) pieces generated on the device.
-    Chunk c of 2^22 rows is seeded with SEED + 7919*c, so every sharding (and tests/test_baseline_shapes_gpu.py)
-    sees the same table."""
-    import torch
-
-    g = torch.Generator(device=dev)
-    pos = lo
-    while pos < hi:
-        cidx = pos // GEN_CHUNK
-        g.manual_seed(SEED + 7919 * cidx)
-        blk = torch.randn((GEN_CHUNK, dim), generator=g, device=dev, dtype=torch.float32)
-        a, b = pos - cidx * GEN_CHUNK, min(hi, (cidx + 1) * GEN_CHUNK) - cidx * GEN_CHUNK
-        yield pos, blk[a:b]
-        pos += b - a
-        del blk
-
-
-def bench_queries(B, dim, dev):
-    import torch
-
-    g = torch.Generator(device=dev)
-    g.manual_seed(SEED + 1)
-    return torch.randn((B, dim), generator=g, device=dev, dtype=torch.float32)
-
-
-def bench_mask(rows, selectivity, dev):
-    """Prefilter of the C5 workload: bool[rows], True = the row may be returned."""
-    import torch
-
-    g = torch.Generator(device=dev)
-    g.manual_seed(SEED + 2)
-    return torch.rand(rows, generator=g, device=dev) < selectivity
+    def stop(self):
+        if not self.proc:
+            return
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
 
 
 def shard_range(rows, rank, world):
@@ -173,30 +210,76 @@ def shard_range(rows, rank, world):
     return rows * rank // world, rows * (rank + 1) // world
 
 
-# ------------------------------------------------------------------------------------------------ reference arm
-_CPU_SAMPLE = {}
+# ------------------------------------------------------------------------------------------------ CPU arm
+def host_threads(oracle):
+    """All the host threads the CPU arm can use.  torchrun exports OMP_NUM_THREADS=1 to its workers, which would
+    make the reference arm single-threaded at N > 1; the affinity mask of the process is what really bounds it."""
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    return max(oracle.num_threads(), avail)
 
 
-def cpu_search_sample(wl, sample_rows, sample_q, threads, seed=SEED):
-    """The oracle's OpenMP fp32 flat search on a bounded sample; returns (seconds, rows, queries).  The sample
-    (generated once per shape) is outside the timed region."""
+def cpu_flat_kernel(oracle, nq):
+    """Batches: the cache-blocked SGEMM-style kernel (6 x 16 register tiles); a few queries: the
+    row-streaming kernel (a query panel of 16 would waste 15 lanes)."""
+    if nq >= 8:
+        return oracle.flat_search_batch_blocked, "oracle_flat_search_batch_blocked (cache-blocked SGEMM-style fp32, OpenMP)"
+    return oracle.flat_search_batch_f32, "oracle_flat_search_batch_f32 (row-streaming fp32, OpenMP)"
+
+
+class CpuFlatSample:
+    """A host table (the full one, or a bounded sample of it) and the timed CPU search over it."""
+
+    def __init__(self, wl, X, Q, allow, full_rows, threads):
+        import oracle
+
+        self.oracle, self.wl, self.X, self.Q, self.allow, self.threads = oracle, wl, X, Q, allow, threads
+        self.full_rows = full_rows
+        self.fn, self.fn_name = cpu_flat_kernel(oracle, Q.shape[0])
+        self.fn(X[:1000], Q[:1], wl["k"], wl["metric"], nthreads=threads)  # warm the thread pool
+
+    def step(self):
+        t0 = time.perf_counter()
+        self.fn(self.X, self.Q, self.wl["k"], self.wl["metric"], allow=self.allow, nthreads=self.threads)
+        return time.perf_counter() - t0
+
+    @property
+    def scale(self):
+        """time of a full step / time of a sample step: one pass over X per batch, every query of the batch."""
+        return (self.full_rows / self.X.shape[0]) * (self.wl["batch"] / self.Q.shape[0])
+
+    def describe(self):
+        r, q = self.X.shape[0], self.Q.shape[0]
+        if r == self.full_rows and q == self.wl["batch"]:
+            return f"{self.fn_name} on the FULL table ({r} rows x {q} queries per step), {self.threads} threads"
+        return (f"{self.fn_name} on {r} of {self.full_rows} rows x {q} of {self.wl['batch']} queries per step, "
+                f"{self.threads} threads; scaled x{self.scale:.4g} (time is linear in rows x queries)")
+
+
+def make_cpu_flat_sample(wl, threads, budget_flop=6.0e11, X_full=None, Q_full=None, allow_full=None, seed=SEED):
+    """Sample shape: all queries of the batch (so the query-panel reuse of the blocked kernel is the real one) and as
+    many rows as `budget_flop` allows, at least 64 K and at most 2 GiB of fp32 (larger than any host cache).  When the
+    caller hands in the device table (X_full), the sample is its leading rows; else it is generated on the host."""
     import oracle
 
-    key = (sample_rows, sample_q, wl["dim"], wl.get("selectivity"))
-    if key not in _CPU_SAMPLE:
-        _CPU_SAMPLE.clear()
+    B, d = wl["batch"], wl["dim"]
+    q = min(B, 4096)
+    rows = int(max(65_536, budget_flop / (2.0 * q * d)))
+    rows = min(rows, wl["rows"], (2 << 30) // (4 * d))
+    if X_full is not None and X_full.shape[0] >= rows:
+        X = X_full[:rows]
+        Q = Q_full[:q]
+        allow = None if allow_full is None else allow_full[: (rows + 31) // 32].copy()
+    else:
         rng = np.random.default_rng(seed)
-        X = rng.standard_normal((sample_rows, wl["dim"]), dtype=np.float32)
-        Q = rng.standard_normal((sample_q, wl["dim"]), dtype=np.float32)
-        allow = None
-        if wl.get("selectivity"):
-            allow = oracle.make_bitmap(rng.random(sample_rows) < wl["selectivity"])
-        oracle.flat_search_batch_f32(X[:1000], Q[:1], wl["k"], wl["metric"], nthreads=threads)  # warm the pool
-        _CPU_SAMPLE[key] = (X, Q, allow)
-    X, Q, allow = _CPU_SAMPLE[key]
-    t0 = time.perf_counter()
-    oracle.flat_search_batch_f32(X, Q, wl["k"], wl["metric"], allow=allow, nthreads=threads)
-    return time.perf_counter() - t0, sample_rows, sample_q
+        X = rng.standard_normal((rows, d), dtype=np.float32)
+        Q = rng.standard_normal((q, d), dtype=np.float32)
+        allow = oracle.make_bitmap(rng.random(rows) < wl["selectivity"]) if wl.get("selectivity") else None
+    if allow is not None and rows % 32:
+        allow[-1] &= np.uint32((1 << (rows % 32)) - 1)
+    return CpuFlatSample(wl, X, Q, allow, wl["rows"], threads)
 
 
 _IVF_CACHE = {}
@@ -233,27 +316,8 @@ def cpu_ivfpq_sample(wl, nq, threads, seed=SEED):
     return time.perf_counter() - t0, nq
 
 
-def host_threads(oracle):
-    """All the host threads the CPU arm can use.  torchrun exports OMP_NUM_THREADS=1 to its workers, which would
-    make the reference arm single-threaded at N > 1; the affinity mask of the process is what really bounds it."""
-    try:
-        avail = len(os.sched_getaffinity(0))
-    except AttributeError:
-        avail = os.cpu_count() or 1
-    return max(oracle.num_threads(), avail)
-
-
-def cpu_sample_shape(wl, budget_pairs):
-    """Pick (rows, queries) of the sample so that rows*queries*dim ~ budget, keeping the batch shape when possible."""
-    q = min(wl["batch"], 64)
-    rows = int(min(wl["rows"], max(10_000, budget_pairs // (q * wl["dim"]))))
-    # bound the host memory of the sample (<= 2 GiB of fp32 rows, larger than any host cache); the time budget is
-    # filled by repeating the sample instead
-    rows = min(rows, (2 << 30) // (4 * wl["dim"]))
-    return rows, q
-
-
-def cpu_baseline(wl, seconds_target=12.0):
+def cpu_baseline(wl, seconds_target=10.0, X_full=None, Q_full=None, allow_full=None):
+    """{"value", "unit", "cores", "kind", "sample", ...}: the oracle port timed on this box's host cores."""
     import oracle
 
     oracle.build()
@@ -262,29 +326,27 @@ def cpu_baseline(wl, seconds_target=12.0):
         dt, nq = cpu_ivfpq_sample(wl, 4 * threads, threads)
         nq = int(max(4 * threads, min(4096, nq * seconds_target / max(dt, 1e-3))))
         dt, nq = cpu_ivfpq_sample(wl, nq, threads)
-        return {"value": nq / dt, "unit": "queries/s", "cores": threads, "kind": "port",
+        return {"value": nq / dt, "unit": "queries/s", "cores": threads, "kind": "port", "extrapolated": False,
                 "sample": f"oracle_ivfpq_search (oracle/oracle.c) on a full-shape index (P={wl['P']}, M={wl['M']}, "
                           f"{wl['rows']} coded rows, random codebooks/codes), {nq} queries, one per host thread, {dt:.2f} s"}
-    # calibrate: ~0.3 s probe, then scale to the target
-    rows, q = cpu_sample_shape(wl, 2_000_000_000)
-    dt, r, qq = cpu_search_sample(wl, min(rows, 200_000), q, threads)
-    rate = r * qq * wl["dim"] / dt
-    rows, q = cpu_sample_shape(wl, int(rate * seconds_target))
-    dt, r, qq = cpu_search_sample(wl, rows, q, threads)
-    reps = 1
-    while dt < 0.5 * seconds_target and reps < 4000:  # small tables / single queries: repeat the sample
-        d2, _, _ = cpu_search_sample(wl, rows, q, threads)
-        dt += d2
+    s = make_cpu_flat_sample(wl, threads, budget_flop=3.0e11, X_full=X_full, Q_full=Q_full, allow_full=allow_full)
+    dt, reps = s.step(), 1
+    while dt < 0.5 * seconds_target and reps < 4000 and dt / reps * (reps + 1) < seconds_target:
+        dt += s.step()
         reps += 1
-    qq *= reps
-    # queries/s on the full table: time scales with rows (one pass over X per batch)
-    qps = qq / (dt * (wl["rows"] / r))
-    return {"value": qps, "unit": "queries/s", "cores": threads, "kind": "port",
-            "sample": f"oracle_flat_search_batch_f32 (OpenMP fp32 port, oracle/oracle.c) on {r} of {wl['rows']} rows x "
-                      f"{qq} queries, {dt:.2f} s, scaled by rows"}
+    per_step = dt / reps
+    qps = wl["batch"] / (per_step * s.scale)
+    return {"value": qps, "unit": "queries/s", "cores": threads, "kind": "port", "extrapolated": s.scale != 1.0,
+            "scale_factor": s.scale, "sample_rows": int(s.X.shape[0]), "sample_queries": int(s.Q.shape[0]),
+            "sample_seconds_per_step": per_step, "sample": s.describe() + f"; {reps} repetitions, {dt:.2f} s"}
 
 
 def run_reference(args, wl):
+    """`--impl reference`: the reference's CPU implementation of the path on the host cores.  LanceDB itself cannot
+    be built here (no Rust toolchain, crates not vendored: DESIGN.md section 2), so this is the oracle port
+    (`kind: "port"`), all host threads.  A step is a BOUNDED SAMPLE of the workload (all queries of the batch, a row
+    range); `ms_per_step` is what was actually timed per step, `value` the full-workload rate it implies
+    (`extrapolated`, `scale_factor`)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -292,6 +354,9 @@ def run_reference(args, wl):
 
     oracle.build()
     threads = host_threads(oracle)
+    common = {"impl": "reference", "metric": "kNN queries/sec", "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps,
+              "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+              "data": "synthetic N(0,1), seeded", "config": workload_config(wl, args)}
     if wl["kind"] == "ivfpq":
         times = []
         nq = 8 * threads
@@ -299,89 +364,134 @@ def run_reference(args, wl):
             dt, _ = cpu_ivfpq_sample(wl, nq, threads)
             if i >= args.warmup:
                 times.append(dt)
-        qps = nq / (sum(times) / len(times))
+        dt = sum(times) / len(times)
+        qps = nq / dt
         sample = (f"oracle IVF_PQ port on a full-shape index (P={wl['P']}, M={wl['M']}, {wl['rows']} coded rows, random "
                   f"codebooks/codes), {nq} queries per step, one per host thread (LanceDB itself cannot be built here)")
-        line = {"impl": "reference", "metric": "kNN queries/sec", "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wl["batch"] / qps,
-                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": workload_config(wl, args),
-                "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": threads, "kind": "port", "sample": sample},
-                "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        line = dict(common, value=qps, ms_per_step=1e3 * dt, extrapolated=False, queries_per_step=nq,
+                    cpu_baseline={"value": qps, "unit": "queries/s", "cores": threads, "kind": "port", "sample": sample},
+                    e2e={"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
         print(json.dumps(line))
         return
-    rows, q = cpu_sample_shape(wl, 1_500_000_000)
-    times, reps_per_step = [], 1
+    s = make_cpu_flat_sample(wl, threads, budget_flop=6.0e11)
+    times = []
     for i in range(args.warmup + args.steps):
-        dt, reps = 0.0, 0
-        while reps < reps_per_step or (dt < 1.0 and reps < 2000):  # a step = at least ~1 s of CPU work
-            d1, r, qq = cpu_search_sample(wl, rows, q, threads)
-            dt += d1
-            reps += 1
-        reps_per_step = reps
+        dt = s.step()
         if i >= args.warmup:
-            times.append(dt / reps)
+            times.append(dt)
     dt = sum(times) / len(times)
-    qps = q / (dt * (wl["rows"] / rows))
-    sample = (f"oracle OpenMP fp32 port of the reference's CPU flat search, {rows} of {wl['rows']} rows x {q} queries per "
-              f"step, scaled by rows (LanceDB itself cannot be built here: no Rust toolchain, crates not vendored)")
-    line = {"impl": "reference", "metric": "kNN queries/sec", "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wl["batch"] / qps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(wl, args),
-            "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": threads, "kind": "port", "sample": sample},
-            "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    qps = wl["batch"] / (dt * s.scale)
+    sample = s.describe() + " (LanceDB itself cannot be built here: no Rust toolchain, crates not vendored)"
+    line = dict(common, value=qps, ms_per_step=1e3 * dt, extrapolated=s.scale != 1.0, scale_factor=s.scale,
+                sample_rows=int(s.X.shape[0]), sample_queries=int(s.Q.shape[0]),
+                full_step_ms_implied=1e3 * dt * s.scale,
+                cpu_baseline={"value": qps, "unit": "queries/s", "cores": threads, "kind": "port", "sample": sample},
+                e2e={"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
     print(json.dumps(line))
 
 
-def workload_config(wl, args):
-    return {"workload": f"{args.workload}: {wl['desc']}", "rows": wl["rows"], "dim": wl["dim"], "metric": wl["metric"],
-            "batch": wl["batch"], "k": wl["k"], "sharding": f"rows/{args.gpus}", "l2_hygiene": "inputs larger than L2"
-            if wl["rows"] * wl["dim"] * 4 // max(args.gpus, 1) > 200e6 else "L2 flushed between steps"}
+def workload_config(wl, args, name=None):
+    cfg = {"workload": f"{name or args.workload}: {wl['desc']}", "rows": wl["rows"], "dim": wl["dim"], "metric": wl["metric"],
+           "batch": wl["batch"], "k": wl["k"], "sharding": f"rows/{args.gpus}", "l2_hygiene": "inputs larger than L2"
+           if wl["rows"] * wl["dim"] * 4 // max(args.gpus, 1) > 200e6 else "L2 flushed between steps"}
+    if wl.get("selectivity"):
+        cfg["selectivity"] = wl["selectivity"]
+    if getattr(args, "data", "gaussian") != "gaussian":
+        cfg["data"] = args.data
+    return cfg
 
 
 # ------------------------------------------------------------------------------------------------ product arm
-def run_b200(args, wl):
-    import torch
-    import torch.distributed as dist
+class Bench:
+    """One process' view of a run: device, rank, the clock sampler."""
 
-    from __graft_entry__ import load_package
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
 
-    pkg = load_package()
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
+        from __graft_entry__ import load_package
+
+        self.torch, self.dist, self.args = torch, dist, args
+        self.pkg = load_package()
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world != args.gpus and self.world == 1 and args.gpus > 1:
             raise SystemExit("launch N>1 with torchrun: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    saved_stdout = None
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL writes its version banner to stdout; stdout must carry exactly one JSON line, so point fd 1 at
-        # stderr until that line is printed
-        sys.stdout.flush()
-        saved_stdout = os.dup(1)
-        os.dup2(2, 1)
-        dist.init_process_group("nccl", device_id=dev)
-    pkg.set_default_device(local)
-    peaks = load_peaks()
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.saved_stdout = None
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            # NCCL writes its version banner to stdout; stdout must carry exactly one JSON line, so point fd 1 at
+            # stderr until that line is printed
+            sys.stdout.flush()
+            self.saved_stdout = os.dup(1)
+            os.dup2(2, 1)
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.pkg.set_default_device(self.local)
+        self.peaks = load_peaks()
+        self.stream = torch.cuda.current_stream()
+        self.sp = self.stream.cuda_stream
+        self.sampler = ClockSampler(self.local)
+        if self.rank == 0:
+            self.sampler.start()
 
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def emit(self, line):
+        if self.saved_stdout is not None:
+            sys.stdout.flush()
+            os.dup2(self.saved_stdout, 1)
+        print(json.dumps(line), flush=True)
+
+    def close(self):
+        self.sampler.stop()
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+class Table:
+    """A workload's table resident in HBM (this rank's shard), optionally with its IVF_PQ index."""
+
+    def __init__(self, b: Bench, wl):
+        torch = b.torch
+        self.b, self.wl = b, wl
+        rows, dim = wl["rows"], wl["dim"]
+        self.lo, self.hi = shard_range(rows, b.rank, b.world)
+        self.n_local = self.hi - self.lo
+        h = b.pkg.LanceHandle(dim, wl["metric"])
+        h.set_label_base(self.lo)
+        h.reserve(self.n_local)
+        for pos, blk in table_chunks(dim, self.lo, self.hi, b.dev, b.args.data):
+            h.add_batch_device(blk.data_ptr(), blk.shape[0], dim, b.sp)
+        assert h.count() == self.n_local
+        self.h = h
+        self.sizes = None
+        self.X_host = None  # host copy of a small table for the full-table CPU figure (fetched once per table)
+        if wl["kind"] == "ivfpq":
+            t0 = time.perf_counter()
+            h.create_index(wl["P"], wl["M"])
+            self.index_build_s = time.perf_counter() - t0
+            self.sizes = np.diff(h.ivfpq_part_offsets())
+        torch.cuda.empty_cache()
+
+    def close(self):
+        self.h.close()
+        self.b.torch.cuda.empty_cache()
+
+
+def measure(b: Bench, tab: Table, wl, name, steps, headline):
+    """Times one configuration on a resident table.  Returns the JSON-line dict (rank 0) or None."""
+    torch, dist, args, pkg, dev = b.torch, b.dist, b.args, b.pkg, b.dev
+    world, rank, stream, sp, h = b.world, b.rank, b.stream, b.sp, tab.h
     rows, dim, metric, B, k = wl["rows"], wl["dim"], wl["metric"], wl["batch"], wl["k"]
-    lo, hi = shard_range(rows, rank, world)
-    n_local = hi - lo
-    stream = torch.cuda.current_stream()
-    sp = stream.cuda_stream
-
-    # ---- build the shard in HBM (synthetic N(0,1), seeded per chunk so any sharding sees the same table)
-    h = pkg.LanceHandle(dim, metric)
-    h.set_label_base(lo)
-    h.reserve(n_local)
-    for pos, blk in table_chunks(dim, lo, hi, dev):
-        h.add_batch_device(blk.data_ptr(), blk.shape[0], dim, sp)
-    assert h.count() == n_local
-    Qd = bench_queries(B, dim, dev)
+    n_local, lo, hi = tab.n_local, tab.lo, tab.hi
+    peaks = b.peaks
+    Qd = bench_queries(B, dim, dev, args.data)
     Qh = Qd.cpu().pin_memory()
 
     d_allow, allow_bits, allow_host = 0, 0, None
@@ -392,15 +502,12 @@ def run_b200(args, wl):
         d_allow, allow_bits = allow_t.data_ptr(), allow_host.shape[0] * 32
 
     nprobes = wl.get("nprobes", 20)
-    adc_bytes = None
+    adc_bytes = ivf_query_bytes = None
     if wl["kind"] == "ivfpq":
-        h.create_index(wl["P"], wl["M"])
-        offs = h.ivfpq_part_offsets()
-        sizes = np.diff(offs)
         probed_rows = 0
         for j in range(min(B, 16)):
             dbg = h.ivfpq_search_debug(Qh[j].numpy(), k, nprobes, 1)
-            probed_rows += int(sizes[dbg["parts"]].sum())
+            probed_rows += int(tab.sizes[dbg["parts"]].sum())
         probed_rows /= min(B, 16)
         # per query: codes (M B/row) + row term (4) + row id (4) of the probed lists + the query's lookup table
         adc_bytes = probed_rows * (wl["M"] + 8) + wl["M"] * 256 * 4
@@ -414,7 +521,7 @@ def run_b200(args, wl):
         import importlib
 
         sharding = importlib.import_module("duckdb_lancedb_b200.sharding")
-        ss = sharding.ShardedSearch(pkg, h, world, B, k, dev, local)
+        ss = sharding.ShardedSearch(pkg, h, world, B, k, dev, b.local)
     Lh = torch.empty((B, k), dtype=torch.int64).pin_memory()
     Dh = torch.empty((B, k), dtype=torch.float32).pin_memory()
     Ch = torch.empty(B, dtype=torch.int32).pin_memory()
@@ -443,11 +550,6 @@ def run_b200(args, wl):
             Ch.copy_(oC, non_blocking=True)
             stream.synchronize()
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
     shard_bytes = n_local * dim * 4 if wl["kind"] == "flat" else 1 << 40
     need_flush = shard_bytes <= 200e6  # the 126 MB L2 would otherwise serve the table on every step after the first
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if need_flush else None
@@ -455,37 +557,37 @@ def run_b200(args, wl):
 
     wall_ms = [0.0]
 
-    def timed(fn, steps):
+    def timed(fn, nsteps):
         """K steps bracketed by barrier + synchronize; device time from CUDA events on the launching stream (max over
         ranks), host wall-clock of the same steps in wall_ms[0]."""
-        barrier()
+        b.barrier()
         if need_flush:
             # one event pair per step.  Between steps (outside the timed intervals): write a buffer larger than L2, read
             # another one — the table is evicted AND the dirty lines of the write are already back in DRAM — and wait,
             # so that a step that runs on the library's own stream cannot overlap the flush
-            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(nsteps)]
             wall = 0.0
-            for a, b in evs:
+            for a, e in evs:
                 flush_buf.fill_(1)
                 flush_rd.sum()
                 torch.cuda.synchronize()
                 t0 = time.perf_counter()
                 a.record(stream)
                 fn()
-                b.record(stream)
-                b.synchronize()
+                e.record(stream)
+                e.synchronize()
                 wall += time.perf_counter() - t0
-            barrier()
-            ms = sum(a.elapsed_time(b) for a, b in evs)
+            b.barrier()
+            ms = sum(a.elapsed_time(e) for a, e in evs)
             wall_ms[0] = wall * 1e3
         else:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             t0 = time.perf_counter()
             e0.record(stream)
-            for _ in range(steps):
+            for _ in range(nsteps):
                 fn()
             e1.record(stream)
-            barrier()
+            b.barrier()
             wall_ms[0] = (time.perf_counter() - t0) * 1e3
             ms = e0.elapsed_time(e1)
         if world > 1:
@@ -494,21 +596,19 @@ def run_b200(args, wl):
             ms = t.item()
         return ms
 
-    # ---- warm-up, then the timed region (device-resident).  nvidia-smi is started before the warm-up so that it is
-    # already streaming when the timed region begins; only samples from the region on are reported.
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    for _ in range(max(args.warmup, 3)):
+    # ---- warm-up, then the timed region (device-resident).  nvidia-smi has been streaming since the process
+    # started; only samples from the region on are reported.
+    warmup = max(args.warmup, 3)
+    for _ in range(warmup):
         step_device(Qd.data_ptr())
-    barrier()
+    b.barrier()
     st0 = h.stats()
     h.profile_enable(True)
     h.profile_read()
     if ss:
         ss.merges = 0
     t_region = time.perf_counter()
-    ms = timed(lambda: step_device(Qd.data_ptr()), args.steps)
+    ms = timed(lambda: step_device(Qd.data_ptr()), steps)
     prof = h.profile_read()
     h.profile_enable(False)
     st1 = h.stats()
@@ -516,35 +616,40 @@ def run_b200(args, wl):
     # ---- end-to-end (host buffers) timed region
     for _ in range(2):
         step_e2e()
-    ms_e2e_dev = timed(step_e2e, args.steps)
+    ms_e2e_dev = timed(step_e2e, steps)
     # N=1: the reference-facing call is synchronous and runs on the library's own stream, so the host wall-clock of
     # the steps is the end-to-end time (the events on torch's stream only bound it from below)
     ms_e2e = max(ms_e2e_dev, wall_ms[0]) if world == 1 else ms_e2e_dev
     # A timed region shorter than a few sampler periods (single queries, small shards) yields no clock sample:
-    # keep the same device step running, untimed, until the region + extension spans ~0.5 s of load.  The count is
-    # derived from the max-reduced times, so every rank runs the same number of steps (the step has a collective).
+    # keep the same device step running, untimed, until the region + extension spans ~0.5 s of load (headline) or
+    # ~0.25 s (sub-configurations).  The count is derived from the max-reduced times, so every rank runs the same
+    # number of steps (the step has a collective).
     ext_steps = 0
-    if ms + ms_e2e < 500.0:
-        ext_steps = int(min(20000, math.ceil((500.0 - ms - ms_e2e) / max(ms / args.steps, 1e-3))))
+    span = 500.0 if headline else 250.0
+    if ms + ms_e2e < span:
+        ext_steps = int(min(20000, math.ceil((span - ms - ms_e2e) / max(ms / steps, 1e-3))))
         for _ in range(ext_steps):
             step_device(Qd.data_ptr())
-        barrier()
-    clocks = sampler.stop(t_region) if rank == 0 else None
+        b.barrier()
+    clocks = b.sampler.summary(t_region, time.perf_counter()) if rank == 0 else None
     if clocks is not None:
         clocks["window"] = ("timed region" if not ext_steps else
-                            f"timed region + {ext_steps} untimed identical steps (region shorter than 0.5 s = five sampler periods)")
+                            f"timed region + {ext_steps} untimed identical steps (region shorter than {span / 1e3:g} s)")
 
     launches = st1["kernel_launches"] - st0["kernel_launches"] + merges_value
-    qps = B * args.steps / (ms / 1e3)
-    qps_e2e = B * args.steps / (ms_e2e / 1e3)
+    qps = B * steps / (ms / 1e3)
+    qps_e2e = B * steps / (ms_e2e / 1e3)
+    step_s = ms / steps / 1e3
 
-    # ---- roofline of the dominant kernel (algorithmic bytes / flops per launch)
+    # ---- roofline of the dominant kernel (algorithmic bytes / flops per launch) and of the
+    # whole step (the same algorithmic work / ms_per_step)
     roof = None
     if prof["flat_gemm_launches"] > 0:
         t = prof["flat_gemm_ms"] / prof["flat_gemm_launches"] / 1e3
-        # one launch = the whole batch against the whole shard: 2*B*n*d flops (one pass, norms/re-rank excluded)
-        flops = 2.0 * B * n_local * dim * (prof["flat_gemm_launches"] and 1)
-        launches_per_step = prof["flat_gemm_launches"] / args.steps
+        # the launches of a step together = the whole batch against the whole shard: 2*B*n*d flops (one pass,
+        # norms / re-rank excluded)
+        flops = 2.0 * B * n_local * dim
+        launches_per_step = prof["flat_gemm_launches"] / steps
         achieved = flops / launches_per_step / t / 1e12
         kk = dim + (3 if metric == "l2" else 0)  # K of the contraction (l2 carries -|x|^2/2 as three bf16 terms)
         nkb = (((kk + 15) // 16 * 16) + 63) // 64
@@ -554,30 +659,39 @@ def run_b200(args, wl):
         bound = "tensor" if ridge >= peak * 1e12 / (peaks["hbm_gbs"] * 1e9) else "hbm"
         if bound == "tensor":
             roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                    "traffic": None, "kernel": variant + " (tcgen05 bf16, all segments of a batch)", "peak_source": peaks["source"] + " bf16 sustained"}
+                    "step_achieved": flops / step_s / 1e12, "step_frac": flops / step_s / 1e12 / peak,
+                    "traffic": None, "kernel": variant + " (tcgen05 bf16, all segments of a batch)",
+                    "peak_source": peaks["source"] + " bf16 sustained"}
         else:
-            bytes_ = (n_local * dim * 2.0) / launches_per_step
-            a = bytes_ / t / 1e9
+            bytes_step = n_local * dim * 2.0
+            a = bytes_step / launches_per_step / t / 1e9
             roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
-                    "traffic": None, "kernel": variant + " (tcgen05 bf16, HBM-bound batch: bf16 shadow read once)", "peak_source": peaks["source"]}
+                    "step_achieved": bytes_step / step_s / 1e9, "step_frac": bytes_step / step_s / 1e9 / peaks["hbm_gbs"],
+                    "traffic": None, "kernel": variant + " (tcgen05 bf16, HBM-bound batch: bf16 shadow read once)",
+                    "peak_source": peaks["source"]}
     elif prof["adc_scan_launches"] > 0:
         t = prof["adc_scan_ms"] / prof["adc_scan_launches"] / 1e3
-        a = adc_bytes * B / t / 1e9
+        launches_per_step = prof["adc_scan_launches"] / steps
+        a = adc_bytes * B / launches_per_step / t / 1e9
+        whole = ivf_query_bytes * B / step_s / 1e9
         roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
+                "step_achieved": whole, "step_frac": whole / peaks["hbm_gbs"],
                 "traffic": None, "kernel": "adc_scan_kernel (codes + row terms + ids of the probed lists + LUT)",
                 "peak_source": peaks["source"], "avg_launch_ms": t * 1e3, "bytes_per_query_scan": adc_bytes,
                 "bytes_per_query_whole_search": ivf_query_bytes,
-                "whole_search_gbs": ivf_query_bytes * B * args.steps / (ms / 1e3) / 1e9}
+                "step_bytes_note": "step level counts the whole search per query: scan bytes + centroid table + codebook + refine rows"}
     elif prof["flat_scan_launches"] > 0:
         t = prof["flat_scan_ms"] / prof["flat_scan_launches"] / 1e3
+        launches_per_step = prof["flat_scan_launches"] / steps
         sel = wl.get("selectivity") or 1.0
         # X read once per pass of <= 4 queries; masked rows are skipped before any load (s*N*D*4 + N/8)
-        bytes_ = n_local * dim * 4.0 * sel + (n_local / 8.0 if wl.get("selectivity") else 0.0)
-        a = bytes_ / t / 1e9
+        bytes_pass = n_local * dim * 4.0 * sel + (n_local / 8.0 if wl.get("selectivity") else 0.0)
+        a = bytes_pass / t / 1e9
         roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
+                "step_achieved": bytes_pass * launches_per_step / step_s / 1e9,
+                "step_frac": bytes_pass * launches_per_step / step_s / 1e9 / peaks["hbm_gbs"],
                 "traffic": None, "kernel": "flat_scan_kernel (fp32, <=4 queries per pass)", "peak_source": peaks["source"],
-                "launches_per_step": prof["flat_scan_launches"] / args.steps, "avg_launch_ms": t * 1e3,
-                "selectivity": sel}
+                "launches_per_step": launches_per_step, "avg_launch_ms": t * 1e3, "selectivity": sel}
 
     if roof is not None:
         if roof["bound"] == "hbm" and roof.get("achieved") is not None:
@@ -585,33 +699,81 @@ def run_b200(args, wl):
             # scan can exceed it) and the nominal 8 TB/s
             roof["peak_nominal"] = 8000.0
             roof["frac_nominal"] = roof["achieved"] / 8000.0
-        # the committed capture is of the default shape of the workload; an overridden shape has no measured traffic
-        stock = not args.rows and (args.selectivity is None or args.selectivity == WORKLOADS[args.workload].get("selectivity"))
-        roof["traffic"], note = load_traffic(args.workload, B) if stock else (None, None)
+        # the committed capture is of the stock shape of the configuration; an overridden shape has no measured traffic
+        stock = not args.rows and not args.k and args.data == "gaussian"
+        roof["traffic"], note = load_traffic(name) if stock else (None, None)
         if note:
             roof["traffic_note"] = note
-    if rank == 0:
-        base = cpu_baseline(wl) if world == 1 and not args.no_cpu_baseline else None
-        line = {"metric": "kNN queries/sec", "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "f32" if st1["flat_tc_batches"] == st0["flat_tc_batches"]
-                else "bf16 candidates + f32 re-rank", "data": "synthetic N(0,1), seeded", "config": workload_config(wl, args),
-                "clocks": clocks,
-                "e2e": {"value": qps_e2e, "unit": "queries/s", "h2d_bytes_per_step": int(Qh.numel() * 4 + (allow_host.nbytes if allow_host is not None and world == 1 else 0)),
-                        "d2h_bytes_per_step": int(Lh.numel() * 8 + Dh.numel() * 4 + Ch.numel() * 4), "ms_per_step": ms_e2e / args.steps},
-                "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": base,
-                "paths": {"flat_simt_batches": st1["flat_simt_batches"] - st0["flat_simt_batches"],
-                          "flat_tc_batches": st1["flat_tc_batches"] - st0["flat_tc_batches"],
-                          "tc_fallback_queries": st1["tc_fallback_queries"] - st0["tc_fallback_queries"],
-                          "ivfpq_batches": st1["ivfpq_batches"] - st0["ivfpq_batches"]},
-                "profile_ms": {kk: vv for kk, vv in prof.items()}}
-        if saved_stdout is not None:
-            sys.stdout.flush()
-            os.dup2(saved_stdout, 1)
-        print(json.dumps(line), flush=True)
-    h.close()
-    if world > 1:
-        dist.destroy_process_group()
+    if rank != 0:
+        return None
+    line = {"metric": "kNN queries/sec", "value": qps, "unit": "queries/s", "n_gpus": world, "steps": steps,
+            "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32" if st1["flat_tc_batches"] == st0["flat_tc_batches"]
+            else "bf16 candidates + f32 re-rank", "data": "synthetic N(0,1), seeded" if args.data == "gaussian" else
+            "synthetic unit-norm mixture of 1000 Gaussians (sigma 0.05), seeded", "config": workload_config(wl, args, name),
+            "clocks": clocks,
+            "e2e": {"value": qps_e2e, "unit": "queries/s", "h2d_bytes_per_step": int(Qh.numel() * 4 + (allow_host.nbytes if allow_host is not None and world == 1 else 0)),
+                    "d2h_bytes_per_step": int(Lh.numel() * 8 + Dh.numel() * 4 + Ch.numel() * 4), "ms_per_step": ms_e2e / steps},
+            "gpu_launches": int(launches), "roofline": roof,
+            "paths": {"flat_simt_batches": st1["flat_simt_batches"] - st0["flat_simt_batches"],
+                      "flat_tc_batches": st1["flat_tc_batches"] - st0["flat_tc_batches"],
+                      "tc_fallback_queries": st1["tc_fallback_queries"] - st0["tc_fallback_queries"],
+                      "ivfpq_batches": st1["ivfpq_batches"] - st0["ivfpq_batches"]},
+            "profile_ms": {kk: vv for kk, vv in prof.items()}}
+    if wl["kind"] == "ivfpq":
+        line["index_build_s"] = tab.index_build_s
+    if not args.no_cpu_baseline and world == 1:
+        # tables of up to 4 GiB come to the host whole (the CPU figure is then measured on the FULL table when a step
+        # fits the budget); larger ones are sampled (all queries of the batch, a row range) and scaled
+        X_full = Q_full = None
+        if wl["kind"] == "flat" and rows * dim * 4 <= (4 << 30) and args.data == "gaussian":
+            if tab.X_host is None:
+                _, tab.X_host = h.get_all_vectors()
+            X_full, Q_full = tab.X_host, Qh.numpy()
+        line["cpu_baseline"] = cpu_baseline(wl, 10.0 if headline else 4.0, X_full, Q_full, allow_host)
+    else:
+        line["cpu_baseline"] = None
+    return line
+
+
+def run_b200(args, wl):
+    b = Bench(args)
+    tab = Table(b, wl)
+    name = args.workload
+    if args.batch and args.batch != WORKLOADS[args.workload]["batch"] or args.workload in ("c2", "c3"):
+        name = f"{args.workload}b{wl['batch']}"
+    if args.workload == "c5" and wl.get("selectivity") == 0.01:
+        name = "c5s01"
+    line = measure(b, tab, wl, name, args.steps, True)
+    tab.close()
+    configs = None
+    if b.world == 1 and args.workload == "c4" and not args.no_configs and not (args.batch or args.rows or args.k):
+        # BASELINE.json's other configurations, each on its own table, same protocol, fewer steps
+        configs, cur, cur_wl = {}, None, None
+        for name, base, over in SUBCONFIGS:
+            sub = dict(WORKLOADS[base])
+            sub.update(over)
+            if "selectivity" in over:
+                sub["desc"] = sub["desc"].replace("80% selectivity", f"{100 * over['selectivity']:g}% selectivity")
+            try:
+                if cur_wl != base:
+                    if cur is not None:
+                        cur.close()
+                    cur, cur_wl = Table(b, sub), base
+                steps = min(args.steps, 10 if sub["batch"] >= 1024 else 20)
+                ln = measure(b, cur, sub, name, steps, False)
+                for drop in ("metric", "unit", "n_gpus", "higher_is_better", "scaling", "vs_baseline", "data"):
+                    ln.pop(drop, None)
+                configs[name] = ln
+            except Exception as e:  # a sub-configuration must never take the headline line down with it
+                configs[name] = {"error": f"{type(e).__name__}: {e}"}
+        if cur is not None:
+            cur.close()
+    if b.rank == 0:
+        if configs is not None:
+            line["configs"] = configs
+        b.emit(line)
+    b.close()
 
 
 def main():
@@ -625,7 +787,10 @@ def main():
     ap.add_argument("--rows", type=int, default=None, help="override the workload's row count (experiments only)")
     ap.add_argument("--k", type=int, default=None)
     ap.add_argument("--selectivity", type=float, default=None, help="c5: fraction of rows the prefilter keeps (0.8 / 0.01)")
+    ap.add_argument("--data", default="gaussian", choices=["gaussian", "clustered"],
+                    help="clustered: unit-norm mixture of 1000 Gaussians, sigma 0.05 (robustness of the candidate bound)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="N=1 default run: skip BASELINE.json's other configurations")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.batch:

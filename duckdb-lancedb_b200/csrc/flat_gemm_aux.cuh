@@ -34,10 +34,13 @@ __global__ void __launch_bounds__(256) shadow_rows_kernel(const float *__restric
 	s = warp_sum(s);
 	const float nrm = sqrtf(s);
 	float scale = 1.f;
-	if (metric == METRIC_COSINE) scale = nrm > 0.f ? 1.0f / nrm : 0.f;
+	// cosine: a row whose norm is zero or not finite has distance 1 in the exact kernels (their `den > 0` test fails),
+	// i.e. similarity 0: its shadow is the zero row
+	const bool cos_null = metric == METRIC_COSINE && !(nrm > 0.f && nrm <= 3.0e38f);
+	if (metric == METRIC_COSINE) scale = cos_null ? 0.f : 1.0f / nrm;
 	for (int i = lane; i < Kpad; i += 32) {
 		float v = 0.f;
-		if (i < d) v = __ldg(x + i) * scale;
+		if (i < d && !cos_null) v = __ldg(x + i) * scale;
 		o[i] = __float2bfloat16_rn(v);
 	}
 	if (metric == METRIC_L2 && lane == 0) {
@@ -52,10 +55,10 @@ __global__ void __launch_bounds__(256) shadow_rows_kernel(const float *__restric
 	// A row with a NaN / Inf component must not poison the margin of every query (max over the finite rows only);
 	// its own scores are NaN / Inf and never pass a threshold, so it can only matter when fewer than k finite rows
 	// survive — count_flags_kernel sends exactly those queries to the exact scan, which ranks such rows last.
-	if (lane == 0) {
+	if (lane == 0 && metric != METRIC_COSINE) {
 		if (!(nrm <= 3.0e38f))
 			atomicOr(max_norm_bits + 1, 1u);
-		else if (metric != METRIC_COSINE)
+		else
 			atomicMax(max_norm_bits, __float_as_uint(nrm));
 	}
 }

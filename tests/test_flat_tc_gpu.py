@@ -328,14 +328,20 @@ def test_tc_nan_and_inf_rows_do_not_poison_the_batch(gpu, oracle_mod, metric):
         assert not np.isin(L, [1234, 4321]).any()
         dele = oracle_mod.make_bitmap(np.isin(np.arange(n), [1234, 4321]))
         check_oracle(oracle_mod, X, Q[:4], L[:4], D[:4], C[:4], k, metric, None, dele, what=f"nan rows {metric}")
-        # fewer finite survivors than k: the exact scan takes over for those queries and ranks the NaN row last
+        # fewer finite survivors than k.  l2 / dot: the exact scan takes over for those queries and ranks the NaN row
+        # last, like the oracle; cosine: a row without a usable norm has distance 1 in every exact kernel (and in the
+        # oracle), so the tensor path serves it as a zero row
         mask = np.zeros(n, bool)
         mask[[10, 20, 30, 1234]] = True
-        L2, D2, C2, fb2 = tc_search(h, Q, k, allow=gpu.make_bitmap(mask))
-        assert fb2 == nq and (C2 == 4).all()
+        bm = gpu.make_bitmap(mask)
+        L2, D2, C2, fb2 = tc_search(h, Q, k, allow=bm)
+        assert (C2 == 4).all() and fb2 == (0 if metric == "cosine" else nq)
+        check_oracle(oracle_mod, X, Q, L2, D2, C2, k, metric, bm, what=f"nan row among 4 survivors {metric}")
         for j in range(nq):
-            l1, d1 = h.search(Q[j], k, allow=gpu.make_bitmap(mask))
-            assert list(l1) == list(L2[j, :4]) and sorted(l1[:3]) == [10, 20, 30] and l1[3] == 1234
+            l1, d1 = h.search(Q[j], k, allow=bm)
+            assert list(l1) == list(L2[j, :4])
+            if metric != "cosine":
+                assert l1[3] == 1234 and np.isnan(d1[3])
 
 
 def test_tc_nonfinite_query_goes_to_the_exact_scan(gpu, oracle_mod):
