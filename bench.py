@@ -260,14 +260,15 @@ class CpuFlatSample:
 
 def make_cpu_flat_sample(wl, threads, budget_flop=6.0e11, X_full=None, Q_full=None, allow_full=None, seed=SEED):
     """Sample shape: all queries of the batch (so the query-panel reuse of the blocked kernel is the real one) and as
-    many rows as `budget_flop` allows, at least 64 K and at most 2 GiB of fp32 (larger than any host cache).  When the
+    many rows as `budget_flop` allows, at least 64 K and at most 2 GiB of fp32 (4 GiB when the device table was fetched;
+    larger than any host cache).  When the
     caller hands in the device table (X_full), the sample is its leading rows; else it is generated on the host."""
     import oracle
 
     B, d = wl["batch"], wl["dim"]
     q = min(B, 4096)
     rows = int(max(65_536, budget_flop / (2.0 * q * d)))
-    rows = min(rows, wl["rows"], (2 << 30) // (4 * d))
+    rows = min(rows, wl["rows"], ((4 << 30) if X_full is not None else (2 << 30)) // (4 * d))
     if X_full is not None and X_full.shape[0] >= rows:
         X = X_full[:rows]
         Q = Q_full[:q]
@@ -673,13 +674,16 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
         t = prof["adc_scan_ms"] / prof["adc_scan_launches"] / 1e3
         launches_per_step = prof["adc_scan_launches"] / steps
         a = adc_bytes * B / launches_per_step / t / 1e9
-        whole = ivf_query_bytes * B / step_s / 1e9
+        # whole search: per query the scan bytes + refine rows; the centroid table and the codebook are read once per
+        # BATCH ("amortised over B if batched")
+        shared = wl["P"] * dim * 4 + wl["M"] * 256 * (dim // wl["M"]) * 4
+        whole = ((ivf_query_bytes - shared) * B + shared) / step_s / 1e9
         roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
                 "step_achieved": whole, "step_frac": whole / peaks["hbm_gbs"],
                 "traffic": None, "kernel": "adc_scan_kernel (codes + row terms + ids of the probed lists + LUT)",
                 "peak_source": peaks["source"], "avg_launch_ms": t * 1e3, "bytes_per_query_scan": adc_bytes,
                 "bytes_per_query_whole_search": ivf_query_bytes,
-                "step_bytes_note": "step level counts the whole search per query: scan bytes + centroid table + codebook + refine rows"}
+                "step_bytes_note": "step level counts the whole search: per query scan bytes + refine rows, per batch centroid table + codebook"}
     elif prof["flat_scan_launches"] > 0:
         t = prof["flat_scan_ms"] / prof["flat_scan_launches"] / 1e3
         launches_per_step = prof["flat_scan_launches"] / steps

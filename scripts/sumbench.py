@@ -1,15 +1,27 @@
 #!/usr/bin/env python
-"""sumbench.py FILE.json ... — one line per bench.py JSON line."""
+"""sumbench.py FILE.json ... — one line per bench.py JSON line (and per entry of its `configs`)."""
 import json, sys
+
+
+def row(name, d):
+    if "error" in d:
+        print("%-12s ERROR %s" % (name, d["error"]))
+        return
+    r = d.get("roofline") or {}
+    cb = d.get("cpu_baseline") or {}
+    f = lambda v, n=3: None if v is None else round(v, n)
+    print("%-12s qps=%11.1f ms=%9.4f e2e=%11.1f (%8.4f ms) %-6s kern=%s step=%s L=%s cpu=%s%s clk=%s" % (
+        name, d["value"], d["ms_per_step"], d["e2e"]["value"], d["e2e"].get("ms_per_step", 0), r.get("bound"),
+        f(r.get("frac")), f(r.get("step_frac")), d.get("gpu_launches"), f(cb.get("value"), 1),
+        "*" if cb.get("extrapolated") else "", (d.get("clocks") or {}).get("sm_mhz")))
+
+
 for f in sys.argv[1:]:
     try:
-        d = json.load(open(f))
+        d = json.loads([l for l in open(f) if l.startswith("{")][-1])
     except Exception as e:
-        print(f, "ERR", e); continue
-    r = d.get("roofline") or {}
-    pm = d.get("profile_ms") or {}
-    ks = {k: round(v, 3) for k, v in pm.items() if v}
-    ach, fr = r.get("achieved"), r.get("frac")
-    print("%-28s qps=%10.1f ms=%9.4f e2e=%10.1f %s ach=%s frac=%s L=%s %s" % (
-        f.split("/")[-1], d["value"], d["ms_per_step"], d["e2e"]["value"], r.get("bound"),
-        None if ach is None else round(ach, 1), None if fr is None else round(fr, 3), d.get("gpu_launches"), ks))
+        print(f, "ERR", e)
+        continue
+    row(f.split("/")[-1][:12], d)
+    for name, sub in (d.get("configs") or {}).items():
+        row("  " + name, sub)
