@@ -293,6 +293,40 @@ class LanceHandle:
         self._check(rc, "search")
         return labels, dist, counts
 
+    def bind_search_batch(self, Q, k: int, out, nprobes: int = 20, refine_factor: int = 1, allow=None):
+        """lance_detached_search_batch with every argument converted ONCE: returns a zero-argument callable that makes
+        exactly the C call (bench.py's end-to-end loop: the per-call cost of building ctypes arguments in Python is
+        harness time, not the library's).  Q / out / allow must stay alive and unchanged in place."""
+        assert isinstance(Q, np.ndarray) and Q.dtype == np.float32 and Q.flags.c_contiguous
+        labels, dist, counts = out
+        bm = None if allow is None else np.ascontiguousarray(allow, np.uint32)
+        fn = lib().lance_detached_search_batch
+        args = (self._h, _ptr(Q), C.c_int32(Q.shape[0]), C.c_int32(Q.shape[1]), C.c_int32(int(k)), C.c_int32(nprobes),
+                C.c_int32(refine_factor), _ptr(bm), C.c_int64(0 if bm is None else bm.shape[0] * 32), _ptr(labels), _ptr(dist),
+                _ptr(counts), self._err, C.c_int(ERR_LEN))
+        keep = (Q, labels, dist, counts, bm)
+
+        def call():
+            if fn(*args) < 0:
+                raise LanceError("Lance search: " + self._err.value.decode())
+            return keep[1], keep[2], keep[3]
+
+        return call
+
+    def bind_search_device(self, d_queries: int, nq: int, k: int, d_labels: int, d_dist: int, d_counts: int,
+                           nprobes: int = 20, refine_factor: int = 1, d_allow: int = 0, allow_bits: int = 0, stream: int = 0):
+        """lance_b200_search_device with the arguments converted once (see bind_search_batch)."""
+        fn = lib().lance_b200_search_device
+        args = (self._h, _ptr(d_queries), C.c_int32(nq), C.c_int32(k), C.c_int32(nprobes), C.c_int32(refine_factor),
+                _ptr(d_allow) if d_allow else None, C.c_int64(allow_bits), _ptr(d_labels), _ptr(d_dist), _ptr(d_counts),
+                _ptr(stream) if stream else None, self._err, C.c_int(ERR_LEN))
+
+        def call():
+            if fn(*args) < 0:
+                raise LanceError("Lance search: " + self._err.value.decode())
+
+        return call
+
     def search_device(self, d_queries: int, nq: int, k: int, d_labels: int, d_dist: int, d_counts: int,
                       nprobes: int = 20, refine_factor: int = 1, d_allow: int = 0, allow_bits: int = 0, stream: int = 0):
         rc = lib().lance_b200_search_device(self._h, _ptr(d_queries), nq, k, nprobes, refine_factor,

@@ -17,131 +17,16 @@
 //   * selection is fused (topk.cuh): nothing but the k best keys per block leaves the SM;
 //   * blocks share their k-th best key through one global word per query (atomicMin) so late
 //     blocks reject almost everything with a single compare.
+#include <algorithm>
+#include <cstring>
+#include <mutex>
+
 #include "kernels.h"
+#include "scan_common.cuh"
+#include "flat_scan1.cuh"
 #include "topk.cuh"
 
 namespace lb {
-
-// Transposed warp reduction: v[i] = this lane's partial sum for row i (8 rows).  Returns the full
-// 32-lane sum of row (lane>>2)&7.  7 + 2 shuffles.
-__device__ __forceinline__ float reduce8(float (&v)[8]) {
-	const unsigned lane = lane_id();
-	{
-		const bool up = lane & 16;
-#pragma unroll
-		for (int i = 0; i < 4; i++) {
-			float send = up ? v[i] : v[i + 4];
-			float keep = up ? v[i + 4] : v[i];
-			v[i] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 16);
-		}
-	}
-	{
-		const bool up = lane & 8;
-#pragma unroll
-		for (int i = 0; i < 2; i++) {
-			float send = up ? v[i] : v[i + 2];
-			float keep = up ? v[i + 2] : v[i];
-			v[i] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 8);
-		}
-	}
-	{
-		const bool up = lane & 4;
-		float send = up ? v[0] : v[1];
-		float keep = up ? v[1] : v[0];
-		v[0] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 4);
-	}
-	float s = v[0];
-	s += __shfl_xor_sync(0xFFFFFFFFu, s, 2);
-	s += __shfl_xor_sync(0xFFFFFFFFu, s, 1);
-	return s;
-}
-
-template <int VEC>
-struct XVec;
-template <>
-struct XVec<4> {
-	float4 v;
-	__device__ __forceinline__ void zero() { v = make_float4(0.f, 0.f, 0.f, 0.f); }
-	__device__ __forceinline__ void load(const float *p) { v = __ldg(reinterpret_cast<const float4 *>(p)); }
-	__device__ __forceinline__ void load_shared(const float *p) { v = *reinterpret_cast<const float4 *>(p); }
-};
-template <>
-struct XVec<1> {
-	float v;
-	__device__ __forceinline__ void zero() { v = 0.f; }
-	__device__ __forceinline__ void load(const float *p) { v = __ldg(p); }
-	__device__ __forceinline__ void load_shared(const float *p) { v = *p; }
-};
-
-template <int METRIC>
-__device__ __forceinline__ void accum(float &acc, const XVec<4> &q, const XVec<4> &x) {
-	if (METRIC == METRIC_L2) {
-		float a = q.v.x - x.v.x, b = q.v.y - x.v.y, c = q.v.z - x.v.z, e = q.v.w - x.v.w;
-		acc = fmaf(a, a, acc);
-		acc = fmaf(b, b, acc);
-		acc = fmaf(c, c, acc);
-		acc = fmaf(e, e, acc);
-	} else {
-		acc = fmaf(q.v.x, x.v.x, acc);
-		acc = fmaf(q.v.y, x.v.y, acc);
-		acc = fmaf(q.v.z, x.v.z, acc);
-		acc = fmaf(q.v.w, x.v.w, acc);
-	}
-}
-template <int METRIC>
-__device__ __forceinline__ void accum(float &acc, const XVec<1> &q, const XVec<1> &x) {
-	if (METRIC == METRIC_L2) {
-		float a = q.v - x.v;
-		acc = fmaf(a, a, acc);
-	} else {
-		acc = fmaf(q.v, x.v, acc);
-	}
-}
-__device__ __forceinline__ void accum_norm(float &acc, const XVec<4> &x) {
-	acc = fmaf(x.v.x, x.v.x, acc);
-	acc = fmaf(x.v.y, x.v.y, acc);
-	acc = fmaf(x.v.z, x.v.z, acc);
-	acc = fmaf(x.v.w, x.v.w, acc);
-}
-__device__ __forceinline__ void accum_norm(float &acc, const XVec<1> &x) { acc = fmaf(x.v, x.v, acc); }
-
-// distance in the reference's reported units from the accumulated sums
-template <int METRIC>
-__device__ __forceinline__ float finish_distance(float acc, float qnorm2, float xnorm2) {
-	if (METRIC == METRIC_L2) return acc;
-	if (METRIC == METRIC_DOT) return 1.0f - acc;
-	float den = sqrtf(qnorm2) * sqrtf(xnorm2);
-	if (!(den > 0.f)) return 1.0f;
-	float sim = acc / den;
-	sim = fminf(1.f, fmaxf(-1.f, sim));
-	return 1.0f - sim;
-}
-
-// liveness of the 8 rows [row0, row0+8), row0 % 8 == 0
-__device__ __forceinline__ unsigned live_mask8(long long row0, long long row_begin, long long n,
-                                               const uint32_t *allow, long long allow_bits,
-                                               const uint32_t *deleted) {
-	unsigned m = 0xFFu;
-	long long left = n - row0;
-	if (left <= 0) return 0u;
-	if (left < 8) m = (1u << (int)left) - 1u;
-	if (row0 < row_begin) {
-		if (row_begin - row0 >= 8) return 0u;
-		m &= ~((1u << (int)(row_begin - row0)) - 1u);
-	}
-	const int sh = (int)(row0 & 31);
-	if (deleted) m &= ~(__ldg(deleted + (row0 >> 5)) >> sh);
-	if (allow) {
-		unsigned a = 0;
-		if (row0 < allow_bits) {
-			a = (__ldg(allow + (row0 >> 5)) >> sh) & 0xFFu;
-			long long aleft = allow_bits - row0;
-			if (aleft < 8) a &= (1u << (int)aleft) - 1u;
-		}
-		m &= a;
-	}
-	return m & 0xFFu;
-}
 
 static constexpr int SCAN_MAXG = 32;       // groups of the two-level final select
 static constexpr int SCAN_HDR_WORDS = 128; // u64 words of control state in front of the lists
@@ -457,6 +342,71 @@ void fill_u64(u64 *p, long long n, u64 v, cudaStream_t s, int64_t *launches) {
 	if (n <= 0) return;
 	fill_u64_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p, n, v);
 	LB_CUDA(cudaGetLastError());
+	if (launches) (*launches)++;
+}
+
+// ------------------------------------------------------------------ single-query latency path (flat_scan1.cuh)
+static constexpr size_t SCAN1_SMEM_MAX = 232448 - 4096; // dynamic part: the kernel has ~3 KB of static shared memory
+
+bool scan1_eligible(const float *X, int d, int k, int nq) {
+	if (nq != 1 || d < 4 || (d & 3) != 0 || k < 1) return false;
+	if ((reinterpret_cast<uintptr_t>(X) & 15) != 0) return false; // bulk copies need 16-byte aligned rows
+	static const bool off = [] { // A/B hook
+		const char *e = getenv("LANCE_B200_SCAN1");
+		return e && atoi(e) == 0;
+	}();
+	if (off) return false;
+	return scan1_smem(d, k).total <= SCAN1_SMEM_MAX;
+}
+
+size_t scan1_scratch_bytes(int k, int num_sms) { return (size_t)num_sms * scan1_slot_keys(k) * sizeof(u64); }
+
+void init_scan1_header(u64 *hdr, cudaStream_t s) {
+	static const u64 init[SCAN1_HDR_WORDS] = {~0ull, 0ull, 0ull, 0ull};
+	LB_CUDA(cudaMemcpyAsync(hdr, init, sizeof(init), cudaMemcpyHostToDevice, s));
+}
+
+template <int METRIC>
+static void launch_scan1(const Scan1Params &p, int grid, size_t smem, cudaStream_t s) {
+	// the kernel also has a few KB of static shared memory (radix-select histograms): raise the dynamic limit to what
+	// this launch needs, once per size
+	static std::mutex mu;
+	static size_t granted = 48 * 1024;
+	{
+		std::lock_guard<std::mutex> g(mu);
+		if (smem > granted) {
+			LB_CUDA(cudaFuncSetAttribute(flat_scan1_kernel<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+			granted = smem;
+		}
+	}
+	flat_scan1_kernel<METRIC><<<grid, SCAN1_WARPS * 32, smem, s>>>(p);
+	LB_CUDA(cudaGetLastError());
+}
+
+void run_flat_scan1(const FlatScanArgs &a, void *scratch, int num_sms, cudaStream_t s, int64_t *launches) {
+	Scan1Params p;
+	p.X = a.X, p.n = a.n, p.row_begin = a.row_begin, p.d = a.d, p.k = a.k, p.cap = warpsel_cap(a.k);
+	p.allow = a.allow, p.allow_bits = a.allow_bits, p.deleted = a.deleted;
+	p.hdr = a.scan1_hdr, p.slots = reinterpret_cast<u64 *>(scratch), p.label_base = a.label_base;
+	p.out_labels = a.out_labels, p.out_dist = a.out_dist, p.out_counts = a.out_counts, p.out_keys = a.out_keys;
+	p.done_flag = a.done_flag, p.done_value = a.done_value;
+	p.trace = nullptr, p.trace2 = nullptr;
+	if (a.hQ && a.d <= SCAN1_QINLINE_MAX) {
+		p.q_dev = nullptr;
+		memcpy(p.qinline, a.hQ, (size_t)a.d * sizeof(float));
+	} else {
+		p.q_dev = a.dQ;
+	}
+	const long long units = ((a.n + 7) >> 3) - (a.row_begin >> 3);
+	int grid = (int)std::min<long long>(std::max<long long>((units + SCAN1_WARPS - 1) / SCAN1_WARPS, 1), num_sms);
+	const size_t smem = scan1_smem(a.d, a.k).total;
+	int tix = a.timer ? a.timer->begin(KC_FLAT_SCAN, s) : -1;
+	switch (a.metric) {
+	case METRIC_COSINE: launch_scan1<METRIC_COSINE>(p, grid, smem, s); break;
+	case METRIC_DOT: launch_scan1<METRIC_DOT>(p, grid, smem, s); break;
+	default: launch_scan1<METRIC_L2>(p, grid, smem, s);
+	}
+	if (a.timer) a.timer->end(tix, s);
 	if (launches) (*launches)++;
 }
 

@@ -94,6 +94,11 @@ struct FlatScanArgs {
 	// pass leaves the header as the next pass needs it, so a pass is one launch instead of memset + launch.
 	u64 *hdr = nullptr;
 	bool *hdr_clean = nullptr;
+	// Single-query latency path (flat_scan1.cuh), used when nq == 1 and scan1_eligible():
+	const float *hQ = nullptr;       // the query in HOST memory: it then rides in the kernel parameters (no H2D copy)
+	u64 *scan1_hdr = nullptr;        // persistent SCAN1 header of the workspace (initialised once, handed back clean)
+	volatile uint32_t *done_flag = nullptr; // completion word in mapped pinned host memory (nullable)
+	uint32_t done_value = 0;
 };
 static constexpr size_t SCAN_HDR_BYTES = 128 * sizeof(u64);
 
@@ -106,6 +111,12 @@ struct FlatScanPlan {
 	bool vec4 = true;
 	const void *kernel = nullptr;
 };
+
+// single-query latency path: eligibility and scratch (slots of the grid's blocks), launch
+bool scan1_eligible(const float *X, int d, int k, int nq);
+size_t scan1_scratch_bytes(int k, int num_sms);
+void init_scan1_header(u64 *hdr, cudaStream_t s);
+void run_flat_scan1(const FlatScanArgs &a, void *scratch, int num_sms, cudaStream_t s, int64_t *launches);
 
 FlatScanPlan plan_flat_scan(const float *X, int metric, int d, int k, int nq, long long n, int num_sms);
 size_t flat_scan_scratch_bytes(const FlatScanPlan &p, int k);

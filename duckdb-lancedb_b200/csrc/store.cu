@@ -307,7 +307,7 @@ int Store::merge_from(Store &src, const int64_t *live_labels, int count, int64_t
 // ------------------------------------------------------------------ search
 void Store::search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
                           int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
-                          cudaStream_t s, bool defer, uint32_t *d_overflow) {
+                          cudaStream_t s, bool defer, uint32_t *d_overflow, HostHints *hints) {
 	std::shared_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));
 	if (nq <= 0) return;
@@ -319,11 +319,19 @@ void Store::search_device(const float *d_queries, int nq, int k, int nprobes, in
 	// reuse it without a host synchronisation (growing a buffer frees the old one, which synchronises).
 	Workspace *ws = scratch_for(s);
 	std::lock_guard<std::mutex> wg(ws->mu);
+	if (hints && !hints->q_uploaded) {
+		// the host call left the query on the host: only the flat single-query scan takes it from its launch parameters
+		const bool inline_ok = !index_ && n_rows_ > 0 && nq == 1 && dim_ <= 1024 && scan1_eligible(X_.as<float>(), dim_, k, 1);
+		if (!inline_ok) {
+			LB_CUDA(cudaMemcpyAsync(hints->d_q_buf, hints->h_queries, (size_t)nq * dim_ * sizeof(float), cudaMemcpyHostToDevice, s));
+			hints->q_uploaded = true;
+		}
+	}
 	if (index_)
 		ivfpq_search_locked(d_queries, nq, k, nprobes, refine, d_allow, allow_bits, d_out_labels, d_out_dist,
 		                    d_out_counts, *ws, s, nullptr, nullptr, nullptr);
 	else
-		flat_search_locked(d_queries, nq, k, d_allow, allow_bits, d_out_labels, d_out_dist, d_out_counts, *ws, s, defer);
+		flat_search_locked(d_queries, nq, k, d_allow, allow_bits, d_out_labels, d_out_dist, d_out_counts, *ws, s, defer, hints);
 	if (d_overflow) {
 		// number of queries whose result is not final until search_finish (0 on every path but a pending tcgen05 batch)
 		const uint32_t *t = (defer && flat_gemm_) ? flat_gemm_->pending_total(s) : nullptr;
@@ -383,7 +391,25 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 		const bool zc_out = staged && zc_mode >= 1;
 		const bool zc_q = zc_out && zc_mode >= 2 && qb <= 8192 && nq < 8;
 		const size_t qoff = (qb + 15) & ~(size_t)15; // results start 16-byte aligned behind the queries
-		char *hs = staged ? static_cast<char *>(io->stage(qoff + lb + db + cb)) : nullptr;
+		const size_t foff = (lb + db + cb + 15) & ~(size_t)15; // completion word behind the results
+		char *hs = staged ? static_cast<char *>(io->stage(qoff + foff + 16)) : nullptr;
+		// single query, results written in place: the kernel can also take the query from its launch parameters (no
+		// H2D copy at all) and publish a completion word next to the results, which is polled instead of a stream
+		// synchronise (LANCE_B200_POLL=0 switches the polling off)
+		static const bool poll_mode = [] {
+			const char *e = getenv("LANCE_B200_POLL");
+			return e ? atoi(e) != 0 : true;
+		}();
+		HostHints hints;
+		const bool single = zc_out && nq == 1;
+		if (single) {
+			hints.h_queries = queries;
+			if (poll_mode) {
+				hints.done_flag = reinterpret_cast<volatile uint32_t *>(hs + qoff + foff);
+				hints.done_value = ++io->done_seq;
+				if (hints.done_value == 0) hints.done_value = ++io->done_seq;
+			}
+		}
 		if (!zc_q) io->q.ensure(qb);
 		if (!zc_out) io->out_labels.ensure(lb + db + cb);
 		char *res = zc_out ? hs + qoff : static_cast<char *>(io->out_labels.p);
@@ -391,7 +417,15 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 		float *d_dist = reinterpret_cast<float *>(res + lb);
 		int32_t *d_counts = reinterpret_cast<int32_t *>(res + lb + db);
 		const float *d_q = zc_q ? reinterpret_cast<const float *>(hs) : io->q.as<float>();
-		if (staged) {
+		if (single) {
+			// the search decides under the store lock whether it can take the query inline; if not it uploads it itself
+			hints.d_q_buf = io->q.as<float>();
+			hints.q_uploaded = false;
+			if (zc_q) { // (LANCE_B200_ZEROCOPY=2) the device reads the query in place from the mapped staging buffer
+				std::memcpy(hs, queries, qb);
+				hints.q_uploaded = true;
+			}
+		} else if (staged) {
 			std::memcpy(hs, queries, qb);
 			if (!zc_q) LB_CUDA(cudaMemcpyAsync(io->q.p, hs, qb, cudaMemcpyHostToDevice, s));
 		} else {
@@ -404,10 +438,27 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 			LB_CUDA(cudaMemcpyAsync(io->allow.p, allow, words * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
 			d_allow = io->allow.as<uint32_t>();
 		}
-		search_device(d_q, nq, k, nprobes, refine, d_allow, allow_bits, d_labels, d_dist, d_counts, s);
+		search_device(d_q, nq, k, nprobes, refine, d_allow, allow_bits, d_labels, d_dist, d_counts, s, false, nullptr,
+		              single ? &hints : nullptr);
 		if (staged) {
 			if (!zc_out) LB_CUDA(cudaMemcpyAsync(hs + qoff, d_labels, lb + db + cb, cudaMemcpyDeviceToHost, s));
-			LB_CUDA(cudaStreamSynchronize(s));
+			if (hints.armed) {
+				// poll the completion word (the kernel writes it behind a system-scope fence, after the results); look at
+				// the stream now and then so that a faulted launch surfaces as an error instead of a hang
+				const volatile uint32_t *flag = hints.done_flag;
+				for (uint32_t spins = 0; *flag != hints.done_value; spins++) {
+					if ((spins & 0x3FFF) == 0x3FFF) {
+						cudaError_t e = cudaStreamQuery(s);
+						if (e == cudaSuccess) break; // drained: the word is there (or the fast path did not run)
+						if (e != cudaErrorNotReady) LB_CUDA(e);
+					}
+#if defined(__x86_64__)
+					__builtin_ia32_pause();
+#endif
+				}
+			} else {
+				LB_CUDA(cudaStreamSynchronize(s));
+			}
 			std::memcpy(out_labels, hs + qoff, lb);
 			std::memcpy(out_dist, hs + qoff + lb, db);
 			std::memcpy(out_counts, hs + qoff + lb + db, cb);
@@ -426,7 +477,7 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 
 void Store::flat_search_locked(const float *d_queries, int nq, int k, const uint32_t *d_allow, int64_t allow_bits,
                                int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts, Workspace &ws,
-                               cudaStream_t s, bool defer) {
+                               cudaStream_t s, bool defer, HostHints *hints) {
 	int64_t launches = 0;
 	const int mode = flat_path_.load();
 	bool use_tc = false;
@@ -469,6 +520,26 @@ void Store::flat_search_locked(const float *d_queries, int nq, int k, const uint
 	a.out_dist = d_out_dist;
 	a.out_counts = d_out_counts;
 	a.timer = &timer_;
+	if (n_rows_ > 0 && scan1_eligible(a.X, dim_, k, nq)) {
+		// one query (what the SQL surface issues): the TMA-staged latency path, one launch, optional inline query and
+		// completion word
+		if (!ws.scan1_hdr.p) {
+			ws.scan1_hdr.alloc(64);
+			init_scan1_header(ws.scan1_hdr.as<u64>(), s);
+		}
+		ws.work.ensure(scan1_scratch_bytes(k, num_sms_));
+		a.scan1_hdr = ws.scan1_hdr.as<u64>();
+		if (hints) {
+			a.hQ = hints->q_uploaded ? nullptr : hints->h_queries;
+			a.done_flag = hints->done_flag, a.done_value = hints->done_value;
+			hints->armed = hints->done_flag != nullptr;
+		}
+		run_flat_scan1(a, ws.work.p, num_sms_, s, &launches);
+		std::lock_guard<std::mutex> g(stat_mu_);
+		simt_batches_++;
+		launches_ += launches;
+		return;
+	}
 	FlatScanPlan p = plan_flat_scan(a.X, metric_, dim_, k, nq, n_rows_, num_sms_);
 	ws.work.ensure(flat_scan_scratch_bytes(p, k));
 	if (!ws.scan_hdr.p) {

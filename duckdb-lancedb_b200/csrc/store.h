@@ -42,6 +42,8 @@ struct Workspace {
 	DevBuf scan_hdr;  // persistent header of the flat scan (kernels.h SCAN_HDR_BYTES), all-ones between passes
 	bool scan_hdr_clean = false;
 	DevBuf adc_tickets; // persistent arrival tickets of the ADC scan (one per query), zero between launches
+	DevBuf scan1_hdr;   // persistent header of the single-query scan (flat_scan1.cuh), handed back clean by every launch
+	uint32_t done_seq = 0; // completion-word sequence of host calls on this workspace (io workspaces)
 	// small host-buffer calls: pinned staging (query in, packed [labels | distances | counts] out) so that the
 	// call is one async H2D + one D2H instead of four pageable copies that each block the host
 	void *h_stage = nullptr;
@@ -49,6 +51,18 @@ struct Workspace {
 	void *stage(size_t bytes);
 	explicit Workspace(bool own_stream);
 	~Workspace();
+};
+
+// What a host-buffer call can tell the device search (all optional): the query as the host holds it (the single-query
+// scan then carries it in its kernel parameters: no H2D copy) and a completion word in mapped pinned memory.  `armed`
+// comes back true when the kernel that was launched will write done_value to done_flag.
+struct HostHints {
+	const float *h_queries = nullptr;
+	float *d_q_buf = nullptr;    // device buffer the search reads the query from when it cannot take it inline
+	bool q_uploaded = false;     // false: the caller skipped the H2D copy, the search uploads it if its path needs it
+	volatile uint32_t *done_flag = nullptr;
+	uint32_t done_value = 0;
+	bool armed = false;
 };
 
 struct IvfPqIndex; // ivfpq.h
@@ -82,7 +96,7 @@ public:
 	// everything on the device, enqueued on s
 	void search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
 	                   int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
-	                   cudaStream_t s, bool defer = false, uint32_t *d_overflow = nullptr);
+	                   cudaStream_t s, bool defer = false, uint32_t *d_overflow = nullptr, HostHints *hints = nullptr);
 	int search_finish(cudaStream_t s);
 
 	// IVF_PQ (ivfpq.cu)
@@ -112,7 +126,7 @@ private:
 	Workspace *scratch_for(cudaStream_t s); // work issued on one stream is ordered, so it can share scratch
 	void flat_search_locked(const float *d_queries, int nq, int k, const uint32_t *d_allow, int64_t allow_bits,
 	                        int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts, Workspace &ws,
-	                        cudaStream_t s, bool defer = false);
+	                        cudaStream_t s, bool defer = false, HostHints *hints = nullptr);
 	void ivfpq_search_locked(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
 	                         int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
 	                         Workspace &ws, cudaStream_t s, int32_t *d_dbg_parts, u64 *d_dbg_cand, int32_t *d_dbg_ncand);
