@@ -104,6 +104,8 @@ SIGNATURES = {
     "lance_b200_stats": (_i32, [_vp, C.POINTER(Stats)]),
     "lance_b200_profile_enable": (_i32, [_vp, _i32]),
     "lance_b200_profile_read": (_i32, [_vp, C.POINTER(Profile)]),
+    "lance_b200_time_search_device": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _vp, _i64,
+                                             _vp] + _ERR),
     "lance_b200_set_flat_path": (_i32, [_vp, _i32]),
     "lance_b200_set_default_device": (_i32, [_i32]),
     "lance_b200_device_count": (_i32, []),
@@ -326,6 +328,18 @@ class LanceHandle:
                 raise LanceError("Lance search: " + self._err.value.decode())
 
         return call
+
+    def time_search_device(self, d_queries: int, nq: int, k: int, d_labels: int, d_dist: int, d_counts: int, iters: int,
+                           nprobes: int = 20, refine_factor: int = 1, d_allow: int = 0, allow_bits: int = 0, stream: int = 0,
+                           d_flush: int = 0, flush_bytes: int = 0) -> np.ndarray:
+        """lance_b200_time_search_device: per-call device milliseconds of `iters` searches, events recorded in C."""
+        out = np.zeros(iters, np.float32)
+        rc = lib().lance_b200_time_search_device(self._h, _ptr(d_queries), nq, k, nprobes, refine_factor,
+                                                 _ptr(d_allow) if d_allow else None, allow_bits, _ptr(d_labels), _ptr(d_dist),
+                                                 _ptr(d_counts), _ptr(stream) if stream else None, iters,
+                                                 _ptr(d_flush) if d_flush else None, flush_bytes, _ptr(out), self._err, ERR_LEN)
+        self._check(rc, "timed search")
+        return out
 
     def search_device(self, d_queries: int, nq: int, k: int, d_labels: int, d_dist: int, d_counts: int,
                       nprobes: int = 20, refine_factor: int = 1, d_allow: int = 0, allow_bits: int = 0, stream: int = 0):

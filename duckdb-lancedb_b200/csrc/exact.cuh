@@ -11,6 +11,8 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 // exact distance of (q, x) by one warp, in the reference's reported units (same formulas as flat_scan.cu)
+// QLDG = false: q may live in shared memory (plain loads instead of the read-only global path); same arithmetic
+template <bool QLDG = true>
 __device__ __forceinline__ float warp_exact_distance(int metric, const float *__restrict__ q, const float *__restrict__ x,
                                                      int d, bool vec4) {
 	const unsigned lane = lane_id();
@@ -19,7 +21,7 @@ __device__ __forceinline__ float warp_exact_distance(int metric, const float *__
 		const float4 *q4 = reinterpret_cast<const float4 *>(q), *x4 = reinterpret_cast<const float4 *>(x);
 #pragma unroll 8
 		for (int c = lane; c < (d >> 2); c += 32) {
-			float4 a = __ldg(q4 + c), b = __ldg(x4 + c);
+			float4 a = QLDG ? __ldg(q4 + c) : q4[c], b = __ldg(x4 + c);
 			if (metric == METRIC_L2) {
 				float e0 = a.x - b.x, e1 = a.y - b.y, e2 = a.z - b.z, e3 = a.w - b.w;
 				acc = fmaf(e0, e0, acc), acc = fmaf(e1, e1, acc), acc = fmaf(e2, e2, acc), acc = fmaf(e3, e3, acc);
@@ -33,7 +35,7 @@ __device__ __forceinline__ float warp_exact_distance(int metric, const float *__
 		}
 	} else {
 		for (int c = lane; c < d; c += 32) {
-			float a = __ldg(q + c), b = __ldg(x + c);
+			float a = QLDG ? __ldg(q + c) : q[c], b = __ldg(x + c);
 			if (metric == METRIC_L2) {
 				float e = a - b;
 				acc = fmaf(e, e, acc);

@@ -375,6 +375,42 @@ int32_t lance_b200_profile_read(void *handle, lance_b200_profile_t *out) {
 	}
 }
 
+int32_t lance_b200_time_search_device(void *handle, const float *d_queries, int32_t nq, int32_t k, int32_t nprobes,
+                                      int32_t refine_factor, const uint32_t *d_allow, int64_t bitmap_bits,
+                                      int64_t *d_out_labels, float *d_out_distances, int32_t *d_out_counts, void *stream,
+                                      int32_t iters, void *d_flush, int64_t flush_bytes, float *out_ms, char *err_buf,
+                                      int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("timed search failed: ", -1, {
+		if (iters <= 0 || !out_ms) throw lb::Error("bad arguments");
+		cudaStream_t s = static_cast<cudaStream_t>(stream);
+		LB_CUDA(cudaSetDevice(h->device()));
+		cudaEvent_t a;
+		cudaEvent_t b;
+		LB_CUDA(cudaEventCreate(&a));
+		LB_CUDA(cudaEventCreate(&b));
+		const size_t half = d_flush ? ((size_t)flush_bytes / 2) & ~(size_t)255 : 0;
+		for (int i = 0; i < iters; i++) {
+			if (half) {
+				// evict: write half the buffer (more than the L2 holds), then read the other half so that no dirty line is
+				// left for the timed search to write back; all of it outside the timed interval
+				LB_CUDA(cudaMemsetAsync(d_flush, i & 0xFF, half, s));
+				lb::launch_read_pass(static_cast<char *>(d_flush) + half, half, reinterpret_cast<unsigned *>(d_flush), s);
+				LB_CUDA(cudaStreamSynchronize(s));
+			}
+			LB_CUDA(cudaEventRecord(a, s));
+			h->search_device(d_queries, nq, k, nprobes, refine_factor, d_allow, bitmap_bits, d_out_labels, d_out_distances,
+			                 d_out_counts, s);
+			LB_CUDA(cudaEventRecord(b, s));
+			LB_CUDA(cudaEventSynchronize(b));
+			LB_CUDA(cudaEventElapsedTime(&out_ms[i], a, b));
+		}
+		cudaEventDestroy(a);
+		cudaEventDestroy(b);
+		return 0;
+	})
+}
+
 int32_t lance_b200_set_flat_path(void *handle, int32_t mode) {
 	if (!handle || mode < 0 || mode > 2) return -1;
 	static_cast<Store *>(handle)->set_flat_path(mode);

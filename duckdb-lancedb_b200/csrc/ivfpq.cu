@@ -21,13 +21,16 @@
 // (M random LDS per row); see DESIGN.md.
 #include "ivfpq.h"
 
+#include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 
 #include "exact.cuh"
+#include "flat_scan1.cuh"
 #include "tc_ptx.cuh"
 #include "topk.cuh"
 
@@ -797,6 +800,7 @@ __global__ void histogram_kernel(const int32_t *__restrict__ assign, long long n
 	if (t < n) atomicAdd(hist + assign[t], 1);
 }
 
+#include "ivfpq1.cuh"
 #include "ivfpq_host.cuh"
 #include "ivfpq_train.cuh"
 

@@ -159,9 +159,44 @@ static void launch_adc(const AdcParams &ap, int nwarps, int S, int nq, size_t sm
 	LB_CUDA(cudaGetLastError());
 }
 
+// ------------------------------------------------------------------ one query, one cooperative launch (ivfpq1.cuh)
+template <int NB>
+static void launch_ivfpq1(const Ivf1Params &p, int grid, size_t smem, cudaStream_t s) {
+	static std::mutex mu;
+	static size_t granted = 48 * 1024;
+	{
+		std::lock_guard<std::mutex> g(mu);
+		if (smem > granted) {
+			LB_CUDA(cudaFuncSetAttribute(ivfpq1_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+			granted = smem;
+		}
+	}
+	void *args[] = {const_cast<Ivf1Params *>(&p)};
+	LB_CUDA(cudaLaunchCooperativeKernel((const void *)ivfpq1_kernel<NB>, dim3(grid), dim3(IVF1_NT), args, smem, s));
+}
+
+static bool ivfpq1_eligible(const IvfPqIndex &ix, int nq, int np, long long kc, int d, bool has_tail) {
+	static const bool off = [] { // A/B hook
+		const char *e = getenv("LANCE_B200_IVF1");
+		return e && atoi(e) == 0;
+	}();
+	if (off || nq != 1 || has_tail) return false;
+	if (ix.gran != 32 || ix.M / 32 > 4) return false;       // rotated layout, table <= 128 KB
+	if (ix.P > IVF1_MAXKEYS * IVF1_NT || np > 32 || kc > 32) return false;
+	return ivf1_smem(d, ix.M).total <= 220 * 1024;
+}
+
+bool Store::ivfpq_takes_inline_query(int k, int nprobes, int refine) {
+	const IvfPqIndex &ix = *index_;
+	const int np = std::min(std::max(nprobes, 1), ix.P);
+	const long long kc = (long long)k * std::max(refine, 1);
+	return ivfpq1_eligible(ix, 1, np, kc, dim_, ix.n_indexed < n_rows_);
+}
+
 void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
                                 int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
-                                Workspace &ws, cudaStream_t s, int32_t *d_dbg_parts, u64 *d_dbg_cand, int32_t *d_dbg_ncand) {
+                                Workspace &ws, cudaStream_t s, int32_t *d_dbg_parts, u64 *d_dbg_cand, int32_t *d_dbg_ncand,
+                                HostHints *hints) {
 	IvfPqIndex &ix = *index_;
 	int64_t launches = 0;
 	const int d = dim_, M = ix.M;
@@ -172,6 +207,54 @@ void Store::ivfpq_search_locked(const float *d_queries, int nq, int k, int nprob
 	if (kc_ll > 8192) throw Error("k * refine_factor > 8192 is not supported by the device ADC scan");
 	const int kc = (int)kc_ll;
 	const uint32_t *deleted = n_deleted_ > 0 ? deleted_.as<uint32_t>() : nullptr;
+
+	if (ivfpq1_eligible(ix, nq, np, kc_ll, d, ix.n_indexed < n_rows_)) {
+		// the single query of the SQL surface: probe, table, scan, refine and select in ONE cooperative launch
+		Ivf1Params p;
+		const bool inline_q = hints && !hints->q_uploaded && hints->h_queries && d <= SCAN1_QINLINE_MAX;
+		p.q_dev = inline_q ? nullptr : d_queries;
+		if (inline_q) memcpy(p.qinline, hints->h_queries, (size_t)d * sizeof(float));
+		p.d = d, p.metric = ix.metric;
+		p.centroids = ix.centroids.as<float>(), p.P = ix.P, p.M = M, p.dsub = ix.dsub, p.codebook = ix.codebook.as<float>();
+		p.pad_offsets = ix.pad_offsets.as<long long>(), p.slot_rows = ix.slot_rows.as<int32_t>();
+		p.codes_il = ix.codes_il.as<uint8_t>(), p.row_term = ix.row_term.as<float>();
+		p.allow = d_allow, p.allow_bits = allow_bits, p.deleted = deleted;
+		p.nprobes = np, p.k = k, p.kc = kc, p.refine = refine >= 1 ? 1 : 0;
+		const int grid = num_sms_;
+		ws.work2.ensure(64 * sizeof(u64));                      // the sorted probe keys (read by the debug entry)
+		ws.work3.ensure((size_t)256 * M * sizeof(float));
+		ws.work4.ensure(((size_t)ix.P + (size_t)grid * 32 + 64) * sizeof(u64));
+		if (!ws.ivf1_hdr.p) {
+			ws.ivf1_hdr.alloc(64);
+			LB_CUDA(cudaMemsetAsync(ws.ivf1_hdr.p, 0, 64, s));
+		}
+		p.probe_sorted = ws.work2.as<u64>();
+		p.lut_g = ws.work3.as<float>();
+		p.probe_keys = ws.work4.as<u64>();
+		p.slots = p.probe_keys + ix.P;
+		p.cand = p.slots + (size_t)grid * 32;
+		p.hdr = ws.ivf1_hdr.as<u64>();
+		p.X = X_.as<float>(), p.label_base = label_base_;
+		p.out_labels = d_out_labels, p.out_dist = d_out_dist, p.out_counts = d_out_counts;
+		p.done_flag = hints ? hints->done_flag : nullptr;
+		p.done_value = hints ? hints->done_value : 0;
+		if (hints) hints->armed = hints->done_flag != nullptr;
+		const size_t smem = ivf1_smem(d, M).total;
+		int tix = timer_.begin(KC_ADC_SCAN, s);
+		switch (M / 32) {
+		case 1: launch_ivfpq1<1>(p, grid, smem, s); break;
+		case 2: launch_ivfpq1<2>(p, grid, smem, s); break;
+		case 3: launch_ivfpq1<3>(p, grid, smem, s); break;
+		default: launch_ivfpq1<4>(p, grid, smem, s);
+		}
+		timer_.end(tix, s);
+		launches++;
+		if (d_dbg_cand) LB_CUDA(cudaMemcpyAsync(d_dbg_cand, p.cand, (size_t)kc * sizeof(u64), cudaMemcpyDeviceToDevice, s));
+		std::lock_guard<std::mutex> g(stat_mu_);
+		ivfpq_batches_++;
+		launches_ += launches;
+		return;
+	}
 
 	// 1. q' and |q'|^2
 	ws.q.ensure((size_t)nq * d * sizeof(float) + (size_t)nq * sizeof(float) + 256);

@@ -130,6 +130,7 @@ void fill_u64(u64 *p, long long n, u64 v, cudaStream_t s, int64_t *launches);
 // ------------------------------------------------------------------ store_kernels.cu
 void launch_gather_rows(const float *X, const int64_t *d_rows, long long m, int d, float *dst, cudaStream_t s,
                         int64_t *launches);
+void launch_read_pass(const void *p, size_t bytes, unsigned *sink, cudaStream_t s);
 void launch_set_bits(uint32_t *bitmap, const int64_t *d_rows, int count, long long nrows, cudaStream_t s,
                      int64_t *launches);
 // Final select over G gathered per-shard lists in one launch.  Shard g's labels / dists / counts start at

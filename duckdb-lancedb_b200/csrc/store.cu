@@ -321,7 +321,11 @@ void Store::search_device(const float *d_queries, int nq, int k, int nprobes, in
 	std::lock_guard<std::mutex> wg(ws->mu);
 	if (hints && !hints->q_uploaded) {
 		// the host call left the query on the host: only the flat single-query scan takes it from its launch parameters
-		const bool inline_ok = !index_ && n_rows_ > 0 && nq == 1 && dim_ <= 1024 && scan1_eligible(X_.as<float>(), dim_, k, 1);
+		// ... and the single-query IVF_PQ kernel, which decides for itself (ivfpq_search_locked): it uploads nothing when
+		// it takes the query inline.  Conservative here: with an index, upload unless the shape is the fused one.
+		const bool inline_ok = nq == 1 && dim_ <= 1024 &&
+		                       (index_ ? ivfpq_takes_inline_query(k, nprobes, refine)
+		                               : (n_rows_ > 0 && scan1_eligible(X_.as<float>(), dim_, k, 1)));
 		if (!inline_ok) {
 			LB_CUDA(cudaMemcpyAsync(hints->d_q_buf, hints->h_queries, (size_t)nq * dim_ * sizeof(float), cudaMemcpyHostToDevice, s));
 			hints->q_uploaded = true;
@@ -329,7 +333,7 @@ void Store::search_device(const float *d_queries, int nq, int k, int nprobes, in
 	}
 	if (index_)
 		ivfpq_search_locked(d_queries, nq, k, nprobes, refine, d_allow, allow_bits, d_out_labels, d_out_dist,
-		                    d_out_counts, *ws, s, nullptr, nullptr, nullptr);
+		                    d_out_counts, *ws, s, nullptr, nullptr, nullptr, hints);
 	else
 		flat_search_locked(d_queries, nq, k, d_allow, allow_bits, d_out_labels, d_out_dist, d_out_counts, *ws, s, defer, hints);
 	if (d_overflow) {

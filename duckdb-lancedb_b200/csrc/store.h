@@ -42,6 +42,7 @@ struct Workspace {
 	DevBuf scan_hdr;  // persistent header of the flat scan (kernels.h SCAN_HDR_BYTES), all-ones between passes
 	bool scan_hdr_clean = false;
 	DevBuf adc_tickets; // persistent arrival tickets of the ADC scan (one per query), zero between launches
+	DevBuf ivf1_hdr;    // persistent ticket word of the single-query IVF_PQ kernel (ivfpq1.cuh), zero between launches
 	DevBuf scan1_hdr;   // persistent header of the single-query scan (flat_scan1.cuh), handed back clean by every launch
 	uint32_t done_seq = 0; // completion-word sequence of host calls on this workspace (io workspaces)
 	// small host-buffer calls: pinned staging (query in, packed [labels | distances | counts] out) so that the
@@ -106,6 +107,7 @@ public:
 	void get_index(lance_b200_ivfpq_info *info, float *centroids, float *codebook, int64_t *part_offsets,
 	               int64_t *row_ids, uint8_t *codes);
 	void drop_index();
+	bool ivfpq_takes_inline_query(int k, int nprobes, int refine); // shared lock held, index_ set
 	void ivfpq_search_debug(const float *query, int k, int nprobes, int refine, const uint32_t *allow,
 	                        int64_t allow_bits, int32_t *out_parts, int64_t *out_cand_labels, float *out_cand_adc,
 	                        int32_t *out_ncand, int64_t *out_labels, float *out_dist, int32_t *out_count);
@@ -129,7 +131,8 @@ private:
 	                        cudaStream_t s, bool defer = false, HostHints *hints = nullptr);
 	void ivfpq_search_locked(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
 	                         int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
-	                         Workspace &ws, cudaStream_t s, int32_t *d_dbg_parts, u64 *d_dbg_cand, int32_t *d_dbg_ncand);
+	                         Workspace &ws, cudaStream_t s, int32_t *d_dbg_parts, u64 *d_dbg_cand, int32_t *d_dbg_ncand,
+	                         HostHints *hints = nullptr);
 
 	std::string db_path_, table_, dir_;
 	int dim_;

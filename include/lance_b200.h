@@ -222,6 +222,17 @@ typedef struct {
 int32_t lance_b200_profile_enable(void *handle, int32_t on);
 int32_t lance_b200_profile_read(void *handle, lance_b200_profile_t *out);
 
+/* Measurement hook (bench.py): `iters` calls of lance_b200_search_device, each bracketed by its own pair of CUDA events
+ * on `stream` (out_ms[i] = that call's device time in milliseconds, recorded and read in C so that a 30 us step is not
+ * measured through an interpreter).  d_flush (nullable, flush_bytes >= 2 x the L2 size): before every call, outside
+ * the timed interval, half of it is written and the other half read, so the table is not served from L2 and no dirty
+ * line is left to write back.  Returns 0 or -1. */
+int32_t lance_b200_time_search_device(void *handle, const float *d_queries, int32_t nq, int32_t k, int32_t nprobes,
+                                      int32_t refine_factor, const uint32_t *d_allow, int64_t bitmap_bits,
+                                      int64_t *d_out_labels, float *d_out_distances, int32_t *d_out_counts, void *stream,
+                                      int32_t iters, void *d_flush, int64_t flush_bytes, float *out_ms, char *err_buf,
+                                      int err_buf_len);
+
 /* Tuning / test hooks: force a flat path.  0 auto, 1 always the fp32 scan, 2 always tcgen05. */
 int32_t lance_b200_set_flat_path(void *handle, int32_t mode);
 
