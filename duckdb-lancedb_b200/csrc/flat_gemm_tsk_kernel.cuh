@@ -64,57 +64,71 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 	const uint32_t tmem_q = tmem_base + 128;
 
 	if (warp == 0) {
-		// ---------------- TMA producer: stages of KS boxes (128 rows x 64 columns each)
-		uint32_t it = 0;
-		for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
-			for (int c = 0; c < nst; c++, it++) {
-				const uint32_t s = it % p.S, ph = (it / p.S) & 1u;
-				const int kb0 = c * p.KS, nk = min(p.KS, p.nkb - kb0);
-				tc::mbar_wait(bar_empty + 8u * s, ph ^ 1u);
-				if (tc::elect_one()) {
-					tc::mbar_expect_tx(bar_full + 8u * s, (uint32_t)nk * TSK_KB_BYTES);
+		// ---------------- TMA producer: stages of KS boxes (128 rows x 64 columns each).  ONE thread runs the whole
+		// loop (stage / phase kept as counters: no division, no per-stage election)
+		if (lane == 0) {
+			uint32_t s = 0, ph = 0;
+			for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
+				const int row0 = (int)(tile * GEMM_BN);
+				for (int kb0 = 0; kb0 < p.nkb; kb0 += p.KS) {
+					const int nk = min(p.KS, p.nkb - kb0);
+					const uint32_t full = bar_full + 8u * s, dst = Xs + s * TSK_STAGE_BYTES;
+					tc::mbar_wait(bar_empty + 8u * s, ph ^ 1u);
+					tc::mbar_expect_tx(full, (uint32_t)nk * TSK_KB_BYTES);
 					for (int kk = 0; kk < nk; kk++)
-						tc::tma_load_2d(Xs + s * TSK_STAGE_BYTES + (uint32_t)kk * TSK_KB_BYTES, &tmX, (kb0 + kk) * 64,
-						                (int)(tile * GEMM_BN), bar_full + 8u * s);
+						tc::tma_load_2d(dst + (uint32_t)kk * TSK_KB_BYTES, &tmX, (kb0 + kk) * 64, row0, full);
+					if (++s == (uint32_t)p.S) s = 0, ph ^= 1u;
 				}
-				__syncwarp();
 			}
 		}
+		__syncwarp();
 	} else if (warp == 1) {
+		// ---------------- MMA issuer: D (128 x 128) = Q (TMEM) x Xtile^T (smem), K streamed.  ncu (round 2) showed this
+		// warp BUSY, not waiting: ~36 instructions of descriptor arithmetic, election and warp barriers between the four
+		// MMAs of a k-block kept the tensor pipe at 32 % — the kernel was dispatch-bound.  Now one thread runs the loop
+		// with running descriptors: a k-block is four tcgen05.mma and two adds.
 		if (has_work) {
-			// ---------------- MMA issuer: D (128 x 128) = Q (TMEM) x Xtile^T (smem), K streamed
+			// the warp stays converged (all values below are warp-uniform, so they live in uniform registers and an MMA is
+			// ONE instruction); one elected lane issues
 			const uint32_t idesc = tc::umma_idesc_bf16(128, GEMM_BN);
 			tc::mbar_wait(bar_q, 0);
 			tc::tc_fence_after();
-			uint32_t it = 0, acc = 0;
-			for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
-				{
-					tc::mbar_wait(bar_tempty, (acc & 1u) ^ 1u);
+			const uint32_t d = tmem_base;
+			const uint64_t desc0 = tc::umma_smem_desc(Xs);
+			const uint64_t stage_step = (uint64_t)(TSK_STAGE_BYTES >> 4), kb_step = (uint64_t)(TSK_KB_BYTES >> 4);
+			const int last_kb = p.nkb - 1, nk_last = p.ksteps_last;
+			uint32_t s = 0, ph = 0, acc = 0;
+			uint64_t sdesc = desc0;
+			for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R, acc++) {
+				tc::mbar_wait(bar_tempty, (acc & 1u) ^ 1u);
+				tc::tc_fence_after();
+				uint32_t qa = tmem_q;
+				for (int kb0 = 0; kb0 < p.nkb; kb0 += p.KS) {
+					const int nkk = min(p.KS, p.nkb - kb0);
+					tc::mbar_wait(bar_full + 8u * s, ph);
 					tc::tc_fence_after();
-					const uint32_t d = tmem_base;
-					for (int c = 0; c < nst; c++, it++) {
-						const uint32_t s = it % p.S, ph = (it / p.S) & 1u;
-						const int kb0 = c * p.KS, nkk = min(p.KS, p.nkb - kb0);
-						tc::mbar_wait(bar_full + 8u * s, ph);
-						tc::tc_fence_after();
-						if (tc::elect_one()) {
-							for (int kk = 0; kk < nkk; kk++) {
-								const int kb = kb0 + kk;
-								const uint64_t bdesc = tc::umma_smem_desc(Xs + s * TSK_STAGE_BYTES + (uint32_t)kk * TSK_KB_BYTES);
-								const uint32_t qa = tmem_q + (uint32_t)(kb * 32);
-								const int nk = (kb == p.nkb - 1) ? p.ksteps_last : 4;
-#pragma unroll
-								for (int k4 = 0; k4 < 4; k4++) {
-									if (k4 >= nk) break;
-									tc::umma_bf16_ts(d, qa + k4 * 8, bdesc + (uint64_t)(2 * k4), idesc, (uint32_t)((kb | k4) != 0));
-								}
+					if (tc::elect_one()) {
+						uint64_t bd = sdesc;
+						uint32_t qk = qa;
+						for (int kk = 0; kk < nkk; kk++, bd += kb_step, qk += 32) {
+							const int kb = kb0 + kk;
+							if (kb != last_kb || nk_last == 4) {
+								tc::umma_bf16_ts(d, qk, bd, idesc, (uint32_t)(kb != 0));
+								tc::umma_bf16_ts(d, qk + 8, bd + 2, idesc, 1u);
+								tc::umma_bf16_ts(d, qk + 16, bd + 4, idesc, 1u);
+								tc::umma_bf16_ts(d, qk + 24, bd + 6, idesc, 1u);
+							} else {
+								for (int k4 = 0; k4 < nk_last; k4++)
+									tc::umma_bf16_ts(d, qk + k4 * 8, bd + (uint64_t)(2 * k4), idesc, (uint32_t)((kb | k4) != 0));
 							}
-							tc::umma_commit(bar_empty + 8u * s);
-							if (c == nst - 1) tc::umma_commit(bar_tfull);
 						}
-						__syncwarp();
+						tc::umma_commit(bar_empty + 8u * s);
+						if (kb0 + nkk >= p.nkb) tc::umma_commit(bar_tfull);
 					}
-					acc++;
+					__syncwarp();
+					qa += (uint32_t)nkk * 32;
+					if (++s == (uint32_t)p.S) s = 0, ph ^= 1u, sdesc = desc0;
+					else sdesc += stage_step;
 				}
 			}
 		}

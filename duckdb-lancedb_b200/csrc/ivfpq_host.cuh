@@ -143,6 +143,49 @@ void Store::get_index(lance_b200_ivfpq_info *info, float *centroids, float *code
 	if (codes) LB_CUDA(cudaMemcpy(codes, ix.ex.codes.p, (size_t)ix.n_indexed * ix.M, cudaMemcpyDeviceToHost));
 }
 
+// ------------------------------------------------------------------ persistence of the index (store.cu: save / open)
+// int64 ihdr[4] = {P, M, n_indexed, metric} | centroids fp32 [P][dim] | codebook fp32 [M][256][dim/M]
+// | part_offsets int64 [P+1] | row_ids int64 [n_indexed] | codes u8 [n_indexed][M]   (the exchange layout)
+static void write_device_array(FILE *f, const void *d_ptr, size_t bytes) {
+	const size_t chunk = 64u << 20;
+	std::vector<unsigned char> buf(std::min(bytes, chunk));
+	for (size_t off = 0; off < bytes; off += chunk) {
+		const size_t c = std::min(chunk, bytes - off);
+		LB_CUDA(cudaMemcpy(buf.data(), static_cast<const unsigned char *>(d_ptr) + off, c, cudaMemcpyDeviceToHost));
+		if (fwrite(buf.data(), 1, c, f) != c) throw Error("short write of the IVF_PQ index");
+	}
+}
+
+void Store::save_index(FILE *f) {
+	IvfPqIndexFull &ix = static_cast<IvfPqIndexFull &>(*index_);
+	int64_t ihdr[4] = {ix.P, ix.M, ix.n_indexed, ix.metric};
+	if (fwrite(ihdr, sizeof(int64_t), 4, f) != 4) throw Error("short write of the IVF_PQ index");
+	write_device_array(f, ix.centroids.p, (size_t)ix.P * ix.dim * sizeof(float));
+	write_device_array(f, ix.codebook.p, (size_t)ix.M * 256 * ix.dsub * sizeof(float));
+	if (fwrite(ix.part_offsets.data(), sizeof(int64_t), (size_t)ix.P + 1, f) != (size_t)ix.P + 1)
+		throw Error("short write of the IVF_PQ index");
+	write_device_array(f, ix.ex.row_ids.p, (size_t)ix.n_indexed * sizeof(int64_t));
+	write_device_array(f, ix.ex.codes.p, (size_t)ix.n_indexed * ix.M);
+}
+
+void Store::load_index(FILE *f, const std::string &path) {
+	int64_t ihdr[4];
+	if (fread(ihdr, sizeof(int64_t), 4, f) != 4) throw Error("truncated IVF_PQ index: " + path);
+	const int64_t P = ihdr[0], M = ihdr[1], ni = ihdr[2];
+	if (P <= 0 || P > (1 << 24) || M <= 0 || M > 4096 || ni < 0 || ni > n_rows_ || dim_ % M != 0)
+		throw Error("corrupt IVF_PQ index header: " + path);
+	const int dsub = dim_ / (int)M;
+	std::vector<float> cen((size_t)P * dim_), cb((size_t)M * 256 * dsub);
+	std::vector<int64_t> off((size_t)P + 1), ids((size_t)ni);
+	std::vector<uint8_t> codes((size_t)ni * M);
+	bool ok = fread(cen.data(), sizeof(float), cen.size(), f) == cen.size() && fread(cb.data(), sizeof(float), cb.size(), f) == cb.size() &&
+	          fread(off.data(), sizeof(int64_t), off.size(), f) == off.size() && fread(ids.data(), sizeof(int64_t), ids.size(), f) == ids.size() &&
+	          fread(codes.data(), 1, codes.size(), f) == codes.size();
+	if (!ok) throw Error("truncated IVF_PQ index: " + path);
+	// the same entry the checker-trained indexes come through: validates offsets and row ids, builds the scan layout
+	set_index((int)P, (int)M, ni, cen.data(), cb.data(), off.data(), ids.data(), codes.data());
+}
+
 void Store::drop_index() {
 	std::unique_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));

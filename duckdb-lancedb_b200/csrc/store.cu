@@ -587,7 +587,14 @@ void Store::read_profile(lance_b200_profile_t *out) {
 }
 
 // ------------------------------------------------------------------ persistence (own format)
-static const char MAGIC[8] = {'L', 'B', '2', '0', '0', 'v', '1', '\0'};
+// <db_path>/<table>.b200/store.bin:
+//   magic "LB200v2\0" | int64 hdr[8] = {dim, metric, n_rows, n_deleted, label_base, has_index, 0, 0}
+//   | tombstone words [(n_rows + 31) / 32] | rows fp32 [n_rows][dim]
+//   | (has_index) the IVF_PQ index in the exchange layout of lance_b200_get_ivfpq (save_index / load_index, ivfpq_host.cuh)
+// The reference keeps its ANN index across a restart (src/lance_index.cpp:492-587 reopens the Lance dataset with its
+// _indices; test/sql/lance_persist.test:20-34): so does this format — an indexed table reopens indexed.
+static const char MAGIC[8] = {'L', 'B', '2', '0', '0', 'v', '2', '\0'};
+static const char MAGIC_V1[8] = {'L', 'B', '2', '0', '0', 'v', '1', '\0'};
 
 void Store::save() {
 	std::shared_lock<std::shared_mutex> lk(mu_);
@@ -598,8 +605,8 @@ void Store::save() {
 	std::string path = dir_ + "/store.bin";
 	FILE *f = fopen((path + ".tmp").c_str(), "wb");
 	if (!f) throw Error("cannot write " + path);
-	int64_t hdr[6] = {dim_, metric_, n_rows_, n_deleted_, label_base_, 0};
-	bool ok = fwrite(MAGIC, 1, 8, f) == 8 && fwrite(hdr, sizeof(int64_t), 6, f) == 6;
+	int64_t hdr[8] = {dim_, metric_, n_rows_, n_deleted_, label_base_, index_ ? 1 : 0, 0, 0};
+	bool ok = fwrite(MAGIC, 1, 8, f) == 8 && fwrite(hdr, sizeof(int64_t), 8, f) == 8;
 	size_t words = (size_t)((n_rows_ + 31) / 32);
 	ok = ok && fwrite(deleted_host_.data(), sizeof(uint32_t), words, f) == words;
 	const int64_t chunk = std::max<int64_t>(1, (64ll << 20) / ((int64_t)dim_ * 4));
@@ -609,6 +616,14 @@ void Store::save() {
 		LB_CUDA(cudaMemcpy(buf.data(), X_.as<float>() + (size_t)r * dim_, (size_t)c * dim_ * sizeof(float),
 		                   cudaMemcpyDeviceToHost));
 		ok = fwrite(buf.data(), sizeof(float), (size_t)c * dim_, f) == (size_t)c * dim_;
+	}
+	if (ok && index_) {
+		try {
+			save_index(f);
+		} catch (...) {
+			fclose(f);
+			throw;
+		}
 	}
 	ok = (fclose(f) == 0) && ok;
 	if (!ok || rename((path + ".tmp").c_str(), path.c_str()) != 0) throw Error("short write to " + path);
@@ -620,21 +635,39 @@ Store *Store::open(const std::string &db_path, const std::string &table, const s
 	FILE *f = fopen(path.c_str(), "rb");
 	if (!f) throw Error("no saved store at " + path);
 	char magic[8];
-	int64_t hdr[6];
-	if (fread(magic, 1, 8, f) != 8 || memcmp(magic, MAGIC, 8) != 0 || fread(hdr, sizeof(int64_t), 6, f) != 6) {
+	int64_t hdr[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+	bool v1 = false;
+	if (fread(magic, 1, 8, f) != 8) {
 		fclose(f);
 		throw Error("not a lance_b200 store: " + path);
 	}
+	if (memcmp(magic, MAGIC_V1, 8) == 0) v1 = true;
+	else if (memcmp(magic, MAGIC, 8) != 0) {
+		fclose(f);
+		throw Error("not a lance_b200 store: " + path);
+	}
+	const size_t nh = v1 ? 6 : 8;
+	if (fread(hdr, sizeof(int64_t), nh, f) != nh) {
+		fclose(f);
+		throw Error("truncated store header: " + path);
+	}
 	std::unique_ptr<Store> st;
 	try {
+		const int64_t dim = hdr[0], n = hdr[2];
+		if (dim <= 0 || dim > (1 << 20) || n < 0 || n >= (1ll << 32)) throw Error("corrupt store header: " + path);
+		// the file must hold what the header promises (a truncated or foreign file is an error, not a short table)
+		struct stat sb;
+		if (fstat(fileno(f), &sb) != 0) throw Error("cannot stat " + path);
+		const size_t words = (size_t)((n + 31) / 32);
+		const uint64_t need = 8 + nh * 8 + (uint64_t)words * 4 + (uint64_t)n * (uint64_t)dim * 4;
+		if ((uint64_t)sb.st_size < need) throw Error("truncated store: " + path);
 		// the caller's metric wins, as in lance_manager.rs:117-161 (open takes the metric from the index options)
 		std::string m = !metric.empty() ? metric : (hdr[1] == METRIC_COSINE ? "cosine" : hdr[1] == METRIC_DOT ? "dot" : "l2");
-		st.reset(new Store(db_path, table, (int)hdr[0], m, device));
-		int64_t n = hdr[2];
+		st.reset(new Store(db_path, table, (int)dim, m, device));
 		st->label_base_ = hdr[4];
 		st->ensure_capacity(std::max<int64_t>(n, 1));
-		size_t words = (size_t)((n + 31) / 32);
 		if (fread(st->deleted_host_.data(), sizeof(uint32_t), words, f) != words) throw Error("truncated store: " + path);
+		if (n & 31) st->deleted_host_[words - 1] &= (1u << (n & 31)) - 1u; // bits beyond the table mean nothing
 		LB_CUDA(cudaMemcpy(st->deleted_.p, st->deleted_host_.data(), words * sizeof(uint32_t), cudaMemcpyHostToDevice));
 		const int64_t chunk = std::max<int64_t>(1, (64ll << 20) / ((int64_t)st->dim_ * 4));
 		std::vector<float> buf((size_t)chunk * st->dim_);
@@ -646,7 +679,11 @@ Store *Store::open(const std::string &db_path, const std::string &table, const s
 			                   cudaMemcpyHostToDevice));
 		}
 		st->n_rows_ = n;
-		st->n_deleted_ = hdr[3];
+		// the tombstone count is what the bitmap says, not what the header claims
+		int64_t nd = 0;
+		for (size_t w = 0; w < words; w++) nd += __builtin_popcount(st->deleted_host_[w]);
+		st->n_deleted_ = nd;
+		if (!v1 && hdr[5] != 0) st->load_index(f, path);
 	} catch (...) {
 		fclose(f);
 		throw;

@@ -7,6 +7,7 @@
 // label == label_base + row, deletes are tombstone bits applied as a prefilter.
 #pragma once
 #include <atomic>
+#include <cstdio>
 #include <memory>
 #include <mutex>
 #include <shared_mutex>
@@ -113,6 +114,8 @@ public:
 	                        int32_t *out_ncand, int64_t *out_labels, float *out_dist, int32_t *out_count);
 
 	void save();
+	void save_index(FILE *f);                          // ivfpq_host.cuh: the IVF_PQ index behind the rows of store.bin
+	void load_index(FILE *f, const std::string &path); // ... and back
 	static Store *open(const std::string &db_path, const std::string &table, const std::string &metric, int device);
 
 	void stats(lance_b200_stats_t *out);

@@ -254,3 +254,53 @@ def test_default_sub_vectors_for_awkward_dimensions_and_bad_exchange_rows(gpu, o
         with pytest.raises(gpu.LanceError, match="permutation"):
             h.set_ivfpq(ix.centroids, ix.codebook, ix.part_offsets, bad, ix.codes)
         h.set_ivfpq(ix.centroids, ix.codebook, ix.part_offsets, ix.row_ids, ix.codes)
+
+
+def test_indexed_table_survives_save_and_open(gpu, oracle_mod, tmp_path):
+    """The reference keeps its ANN index across CHECKPOINT + restart (src/lance_index.cpp:492-587 reopens the Lance
+    dataset with its _indices; test/sql/lance_persist.test:20-34): an indexed table saved by lance_b200_save reopens
+    INDEXED through lance_open_detached — same partitions, same candidates, same lists — with its deletes, and rows
+    inserted after the restart are found through the unindexed tail."""
+    import os
+
+    rng = np.random.default_rng(19)
+    n, d, P, M = 6000, 32, 16, 8
+    X = rng.standard_normal((n + 50, d), dtype=np.float32)
+    Q = rng.standard_normal((3, d), dtype=np.float32)
+    dead = rng.choice(n, 200, replace=False)
+    with gpu.LanceHandle(d, "l2", db_path=str(tmp_path), table_name="t_ann") as h:
+        h.add_batch(X[:n])
+        h.create_index(P, M)
+        h.delete_batch(dead)
+        g0 = h.get_ivfpq()
+        want = [h.ivfpq_search_debug(Q[j], 10, 6, 1) for j in range(3)]
+        h.save()
+    with gpu.LanceHandle.open(str(tmp_path), "t_ann", "l2") as h2:
+        assert h2.stats()["has_index"] == 1 and h2.count() == n - 200
+        g1 = h2.get_ivfpq()
+        for key in ("centroids", "codebook", "part_offsets", "row_ids", "codes"):
+            np.testing.assert_array_equal(g0[key], g1[key])
+        ix = oracle_mod.IvfPqIndex("l2", d, P, M, g1["centroids"], g1["codebook"], g1["part_offsets"], g1["row_ids"], g1["codes"])
+        deleted = oracle_mod.make_bitmap(np.isin(np.arange(n + 50), dead))
+        for j in range(3):
+            got = h2.ivfpq_search_debug(Q[j], 10, 6, 1)
+            for key in ("parts", "cand_labels", "labels"):
+                assert list(got[key]) == list(want[j][key]), key
+            np.testing.assert_array_equal(got["dist"], want[j]["dist"])
+            compare_with_oracle(oracle_mod, h2, ix, X[:n], Q[j], 10, 6, 1, "l2", None, deleted, what=f"reopened q{j}")
+        # insert after restart: labels continue, the new rows are searched exactly (lance_persist.test:29-34)
+        new = h2.add_batch(X[n:])
+        assert list(new) == list(range(n, n + 50))
+        l, dd = h2.search(X[n + 7], 5, nprobes=6, refine_factor=1)
+        assert l[0] == n + 7 and dd[0] < 1e-6
+    # a truncated file is an error, not a short table
+    path = os.path.join(str(tmp_path), "t_ann.b200", "store.bin")
+    size = os.path.getsize(path)
+    with open(path, "r+b") as f:
+        f.truncate(size - 1000)
+    with pytest.raises(gpu.LanceError, match="truncated"):
+        gpu.LanceHandle.open(str(tmp_path), "t_ann", "l2")
+    with open(path, "r+b") as f:
+        f.truncate(200)
+    with pytest.raises(gpu.LanceError, match="truncated"):
+        gpu.LanceHandle.open(str(tmp_path), "t_ann", "l2")
