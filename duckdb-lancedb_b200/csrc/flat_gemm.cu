@@ -71,7 +71,7 @@ struct FlatGemm::Impl {
 	DevBuf shadow;   // bf16 [cap_rows][Kpad]
 	DevBuf max_norm; // one float (as bits)
 	long long rows_done = 0, cap_rows = 0;
-	CUtensorMap tmX, tmX64; // 128-row and 64-row boxes over the shadow
+	CUtensorMap tmX, tmX64, tmX32; // 128-, 64- and 32-row boxes over the shadow
 	const void *tmX_base = nullptr;
 	long long tmX_rows = -1;
 	std::once_flag attr_once;
@@ -176,6 +176,7 @@ void FlatGemm::sync_rows(const float *X, long long n, long long cap_rows, cudaSt
 	if (im.tmX_base != im.shadow.p || im.tmX_rows != n) {
 		encode_rows_map(&im.tmX, im.shadow.p, n, im.Kpad); // rows beyond n read as zeros (TMA out-of-bounds fill)
 		encode_rows_map(&im.tmX64, im.shadow.p, n, im.Kpad, 64);
+		encode_rows_map(&im.tmX32, im.shadow.p, n, im.Kpad, 32);
 		im.tmX_base = im.shadow.p;
 		im.tmX_rows = n;
 	}
@@ -186,6 +187,7 @@ struct GemmPlan {
 	size_t smem;
 	bool ts;  // queries resident in tensor memory, whole-K X tiles (flat_gemm_ts_kernel, K <= 256)
 	bool tsk; // queries resident in tensor memory, K streamed (flat_gemm_tsk_kernel, K <= 768)
+	bool mc = false; // tsk: clusters of two query groups share every X tile through TMA multicast (NG even)
 };
 
 // 0 auto, 1 all-shared operands, 2 queries in TMEM (needs Kpad <= 256); LANCE_B200_GEMM=ss|ts
@@ -224,6 +226,11 @@ static GemmPlan plan_gemm(int tilesQ, int nkb, int num_sms) {
 		while (best.S < 12 && gemm_tsk_smem_bytes(best.S + 1, best.KS, best.EB) <= TC_SMEM_MAX) best.S++;
 		best.R = std::max(1, num_sms / best.NG);
 		best.smem = gemm_tsk_smem_bytes(best.S, best.KS, best.EB);
+		static const bool mc_on = [] {
+			const char *e = getenv("LANCE_B200_TSK_MC");
+			return e ? atoi(e) != 0 : true;
+		}();
+		best.mc = mc_on && best.NG >= 2 && (best.NG % 2) == 0;
 		return best;
 	}
 	if (variant == 2) throw Error("LANCE_B200_GEMM=ts needs K <= 768");
@@ -262,7 +269,8 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	const int d = im.dim, Kpad = im.Kpad;
 	std::call_once(im.attr_once, [] {
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
-		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
@@ -294,9 +302,13 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		// count c with c * floor(SMs / c) close to the SM count (32 tiles on 148 SMs would idle 20 of them)
 		int rem_tiles = (std::min(TC_QCHUNK, nq_total - q0) + 127) / 128;
 		int take = rem_tiles;
+		const GemmPlan probe = plan_gemm(std::max(2, rem_tiles & ~1), im.nkb, im.num_sms);
 		if (plan_gemm(rem_tiles, im.nkb, im.num_sms).QT == 1 && rem_tiles > 1) {
+			// K-streamed kernel with multicast pairs: only EVEN tile counts pair up (24 + 8 tiles for a batch of 4096:
+			// 144 of 148 SMs in both passes, every X tile out of the L2 once per pair)
+			const bool want_even = probe.tsk && probe.mc && rem_tiles >= 4;
 			int best_used = 0;
-			for (int c = rem_tiles; c >= (rem_tiles + 1) / 2; c--) {
+			for (int c = want_even ? (rem_tiles & ~1) : rem_tiles; c >= (rem_tiles + 1) / 2; c -= want_even ? 2 : 1) {
 				int used = c * std::max(1, im.num_sms / c);
 				if (used > im.num_sms) used = im.num_sms;
 				if (used * 100 >= im.num_sms * 95) {
@@ -336,6 +348,11 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		p.n_rows = n, p.thr = thr, p.cnt = cnt, p.cand = cand, p.CAP = TC_CAP;
 		p.deleted = deleted, p.allow = d_allow, p.allow_bits = allow_bits;
 		p.Qs = Qs, p.Kpad = Kpad, p.EB = pl.EB;
+		static const int tsk_dbg = [] {
+			const char *e = getenv("LANCE_B200_TSK_DBG");
+			return e ? atoi(e) : 0;
+		}();
+		p.dbg = tsk_dbg;
 		long long t0 = 0, seg = seed_tiles;
 		while (t0 < ntiles) {
 			long long t1 = std::min(ntiles, t0 + seg);
@@ -344,7 +361,17 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 			p.R = (int)std::min<long long>(pl.R, t1 - t0);
 			int tix = timer ? timer->begin(KC_FLAT_GEMM, s) : -1;
 			if (pl.tsk) {
-				flat_gemm_tsk_kernel<<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+				if (pl.mc) {
+					cudaLaunchConfig_t cfg = {};
+					cfg.gridDim = dim3(pl.NG * p.R), cfg.blockDim = dim3(GEMM_THREADS), cfg.dynamicSmemBytes = pl.smem, cfg.stream = s;
+					cudaLaunchAttribute at[1];
+					at[0].id = cudaLaunchAttributeClusterDimension;
+					at[0].val.clusterDim.x = 2, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
+					cfg.attrs = at, cfg.numAttrs = 1;
+					LB_CUDA(cudaLaunchKernelEx(&cfg, flat_gemm_tsk_kernel<true>, im.tmX64, p));
+				} else {
+					flat_gemm_tsk_kernel<false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+				}
 			} else if (pl.ts) {
 				switch (im.nkb) {
 				case 1: flat_gemm_ts_kernel<1><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;

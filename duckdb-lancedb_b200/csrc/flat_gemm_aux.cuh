@@ -9,11 +9,18 @@
 
 namespace lb {
 
-// Worst-case |bf16 score - exact score| <= ERR_C * |q| * |x|: both operands are rounded to bf16 (2^-9
-// relative each, 2^-8 + 2^-18 on a product, Cauchy-Schwarz over the sum) plus the fp32 accumulation in
-// the tensor core; 2^-8 = 0.00390625, the rest is slack.
-static constexpr float GEMM_ERR_C = 0.0041f;
-
+// Error bound of a bf16 score.  With q^ = bf16(q'), x^ = bf16(x') (q', x' = the fp32 rows that are rounded: x, x/|x| or
+// [x, -|x|^2/2 split] against q or [q, 1, 1, 1]) the tensor core computes fl(q^.x^) and
+//   |q^.x^ - q'.x'| = |(q^-q').x^ + q'.(x^-x')| <= rq |x^| + |q| rx,     rq = |q^-q'|, rx = |x^-x'|  (Cauchy-Schwarz),
+// where rq, |q| are MEASURED per query and rx, |x^| per row (their maxima over the table are kept).  Round 1 used
+// the a-priori worst case 2^-8 |q||x| of round-to-nearest; the measured residuals are about half of it (a rounding
+// error is rarely the full half ulp in every component), and a halved margin means ~30 % fewer candidates to emit,
+// refresh and re-rank at C2.  For l2 the constant columns (1.0) and the split of -|x|^2/2 are exact bf16 numbers, so
+// both residuals live on the first d columns only.  On top: the fp32 accumulation inside the tensor core (order
+// unknown, truncating adders: 2^-22 per term is generous) plus the rounding of the exact fp32 re-rank the candidates
+// are compared by (2^-23 per term, worst case), together GEMM_ACC_C K |q^||x^|, and an absolute slack for the residual
+// of the three-term split.
+static constexpr float GEMM_ACC_C = 3.6e-7f; // per accumulated term
 
 // ------------------------------------------------------------------ shadow rows
 // One warp per row: Xs[row] = bf16 of  x (dot) | x/|x| (cosine) | [x, -|x|^2/2 as three bf16 terms] (l2),
@@ -38,11 +45,20 @@ __global__ void __launch_bounds__(256) shadow_rows_kernel(const float *__restric
 	// i.e. similarity 0: its shadow is the zero row
 	const bool cos_null = metric == METRIC_COSINE && !(nrm > 0.f && nrm <= 3.0e38f);
 	if (metric == METRIC_COSINE) scale = cos_null ? 0.f : 1.0f / nrm;
+	float res2 = 0.f, hat2 = 0.f; // |x^ - x'|^2 and |x^|^2 over the first d columns
 	for (int i = lane; i < Kpad; i += 32) {
 		float v = 0.f;
 		if (i < d && !cos_null) v = __ldg(x + i) * scale;
-		o[i] = __float2bfloat16_rn(v);
+		const __nv_bfloat16 b = __float2bfloat16_rn(v);
+		o[i] = b;
+		if (i < d) {
+			const float bf = __bfloat162float(b), e = bf - v;
+			res2 = fmaf(e, e, res2);
+			hat2 = fmaf(bf, bf, hat2);
+		}
 	}
+	res2 = warp_sum(res2);
+	hat2 = warp_sum(hat2);
 	if (metric == METRIC_L2 && lane == 0) {
 		float h = -0.5f * s;
 		__nv_bfloat16 h1 = __float2bfloat16_rn(h);
@@ -52,14 +68,19 @@ __global__ void __launch_bounds__(256) shadow_rows_kernel(const float *__restric
 		__nv_bfloat16 h3 = __float2bfloat16_rn(r2);
 		o[d] = h1, o[d + 1] = h2, o[d + 2] = h3;
 	}
-	// A row with a NaN / Inf component must not poison the margin of every query (max over the finite rows only);
-	// its own scores are NaN / Inf and never pass a threshold, so it can only matter when fewer than k finite rows
-	// survive — count_flags_kernel sends exactly those queries to the exact scan, which ranks such rows last.
-	if (lane == 0 && metric != METRIC_COSINE) {
-		if (!(nrm <= 3.0e38f))
+	// max_norm words: [0] max |x| (dot, l2) | [1] "a row with a non-finite norm exists" | [2] max |x^ - x'| | [3] max |x^|
+	// (float bits of non-negative values order like unsigned integers).  A row with a NaN / Inf component must not
+	// poison the margin of every query (maxima over the finite rows only); its own scores are NaN / Inf and never pass
+	// a threshold, so it can only matter when fewer than k finite rows survive — count_flags_kernel sends exactly
+	// those queries to the exact scan, which ranks such rows last.
+	if (lane == 0) {
+		if (metric != METRIC_COSINE && !(nrm <= 3.0e38f)) {
 			atomicOr(max_norm_bits + 1, 1u);
-		else
-			atomicMax(max_norm_bits, __float_as_uint(nrm));
+		} else {
+			if (metric != METRIC_COSINE) atomicMax(max_norm_bits, __float_as_uint(nrm));
+			atomicMax(max_norm_bits + 2, __float_as_uint(sqrtf(res2)));
+			atomicMax(max_norm_bits + 3, __float_as_uint(sqrtf(hat2)));
+		}
 	}
 }
 
@@ -76,19 +97,27 @@ __global__ void __launch_bounds__(256) prep_query_tiles_kernel(const float *__re
 	const unsigned lane = lane_id();
 	__nv_bfloat16 *o = Qs + (size_t)q * Kpad;
 	const bool real = q < nq;
-	float s = 0.f;
+	float s = 0.f, res2 = 0.f;
 	for (int i = lane; i < Kpad; i += 32) {
 		float v = (real && i < d) ? __ldg(Q + (size_t)q * d + i) : 0.f;
-		if (real && metric == METRIC_L2 && i >= d && i < d + 3) v = 1.0f;
+		if (real && metric == METRIC_L2 && i >= d && i < d + 3) v = 1.0f; // exact in bf16: no residual
 		else s = fmaf(v, v, s);
-		o[i] = __float2bfloat16_rn(v);
+		const __nv_bfloat16 b = __float2bfloat16_rn(v);
+		o[i] = b;
+		const float e = __bfloat162float(b) - v;
+		res2 = fmaf(e, e, res2);
 	}
 	s = warp_sum(s);
+	res2 = warp_sum(res2);
 	if (lane == 0) {
-		float xn = metric == METRIC_COSINE ? 1.01f : __uint_as_float(*max_norm_bits);
-		float qn = sqrtf(s);
-		// l2: the folded -|x|^2/2 term is exact to ~2^-24 relative; covered by the absolute slack below
-		const float mg = 2.0f * (GEMM_ERR_C * qn * xn + 1e-6f * (1.0f + xn * xn));
+		const float xn = metric == METRIC_COSINE ? 1.01f : __uint_as_float(max_norm_bits[0]);
+		const float rx = __uint_as_float(max_norm_bits[2]), xh = __uint_as_float(max_norm_bits[3]);
+		const float qn = sqrtf(s), rq = sqrtf(res2);
+		// full operand norms for the accumulation term: l2 rows carry -|x|^2/2, the query three ones
+		const float qfull = metric == METRIC_L2 ? sqrtf(s + 3.0f) : qn;
+		const float xfull = metric == METRIC_L2 ? sqrtf(xh * xh + 0.25f * xn * xn * xn * xn) * 1.01f : xh;
+		const float err = 1.02f * (rq * xh + qn * rx) + GEMM_ACC_C * (float)Kpad * qfull * xfull + 1e-6f * (1.0f + xn * xn);
+		const float mg = 2.0f * err;
 		// a query (or table) whose bound is not finite cannot be certified: straight to the exact scan, emit nothing
 		const bool certifiable = mg <= 3.0e38f;
 		margin[q] = mg;

@@ -38,6 +38,8 @@ struct GemmParams {
 	const void *Qs;          // bf16 [NG*QT*128][Kpad] query tiles in global memory (TMEM-resident variant)
 	int Kpad;
 	int EB;                  // per-(epilogue group, query) shared-memory emit buffer entries (0 = append directly)
+	int dbg;                 // LANCE_B200_TSK_DBG (ceiling experiments): 1 = epilogue drains but does not filter, 2 = X stages
+	                         // are loaded once and re-used (no TMA traffic), 4 = epilogue does not even read the accumulator
 };
 
 static constexpr int GEMM_BN = 128;
@@ -271,10 +273,14 @@ __device__ __forceinline__ void gemm_process_chunk_inline(const GemmParams &p, c
 	for (int c = 0; c < 32; c++) hits |= (__uint_as_float(r[c]) >= thr ? 1u : 0u) << c;
 	if (hits) hits &= gemm_chunk_valid(p, row0);
 	const int h = __popc(hits);
-	if (h == 0) return;
 	const uint32_t rbase = (uint32_t)row0;
 	int n = eb.slots ? *eb.count : 0;
-	if (eb.slots && n + h <= p.EB) {
+	// Flushing is WARP-WIDE: a lane whose buffer cannot take its hits makes every lane of the warp flush in the same
+	// instruction (32 atomics to 32 lists, one L2 round trip), instead of each lane stalling the warp on its own
+	// atomic some other time.  At k = 100 a lane overflows its 8 slots ~150 times per large segment; flushing lane by
+	// lane that was ~4 dependent atomic round trips per warp and tile — as long as the tile's MMAs (round-2 timers).
+	const bool overflow = !eb.slots || n + h > p.EB;
+	if (!__any_sync(0xFFFFFFFFu, overflow)) {
 #pragma unroll
 		for (int c = 0; c < 32; c++)
 			if ((hits >> c) & 1u) {
@@ -284,6 +290,7 @@ __device__ __forceinline__ void gemm_process_chunk_inline(const GemmParams &p, c
 		*eb.count = n;
 		return;
 	}
+	if (n + h == 0) return;
 	uint32_t pos = atomicAdd(p.cnt + q, (uint32_t)(n + h));
 	uint2 *dst = p.cand + (size_t)q * p.CAP;
 	for (int i = 0; i < n; i++, pos++)

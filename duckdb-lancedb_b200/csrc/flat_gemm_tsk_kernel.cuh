@@ -1,29 +1,43 @@
 // flat_gemm_tsk_kernel.cuh — large-K variant (256 < K <= 768) of the TMEM-resident candidate kernel.
 //
 // One query tile (128 queries x K bf16 = K/2 TMEM columns, up to 384) stays in tensor memory for the CTA's
-// life; X streams through shared memory in stages of 128 rows x KS 64-wide k-blocks (KS x 16 KB; the MMA warp
-// pays one barrier wait and one commit per stage, so a stage carries 4*KS MMAs), as many stages as fit.
-// TMEM map: [0,128) the ONE 128 x 128 accumulator | [128, 128 + K/2) the query tile.  With 384 columns taken
-// by the queries there is no room for a second N=128 accumulator (N=64 pairs were tried: dispatch-bound), so
-// the tile's MMAs (12 x 4 x 64 clk) and the drain alternate; the drain is kept short by having all 8 epilogue
-// warps pull their 64 columns into registers at once and release the accumulator BEFORE filtering.
-// UMMA M=128, N=128, A from TMEM.  Epilogue filter and emit buffers as in flat_gemm_ts_kernel.
+// life; X streams through shared memory in stages of KS 64-wide k-blocks.
+//
+// TMEM map: [0,128) the ONE 128 x 128 accumulator | [128, 128 + K/2) the query tile.  With 384 columns taken by the
+// queries there is no room for a second N=128 accumulator, so the tile's MMAs (12 x 4 x 64 clk) and the drain
+// alternate; the drain is kept short by having all 8 epilogue warps pull their 64 columns into registers at once and
+// release the accumulator BEFORE filtering.  Round-2 experiments on C2, B = 4096 (LANCE_B200_TSK_DBG):
+// MMAs alone 3.9 ms per batch, + TMA traffic 4.3 ms, + threshold filter 5.75 ms.  Tried and measured slower:
+//   * a hybrid operand placement (k-blocks 0..7 of the queries in TMEM, the rest in shared memory as SS-form MMAs) to
+//     make room for a second accumulator: the SS MMAs read 128 B/clk of shared memory next to the TMA's 64 B/clk
+//     writes — 13.5 ms per batch (scripts/dev/attic/flat_gemm_tsk_hybrid_kernel.cuh.txt);
+//   * 64-row tiles with two N=64 accumulators in the same 128 columns: an N=64 MMA re-reads the A operand from TMEM
+//     twice as often per flop — 8.7 ms per batch (scripts/dev/attic/flat_gemm_tsk_n64_double_acc.cuh.txt).
+// What did help: the issue loop (one elected lane, running descriptors: a k-block is four tcgen05.mma and a few
+// uniform adds instead of ~36 instructions) and, marginally, multicast pairs.
+//
+// MC = true: launched as clusters of two CTAs that hold two DIFFERENT query tiles (g, g+1) and walk the SAME X tiles.
+// Each CTA fetches half of every 128-row box (64 rows, tmX is then the 64-row map) and the TMA engine multicasts it
+// into both CTAs' shared memory: every X byte leaves the L2 once per PAIR (measured: +1 %; the L2 was not the limit).
 #pragma once
 #include "flat_gemm_kernel.cuh"
 
 namespace lb {
 
-static constexpr int TSK_KB_BYTES = GEMM_KB_BYTES; // 128 rows x 64 bf16
+static constexpr int TSK_BN = GEMM_BN;                // rows of an X tile
+static constexpr int TSK_KB_BYTES = GEMM_KB_BYTES;    // one 64-wide k-block of a 128-row tile (16 KB)
 
+template <bool MC>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p) {
 	extern __shared__ uint8_t smem_raw[];
 	const int warp = threadIdx.x >> 5;
 	const int lane = threadIdx.x & 31;
-	const int g = blockIdx.x % p.NG;
-	const int r = blockIdx.x / p.NG;
+	const uint32_t crank = MC ? tc::cluster_ctarank() : 0u;
+	// MC: cluster c = blockIdx.x / 2 serves query groups 2*(c % (NG/2)) + {0,1} on row slice r = c / (NG/2)
+	const int g = MC ? 2 * (int)((blockIdx.x >> 1) % (p.NG >> 1)) + (int)crank : (int)(blockIdx.x % p.NG);
+	const int r = MC ? (int)((blockIdx.x >> 1) / (p.NG >> 1)) : (int)(blockIdx.x / p.NG);
 	const int KC = p.nkb * 32; // TMEM columns of the query tile
-	const int nst = (p.nkb + p.KS - 1) / p.KS; // stages per half-tile (the last one may hold fewer k-blocks)
 	const uint32_t TSK_STAGE_BYTES = (uint32_t)p.KS * TSK_KB_BYTES;
 
 	const uint32_t sbase = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -45,7 +59,7 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 		tc::tma_prefetch_desc(&tmX);
 		for (int s = 0; s < p.S; s++) {
 			tc::mbar_init(bar_full + 8u * s, 1);
-			tc::mbar_init(bar_empty + 8u * s, 1);
+			tc::mbar_init(bar_empty + 8u * s, MC ? 2 : 1); // MC: a stage is free when BOTH CTAs' MMAs have read it
 		}
 		tc::mbar_init(bar_q, 8);
 		tc::mbar_init(bar_tfull, 1);
@@ -59,6 +73,7 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 	for (int i = threadIdx.x; i < 128; i += GEMM_THREADS) thr_s[i] = p.thr[(size_t)g * 128 + i];
 	tc::tc_fence_before();
 	__syncthreads();
+	if (MC) tc::cluster_sync(); // the peer's barriers exist before anything is multicast at them
 	tc::tc_fence_after();
 	const uint32_t tmem_base = *tmem_slot;
 	const uint32_t tmem_q = tmem_base + 128;
@@ -68,29 +83,37 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 		// loop (stage / phase kept as counters: no division, no per-stage election)
 		if (lane == 0) {
 			uint32_t s = 0, ph = 0;
+			bool first = true;
 			for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
 				const int row0 = (int)(tile * GEMM_BN);
 				for (int kb0 = 0; kb0 < p.nkb; kb0 += p.KS) {
 					const int nk = min(p.KS, p.nkb - kb0);
 					const uint32_t full = bar_full + 8u * s, dst = Xs + s * TSK_STAGE_BYTES;
 					tc::mbar_wait(bar_empty + 8u * s, ph ^ 1u);
-					tc::mbar_expect_tx(full, (uint32_t)nk * TSK_KB_BYTES);
-					for (int kk = 0; kk < nk; kk++)
-						tc::tma_load_2d(dst + (uint32_t)kk * TSK_KB_BYTES, &tmX, (kb0 + kk) * 64, row0, full);
-					if (++s == (uint32_t)p.S) s = 0, ph ^= 1u;
+					if ((p.dbg & 2) && !(first && ph == 0)) { // experiment: no TMA traffic after the first fill
+						tc::mbar_arrive(full);
+					} else {
+						tc::mbar_expect_tx(full, (uint32_t)nk * TSK_KB_BYTES);
+						for (int kk = 0; kk < nk; kk++) {
+							if (MC) // my half of the box (rows 64*crank ..), into both CTAs
+								tc::tma_load_2d_mc(dst + (uint32_t)kk * TSK_KB_BYTES + crank * (TSK_KB_BYTES / 2), &tmX, (kb0 + kk) * 64,
+								                   row0 + (TSK_BN / 2) * (int)crank, full, (uint16_t)3);
+							else
+								tc::tma_load_2d(dst + (uint32_t)kk * TSK_KB_BYTES, &tmX, (kb0 + kk) * 64, row0, full);
+						}
+					}
+					if (++s == (uint32_t)p.S) s = 0, ph ^= 1u, first = false;
 				}
 			}
 		}
 		__syncwarp();
 	} else if (warp == 1) {
-		// ---------------- MMA issuer: D (128 x 128) = Q (TMEM) x Xtile^T (smem), K streamed.  ncu (round 2) showed this
-		// warp BUSY, not waiting: ~36 instructions of descriptor arithmetic, election and warp barriers between the four
-		// MMAs of a k-block kept the tensor pipe at 32 % — the kernel was dispatch-bound.  Now one thread runs the loop
-		// with running descriptors: a k-block is four tcgen05.mma and two adds.
+		// ---------------- MMA issuer: D (128 x 128) = Q (TMEM) x Xtile^T (smem), K streamed.  ncu (round 2) showed this warp
+		// BUSY, not waiting: ~36 instructions of descriptor arithmetic, election and warp barriers per k-block.  Now the
+		// warp stays converged (all values below are warp-uniform, so they live in uniform registers and an MMA is ONE
+		// instruction with running descriptors) and one elected lane issues
 		if (has_work) {
-			// the warp stays converged (all values below are warp-uniform, so they live in uniform registers and an MMA is
-			// ONE instruction); one elected lane issues
-			const uint32_t idesc = tc::umma_idesc_bf16(128, GEMM_BN);
+			const uint32_t idesc = tc::umma_idesc_bf16(128, TSK_BN);
 			tc::mbar_wait(bar_q, 0);
 			tc::tc_fence_after();
 			const uint32_t d = tmem_base;
@@ -122,7 +145,8 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 									tc::umma_bf16_ts(d, qk + k4 * 8, bd + (uint64_t)(2 * k4), idesc, (uint32_t)((kb | k4) != 0));
 							}
 						}
-						tc::umma_commit(bar_empty + 8u * s);
+						if (MC) tc::umma_commit_mc(bar_empty + 8u * s, (uint16_t)3);
+						else tc::umma_commit(bar_empty + 8u * s);
 						if (kb0 + nkk >= p.nkb) tc::umma_commit(bar_tfull);
 					}
 					__syncwarp();
@@ -158,22 +182,23 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 		// ---------------- epilogue: every warp pulls 64 columns (group e: [64e, 64e+64)) of its lane quadrant
 		const float thr = thr_s[lrow];
 		const EmitBuf eb{p.EB ? eslots + (size_t)(e * p.EB) * 128 + lrow : nullptr, ecnt + e * 128 + lrow};
+		const uint32_t taddr = tmem_base + lane_base + (uint32_t)e * 64;
 		uint32_t acc = 0;
-		for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R) {
-			{
-				tc::mbar_wait(bar_tfull, acc & 1u);
-				acc++;
-				tc::tc_fence_after();
-				const uint32_t taddr = tmem_base + lane_base + (uint32_t)e * 64;
-				const long long row0 = tile * GEMM_BN + e * 64;
-				uint32_t va[32], vb[32];
+		for (long long tile = p.tile_lo + r; tile < p.tile_hi; tile += p.R, acc++) {
+			tc::mbar_wait(bar_tfull, acc & 1u);
+			tc::tc_fence_after();
+			const long long row0 = tile * GEMM_BN + e * 64;
+			uint32_t va[32], vb[32];
+			if (!(p.dbg & 4)) {
 				tc::tmem_ld32(taddr, va);
 				tc::tmem_ld32(taddr + 32, vb);
 				tmem_wait_regs(va);
 				tmem_wait_regs(vb);
-				tc::tc_fence_before();
-				__syncwarp();
-				if (lane == 0) tc::mbar_arrive(bar_tempty);
+			}
+			tc::tc_fence_before();
+			__syncwarp();
+			if (lane == 0) tc::mbar_arrive(bar_tempty);
+			if (!(p.dbg & 5)) {
 				gemm_process_chunk_inline(p, va, thr, q, row0, eb);
 				gemm_process_chunk_inline(p, vb, thr, q, row0 + 32, eb);
 			}
@@ -182,6 +207,7 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 	}
 	tc::tc_fence_before();
 	__syncthreads();
+	if (MC) tc::cluster_sync(); // nobody leaves while the peer may still multicast into this CTA or arrive on its barriers
 	if (warp == 1) {
 		tc::tc_fence_after();
 		tc::tmem_dealloc(tmem_base, 512);

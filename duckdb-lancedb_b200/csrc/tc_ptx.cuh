@@ -65,6 +65,26 @@ __device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap
 	    : "memory");
 }
 
+// same, multicast: the box lands at the same shared-memory offset of every CTA of the cluster named in cta_mask, and the
+// bytes complete on the mbarrier at the same offset in each of them
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t smem_dst, const CUtensorMap *m, int c0, int c1, uint32_t bar, uint16_t cta_mask) {
+	asm volatile(
+	    "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%2, %3}], [%4], %5;"
+	    :
+	    : "r"(smem_dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(bar), "h"(cta_mask)
+	    : "memory");
+}
+
+// ------------------------------------------------------------------ thread-block clusters
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+	uint32_t r;
+	asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+	return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+	asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // 1-D bulk copy global -> shared (multiple of 16 bytes, 16-byte aligned), completion (bytes) on mbarrier `bar`
 __device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void *gsrc, uint32_t bytes, uint32_t bar) {
 	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -112,6 +132,13 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, u
 // arrive on `bar` once all MMAs issued so far by this thread have completed (implies fence::before_thread_sync)
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
 	asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// same, arriving on the barrier at this offset in every CTA of cta_mask (multicast pipelines: a stage is free once all
+// the CTAs that received it have consumed it)
+__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t cta_mask) {
+	asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(cta_mask)
+	             : "memory");
 }
 
 // 32 lanes x 32 consecutive columns -> 32 registers per thread (thread i of the warp = lane base + i)

@@ -37,7 +37,9 @@ def check_oracle(oracle_mod, X, Q, L, D, C, k, metric, allow=None, deleted=None,
 
 @pytest.mark.parametrize("metric", ["l2", "cosine", "dot"])
 @pytest.mark.parametrize("n,d,k,nq", [(70_000, 128, 10, 130), (66_000, 768, 100, 64), (65_537, 100, 7, 9),
-                                      (80_000, 384, 10, 257), (70_001, 16, 3, 33)])
+                                      (80_000, 384, 10, 257), (70_001, 16, 3, 33),
+                                      # 4 and 6 query tiles on the K-streamed kernel: cluster pairs sharing X tiles by TMA multicast
+                                      (70_000, 320, 10, 512), (66_000, 768, 20, 700)])
 def test_tc_random_parity(gpu, oracle_mod, metric, n, d, k, nq):
     if metric == "l2" and d == 768:
         pytest.skip("l2 at d=768 needs 13 k-blocks: outside the tensor path's shared-memory budget (fp32 scan serves it)")
