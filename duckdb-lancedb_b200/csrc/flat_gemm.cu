@@ -221,7 +221,8 @@ static GemmPlan plan_gemm(int tilesQ, int nkb, int num_sms) {
 		best.NG = tilesQ;
 		best.KS = std::min(4, nkb);
 		if (const char *e = getenv("LANCE_B200_TSK_KS")) best.KS = std::max(1, std::min(nkb, atoi(e)));
-		best.EB = 8;
+		best.EB = 12; // 8 -> 12 slots per lane: fewer warp-wide flushes (C2: 6.81 -> 6.75 ms), 16 no better
+		if (const char *e = getenv("LANCE_B200_TSK_EB")) best.EB = std::max(1, std::min(32, atoi(e)));
 		best.S = 2;
 		while (best.S < 12 && gemm_tsk_smem_bytes(best.S + 1, best.KS, best.EB) <= TC_SMEM_MAX) best.S++;
 		best.R = std::max(1, num_sms / best.NG);
@@ -287,8 +288,11 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	// A single query tile (<= 128 queries) emits little, so its launches + refreshes dominate: grow faster
 	// (B200, B=64: C2 0.535 -> 0.49 ms, C5 shape 1.53 -> 1.44 ms per batch); full batches are emission-bound at 4.
 	const bool one_tile = nq_total <= 128; // query tile rows (the MMA M dimension)
-	const int growth_hi = one_tile ? (k <= 32 ? 16 : 8) : 4;
-	int growth = std::max(2, std::min(growth_hi, std::min(TC_CAP / (8 * k), (one_tile ? 2048 : 512) / k)));
+	// K-streamed kernel (K > 256, C2): with the warp-wide emit flush a hit is cheap there, and x8 beats x4 (round 2, C2
+	// B = 4096: 6.81 -> 6.50 ms per batch; x12 6.62, x16 6.95); the TMEM-resident kernel of C4 stays at x4 (x8: +3 %)
+	const bool streamed = im.nkb > 4;
+	const int growth_hi = one_tile ? (k <= 32 ? 16 : 8) : (streamed ? 8 : 4);
+	int growth = std::max(2, std::min(growth_hi, std::min(TC_CAP / (8 * k), (one_tile ? 2048 : (streamed ? 1024 : 512)) / k)));
 	long long seed_tiles = TC_SEED_TILES;
 	if (const char *e = getenv("LANCE_B200_TC_GROWTH")) growth = std::max(2, atoi(e)); // tuning hooks
 	if (const char *e = getenv("LANCE_B200_TC_SEED")) seed_tiles = std::max(1, atoi(e));
