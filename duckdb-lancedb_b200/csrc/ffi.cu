@@ -3,6 +3,7 @@
 // Nothing throws across this file: every entry catches and writes err_buf.
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <new>
 
 #include "store.h"
@@ -45,11 +46,20 @@ void *lance_create_detached(const char *db_path, int32_t dimension, const char *
 	})
 }
 
-void *lance_create_detached_from_arrow(const char *, void *, const char *, const char *, char *err_buf,
-                                       int err_buf_len) {
-	write_err(err_buf, err_buf_len,
-	          "create_from_arrow failed: multi-column Arrow tables are outside the kNN path of the B200 backend");
-	return nullptr;
+void *lance_create_detached_from_arrow(const char *db_path, void *arrow_schema, const char *metric,
+                                       const char *table_name, char *err_buf, int err_buf_len) {
+	// rust_lib/src/ffi.rs:63-90, lance_manager.rs:67-135: the vector dimension comes from the FixedSizeList column,
+	// the other fields become extra columns (on the device here: columns.h); the schema is borrowed, not consumed
+	if (!arrow_schema) {
+		write_err(err_buf, err_buf_len, "null arrow schema");
+		return nullptr;
+	}
+	LB_TRY("create_from_arrow failed: ", nullptr, {
+		const int dim = lb::arrow_schema_vector_dim(arrow_schema);
+		std::unique_ptr<Store> st(new Store(cstr(db_path), cstr(table_name), dim, cstr(metric), lb::default_device()));
+		st->define_columns_from_arrow(arrow_schema);
+		return st.release();
+	})
 }
 
 void *lance_open_detached(const char *db_path, const char *table_name, const char *metric, char *err_buf,
@@ -66,7 +76,15 @@ void lance_free_detached(void *handle) {
 	}
 }
 
-int32_t lance_detached_has_extra_columns(void *) { return 0; }
+int32_t lance_detached_has_extra_columns(void *handle) {
+	// rust_lib/src/ffi.rs:115-123
+	if (!handle) return 0;
+	try {
+		return static_cast<Store *>(handle)->has_extra_columns() ? 1 : 0;
+	} catch (...) {
+		return 0;
+	}
+}
 
 int32_t lance_detached_dimension(void *handle) { return handle ? static_cast<Store *>(handle)->dim() : 0; }
 
@@ -93,10 +111,92 @@ int32_t lance_detached_add_batch(void *handle, const float *vectors, int32_t num
 	})
 }
 
-int32_t lance_detached_add_batch_arrow(void *, void *, void *, int64_t *, char *err_buf, int err_buf_len) {
-	write_err(err_buf, err_buf_len,
-	          "add_batch_arrow failed: multi-column Arrow batches are outside the kNN path of the B200 backend");
-	return -1;
+int32_t lance_detached_add_batch_arrow(void *handle, void *arrow_schema, void *arrow_array, int64_t *out_labels,
+                                       char *err_buf, int err_buf_len) {
+	// rust_lib/src/ffi.rs:148-182: consumes the array, borrows the schema, labels are consecutive
+	LB_HANDLE(-1)
+	if (!arrow_schema || !arrow_array) {
+		write_err(err_buf, err_buf_len, "null arrow schema/array");
+		return -1;
+	}
+	LB_TRY("add_batch_arrow failed: ", -1, {
+		int64_t n = 0;
+		const int64_t first = h->add_arrow(arrow_schema, arrow_array, &n);
+		if (out_labels)
+			for (int64_t i = 0; i < n; i++) out_labels[i] = first + i;
+		return (int32_t)n;
+	})
+}
+
+int32_t lance_detached_search_batch_predicate(void *handle, const float *queries, int32_t nq, int32_t dim, int32_t k,
+                                              int32_t nprobes, int32_t refine_factor, const char *predicate,
+                                              int64_t *out_labels, float *out_distances, int32_t *out_counts,
+                                              char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("search failed: ", -1, {
+		if (dim != h->dim())
+			throw lb::Error("expected query dimension " + std::to_string(h->dim()) + ", got " + std::to_string(dim));
+		if (nq < 0 || k < 0) throw lb::Error("negative batch size or k");
+		if (nq == 0) return 0;
+		if (!queries || !out_labels || !out_distances || !out_counts) throw lb::Error("null buffer");
+		h->search_host_predicate(queries, nq, k, nprobes, refine_factor, predicate, out_labels, out_distances, out_counts);
+		return nq;
+	})
+}
+
+int32_t lance_detached_search_predicate(void *handle, const float *query, int32_t dim, int32_t k, int32_t nprobes,
+                                        int32_t refine_factor, const char *predicate, int64_t *out_labels,
+                                        float *out_distances, char *err_buf, int err_buf_len) {
+	int32_t count = 0;
+	int32_t rc = lance_detached_search_batch_predicate(handle, query, 1, dim, k, nprobes, refine_factor, predicate,
+	                                                   out_labels, out_distances, &count, err_buf, err_buf_len);
+	return rc < 0 ? -1 : count;
+}
+
+int32_t lance_detached_create_scalar_index(void *handle, const char *column, const char *index_type, char *err_buf,
+                                           int err_buf_len) {
+	// src/lance_index.cpp:481-486 (newer revision): a scalar index only speeds up Lance's prefilter; here the
+	// predicate kernel scans the column at HBM rate and its bitmap is cached, so there is nothing to build —
+	// the call validates its arguments and succeeds
+	LB_HANDLE(-1)
+	LB_TRY("create_scalar_index failed: ", -1, {
+		(void)index_type;
+		const std::string name = cstr(column);
+		for (int i = 0; i < h->column_count(); i++) {
+			std::string n;
+			if (h->column_info(i, &n, nullptr) && n == name) return 0;
+		}
+		throw lb::Error("no extra column named \"" + name + "\"");
+	})
+}
+
+int32_t lance_b200_set_column(void *handle, const char *name, int32_t type, int64_t first_label, int64_t count,
+                              const void *values, const int64_t *offsets, const uint8_t *valid, char *err_buf,
+                              int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("set_column failed: ", -1, {
+		if (type < 0 || type > lb::COL_STR) throw lb::Error("unknown column type");
+		h->set_column(cstr(name), (lb::ColType)type, first_label, count, values, offsets, valid);
+		return 0;
+	})
+}
+
+int64_t lance_b200_predicate_bitmap(void *handle, const char *predicate, uint32_t *out_bitmap, int64_t out_words,
+                                    const uint32_t **out_device_bitmap, int32_t *out_was_cached, char *err_buf,
+                                    int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("predicate failed: ", -1, {
+		bool cached = false;
+		std::shared_ptr<lb::DevBitmap> bm = h->predicate_bitmap(cstr(predicate), &cached);
+		if (out_was_cached) *out_was_cached = cached ? 1 : 0;
+		if (out_device_bitmap) *out_device_bitmap = bm->data(); // stays valid while the predicate is cached
+		if (out_bitmap && out_words > 0) {
+			const int64_t w = bm->words < out_words ? bm->words : out_words;
+			memset(out_bitmap, 0, (size_t)out_words * sizeof(uint32_t));
+			if (w > 0) LB_CUDA(cudaMemcpy(out_bitmap, bm->data(), (size_t)w * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+		}
+		return bm->bits;
+	})
 }
 
 int32_t lance_detached_merge(void *target_handle, void *source_handle, const int64_t *live_source_labels,

@@ -149,6 +149,7 @@ void Store::ensure_capacity(int64_t rows) {
 	std::swap(deleted_.p, nd.p);
 	std::swap(deleted_.bytes, nd.bytes);
 	cap_rows_ = ncap;
+	columns_.grow(ncap, copy_stream_);
 	deleted_host_.resize((size_t)(ncap / 32), 0u);
 	if (flat_gemm_) flat_gemm_->invalidate();
 }
@@ -264,6 +265,7 @@ int Store::merge_from(Store &src, const int64_t *live_labels, int count, int64_t
 	std::vector<int64_t> rows;
 	rows.reserve(count);
 	DevBuf tmp; // [m][dim] on the source's device
+	DevBuf d_rows;
 	int64_t src_base = 0, l = 0;
 	{
 		std::shared_lock<std::shared_mutex> lk(src.mu_);
@@ -277,7 +279,6 @@ int Store::merge_from(Store &src, const int64_t *live_labels, int count, int64_t
 		std::sort(rows.begin(), rows.end());
 		rows.erase(std::unique(rows.begin(), rows.end()), rows.end());
 		if (rows.empty()) return 0;
-		DevBuf d_rows;
 		d_rows.alloc(rows.size() * sizeof(int64_t));
 		tmp.alloc(rows.size() * (size_t)dim_ * sizeof(float));
 		LB_CUDA(cudaMemcpyAsync(d_rows.p, rows.data(), rows.size() * sizeof(int64_t), cudaMemcpyHostToDevice, src.copy_stream_));
@@ -296,6 +297,16 @@ int Store::merge_from(Store &src, const int64_t *live_labels, int count, int64_t
 		here.alloc((size_t)m * dim_ * sizeof(float));
 		LB_CUDA(cudaMemcpyPeer(here.p, device_, tmp.p, src.device_, (size_t)m * dim_ * sizeof(float)));
 		first = add_device(here.as<float>(), m, copy_stream_);
+	}
+	if (!src.columns_.empty()) {
+		// the rows' extra column values follow them (the reference moves whole Arrow batches, lance_manager.rs:307-345)
+		if (src.device_ != device_) throw Error("merging extra columns across devices is not supported");
+		std::unique_lock<std::shared_mutex> lk(mu_);
+		std::shared_lock<std::shared_mutex> ls(src.mu_);
+		LB_CUDA(cudaSetDevice(device_));
+		int64_t lc = 0;
+		columns_.gather_from(src.columns_, d_rows.as<int64_t>(), m, first - label_base_, cap_rows_, copy_stream_, &lc);
+		add_launches(lc);
 	}
 	for (int64_t i = 0; i < m; i++) {
 		out_old[i] = src_base + rows[(size_t)i];
@@ -369,7 +380,8 @@ int Store::search_finish(cudaStream_t s) {
 }
 
 void Store::search_host(const float *queries, int nq, int k, int nprobes, int refine, const uint32_t *allow,
-                        int64_t allow_bits, int64_t *out_labels, float *out_dist, int32_t *out_counts) {
+                        int64_t allow_bits, int64_t *out_labels, float *out_dist, int32_t *out_counts,
+                        const DevBitmap *resident) {
 	if (nq <= 0) return;
 	if (k <= 0) {
 		for (int i = 0; i < nq; i++) out_counts[i] = 0;
@@ -436,7 +448,10 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 			LB_CUDA(cudaMemcpyAsync(io->q.p, queries, qb, cudaMemcpyHostToDevice, s));
 		}
 		const uint32_t *d_allow = nullptr;
-		if (allow) {
+		if (resident) { // evaluated on the device (columns.h): nothing to upload
+			d_allow = resident->data();
+			allow_bits = resident->bits;
+		} else if (allow) {
 			size_t words = (size_t)((allow_bits + 31) / 32);
 			io->allow.ensure(std::max<size_t>(words, 1) * sizeof(uint32_t));
 			LB_CUDA(cudaMemcpyAsync(io->allow.p, allow, words * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
@@ -605,7 +620,7 @@ void Store::save() {
 	std::string path = dir_ + "/store.bin";
 	FILE *f = fopen((path + ".tmp").c_str(), "wb");
 	if (!f) throw Error("cannot write " + path);
-	int64_t hdr[8] = {dim_, metric_, n_rows_, n_deleted_, label_base_, index_ ? 1 : 0, 0, 0};
+	int64_t hdr[8] = {dim_, metric_, n_rows_, n_deleted_, label_base_, index_ ? 1 : 0, columns_.empty() ? 0 : 1, 0};
 	bool ok = fwrite(MAGIC, 1, 8, f) == 8 && fwrite(hdr, sizeof(int64_t), 8, f) == 8;
 	size_t words = (size_t)((n_rows_ + 31) / 32);
 	ok = ok && fwrite(deleted_host_.data(), sizeof(uint32_t), words, f) == words;
@@ -620,6 +635,14 @@ void Store::save() {
 	if (ok && index_) {
 		try {
 			save_index(f);
+		} catch (...) {
+			fclose(f);
+			throw;
+		}
+	}
+	if (ok && !columns_.empty()) {
+		try {
+			columns_.save(f, n_rows_, copy_stream_);
 		} catch (...) {
 			fclose(f);
 			throw;
@@ -684,6 +707,7 @@ Store *Store::open(const std::string &db_path, const std::string &table, const s
 		for (size_t w = 0; w < words; w++) nd += __builtin_popcount(st->deleted_host_[w]);
 		st->n_deleted_ = nd;
 		if (!v1 && hdr[5] != 0) st->load_index(f, path);
+		if (!v1 && hdr[6] != 0) st->columns_.load(f, path, n, st->cap_rows_, st->copy_stream_);
 	} catch (...) {
 		fclose(f);
 		throw;

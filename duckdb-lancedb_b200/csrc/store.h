@@ -15,6 +15,7 @@
 #include <utility>
 #include <vector>
 
+#include "columns.h"
 #include "kernels.h"
 #include "../../include/lance_b200.h"
 
@@ -94,7 +95,25 @@ public:
 
 	// host buffers in, host buffers out (the reference-facing call)
 	void search_host(const float *queries, int nq, int k, int nprobes, int refine, const uint32_t *allow,
-	                 int64_t allow_bits, int64_t *out_labels, float *out_dist, int32_t *out_counts);
+	                 int64_t allow_bits, int64_t *out_labels, float *out_dist, int32_t *out_counts,
+	                 const DevBitmap *resident = nullptr);
+	// the newer revision's call (src/lance_index.cpp:452-453): the pushed-down WHERE arrives as a string and is
+	// evaluated on the device over the extra columns (columns.h); NULL / empty predicate = no filter
+	void search_host_predicate(const float *queries, int nq, int k, int nprobes, int refine, const char *predicate,
+	                           int64_t *out_labels, float *out_dist, int32_t *out_counts);
+	// the device-resident allow bitmap of a predicate (cached per predicate and column epoch)
+	std::shared_ptr<DevBitmap> predicate_bitmap(const std::string &predicate, bool *was_cached = nullptr);
+
+	// extra columns (columns.h): values for the rows of labels [first_label, first_label + count)
+	void set_column(const std::string &name, ColType type, int64_t first_label, int64_t count, const void *values,
+	                const int64_t *offsets, const uint8_t *valid);
+	bool has_extra_columns();
+	int column_count();
+	bool column_info(int i, std::string *name, int32_t *type);
+	// Arrow C data interface ingest (rust_lib/src/ffi.rs:148-182): a struct array whose first FixedSizeList<float>
+	// child is the vector column and whose other children are extra columns; returns the first label
+	int64_t add_arrow(void *arrow_schema, void *arrow_array, int64_t *out_count);
+	void define_columns_from_arrow(void *arrow_schema);
 	// everything on the device, enqueued on s
 	void search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
 	                   int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
@@ -154,6 +173,7 @@ private:
 	cudaStream_t copy_stream_ = nullptr;
 
 	std::unique_ptr<IvfPqIndex> index_;
+	ColumnStore columns_; // mutated under the exclusive lock; bitmaps are evaluated under the shared one
 
 	std::mutex ws_mu_;
 	std::vector<std::unique_ptr<Workspace>> io_pool_;
@@ -174,6 +194,7 @@ private:
 	}
 };
 
+int arrow_schema_vector_dim(void *arrow_schema); // store_columns.cu: dimension of the FixedSizeList<float> child; throws
 int default_device();
 void set_default_device(int d);
 

@@ -233,6 +233,39 @@ int32_t lance_b200_time_search_device(void *handle, const float *d_queries, int3
                                       int32_t iters, void *d_flush, int64_t flush_bytes, float *out_ms, char *err_buf,
                                       int err_buf_len);
 
+/* ---------------------------------------------------------------- extra columns + predicate pushdown
+ * The newer revision of the extension passes the pushed-down WHERE as a Lance SQL string
+ * (src/lance_index.cpp:452-453 calls LanceDetachedSearch(.., predicate, ..); generator src/lance_optimizer.cpp:204-344)
+ * and ships the index's extra columns through the Arrow C data interface (src/lance_index.cpp:321-359 ->
+ * rust_lib/src/ffi.rs:63-90, 148-182; both are implemented above).  Here the columns live in HBM and the string is
+ * compiled and evaluated on the device (SQL three-valued logic, prefilter semantics of
+ * test/sql/lance_optimizer_filter.test:23-99); the bitmap is cached per (predicate, column epoch).
+ * predicate NULL or "" = no filter.  Same returns as lance_detached_search / _search_batch. */
+int32_t lance_detached_search_predicate(void *handle, const float *query, int32_t dim, int32_t k, int32_t nprobes,
+                                        int32_t refine_factor, const char *predicate, int64_t *out_labels,
+                                        float *out_distances, char *err_buf, int err_buf_len);
+int32_t lance_detached_search_batch_predicate(void *handle, const float *queries, int32_t nq, int32_t dim, int32_t k,
+                                              int32_t nprobes, int32_t refine_factor, const char *predicate,
+                                              int64_t *out_labels, float *out_distances, int32_t *out_counts,
+                                              char *err_buf, int err_buf_len);
+/* src/lance_index.cpp:481-486 (LanceDetachedCreateScalarIndex, newer revision): nothing to build on the device —
+ * validates that the column exists, returns 0 or -1. */
+int32_t lance_detached_create_scalar_index(void *handle, const char *column, const char *index_type, char *err_buf,
+                                           int err_buf_len);
+/* Typed host-buffer ingest of one extra column for the rows of labels [first_label, first_label + count) (they must
+ * exist).  type: 0 int64 values, 1 double values, 2 boolean (uint8 values), 3 UTF-8 (values = bytes,
+ * offsets[count + 1]).  valid: one byte per row or NULL (all valid).  Rows never written are NULL.  Returns 0 or -1. */
+int32_t lance_b200_set_column(void *handle, const char *name, int32_t type, int64_t first_label, int64_t count,
+                              const void *values, const int64_t *offsets, const uint8_t *valid, char *err_buf,
+                              int err_buf_len);
+/* Evaluates (or fetches from the cache) the allow bitmap of a predicate.  out_bitmap (nullable): host copy of the
+ * first out_words words; out_device_bitmap (nullable): the device pointer, valid while the predicate stays cached
+ * (for lance_b200_search_device / _time_search_device); out_was_cached (nullable).  Returns the number of rows the
+ * bitmap covers, or -1. */
+int64_t lance_b200_predicate_bitmap(void *handle, const char *predicate, uint32_t *out_bitmap, int64_t out_words,
+                                    const uint32_t **out_device_bitmap, int32_t *out_was_cached, char *err_buf,
+                                    int err_buf_len);
+
 /* Tuning / test hooks: force a flat path.  0 auto, 1 always the fp32 scan, 2 always tcgen05. */
 int32_t lance_b200_set_flat_path(void *handle, int32_t mode);
 
