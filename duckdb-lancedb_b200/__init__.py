@@ -78,6 +78,11 @@ SIGNATURES = {
     "lance_detached_add_batch_arrow": (_i32, [_vp, _vp, _vp, _vp] + _ERR),
     "lance_detached_merge": (_i32, [_vp, _vp, _vp, _i32, _vp, _vp] + _ERR),
     "lance_detached_search": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp] + _ERR),
+    "lance_detached_search_predicate": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _cp, _vp, _vp] + _ERR),
+    "lance_detached_search_batch_predicate": (_i32, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _cp, _vp, _vp, _vp] + _ERR),
+    "lance_detached_create_scalar_index": (_i32, [_vp, _cp, _cp] + _ERR),
+    "lance_b200_set_column": (_i32, [_vp, _cp, _i32, _i64, _i64, _vp, _vp, _vp] + _ERR),
+    "lance_b200_predicate_bitmap": (_i64, [_vp, _cp, _vp, _i64, _vp, _vp] + _ERR),
     "lance_detached_count": (_i64, [_vp] + _ERR),
     "lance_detached_delete": (_i32, [_vp, _i64] + _ERR),
     "lance_detached_delete_batch": (_i32, [_vp, _vp, _i32] + _ERR),
@@ -257,6 +262,91 @@ class LanceHandle:
 
     def compact(self):
         self._check(lib().lance_detached_compact(self._h, self._err, ERR_LEN), "compact")
+
+    # ---- extra columns + predicate pushdown (include/lance_b200.h, "extra columns")
+    def set_column(self, name: str, values, first_label: int = 0, valid=None, type: str | None = None):
+        """lance_b200_set_column: values for the rows of labels [first_label, first_label + len(values))."""
+        vb = None if valid is None else np.ascontiguousarray(np.asarray(valid, bool).astype(np.uint8))
+        if type == "str":
+            enc = [b"" if v is None else (v.encode() if isinstance(v, str) else bytes(v)) for v in values]
+            if valid is None and any(v is None for v in values):
+                vb = np.array([v is not None for v in values], np.uint8)
+            off = np.zeros(len(enc) + 1, np.int64)
+            if enc:
+                off[1:] = np.cumsum([len(e) for e in enc])
+            data = np.frombuffer(b"".join(enc) + b"\0", np.uint8).copy()
+            rc = lib().lance_b200_set_column(self._h, name.encode(), 3, int(first_label), len(enc), _ptr(data), _ptr(off),
+                                             _ptr(vb), self._err, ERR_LEN)
+            return self._check(rc, "set_column")
+        a = np.asarray(values)
+        if type == "bool" or (type is None and a.dtype == np.bool_):
+            t, a = 2, np.ascontiguousarray(a.astype(np.uint8))
+        elif type == "double" or (type is None and a.dtype.kind == "f"):
+            t, a = 1, np.ascontiguousarray(a, np.float64)
+        else:
+            t, a = 0, np.ascontiguousarray(a, np.int64)
+        rc = lib().lance_b200_set_column(self._h, name.encode(), t, int(first_label), a.shape[0], _ptr(a), None, _ptr(vb),
+                                         self._err, ERR_LEN)
+        return self._check(rc, "set_column")
+
+    def has_extra_columns(self) -> bool:
+        return bool(lib().lance_detached_has_extra_columns(self._h))
+
+    def create_scalar_index(self, column: str, index_type: str = "BTREE"):
+        self._check(lib().lance_detached_create_scalar_index(self._h, column.encode(), index_type.encode(), self._err,
+                                                             ERR_LEN), "create_scalar_index")
+
+    def add_batch_arrow(self, schema_ptr: int, array_ptr: int, n: int) -> np.ndarray:
+        """lance_detached_add_batch_arrow over exported ArrowSchema / ArrowArray structs (consumes the array)."""
+        labels = np.empty(max(n, 1), np.int64)
+        c = self._check(lib().lance_detached_add_batch_arrow(self._h, C.c_void_p(schema_ptr), C.c_void_p(array_ptr),
+                                                             _ptr(labels), self._err, ERR_LEN), "add_batch_arrow")
+        return labels[:c].copy()
+
+    @classmethod
+    def create_from_arrow(cls, schema_ptr: int, metric: str = "l2", db_path: str = "", table_name: str = "vectors"):
+        err = C.create_string_buffer(ERR_LEN)
+        h = lib().lance_create_detached_from_arrow(db_path.encode(), C.c_void_p(schema_ptr), metric.encode(),
+                                                   table_name.encode(), err, ERR_LEN)
+        if not h:
+            raise LanceError("Lance create_from_arrow: " + err.value.decode())
+        return cls(0, metric, _raw=h)
+
+    def predicate_bitmap(self, predicate: str, words: int | None = None):
+        """Returns (host copy of the allow bitmap uint32[words], rows covered, device pointer, was_cached)."""
+        w = int(words) if words is not None else (int(self.stats()["rows"]) + 31) // 32 + 1
+        out = np.zeros(max(w, 1), np.uint32)
+        dptr = C.c_void_p(0)
+        cached = C.c_int32(0)
+        bits = lib().lance_b200_predicate_bitmap(self._h, predicate.encode(), _ptr(out), out.shape[0], C.byref(dptr),
+                                                 C.byref(cached), self._err, ERR_LEN)
+        self._check(bits, "predicate")
+        return out, int(bits), int(dptr.value or 0), bool(cached.value)
+
+    def search_predicate(self, query, k: int, predicate: str | None, nprobes: int = 20, refine_factor: int = 1):
+        """The newer revision's LanceDetachedSearch(.., predicate, ..) (src/lance_index.cpp:452-453)."""
+        q = _f32(query)
+        kk = max(int(k), 1)
+        labels = np.empty(kk, np.int64)
+        dist = np.empty(kk, np.float32)
+        c = lib().lance_detached_search_predicate(self._h, _ptr(q), q.shape[0], int(k), nprobes, refine_factor,
+                                                  None if predicate is None else predicate.encode(), _ptr(labels),
+                                                  _ptr(dist), self._err, ERR_LEN)
+        self._check(c, "search")
+        return labels[:c].copy(), dist[:c].copy()
+
+    def search_batch_predicate(self, queries, k: int, predicate: str | None, nprobes: int = 20, refine_factor: int = 1):
+        Q = _f32(queries)
+        nq, d = Q.shape
+        kk = max(int(k), 1)
+        labels = np.empty((nq, kk), np.int64)
+        dist = np.empty((nq, kk), np.float32)
+        counts = np.empty(nq, np.int32)
+        rc = lib().lance_detached_search_batch_predicate(self._h, _ptr(Q), nq, d, int(k), nprobes, refine_factor,
+                                                         None if predicate is None else predicate.encode(), _ptr(labels),
+                                                         _ptr(dist), _ptr(counts), self._err, ERR_LEN)
+        self._check(rc, "search")
+        return labels, dist, counts
 
     # ---- search
     def search(self, query, k: int, nprobes: int = 20, refine_factor: int = 1, allow=None):
