@@ -44,6 +44,12 @@ int32_t LanceDetachedAddBatch(LanceHandle handle, const float *vectors, int32_t 
 int32_t LanceDetachedSearch(LanceHandle handle, const float *query, int32_t dim, int32_t k, int32_t nprobes,
                             int32_t refine_factor, const uint32_t *allow_bitmap, int64_t bitmap_bits,
                             int64_t *out_labels, float *out_distances);
+// the newer revision's form (src/lance_index.cpp:452-453): the pushed-down WHERE as a string, evaluated on the device
+int32_t LanceDetachedSearch(LanceHandle handle, const float *query, int32_t dim, int32_t k, int32_t nprobes,
+                            int32_t refine_factor, const char *predicate, int64_t *out_labels, float *out_distances);
+int32_t LanceDetachedSearchBatch(LanceHandle handle, const float *queries, int32_t nq, int32_t dim, int32_t k,
+                                 int32_t nprobes, int32_t refine_factor, const char *predicate, int64_t *out_labels,
+                                 float *out_distances, int32_t *out_counts);
 int32_t LanceDetachedSearchBatch(LanceHandle handle, const float *queries, int32_t nq, int32_t dim, int32_t k,
                                  int32_t nprobes, int32_t refine_factor, const uint32_t *allow_bitmap,
                                  int64_t bitmap_bits, int64_t *out_labels, float *out_distances, int32_t *out_counts);
@@ -60,7 +66,9 @@ int32_t LanceDetachedGetVector(LanceHandle handle, int64_t label, float *out_vec
 
 // ------------------------------------------------------------------ extra columns + predicate
 // The index's extra columns (src/lance_index.cpp:233-245 allows VARCHAR, INTEGER, BIGINT, DOUBLE, BOOLEAN),
-// kept on the host per label; the reference ships them to Lance and lets it evaluate the predicate string.
+// staged on the host per label and pushed to the device store before a filtered search; the reference ships them to
+// Lance and lets it evaluate the predicate string — the device store does the same (csrc/columns.h).  The host
+// evaluator below is the CPU checker of the device one.
 enum class ColumnType { VARCHAR, BIGINT, DOUBLE, BOOLEAN };
 struct Column {
 	ColumnType type = ColumnType::BIGINT;
@@ -129,15 +137,11 @@ private:
 	std::vector<row_t> label_to_rowid_;
 	std::unordered_map<row_t, int64_t> rowid_to_label_;
 	ColumnSet columns_;
-	// predicate string -> allow bitmap, reused while the labels and the extra columns are unchanged: the WHERE of the
-	// rewritten query is constant across a workload, evaluating it over N rows on the host is not
-	struct CachedBitmap {
-		uint64_t signature = 0;
-		std::shared_ptr<const std::vector<uint32_t>> bitmap;
-	};
-	std::map<std::string, CachedBitmap> predicate_cache_;
+	// rows of every extra column already pushed to the device store (lance_b200_set_column); the predicate string
+	// itself goes through the FFI as in the reference and is evaluated (and cached) on the device
+	std::map<std::string, int64_t> synced_rows_;
 	std::mutex predicate_mu_;
-	std::shared_ptr<const std::vector<uint32_t>> PredicateBitmap(const std::string &predicate);
+	void SyncColumnsToDevice();
 };
 
 // ------------------------------------------------------------------ lance_search table function (src/lance_search.cpp)

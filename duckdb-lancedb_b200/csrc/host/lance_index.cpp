@@ -52,6 +52,24 @@ int32_t LanceDetachedSearch(LanceHandle handle, const float *query, int32_t dim,
 	if (n < 0) throw IOException(std::string("Lance search: ") + err);
 	return n;
 }
+// the newer revision's signature (called at src/lance_index.cpp:452-453): predicate string, nullable
+int32_t LanceDetachedSearch(LanceHandle handle, const float *query, int32_t dim, int32_t k, int32_t nprobes,
+                            int32_t refine_factor, const char *predicate, int64_t *out_labels, float *out_distances) {
+	char err[ERR_BUF] = {0};
+	int32_t n = lance_detached_search_predicate(handle, query, dim, k, nprobes, refine_factor, predicate, out_labels,
+	                                            out_distances, err, ERR_BUF);
+	if (n < 0) throw IOException(std::string("Lance search: ") + err);
+	return n;
+}
+int32_t LanceDetachedSearchBatch(LanceHandle handle, const float *queries, int32_t nq, int32_t dim, int32_t k,
+                                 int32_t nprobes, int32_t refine_factor, const char *predicate, int64_t *out_labels,
+                                 float *out_distances, int32_t *out_counts) {
+	char err[ERR_BUF] = {0};
+	int32_t n = lance_detached_search_batch_predicate(handle, queries, nq, dim, k, nprobes, refine_factor, predicate,
+	                                                  out_labels, out_distances, out_counts, err, ERR_BUF);
+	if (n < 0) throw IOException(std::string("Lance search: ") + err);
+	return n;
+}
 int32_t LanceDetachedSearchBatch(LanceHandle handle, const float *queries, int32_t nq, int32_t dim, int32_t k,
                                  int32_t nprobes, int32_t refine_factor, const uint32_t *allow_bitmap,
                                  int64_t bitmap_bits, int64_t *out_labels, float *out_distances, int32_t *out_counts) {
@@ -209,21 +227,47 @@ int32_t LanceIndex::MergeIndexes(LanceIndex &other) {
 	return n;
 }
 
-std::shared_ptr<const std::vector<uint32_t>> LanceIndex::PredicateBitmap(const std::string &predicate) {
-	// signature of what the bitmap depends on: the number of labels and the length of every extra column (append-only)
-	uint64_t sig = 1469598103934665603ull ^ (uint64_t)label_to_rowid_.size();
-	for (const auto &kv : columns_) sig = (sig * 1099511628211ull) ^ (uint64_t)kv.second.size() ^ ((uint64_t)kv.first.size() << 48);
-	{
-		std::lock_guard<std::mutex> g(predicate_mu_);
-		auto it = predicate_cache_.find(predicate);
-		if (it != predicate_cache_.end() && it->second.signature == sig) return it->second.bitmap;
-	}
-	auto bm = std::make_shared<const std::vector<uint32_t>>(
-	    EvaluatePredicate(predicate, columns_, (int64_t)label_to_rowid_.size()));
+// The index's extra columns travel to the device store (the reference ships them to Lance with every Append,
+// src/lance_index.cpp:321-359); here the mirror pushes what was appended to `columns_` since the last search.
+void LanceIndex::SyncColumnsToDevice() {
 	std::lock_guard<std::mutex> g(predicate_mu_);
-	if (predicate_cache_.size() >= 16) predicate_cache_.clear();
-	predicate_cache_[predicate] = CachedBitmap{sig, bm};
-	return bm;
+	const int64_t n_labels = (int64_t)label_to_rowid_.size();
+	for (auto &kv : columns_) {
+		const Column &c = kv.second;
+		int64_t &done = synced_rows_[kv.first];
+		const int64_t upto = std::min<int64_t>((int64_t)c.size(), n_labels);
+		if (upto <= done) continue;
+		const int64_t cnt = upto - done;
+		char err[ERR_BUF] = {0};
+		int32_t rc = 0;
+		switch (c.type) {
+		case ColumnType::BIGINT:
+			rc = lance_b200_set_column(rust_handle_, kv.first.c_str(), 0, done, cnt, c.i.data() + done, nullptr, c.valid.data() + done, err, ERR_BUF);
+			break;
+		case ColumnType::DOUBLE:
+			rc = lance_b200_set_column(rust_handle_, kv.first.c_str(), 1, done, cnt, c.d.data() + done, nullptr, c.valid.data() + done, err, ERR_BUF);
+			break;
+		case ColumnType::BOOLEAN: {
+			std::vector<uint8_t> b((size_t)cnt);
+			for (int64_t i = 0; i < cnt; i++) b[(size_t)i] = c.i[(size_t)(done + i)] ? 1 : 0;
+			rc = lance_b200_set_column(rust_handle_, kv.first.c_str(), 2, done, cnt, b.data(), nullptr, c.valid.data() + done, err, ERR_BUF);
+			break;
+		}
+		case ColumnType::VARCHAR: {
+			std::string bytes;
+			std::vector<int64_t> off((size_t)cnt + 1, 0);
+			for (int64_t i = 0; i < cnt; i++) {
+				bytes += c.s[(size_t)(done + i)];
+				off[(size_t)i + 1] = (int64_t)bytes.size();
+			}
+			bytes.push_back('\0');
+			rc = lance_b200_set_column(rust_handle_, kv.first.c_str(), 3, done, cnt, bytes.data(), off.data(), c.valid.data() + done, err, ERR_BUF);
+			break;
+		}
+		}
+		if (rc < 0) throw IOException(std::string("Lance set_column: ") + err);
+		done = upto;
+	}
 }
 
 std::vector<std::pair<row_t, float>> LanceIndex::Search(const float *query, int32_t dimension, int32_t k,
@@ -232,11 +276,10 @@ std::vector<std::pair<row_t, float>> LanceIndex::Search(const float *query, int3
 	if (k <= 0) return {};
 	std::vector<int64_t> labels(k);
 	std::vector<float> distances(k);
-	std::shared_ptr<const std::vector<uint32_t>> bitmap;
-	if (!predicate.empty()) bitmap = PredicateBitmap(predicate);
+	if (!predicate.empty()) SyncColumnsToDevice();
+	// :452-453 verbatim: the predicate string goes through the FFI; the device evaluates it
 	const int32_t n = LanceDetachedSearch(rust_handle_, query, dimension, k, nprobes_, refine_factor_,
-	                                      bitmap ? bitmap->data() : nullptr, bitmap ? (int64_t)bitmap->size() * 32 : 0,
-	                                      labels.data(), distances.data());
+	                                      predicate.empty() ? nullptr : predicate.c_str(), labels.data(), distances.data());
 	std::vector<std::pair<row_t, float>> results;
 	results.reserve(n);
 	for (int32_t i = 0; i < n; i++) {
@@ -254,11 +297,9 @@ std::vector<std::vector<std::pair<row_t, float>>> LanceIndex::SearchBatch(const 
 	std::vector<int64_t> labels((size_t)nq * k);
 	std::vector<float> distances((size_t)nq * k);
 	std::vector<int32_t> counts(nq);
-	std::shared_ptr<const std::vector<uint32_t>> bitmap;
-	if (!predicate.empty()) bitmap = PredicateBitmap(predicate);
+	if (!predicate.empty()) SyncColumnsToDevice();
 	LanceDetachedSearchBatch(rust_handle_, queries, nq, dimension, k, nprobes_, refine_factor_,
-	                         bitmap ? bitmap->data() : nullptr, bitmap ? (int64_t)bitmap->size() * 32 : 0, labels.data(),
-	                         distances.data(), counts.data());
+	                         predicate.empty() ? nullptr : predicate.c_str(), labels.data(), distances.data(), counts.data());
 	for (int32_t q = 0; q < nq; q++) {
 		out[q].reserve(counts[q]);
 		for (int32_t i = 0; i < counts[q]; i++) {
