@@ -146,6 +146,16 @@ def bench_mask(rows, selectivity, dev):
     return torch.rand(rows, generator=g, device=dev) < selectivity
 
 
+def bench_scores(rows, dev):
+    """The C5 table's extra column `score INT ~ U[0,100)`, drawn from the same stream as bench_mask so
+    that `score < round(100 s)` selects exactly the rows bench_mask(rows, s) keeps (s a multiple of 0.01)."""
+    import torch
+
+    g = torch.Generator(device=dev)
+    g.manual_seed(SEED + 2)
+    return (torch.rand(rows, generator=g, device=dev).double() * 100.0).floor().to(torch.int64)
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
 
@@ -501,6 +511,16 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
         allow_host = pkg.make_bitmap(mask.cpu().numpy())
         allow_t = torch.from_numpy(allow_host.view(np.int32)).to(dev)
         d_allow, allow_bits = allow_t.data_ptr(), allow_host.shape[0] * 32
+    # N=1: the reference-facing call takes the pushed-down WHERE as a STRING (src/lance_index.cpp:452-453); the index's
+    # extra column lives in HBM and the predicate is evaluated (once, then cached) on the device
+    predicate = None
+    if allow_host is not None and world == 1:
+        predicate = "score < %d" % int(round(100 * wl["selectivity"]))
+        if not h.has_extra_columns():
+            h.set_column("score", bench_scores(rows, dev)[lo:hi].cpu().numpy(), first_label=lo)
+        bm, bits, _, _ = h.predicate_bitmap(predicate, words=allow_host.shape[0])
+        if bits != n_local or not np.array_equal(bm, allow_host):
+            raise RuntimeError("device predicate bitmap differs from the bench mask")
 
     nprobes = wl.get("nprobes", 20)
     adc_bytes = ivf_query_bytes = None
@@ -531,8 +551,10 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
     # the two C calls of a step with their ctypes arguments built once: what is timed is the library, not the harness
     call_device = h.bind_search_device(Qd.data_ptr(), B, k, L.data_ptr(), D.data_ptr(), C.data_ptr(), nprobes=nprobes,
                                        refine_factor=1, d_allow=d_allow, allow_bits=allow_bits, stream=sp)
-    call_host = h.bind_search_batch(Qh.numpy(), k, (Lh.numpy(), Dh.numpy(), Ch.numpy()), nprobes=nprobes, refine_factor=1,
-                                    allow=allow_host)
+    call_host_bitmap = h.bind_search_batch(Qh.numpy(), k, (Lh.numpy(), Dh.numpy(), Ch.numpy()), nprobes=nprobes,
+                                           refine_factor=1, allow=allow_host)
+    call_host = call_host_bitmap if predicate is None else h.bind_search_batch(
+        Qh.numpy(), k, (Lh.numpy(), Dh.numpy(), Ch.numpy()), nprobes=nprobes, refine_factor=1, predicate=predicate)
 
     def step_device(q_ptr):
         """local top-k -> (N>1) one NCCL all_gather of the packed lists -> final device select -> settle."""
@@ -637,6 +659,12 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
     # N=1: the reference-facing call is synchronous and runs on the library's own stream, so the host wall-clock of
     # the steps is the end-to-end time (the events on torch's stream only bound it from below)
     ms_e2e = max(ms_e2e_dev, wall_ms[0]) if world == 1 else ms_e2e_dev
+    ms_e2e_bitmap = None
+    if predicate is not None:  # the same call with the bitmap evaluated on the host and uploaded per call
+        for _ in range(2):
+            call_host_bitmap()
+        t_dev = timed(call_host_bitmap, steps, host_call=True)
+        ms_e2e_bitmap = max(t_dev, wall_ms[0])
     # A timed region shorter than a few sampler periods (single queries, small shards) yields no clock sample:
     # keep the same device step running, untimed, until the region + extension spans ~0.5 s of load (headline) or
     # ~0.25 s (sub-configurations).  The count is derived from the max-reduced times, so every rank runs the same
@@ -732,9 +760,12 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
             else "bf16 candidates + f32 re-rank", "data": "synthetic N(0,1), seeded" if args.data == "gaussian" else
             "synthetic unit-norm mixture of 1000 Gaussians (sigma 0.05), seeded", "config": workload_config(wl, args, name),
             "clocks": clocks,
-            "e2e": {"value": qps_e2e, "unit": "queries/s", "h2d_bytes_per_step": int(Qh.numel() * 4 + (allow_host.nbytes if allow_host is not None and world == 1 else 0)),
+            "e2e": {"value": qps_e2e, "unit": "queries/s", "h2d_bytes_per_step": int(Qh.numel() * 4 + (allow_host.nbytes if allow_host is not None and world == 1 and predicate is None else 0)),
                     "d2h_bytes_per_step": int(Lh.numel() * 8 + Dh.numel() * 4 + Ch.numel() * 4), "ms_per_step": ms_e2e / steps},
             "gpu_launches": int(launches), "roofline": roof,
+            **({"prefilter": {"predicate": predicate, "evaluated": "on the device over the HBM-resident column, bitmap cached per (predicate, epoch)",
+                              "e2e_host_bitmap_ms_per_step": ms_e2e_bitmap / steps,
+                              "host_bitmap_h2d_bytes_per_step": int(allow_host.nbytes)}} if predicate is not None else {}),
             "paths": {"flat_simt_batches": st1["flat_simt_batches"] - st0["flat_simt_batches"],
                       "flat_tc_batches": st1["flat_tc_batches"] - st0["flat_tc_batches"],
                       "tc_fallback_queries": st1["tc_fallback_queries"] - st0["tc_fallback_queries"],

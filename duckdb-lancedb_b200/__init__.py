@@ -385,7 +385,7 @@ class LanceHandle:
         self._check(rc, "search")
         return labels, dist, counts
 
-    def bind_search_batch(self, Q, k: int, out, nprobes: int = 20, refine_factor: int = 1, allow=None):
+    def bind_search_batch(self, Q, k: int, out, nprobes: int = 20, refine_factor: int = 1, allow=None, predicate=None):
         """lance_detached_search_batch with every argument converted ONCE: returns a zero-argument callable that makes
         exactly the C call (bench.py's end-to-end loop: the per-call cost of building ctypes arguments in Python is
         harness time, not the library's).  Q / out / allow must stay alive and unchanged in place."""
@@ -396,6 +396,11 @@ class LanceHandle:
         args = (self._h, _ptr(Q), C.c_int32(Q.shape[0]), C.c_int32(Q.shape[1]), C.c_int32(int(k)), C.c_int32(nprobes),
                 C.c_int32(refine_factor), _ptr(bm), C.c_int64(0 if bm is None else bm.shape[0] * 32), _ptr(labels), _ptr(dist),
                 _ptr(counts), self._err, C.c_int(ERR_LEN))
+        if predicate is not None:  # lance_detached_search_batch_predicate: the WHERE as a string, evaluated on the device
+            fn = lib().lance_detached_search_batch_predicate
+            pred = C.c_char_p(predicate.encode())
+            args = (self._h, _ptr(Q), C.c_int32(Q.shape[0]), C.c_int32(Q.shape[1]), C.c_int32(int(k)), C.c_int32(nprobes),
+                    C.c_int32(refine_factor), pred, _ptr(labels), _ptr(dist), _ptr(counts), self._err, C.c_int(ERR_LEN))
         keep = (Q, labels, dist, counts, bm)
 
         def call():
