@@ -83,6 +83,7 @@ SIGNATURES = {
     "lance_detached_create_scalar_index": (_i32, [_vp, _cp, _cp] + _ERR),
     "lance_b200_set_column": (_i32, [_vp, _cp, _i32, _i64, _i64, _vp, _vp, _vp] + _ERR),
     "lance_b200_predicate_bitmap": (_i64, [_vp, _cp, _vp, _i64, _vp, _vp] + _ERR),
+    "lance_b200_flat_search_noalloc": (_i32, [_i32, _vp, _i64, _i32, _i32, _vp, _i32, _i64, _vp, _i64, _vp, _vp, _vp, _vp] + _ERR),
     "lance_detached_count": (_i64, [_vp] + _ERR),
     "lance_detached_delete": (_i32, [_vp, _i64] + _ERR),
     "lance_detached_delete_batch": (_i32, [_vp, _vp, _i32] + _ERR),
@@ -562,6 +563,17 @@ def merge_topk_strided_device(device: int, d_labels: int, d_dists: int, d_counts
                                                     _ptr(stream) if stream else None, err, ERR_LEN)
     if rc != 0:
         raise LanceError("Lance merge: " + err.value.decode())
+
+
+def flat_search_noalloc(device: int, d_vectors: int, rows: int, dim: int, metric: int, d_query: int, k: int, d_labels: int,
+                        d_dist: int, d_count: int, label_base: int = 0, d_allow: int = 0, allow_bits: int = 0, stream: int = 0):
+    """lance_b200_flat_search_noalloc: device pointers in and out, enqueued on `stream`, no allocation (static scratch)."""
+    err = C.create_string_buffer(ERR_LEN)
+    rc = lib().lance_b200_flat_search_noalloc(device, _ptr(d_vectors) if d_vectors else None, rows, dim, metric, _ptr(d_query), k,
+                                              label_base, _ptr(d_allow) if d_allow else None, allow_bits, _ptr(d_labels),
+                                              _ptr(d_dist), _ptr(d_count), _ptr(stream) if stream else None, err, ERR_LEN)
+    if rc < 0:
+        raise LanceError("Lance " + err.value.decode())
 
 
 def device_count() -> int:

@@ -266,6 +266,22 @@ int64_t lance_b200_predicate_bitmap(void *handle, const char *predicate, uint32_
                                     const uint32_t **out_device_bitmap, int32_t *out_was_cached, char *err_buf,
                                     int err_buf_len);
 
+/* ---------------------------------------------------------------- allocation-free flat search
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Exact flat top-k of ONE
+ * query over a caller-owned device table d_vectors[rows][dim] (fp32 row-major); metric 0 l2 (squared), 1 cosine, 2 dot
+ * (reported as 1 - q.x), the conventions of lance_detached_search.  d_allow: nullable prefilter bitmap over rows.
+ * Writes d_out_labels[k] (label_base + row, -1 beyond the count), d_out_distances[k] (+inf beyond it) and
+ * d_out_count[0]; enqueued on `stream`, no host synchronisation.  Performs NO allocation: its partial top-k lists live in
+ * a file-scope device array of 2 424 832 bytes (296 blocks x 8 warps x 128 keys x 8 B) that every GPU loading the
+ * library holds until exit.  Limits: 1 <= k <= 128, rows < 2^32 — larger values are rejected with a message.  All calls
+ * on one device share that array: calls that overlap on the GPU (different streams) race — serialise them; an
+ * overlap that the call can detect yields count -1.  Returns 0 or -1. */
+int32_t lance_b200_flat_search_noalloc(int32_t device, const float *d_vectors, int64_t rows, int32_t dim, int32_t metric,
+                                       const float *d_query, int32_t k, int64_t label_base, const uint32_t *d_allow,
+                                       int64_t bitmap_bits, int64_t *d_out_labels, float *d_out_distances,
+                                       int32_t *d_out_count, void *stream, char *err_buf, int err_buf_len);
+
 /* Tuning / test hooks: force a flat path.  0 auto, 1 always the fp32 scan, 2 always tcgen05. */
 int32_t lance_b200_set_flat_path(void *handle, int32_t mode);
 
