@@ -93,3 +93,62 @@ void LanceDetachedSave(LanceHandle handle) {
 
 int64_t LanceDetachedCount(LanceHandle handle) {"""),
 ])
+
+# ---------------------------------------------------------------- include/lance_index.hpp
+edit("include/lance_index.hpp", [
+    ("	vector<pair<row_t, float>> Search(const float *query, int32_t dimension, int32_t k);\n",
+     """	// `predicate`: pushed-down WHERE as a Lance SQL string (lance_optimizer.cpp), evaluated as a prefilter
+	vector<pair<row_t, float>> Search(const float *query, int32_t dimension, int32_t k, const string &predicate = "");
+	// One call for a whole query batch: queries[nq][dimension]; result[q] as Search()
+	vector<vector<pair<row_t, float>>> SearchBatch(const float *queries, int32_t nq, int32_t dimension, int32_t k,
+	                                               const string &predicate = "");
+"""),
+    ("	void CreateHnswIndex(int32_t m, int32_t ef_construction);\n",
+     """	void CreateHnswIndex(int32_t m, int32_t ef_construction);
+	void CreateScalarIndex(const string &column, const string &index_type);
+"""),
+])
+
+# ---------------------------------------------------------------- lance_index.cpp
+edit("lance_index.cpp", [
+    ("void LanceIndex::CreateAnnIndex(int32_t num_partitions, int32_t num_sub_vectors) {",
+     """vector<vector<pair<row_t, float>>> LanceIndex::SearchBatch(const float *queries, int32_t nq, int32_t dimension,
+                                                           int32_t k, const string &predicate) {
+	vector<vector<pair<row_t, float>>> results(nq > 0 ? nq : 0);
+	if (!rust_handle_ || dimension != dimension_ || nq <= 0 || k <= 0) {
+		return results;
+	}
+
+	// One FFI call for the whole batch: a single H2D of the queries, one tensor-core pass over the table
+	// (or one batched IVF_PQ probe + scan), a single D2H of the packed results.
+	vector<int64_t> labels(static_cast<size_t>(nq) * k);
+	vector<float> distances(static_cast<size_t>(nq) * k);
+	vector<int32_t> counts(nq);
+	LanceDetachedSearchBatch(rust_handle_, queries, nq, dimension, k, nprobes_, refine_factor_,
+	                         predicate.empty() ? nullptr : predicate.c_str(), labels.data(), distances.data(),
+	                         counts.data());
+
+	for (int32_t q = 0; q < nq; q++) {
+		results[q].reserve(counts[q]);
+		for (int32_t i = 0; i < counts[q]; i++) {
+			auto label = labels[static_cast<size_t>(q) * k + i];
+			if (label >= 0 && label < static_cast<int64_t>(label_to_rowid_.size())) {
+				results[q].emplace_back(label_to_rowid_[label], distances[static_cast<size_t>(q) * k + i]);
+			}
+		}
+	}
+	return results;
+}
+
+void LanceIndex::CreateAnnIndex(int32_t num_partitions, int32_t num_sub_vectors) {"""),
+    ("""	writer.Write(reinterpret_cast<const uint8_t *>(lance_path.data()), path_len);
+
+	is_dirty_ = false;""",
+     """	writer.Write(reinterpret_cast<const uint8_t *>(lance_path.data()), path_len);
+
+	// Lance commits every add/delete to its dataset; the device store lives in HBM and is written here, next to the
+	// metadata, so that LoadFromStorage (LanceOpenDetached) finds vectors, tombstones, IVF_PQ index and extra columns.
+	LanceDetachedSave(rust_handle_);
+
+	is_dirty_ = false;"""),
+])
