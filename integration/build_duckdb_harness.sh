@@ -1,0 +1,26 @@
+#!/bin/bash
+# Builds the vendored DuckDB's `unittest` with the PATCHED extension linked in (integration/patch/*.patch applied to a
+# copy of the reference's src/, integration/cmake/CMakeLists.txt in place of the cargo build, liblance_b200.so as the
+# backend) and stages what a GPU box needs under integration/_build/ (git-ignored; travels with gpurun).
+# Needs /root/reference (this container).  ~25 min of 8 cores for a cold DuckDB build.
+set -e
+ROOT=$(cd "$(dirname "$0")/.." && pwd)
+REF=${REF:-/root/reference}
+EXT=/tmp/lance_ext
+BUILD=${BUILD:-/tmp/duckdb_build}
+rm -rf $EXT && mkdir -p $EXT
+cp -r $REF/src $REF/test $REF/extension_config.cmake $EXT/ && chmod -R u+w $EXT
+for p in $ROOT/integration/patch/*.patch; do patch -s -p1 -d $EXT < $p; done
+cp $ROOT/integration/cmake/CMakeLists.txt $EXT/CMakeLists.txt
+cp $ROOT/integration/test/sql/*.test $EXT/test/sql/
+make -C $ROOT/duckdb-lancedb_b200/csrc >/dev/null
+cmake -G Ninja -S $REF/duckdb -B $BUILD -DCMAKE_BUILD_TYPE=Release -DOVERRIDE_GIT_DESCRIBE=v1.4.0 -DBUILD_UNITTESTS=1 \
+  -DBUILD_SHELL=1 -DBUILD_EXTENSIONS="core_functions" -DENABLE_EXTENSION_AUTOLOADING=0 -DENABLE_EXTENSION_AUTOINSTALL=0 \
+  -DDUCKDB_EXTENSION_CONFIGS=$EXT/extension_config.cmake \
+  -DLANCE_B200_PREBUILT=$ROOT/duckdb-lancedb_b200/liblance_b200.so > $BUILD.cmake.log 2>&1
+ninja -C $BUILD -j${JOBS:-8} unittest > $BUILD.ninja.log 2>&1
+OUT=$ROOT/integration/_build
+rm -rf $OUT && mkdir -p $OUT/test
+cp $BUILD/test/unittest $BUILD/src/libduckdb.so $OUT/
+cp -r $EXT/test/sql $OUT/test/
+echo "staged: $(ls $OUT)"
