@@ -212,6 +212,13 @@ rep('''		// Try to push filter predicates to Lance
 		// Try to push filter predicates to Lance
 		bool filter_fully_pushed = false;''')
 
+# DuckDB 1.4's late-materialization pass (optimizer.cpp: runs right after TOP_N) turns "TOP_N over a scan" into a
+# semi-join on the row id whose right side is TOP_N -> PROJ -> GET(.., rowid): the replacement GET must know the
+# scan's virtual columns, or binding the row id column throws "Failed to find referenced virtual column".
+rep('''		    make_uniq<LogicalGet>(get.table_index, scan_func, std::move(bind_data), get.returned_types, get.names);''',
+    '''		    make_uniq<LogicalGet>(get.table_index, scan_func, std::move(bind_data), get.returned_types, get.names,
+		                          get.virtual_columns);''')
+
 a = s.index('		// Replace the LIMIT → ORDER → [FILTER →] [PROJ →] GET subtree')
 b = s.index('void RegisterLanceOptimizer')
 NEW_TAIL = '''		// Replace the [FILTER ->] [PROJ ->] GET chain below the sort (below the key projection when there is one)

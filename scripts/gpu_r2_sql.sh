@@ -8,7 +8,7 @@ mkdir -p /tmp/lance_ext/test && rm -rf /tmp/lance_ext/test/sql && cp -r $B/test/
 export LD_LIBRARY_PATH=$PWD/$B:$LD_LIBRARY_PATH
 rc=0
 for t in /tmp/lance_ext/test/sql/*.test; do
-  timeout 300 $B/unittest "$t" > $O/$(basename $t).log 2>&1; r=$?
+  timeout 300 $PWD/$B/unittest --test-dir /tmp/lance_ext "$t" > $O/$(basename $t).log 2>&1; r=$?
   echo "$(basename $t) rc=$r $(grep -E 'All tests passed|test cases:' $O/$(basename $t).log | tail -1)" | tee -a $O/summary.txt
   [ $r -ne 0 ] && rc=1
 done
