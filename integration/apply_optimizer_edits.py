@@ -219,6 +219,27 @@ rep('''		    make_uniq<LogicalGet>(get.table_index, scan_func, std::move(bind_da
     '''		    make_uniq<LogicalGet>(get.table_index, scan_func, std::move(bind_data), get.returned_types, get.names,
 		                          get.virtual_columns);''')
 
+# The scan already emits exactly the requested columns (input.column_ids): declare it, so that virtual columns (rowid)
+# are legal on it (plan_get.cpp: "Virtual columns require projection pushdown"), and honour projection_ids when the
+# original scan had filter-only columns pruned.
+rep('''		TableFunction scan_func("lance_index_scan", {}, LanceIndexScanScan, LanceIndexScanBind, LanceIndexScanInit);
+''', '''		TableFunction scan_func("lance_index_scan", {}, LanceIndexScanScan, LanceIndexScanBind, LanceIndexScanInit);
+		scan_func.projection_pushdown = true;
+''')
+rep('''	for (auto &col_id : input.column_ids) {
+		state->storage_ids.push_back(StorageIndex(col_id));
+	}
+''', '''	if (input.projection_ids.empty()) {
+		for (auto &col_id : input.column_ids) {
+			state->storage_ids.push_back(StorageIndex(col_id));
+		}
+	} else {
+		for (auto &proj_id : input.projection_ids) {
+			state->storage_ids.push_back(StorageIndex(input.column_ids[proj_id]));
+		}
+	}
+''')
+
 a = s.index('		// Replace the LIMIT → ORDER → [FILTER →] [PROJ →] GET subtree')
 b = s.index('void RegisterLanceOptimizer')
 NEW_TAIL = '''		// Replace the [FILTER ->] [PROJ ->] GET chain below the sort (below the key projection when there is one)
