@@ -152,3 +152,155 @@ void LanceIndex::CreateAnnIndex(int32_t num_partitions, int32_t num_sub_vectors)
 
 	is_dirty_ = false;"""),
 ])
+
+# ---------------------------------------------------------------- lance_search.cpp
+# lance_search keeps its four positional arguments and its (row_id, distance) schema; optional named parameter
+# `prefilter` (a predicate over the index's extra columns, same grammar as the optimizer's pushdown).  New:
+# lance_search_batch(table, index, LIST(LIST(FLOAT)), k [, prefilter := ..]) -> (query_idx, row_id, distance):
+# the whole batch is one FFI call (LanceIndex::SearchBatch -> lance_detached_search_batch_predicate).
+edit("lance_search.cpp", [
+    ("""	vector<float> query;
+	int32_t k;
+};""",
+     """	vector<float> query;
+	int32_t k;
+	string prefilter;
+	//! lance_search_batch: row-major queries [nq][dim]
+	int32_t nq = 0;
+	int32_t dim = 0;
+};"""),
+    ("""	vector<row_t> row_ids;
+	vector<float> distances;
+	idx_t position = 0;""",
+     """	vector<row_t> row_ids;
+	vector<float> distances;
+	vector<int32_t> query_idx; // lance_search_batch only
+	idx_t position = 0;"""),
+    ("""	bind_data->k = input.inputs[3].GetValue<int32_t>();
+
+	return_types.push_back(LogicalType::BIGINT);""",
+     """	bind_data->k = input.inputs[3].GetValue<int32_t>();
+	auto prefilter_entry = input.named_parameters.find("prefilter");
+	if (prefilter_entry != input.named_parameters.end() && !prefilter_entry->second.IsNull()) {
+		bind_data->prefilter = prefilter_entry->second.GetValue<string>();
+	}
+
+	return_types.push_back(LogicalType::BIGINT);"""),
+    ("""	    lance_idx.Search(bind.query.data(), static_cast<int32_t>(bind.query.size()), bind.k);""",
+     """	    lance_idx.Search(bind.query.data(), static_cast<int32_t>(bind.query.size()), bind.k, bind.prefilter);"""),
+])
+edit("lance_search.cpp", [
+    ("""void RegisterLanceSearchFunction(ExtensionLoader &loader) {""",
+     """// ========================================
+// lance_search_batch(table, index, [[..], [..], ..], k)
+// Returns (query_idx INTEGER, row_id BIGINT, distance FLOAT), query by query, ascending distance within a query
+// ========================================
+
+static unique_ptr<FunctionData> LanceSearchBatchBind(ClientContext &context, TableFunctionBindInput &input,
+                                                     vector<LogicalType> &return_types, vector<string> &names) {
+	auto bind_data = make_uniq<LanceSearchBindData>();
+	bind_data->table_name = input.inputs[0].GetValue<string>();
+	bind_data->index_name = input.inputs[1].GetValue<string>();
+
+	auto &queries = ListValue::GetChildren(input.inputs[2]);
+	bind_data->nq = static_cast<int32_t>(queries.size());
+	for (auto &query : queries) {
+		if (query.IsNull()) {
+			throw InvalidInputException("lance_search_batch: NULL query vector");
+		}
+		auto &children = ListValue::GetChildren(query);
+		if (bind_data->dim == 0) {
+			bind_data->dim = static_cast<int32_t>(children.size());
+		} else if (static_cast<int32_t>(children.size()) != bind_data->dim) {
+			throw InvalidInputException("lance_search_batch: all query vectors must have the same length");
+		}
+		for (auto &child : children) {
+			bind_data->query.push_back(child.GetValue<float>());
+		}
+	}
+	bind_data->k = input.inputs[3].GetValue<int32_t>();
+	auto prefilter_entry = input.named_parameters.find("prefilter");
+	if (prefilter_entry != input.named_parameters.end() && !prefilter_entry->second.IsNull()) {
+		bind_data->prefilter = prefilter_entry->second.GetValue<string>();
+	}
+
+	return_types.push_back(LogicalType::INTEGER);
+	return_types.push_back(LogicalType::BIGINT);
+	return_types.push_back(LogicalType::FLOAT);
+	names.push_back("query_idx");
+	names.push_back("row_id");
+	names.push_back("distance");
+	return std::move(bind_data);
+}
+
+static unique_ptr<GlobalTableFunctionState> LanceSearchBatchInit(ClientContext &context,
+                                                                 TableFunctionInitInput &input) {
+	auto state = make_uniq<LanceSearchState>();
+	auto &bind = input.bind_data->Cast<LanceSearchBindData>();
+
+	auto &catalog = Catalog::GetCatalog(context, "");
+	auto &table_entry = catalog.GetEntry<TableCatalogEntry>(context, DEFAULT_SCHEMA, bind.table_name);
+	auto &duck_table = table_entry.Cast<DuckTableEntry>();
+	auto &storage = duck_table.GetStorage();
+	auto &table_info = *storage.GetDataTableInfo();
+	auto &indexes = table_info.GetIndexes();
+
+	indexes.Bind(context, table_info, LanceIndex::TYPE_NAME);
+
+	auto index_ptr = indexes.Find(bind.index_name);
+	if (!index_ptr) {
+		throw InvalidInputException("Index '%s' not found on table '%s'", bind.index_name, bind.table_name);
+	}
+
+	auto &lance_idx = index_ptr->Cast<LanceIndex>();
+	auto results = lance_idx.SearchBatch(bind.query.data(), bind.nq, bind.dim, bind.k, bind.prefilter);
+
+	for (idx_t q = 0; q < results.size(); q++) {
+		for (auto &result : results[q]) {
+			state->query_idx.push_back(static_cast<int32_t>(q));
+			state->row_ids.push_back(result.first);
+			state->distances.push_back(result.second);
+		}
+	}
+
+	return std::move(state);
+}
+
+static void LanceSearchBatchScan(ClientContext &context, TableFunctionInput &data, DataChunk &output) {
+	auto &state = data.global_state->Cast<LanceSearchState>();
+
+	if (state.position >= state.row_ids.size()) {
+		output.SetCardinality(0);
+		return;
+	}
+
+	idx_t chunk_size = MinValue<idx_t>(STANDARD_VECTOR_SIZE, state.row_ids.size() - state.position);
+
+	auto query_data = FlatVector::GetData<int32_t>(output.data[0]);
+	auto rowid_data = FlatVector::GetData<int64_t>(output.data[1]);
+	auto dist_data = FlatVector::GetData<float>(output.data[2]);
+
+	for (idx_t i = 0; i < chunk_size; i++) {
+		query_data[i] = state.query_idx[state.position + i];
+		rowid_data[i] = state.row_ids[state.position + i];
+		dist_data[i] = state.distances[state.position + i];
+	}
+
+	state.position += chunk_size;
+	output.SetCardinality(chunk_size);
+}
+
+void RegisterLanceSearchFunction(ExtensionLoader &loader) {"""),
+    ("""	func.cardinality = LanceSearchCardinality;
+	loader.RegisterFunction(func);""",
+     """	func.cardinality = LanceSearchCardinality;
+	func.named_parameters["prefilter"] = LogicalType::VARCHAR;
+	loader.RegisterFunction(func);
+
+	TableFunction batch_func("lance_search_batch",
+	                         {LogicalType::VARCHAR, LogicalType::VARCHAR,
+	                          LogicalType::LIST(LogicalType::LIST(LogicalType::FLOAT)), LogicalType::INTEGER},
+	                         LanceSearchBatchScan, LanceSearchBatchBind, LanceSearchBatchInit);
+	batch_func.named_parameters["prefilter"] = LogicalType::VARCHAR;
+	loader.RegisterFunction(batch_func);"""),
+])
