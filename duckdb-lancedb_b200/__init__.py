@@ -84,6 +84,7 @@ SIGNATURES = {
     "lance_b200_set_column": (_i32, [_vp, _cp, _i32, _i64, _i64, _vp, _vp, _vp] + _ERR),
     "lance_b200_predicate_bitmap": (_i64, [_vp, _cp, _vp, _i64, _vp, _vp] + _ERR),
     "lance_b200_flat_search_noalloc": (_i32, [_i32, _vp, _i64, _i32, _i32, _vp, _i32, _i64, _vp, _i64, _vp, _vp, _vp, _vp] + _ERR),
+    "lance_b200_add_batch_labeled": (_i32, [_vp, _vp, _i64, _i32, _i64] + _ERR),
     "lance_detached_count": (_i64, [_vp] + _ERR),
     "lance_detached_delete": (_i32, [_vp, _i64] + _ERR),
     "lance_detached_delete_batch": (_i32, [_vp, _vp, _i32] + _ERR),
@@ -207,6 +208,12 @@ class LanceHandle:
         self._check(lib().lance_detached_add_batch(self._h, _ptr(v), v.shape[0], v.shape[1], _ptr(labels), self._err,
                                                    ERR_LEN), "add_batch")
         return labels
+
+    def add_batch_labeled(self, vectors, first_label: int):
+        """lance_b200_add_batch_labeled: rows with the caller's labels first_label .. first_label + n - 1."""
+        v = _f32(vectors)
+        self._check(lib().lance_b200_add_batch_labeled(self._h, _ptr(v), v.shape[0], v.shape[1], int(first_label), self._err,
+                                                       ERR_LEN), "add_batch")
 
     def add(self, vector) -> int:
         v = _f32(vector)

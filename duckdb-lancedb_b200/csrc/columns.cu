@@ -202,6 +202,23 @@ ColumnStore::Column &ColumnStore::define(const std::string &name, ColType type) 
 	return *cols_.back();
 }
 
+void ColumnStore::define_like(const ColumnStore &other) {
+	for (auto &oc : other.cols_) {
+		Column &c = define(oc->name, oc->type);
+		c.dict = oc->dict;
+		c.dict_index = oc->dict_index;
+	}
+}
+
+void ColumnStore::swap(ColumnStore &other) {
+	std::lock_guard<std::mutex> g(cache_mu_);
+	cols_.swap(other.cols_);
+	cache_.clear();
+	other.cache_.clear();
+	epoch_ = std::max(epoch_, other.epoch_) + 1;
+	other.epoch_ = epoch_;
+}
+
 void ColumnStore::grow(int64_t cap_rows, cudaStream_t s) {
 	for (auto &c : cols_) ensure_cap(*c, cap_rows, s);
 }

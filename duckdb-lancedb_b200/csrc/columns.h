@@ -112,6 +112,8 @@ public:
 	                 int value_width, const void *offsets, bool large_offsets, const uint8_t *valid_bits, int64_t off,
 	                 int64_t cap_rows, cudaStream_t s);
 	void grow(int64_t cap_rows, cudaStream_t s); // the vector table was reallocated / a column was just defined
+	void define_like(const ColumnStore &other); // same columns (names, types, dictionaries), no rows
+	void swap(ColumnStore &other);              // contents and cache; the epoch moves forward on both
 	void touch() { epoch_++; }                   // rows appended / merged / compacted
 	uint64_t epoch() const { return epoch_; }
 

@@ -170,6 +170,19 @@ int32_t lance_detached_create_scalar_index(void *handle, const char *column, con
 	})
 }
 
+int32_t lance_b200_add_batch_labeled(void *handle, const float *vectors, int64_t num, int32_t dim, int64_t first_label,
+                                     char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("add_batch failed: ", -1, {
+		if (dim != h->dim())
+			throw lb::Error("dimension mismatch: expected " + std::to_string(h->dim()) + ", got " + std::to_string(dim));
+		if (num < 0) throw lb::Error("negative count");
+		if (num > 0 && !vectors) throw lb::Error("null buffer");
+		h->add_host_labeled(vectors, num, first_label);
+		return 0;
+	})
+}
+
 int32_t lance_b200_set_column(void *handle, const char *name, int32_t type, int64_t first_label, int64_t count,
                               const void *values, const int64_t *offsets, const uint8_t *valid, char *err_buf,
                               int err_buf_len) {
@@ -289,9 +302,13 @@ int32_t lance_detached_create_hnsw_index(void *handle, int32_t, int32_t, char *e
 }
 
 int32_t lance_detached_compact(void *handle, char *err_buf, int err_buf_len) {
+	// rust_lib/src/ffi.rs:448-465 -> lance_manager.rs:553-566 (compact_files): tombstoned rows are dropped for good, the
+	// HBM they held is released, labels are kept
 	LB_HANDLE(-1)
-	(void)h;
-	return 0; // nothing to compact: one contiguous device store, tombstones are bits
+	LB_TRY("compact failed: ", -1, {
+		h->compact();
+		return 0;
+	})
 }
 
 int32_t lance_detached_get_vector(void *handle, int64_t label, float *out_vec, int32_t capacity, char *err_buf,

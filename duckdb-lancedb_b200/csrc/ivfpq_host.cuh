@@ -91,6 +91,13 @@ void Store::set_index(int P, int M, int64_t n_indexed, const float *centroids, c
                       const int64_t *part_offsets, const int64_t *row_ids, const uint8_t *codes) {
 	std::unique_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));
+	install_index_locked(P, M, n_indexed, centroids, codebook, part_offsets, row_ids, codes);
+}
+
+// row_ids are labels of the implicit numbering (label_base_ + row); on a store with explicit labels (compacted /
+// sharded) label_base_ is 0 and the exchange layout is in ROW numbers
+void Store::install_index_locked(int P, int M, int64_t n_indexed, const float *centroids, const float *codebook,
+                                 const int64_t *part_offsets, const int64_t *row_ids, const uint8_t *codes) {
 	check_shape(dim_, P, M);
 	if (n_indexed < 0 || n_indexed > n_rows_) throw Error("index covers more rows than the table holds");
 	if (part_offsets[0] != 0 || part_offsets[P] != n_indexed) throw Error("part_offsets must span [0, n_indexed]");
@@ -125,6 +132,37 @@ void Store::set_index(int P, int M, int64_t n_indexed, const float *centroids, c
 	finalize_index(*ix, ix->ex, label_base_, s, &l);
 	add_launches(l);
 	index_.reset(ix.release());
+}
+
+// The index restricted to the rows that survive a compaction, in the exchange layout with ROW numbers of the compacted
+// table (order inside a partition is kept).  Exclusive lock held; nothing is modified.
+void Store::extract_index_for_compaction(const std::vector<int64_t> &new_row_of, CompactedIndex &out) {
+	IvfPqIndexFull &ix = static_cast<IvfPqIndexFull &>(*index_);
+	out.present = true;
+	out.P = ix.P, out.M = ix.M;
+	out.centroids.resize((size_t)ix.P * ix.dim);
+	out.codebook.resize((size_t)ix.M * 256 * ix.dsub);
+	std::vector<int64_t> ids((size_t)ix.n_indexed);
+	std::vector<uint8_t> codes((size_t)ix.n_indexed * ix.M);
+	LB_CUDA(cudaMemcpy(out.centroids.data(), ix.centroids.p, out.centroids.size() * sizeof(float), cudaMemcpyDeviceToHost));
+	LB_CUDA(cudaMemcpy(out.codebook.data(), ix.codebook.p, out.codebook.size() * sizeof(float), cudaMemcpyDeviceToHost));
+	if (ix.n_indexed > 0) {
+		LB_CUDA(cudaMemcpy(ids.data(), ix.ex.row_ids.p, ids.size() * sizeof(int64_t), cudaMemcpyDeviceToHost));
+		LB_CUDA(cudaMemcpy(codes.data(), ix.ex.codes.p, codes.size(), cudaMemcpyDeviceToHost));
+	}
+	out.part_offsets.assign((size_t)ix.P + 1, 0);
+	out.row_ids.reserve(ids.size());
+	out.codes.reserve(codes.size());
+	for (int p = 0; p < ix.P; p++) {
+		for (int64_t i = ix.part_offsets[(size_t)p]; i < ix.part_offsets[(size_t)p + 1]; i++) {
+			const int64_t nr = new_row_of[(size_t)(ids[(size_t)i] - label_base_)];
+			if (nr < 0) continue;
+			out.row_ids.push_back(nr);
+			out.codes.insert(out.codes.end(), codes.begin() + (size_t)i * ix.M, codes.begin() + (size_t)(i + 1) * ix.M);
+		}
+		out.part_offsets[(size_t)p + 1] = (int64_t)out.row_ids.size();
+	}
+	out.n_indexed = (int64_t)out.row_ids.size();
 }
 
 void Store::get_index(lance_b200_ivfpq_info *info, float *centroids, float *codebook, int64_t *part_offsets,

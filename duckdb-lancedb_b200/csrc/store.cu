@@ -126,6 +126,7 @@ void Store::set_label_base(int64_t base) {
 	std::unique_lock<std::shared_mutex> lk(mu_);
 	if (n_rows_ != 0) throw Error("label base can only be set on an empty store");
 	label_base_ = base;
+	next_label_ = base;
 }
 
 void Store::ensure_capacity(int64_t rows) {
@@ -150,6 +151,15 @@ void Store::ensure_capacity(int64_t rows) {
 	std::swap(deleted_.bytes, nd.bytes);
 	cap_rows_ = ncap;
 	columns_.grow(ncap, copy_stream_);
+	if (explicit_labels_) {
+		DevBuf nl;
+		nl.alloc((size_t)ncap * sizeof(int64_t));
+		if (n_rows_ > 0)
+			LB_CUDA(cudaMemcpyAsync(nl.p, row_labels_.p, (size_t)n_rows_ * sizeof(int64_t), cudaMemcpyDeviceToDevice, copy_stream_));
+		LB_CUDA(cudaStreamSynchronize(copy_stream_));
+		std::swap(row_labels_.p, nl.p);
+		std::swap(row_labels_.bytes, nl.bytes);
+	}
 	deleted_host_.resize((size_t)(ncap / 32), 0u);
 	if (flat_gemm_) flat_gemm_->invalidate();
 }
@@ -163,12 +173,13 @@ void Store::reserve(int64_t rows) {
 int64_t Store::add_host(const float *vectors, int64_t num) {
 	std::unique_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));
-	if (num <= 0) return label_base_ + n_rows_;
+	if (num <= 0) return next_label_;
 	ensure_capacity(n_rows_ + num);
 	LB_CUDA(cudaMemcpyAsync(X_.as<float>() + (size_t)n_rows_ * dim_, vectors, (size_t)num * dim_ * sizeof(float),
 	                        cudaMemcpyHostToDevice, copy_stream_));
 	LB_CUDA(cudaStreamSynchronize(copy_stream_));
-	int64_t first = label_base_ + n_rows_;
+	const int64_t first = next_label_;
+	append_labels(first, num);
 	n_rows_ += num;
 	return first;
 }
@@ -176,12 +187,13 @@ int64_t Store::add_host(const float *vectors, int64_t num) {
 int64_t Store::add_device(const float *d_vectors, int64_t num, cudaStream_t s) {
 	std::unique_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));
-	if (num <= 0) return label_base_ + n_rows_;
+	if (num <= 0) return next_label_;
 	ensure_capacity(n_rows_ + num);
 	LB_CUDA(cudaMemcpyAsync(X_.as<float>() + (size_t)n_rows_ * dim_, d_vectors, (size_t)num * dim_ * sizeof(float),
 	                        cudaMemcpyDeviceToDevice, s));
 	LB_CUDA(cudaStreamSynchronize(s));
-	int64_t first = label_base_ + n_rows_;
+	const int64_t first = next_label_;
+	append_labels(first, num);
 	n_rows_ += num;
 	return first;
 }
@@ -193,7 +205,7 @@ void Store::delete_labels(const int64_t *labels, int count) {
 	std::vector<int64_t> rows;
 	rows.reserve(count);
 	for (int i = 0; i < count; i++) {
-		int64_t r = labels[i] - label_base_;
+		int64_t r = row_of_label(labels[i]);
 		if (r < 0 || r >= n_rows_) continue; // deleting an unknown label matches nothing (lance_manager.rs:461-471)
 		uint32_t &w = deleted_host_[(size_t)(r >> 5)];
 		uint32_t bit = 1u << (r & 31);
@@ -224,7 +236,7 @@ int64_t Store::rows() {
 void Store::get_vector(int64_t label, float *out) {
 	std::shared_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));
-	int64_t r = label - label_base_;
+	int64_t r = row_of_label(label);
 	if (r < 0 || r >= n_rows_ || ((deleted_host_[(size_t)(r >> 5)] >> (r & 31)) & 1u))
 		throw Error("label " + std::to_string(label) + " not found");
 	LB_CUDA(cudaMemcpy(out, X_.as<float>() + (size_t)r * dim_, (size_t)dim_ * sizeof(float), cudaMemcpyDeviceToHost));
@@ -246,7 +258,7 @@ int64_t Store::get_all(int64_t *out_labels, float *out_vectors) {
 				LB_CUDA(cudaMemcpy(out_vectors + (size_t)w * dim_, X_.as<float>() + (size_t)b * dim_,
 				                   (size_t)(r - b) * dim_ * sizeof(float), cudaMemcpyDeviceToHost));
 			if (out_labels)
-				for (int64_t i = b; i < r; i++) out_labels[w + (i - b)] = label_base_ + i;
+				for (int64_t i = b; i < r; i++) out_labels[w + (i - b)] = label_of_row(i);
 			w += r - b;
 		}
 	}
@@ -272,7 +284,7 @@ int Store::merge_from(Store &src, const int64_t *live_labels, int count, int64_t
 		LB_CUDA(cudaSetDevice(src.device_));
 		src_base = src.label_base_;
 		for (int i = 0; i < count; i++) {
-			const int64_t r = live_labels[i] - src_base;
+			const int64_t r = src.row_of_label(live_labels[i]);
 			if (r < 0 || r >= src.n_rows_ || ((src.deleted_host_[(size_t)(r >> 5)] >> (r & 31)) & 1u)) continue;
 			rows.push_back(r);
 		}
@@ -305,13 +317,17 @@ int Store::merge_from(Store &src, const int64_t *live_labels, int count, int64_t
 		std::shared_lock<std::shared_mutex> ls(src.mu_);
 		LB_CUDA(cudaSetDevice(device_));
 		int64_t lc = 0;
-		columns_.gather_from(src.columns_, d_rows.as<int64_t>(), m, first - label_base_, cap_rows_, copy_stream_, &lc);
+		columns_.gather_from(src.columns_, d_rows.as<int64_t>(), m, row_of_label(first), cap_rows_, copy_stream_, &lc);
 		add_launches(lc);
 	}
-	for (int64_t i = 0; i < m; i++) {
-		out_old[i] = src_base + rows[(size_t)i];
-		out_new[i] = first + i;
+	{
+		std::shared_lock<std::shared_mutex> ls(src.mu_);
+		for (int64_t i = 0; i < m; i++) {
+			out_old[i] = src.label_of_row(rows[(size_t)i]);
+			out_new[i] = first + i;
+		}
 	}
+	(void)src_base;
 	return (int)m;
 }
 
@@ -330,6 +346,19 @@ void Store::search_device(const float *d_queries, int nq, int k, int nprobes, in
 	// reuse it without a host synchronisation (growing a buffer frees the old one, which synchronises).
 	Workspace *ws = scratch_for(s);
 	std::lock_guard<std::mutex> wg(ws->mu);
+	if (explicit_labels_) {
+		// kernels work in ROW space: a caller's bitmap (by label) is translated, results are settled at once (a later
+		// search_finish would rewrite re-run queries in row space) and mapped row -> label before the call returns
+		defer = false;
+		if (d_allow) {
+			const size_t words = (size_t)((n_rows_ + 31) / 32);
+			ws->allow_rows.ensure(std::max<size_t>(words, 1) * sizeof(uint32_t));
+			launch_allow_by_row(d_allow, allow_bits, row_labels_.as<int64_t>(), n_rows_, ws->allow_rows.as<uint32_t>(), s);
+			add_launches(1);
+			d_allow = ws->allow_rows.as<uint32_t>();
+			allow_bits = n_rows_;
+		}
+	}
 	if (hints && !hints->q_uploaded) {
 		// the host call left the query on the host: only the flat single-query scan takes it from its launch parameters
 		// ... and the single-query IVF_PQ kernel, which decides for itself (ivfpq_search_locked): it uploads nothing when
@@ -347,6 +376,10 @@ void Store::search_device(const float *d_queries, int nq, int k, int nprobes, in
 		                    d_out_counts, *ws, s, nullptr, nullptr, nullptr, hints);
 	else
 		flat_search_locked(d_queries, nq, k, d_allow, allow_bits, d_out_labels, d_out_dist, d_out_counts, *ws, s, defer, hints);
+	if (explicit_labels_) {
+		launch_relabel(d_out_labels, (long long)nq * k, row_labels_.as<int64_t>(), n_rows_, s);
+		add_launches(1);
+	}
 	if (d_overflow) {
 		// number of queries whose result is not final until search_finish (0 on every path but a pending tcgen05 batch)
 		const uint32_t *t = (defer && flat_gemm_) ? flat_gemm_->pending_total(s) : nullptr;
@@ -417,7 +450,8 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 			return e ? atoi(e) != 0 : true;
 		}();
 		HostHints hints;
-		const bool single = zc_out && nq == 1;
+		// (explicit labels: the result is re-labelled after the search kernel, so no completion word from inside it)
+		const bool single = zc_out && nq == 1 && !explicit_labels_;
 		if (single) {
 			hints.h_queries = queries;
 			if (poll_mode) {
@@ -620,7 +654,7 @@ void Store::save() {
 	std::string path = dir_ + "/store.bin";
 	FILE *f = fopen((path + ".tmp").c_str(), "wb");
 	if (!f) throw Error("cannot write " + path);
-	int64_t hdr[8] = {dim_, metric_, n_rows_, n_deleted_, label_base_, index_ ? 1 : 0, columns_.empty() ? 0 : 1, 0};
+	int64_t hdr[8] = {dim_, metric_, n_rows_, n_deleted_, label_base_, index_ ? 1 : 0, columns_.empty() ? 0 : 1, explicit_labels_ ? 1 : 0};
 	bool ok = fwrite(MAGIC, 1, 8, f) == 8 && fwrite(hdr, sizeof(int64_t), 8, f) == 8;
 	size_t words = (size_t)((n_rows_ + 31) / 32);
 	ok = ok && fwrite(deleted_host_.data(), sizeof(uint32_t), words, f) == words;
@@ -639,6 +673,11 @@ void Store::save() {
 			fclose(f);
 			throw;
 		}
+	}
+	if (ok && explicit_labels_) {
+		int64_t lh[2] = {next_label_, n_rows_};
+		ok = fwrite(lh, sizeof(int64_t), 2, f) == 2 &&
+		     fwrite(row_labels_host_.data(), sizeof(int64_t), (size_t)n_rows_, f) == (size_t)n_rows_;
 	}
 	if (ok && !columns_.empty()) {
 		try {
@@ -706,7 +745,23 @@ Store *Store::open(const std::string &db_path, const std::string &table, const s
 		int64_t nd = 0;
 		for (size_t w = 0; w < words; w++) nd += __builtin_popcount(st->deleted_host_[w]);
 		st->n_deleted_ = nd;
+		st->next_label_ = st->label_base_ + n;
+		if (!v1 && hdr[7] != 0) st->explicit_labels_ = true; // the index installs in row space: decide before it loads
+		if (st->explicit_labels_) st->label_base_ = 0;
 		if (!v1 && hdr[5] != 0) st->load_index(f, path);
+		if (st->explicit_labels_) {
+			int64_t lh[2];
+			if (fread(lh, sizeof(int64_t), 2, f) != 2 || lh[1] != n) throw Error("corrupt label section: " + path);
+			st->row_labels_host_.resize((size_t)n);
+			if (fread(st->row_labels_host_.data(), sizeof(int64_t), (size_t)n, f) != (size_t)n) throw Error("truncated store: " + path);
+			for (int64_t i = 1; i < n; i++)
+				if (st->row_labels_host_[(size_t)i] <= st->row_labels_host_[(size_t)i - 1]) throw Error("corrupt label section: " + path);
+			if (n > 0 && lh[0] <= st->row_labels_host_[(size_t)n - 1]) throw Error("corrupt label section: " + path);
+			st->next_label_ = lh[0];
+			st->row_labels_.alloc((size_t)st->cap_rows_ * sizeof(int64_t));
+			if (n > 0)
+				LB_CUDA(cudaMemcpy(st->row_labels_.p, st->row_labels_host_.data(), (size_t)n * sizeof(int64_t), cudaMemcpyHostToDevice));
+		}
 		if (!v1 && hdr[6] != 0) st->columns_.load(f, path, n, st->cap_rows_, st->copy_stream_);
 	} catch (...) {
 		fclose(f);

@@ -39,6 +39,7 @@ struct DevBuf {
 struct Workspace {
 	cudaStream_t stream = nullptr; // owned (io workspaces only)
 	std::mutex mu;                 // held while work that uses the buffers is being enqueued
+	DevBuf allow_rows; // a caller's label-indexed prefilter translated to row space (explicit labels)
 	DevBuf q, allow, out_labels, out_dist, out_counts, work, work2, work3, work4;
 	DevBuf probe_mat; // batched IVF probe: (distance, partition) keys [queries][P]
 	DevBuf scan_hdr;  // persistent header of the flat scan (kernels.h SCAN_HDR_BYTES), all-ones between passes
@@ -69,6 +70,15 @@ struct HostHints {
 };
 
 struct IvfPqIndex; // ivfpq.h
+// an IVF_PQ index in its exchange layout on the host, restricted to the rows that survive a compaction
+struct CompactedIndex {
+	bool present = false;
+	int P = 0, M = 0;
+	int64_t n_indexed = 0;
+	std::vector<float> centroids, codebook;
+	std::vector<int64_t> part_offsets, row_ids;
+	std::vector<uint8_t> codes;
+};
 class FlatGemm;    // flat_gemm.h
 
 class Store {
@@ -85,6 +95,14 @@ public:
 	void reserve(int64_t rows);
 	int64_t add_host(const float *vectors, int64_t num);                    // returns first label
 	int64_t add_device(const float *d_vectors, int64_t num, cudaStream_t s); // returns first label
+	// Rows with caller-chosen labels first_label .. first_label + num - 1 (first_label >= every label handed out so far):
+	// what a sharded handle uses to place chunks of one global label sequence on several devices (store_labels.cu)
+	void add_host_labeled(const float *vectors, int64_t num, int64_t first_label);
+	// Drops the tombstoned rows for good (src/lance_index.cpp:728-751 Vacuum -> LanceDetachedCompact): vectors, extra
+	// columns and the IVF_PQ index are rewritten without them, labels are kept (they become explicit).  Returns the
+	// number of rows removed.
+	int64_t compact();
+	bool labels_explicit();
 	void delete_labels(const int64_t *labels, int count);
 	int64_t live_rows();
 	int64_t rows();
@@ -169,6 +187,20 @@ private:
 	int64_t n_rows_ = 0;
 	int64_t n_deleted_ = 0;
 	int64_t label_base_ = 0;
+	// Labels.  Implicit (default): label = label_base_ + row, nothing stored.  Explicit (after compact() or
+	// add_host_labeled with a gap): label_base_ is 0, every kernel works in ROW space and the API boundary translates —
+	// row_labels_ (device) / row_labels_host_ (ascending) give row -> label, a binary search gives label -> row.
+	bool explicit_labels_ = false;
+	int64_t next_label_ = 0; // the label the next appended row gets
+	DevBuf row_labels_;      // int64 [cap_rows_], explicit only
+	std::vector<int64_t> row_labels_host_;
+	void make_labels_explicit();                 // exclusive lock held
+	void append_labels(int64_t first, int64_t num); // exclusive lock held, capacity ensured, before n_rows_ grows
+	int64_t row_of_label(int64_t label) const;   // -1 when the label is not in the table (tombstoned rows still are)
+	int64_t label_of_row(int64_t row) const { return explicit_labels_ ? row_labels_host_[(size_t)row] : label_base_ + row; }
+	void extract_index_for_compaction(const std::vector<int64_t> &new_row_of, CompactedIndex &out); // ivfpq_host.cuh
+	void install_index_locked(int P, int M, int64_t n_indexed, const float *centroids, const float *codebook,
+	                          const int64_t *part_offsets, const int64_t *row_ids, const uint8_t *codes);
 	std::vector<uint32_t> deleted_host_; // mirror of the tombstones (count + save)
 	cudaStream_t copy_stream_ = nullptr;
 
@@ -194,6 +226,9 @@ private:
 	}
 };
 
+void launch_relabel(int64_t *labels, long long n, const int64_t *row_labels, long long n_rows, cudaStream_t s);   // store_labels.cu
+void launch_allow_by_row(const uint32_t *allow_by_label, long long allow_bits, const int64_t *row_labels, long long n_rows,
+                         uint32_t *out, cudaStream_t s);
 int arrow_schema_vector_dim(void *arrow_schema); // store_columns.cu: dimension of the FixedSizeList<float> child; throws
 int default_device();
 void set_default_device(int d);

@@ -111,8 +111,9 @@ void Store::set_column(const std::string &name, ColType type, int64_t first_labe
                        const int64_t *offsets, const uint8_t *valid) {
 	std::unique_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));
-	const int64_t first = first_label - label_base_;
-	if (count < 0 || first < 0 || first + count > n_rows_)
+	const int64_t first = count > 0 ? row_of_label(first_label) : 0;
+	// the labels of the range must sit in consecutive rows (true for rows as they were appended)
+	if (count < 0 || first < 0 || first + count > n_rows_ || (count > 0 && label_of_row(first + count - 1) != first_label + count - 1))
 		throw Error("column values for labels [" + std::to_string(first_label) + ", " + std::to_string(first_label + count) +
 		            ") fall outside the table");
 	if (count == 0) {
@@ -181,9 +182,9 @@ int64_t Store::add_arrow(void *arrow_schema, void *arrow_array, int64_t *out_cou
 		const uint8_t *vbits = (c->null_count != 0 && c->buffers[0]) ? static_cast<const uint8_t *>(c->buffers[0]) : nullptr;
 		const char *nm = s->children[i]->name ? s->children[i]->name : "";
 		if (t.type == COL_STR)
-			columns_.write_arrow(nm, t.type, first - label_base_, n, c->buffers[2], 1, c->buffers[1], t.large, vbits, off, cap_rows_, copy_stream_);
+			columns_.write_arrow(nm, t.type, row_of_label(first), n, c->buffers[2], 1, c->buffers[1], t.large, vbits, off, cap_rows_, copy_stream_);
 		else
-			columns_.write_arrow(nm, t.type, first - label_base_, n, c->buffers[1], t.width, nullptr, false, vbits, off, cap_rows_, copy_stream_);
+			columns_.write_arrow(nm, t.type, row_of_label(first), n, c->buffers[1], t.width, nullptr, false, vbits, off, cap_rows_, copy_stream_);
 	}
 	return first;
 }

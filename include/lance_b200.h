@@ -266,6 +266,14 @@ int64_t lance_b200_predicate_bitmap(void *handle, const char *predicate, uint32_
                                     const uint32_t **out_device_bitmap, int32_t *out_was_cached, char *err_buf,
                                     int err_buf_len);
 
+/* Appends `num` rows that carry the caller's labels first_label .. first_label + num - 1 (first_label must not be
+ * below any label handed out so far).  A store whose labels stop being consecutive keeps them explicitly (8 B per row
+ * on the device and on the host); results, deletes, bitmaps and columns keep speaking labels.  This is how one global
+ * label sequence (rust_lib/src/lance_manager.rs:214, 232: an atomic counter) is spread over several device stores by
+ * lance_b200_create_sharded.  Returns 0 or -1. */
+int32_t lance_b200_add_batch_labeled(void *handle, const float *vectors, int64_t num, int32_t dim, int64_t first_label,
+                                     char *err_buf, int err_buf_len);
+
 /* ---------------------------------------------------------------- allocation-free flat search
  * No counterpart in the reference: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Exact flat top-k of ONE
