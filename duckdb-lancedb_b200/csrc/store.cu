@@ -334,7 +334,7 @@ int Store::merge_from(Store &src, const int64_t *live_labels, int count, int64_t
 // ------------------------------------------------------------------ search
 void Store::search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
                           int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
-                          cudaStream_t s, bool defer, uint32_t *d_overflow, HostHints *hints) {
+                          cudaStream_t s, bool defer, uint32_t *d_overflow, HostHints *hints, bool allow_in_row_space) {
 	std::shared_lock<std::shared_mutex> lk(mu_);
 	LB_CUDA(cudaSetDevice(device_));
 	if (nq <= 0) return;
@@ -350,7 +350,7 @@ void Store::search_device(const float *d_queries, int nq, int k, int nprobes, in
 		// kernels work in ROW space: a caller's bitmap (by label) is translated, results are settled at once (a later
 		// search_finish would rewrite re-run queries in row space) and mapped row -> label before the call returns
 		defer = false;
-		if (d_allow) {
+		if (d_allow && !allow_in_row_space) {
 			const size_t words = (size_t)((n_rows_ + 31) / 32);
 			ws->allow_rows.ensure(std::max<size_t>(words, 1) * sizeof(uint32_t));
 			launch_allow_by_row(d_allow, allow_bits, row_labels_.as<int64_t>(), n_rows_, ws->allow_rows.as<uint32_t>(), s);
@@ -492,7 +492,7 @@ void Store::search_host(const float *queries, int nq, int k, int nprobes, int re
 			d_allow = io->allow.as<uint32_t>();
 		}
 		search_device(d_q, nq, k, nprobes, refine, d_allow, allow_bits, d_labels, d_dist, d_counts, s, false, nullptr,
-		              single ? &hints : nullptr);
+		              single ? &hints : nullptr, resident != nullptr);
 		if (staged) {
 			if (!zc_out) LB_CUDA(cudaMemcpyAsync(hs + qoff, d_labels, lb + db + cb, cudaMemcpyDeviceToHost, s));
 			if (hints.armed) {

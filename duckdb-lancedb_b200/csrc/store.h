@@ -135,7 +135,8 @@ public:
 	// everything on the device, enqueued on s
 	void search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,
 	                   int64_t allow_bits, int64_t *d_out_labels, float *d_out_dist, int32_t *d_out_counts,
-	                   cudaStream_t s, bool defer = false, uint32_t *d_overflow = nullptr, HostHints *hints = nullptr);
+	                   cudaStream_t s, bool defer = false, uint32_t *d_overflow = nullptr, HostHints *hints = nullptr,
+	                   bool allow_in_row_space = false); // true: d_allow is indexed by row (a predicate bitmap), not by label
 	int search_finish(cudaStream_t s);
 
 	// IVF_PQ (ivfpq.cu)
