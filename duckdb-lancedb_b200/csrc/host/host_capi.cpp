@@ -111,6 +111,12 @@ int32_t lbh_index_delete(void *index, const int64_t *row_ids, int64_t count, cha
 		return 0;
 	})
 }
+int32_t lbh_index_vacuum(void *index, char *err_buf, int err_buf_len) {
+	HTRY(-1, {
+		static_cast<LanceIndex *>(index)->Vacuum();
+		return 0;
+	})
+}
 int32_t lbh_index_merge(void *index, void *other, char *err_buf, int err_buf_len) {
 	HTRY(-1, { return static_cast<LanceIndex *>(index)->MergeIndexes(*static_cast<LanceIndex *>(other)); })
 }

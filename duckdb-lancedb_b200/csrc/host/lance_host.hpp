@@ -106,6 +106,10 @@ public:
 	void Append(const float *vectors, int64_t count, const row_t *row_ids);
 	// Delete (src/lance_index.cpp:389-425): unknown row ids are ignored
 	void Delete(const row_t *row_ids, int64_t count);
+	// Vacuum (src/lance_index.cpp:728-751): LanceDetachedCompact when deletes are pending, then the forward map is
+	// rebuilt from the reverse one
+	void Vacuum();
+	bool HasPendingDeletes() const { return has_pending_deletes_; }
 	// ANN search (src/lance_index.cpp:442-465): dimension mismatch -> empty result (lance_basic.test:55-59);
 	// labels outside label_to_rowid_ are dropped; results ascending by distance.
 	std::vector<std::pair<row_t, float>> Search(const float *query, int32_t dimension, int32_t k,
@@ -137,6 +141,7 @@ private:
 	std::vector<row_t> label_to_rowid_;
 	std::unordered_map<row_t, int64_t> rowid_to_label_;
 	ColumnSet columns_;
+	bool has_pending_deletes_ = false;
 	// rows of every extra column already pushed to the device store (lance_b200_set_column); the predicate string
 	// itself goes through the FFI as in the reference and is evaluated (and cached) on the device
 	std::map<std::string, int64_t> synced_rows_;

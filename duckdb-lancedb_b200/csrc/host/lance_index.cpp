@@ -178,7 +178,25 @@ void LanceIndex::Delete(const row_t *row_ids, int64_t count) {
 		if (it->second >= 0 && (size_t)it->second < label_to_rowid_.size()) label_to_rowid_[(size_t)it->second] = (row_t)-1;
 		rowid_to_label_.erase(it);
 	}
-	if (!labels.empty()) LanceDetachedDeleteBatch(rust_handle_, labels.data(), (int32_t)labels.size());
+	if (!labels.empty()) {
+		LanceDetachedDeleteBatch(rust_handle_, labels.data(), (int32_t)labels.size());
+		has_pending_deletes_ = true; // :419-421
+	}
+}
+
+// src/lance_index.cpp:728-751: compact the backing store, then rebuild label_to_rowid_ from the authoritative
+// rowid_to_label_ map (drops the dead slots at its tail; labels themselves never change)
+void LanceIndex::Vacuum() {
+	if (!has_pending_deletes_ || !rust_handle_) return;
+	LanceDetachedCompact(rust_handle_);
+	has_pending_deletes_ = false;
+	std::vector<row_t> new_map;
+	for (auto &kv : rowid_to_label_) {
+		if (kv.second < 0) continue;
+		if ((size_t)kv.second >= new_map.size()) new_map.resize((size_t)kv.second + 1, (row_t)-1);
+		new_map[(size_t)kv.second] = kv.first;
+	}
+	label_to_rowid_ = std::move(new_map);
 }
 
 static void AppendColumnValue(Column &dst, const Column *src, size_t at) {

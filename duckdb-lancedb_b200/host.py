@@ -32,6 +32,7 @@ HOST_SIGNATURES = {
     "lbh_index_columns": (_vp, [_vp]),
     "lbh_index_append": (_i32, [_vp, _vp, _i64, _vp] + _ERR),
     "lbh_index_delete": (_i32, [_vp, _vp, _i64] + _ERR),
+    "lbh_index_vacuum": (_i32, [_vp] + _ERR),
     "lbh_index_merge": (_i32, [_vp, _vp] + _ERR),
     "lbh_index_count": (_i64, [_vp] + _ERR),
     "lbh_index_create_ann": (_i32, [_vp, _i32, _i32] + _ERR),
@@ -151,6 +152,9 @@ class HostIndex:
     def delete(self, row_ids):
         r = np.ascontiguousarray(row_ids, np.int64)
         self._check(lib().lbh_index_delete(self._h, _p(r), r.shape[0], self._err, ERR_LEN))
+
+    def vacuum(self):
+        self._check(lib().lbh_index_vacuum(self._h, self._err, ERR_LEN))
 
     def merge_indexes(self, other) -> int:
         """LanceIndex::MergeIndexes (src/lance_index.cpp:624-668): the live rows of `other` move into this index."""

@@ -36,6 +36,8 @@ void lbh_index_free(void *index);
 void *lbh_index_columns(void *index);
 int32_t lbh_index_append(void *index, const float *vectors, int64_t count, const int64_t *row_ids, char *err_buf, int err_buf_len);
 int32_t lbh_index_delete(void *index, const int64_t *row_ids, int64_t count, char *err_buf, int err_buf_len);
+/* LanceIndex::Vacuum (src/lance_index.cpp:728-751) */
+int32_t lbh_index_vacuum(void *index, char *err_buf, int err_buf_len);
 /* LanceIndex::MergeIndexes (src/lance_index.cpp:624-668): live rows of `other` into `index`; returns the merged count */
 int32_t lbh_index_merge(void *index, void *other, char *err_buf, int err_buf_len);
 int64_t lbh_index_count(void *index, char *err_buf, int err_buf_len);

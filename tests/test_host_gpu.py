@@ -188,3 +188,36 @@ def test_merge_indexes_moves_live_rows_and_their_columns(gpu, host, oracle_mod):
         # merging an index without live rows is a no-op
         with host.HostIndex(d, "l2") as ie:
             assert ia.merge_indexes(ie) == 0
+
+
+def test_vacuum_compacts_the_device_store_and_keeps_row_ids(gpu, host, oracle_mod):
+    """LanceIndex::Vacuum (src/lance_index.cpp:728-751): after deletes, the rows are dropped from HBM for good and
+    searches, filtered searches and later appends still speak the table's row ids."""
+    rng = np.random.default_rng(51)
+    n, d, k = 4000, 16, 8
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    row_ids = np.arange(n, dtype=np.int64) * 3 + 7
+    score = rng.integers(0, 100, n)
+    with host.HostIndex(d, "l2") as ix:
+        ix.append(X, row_ids)
+        ix.columns.append("score", [int(v) for v in score])
+        dead = np.sort(rng.choice(n, 1500, replace=False))
+        ix.delete(row_ids[dead])
+        keep = np.setdiff1d(np.arange(n), dead)
+        q = rng.standard_normal(d).astype(np.float32)
+        before, bd = ix.search(q, k)
+        fb, _ = ix.search(q, k, "score < 40")
+        ix.vacuum()
+        assert ix.count() == len(keep)
+        after, ad = ix.search(q, k)
+        assert np.array_equal(after, before) and np.allclose(ad, bd, rtol=1e-6)
+        wl, _, _ = oracle_mod.flat_search(X[keep], q, k, "l2")
+        assert np.array_equal(after, row_ids[keep[wl]])
+        fa, _ = ix.search(q, k, "score < 40")
+        assert np.array_equal(fa, fb) and (score[(fa - 7) // 3] < 40).all()
+        more = rng.standard_normal((5, d)).astype(np.float32)
+        ix.append(more, np.arange(5, dtype=np.int64) + 10**6)
+        ix.columns.append("score", [1] * 5)
+        got, _ = ix.search(more[2], 1)
+        assert got[0] == 10**6 + 2
+        ix.vacuum()  # nothing pending: a no-op
