@@ -85,6 +85,8 @@ SIGNATURES = {
     "lance_b200_predicate_bitmap": (_i64, [_vp, _cp, _vp, _i64, _vp, _vp] + _ERR),
     "lance_b200_flat_search_noalloc": (_i32, [_i32, _vp, _i64, _i32, _i32, _vp, _i32, _i64, _vp, _i64, _vp, _vp, _vp, _vp] + _ERR),
     "lance_b200_add_batch_labeled": (_i32, [_vp, _vp, _i64, _i32, _i64] + _ERR),
+    "lance_b200_create_sharded": (_vp, [_vp, _i32, _i32, _cp] + _ERR),
+    "lance_b200_sharded_rows": (_i32, [_vp, _vp, _i32]),
     "lance_detached_count": (_i64, [_vp] + _ERR),
     "lance_detached_delete": (_i32, [_vp, _i64] + _ERR),
     "lance_detached_delete_batch": (_i32, [_vp, _vp, _i32] + _ERR),
@@ -180,6 +182,23 @@ class LanceHandle:
         if not h:
             raise LanceError("Lance open: " + err.value.decode())
         return cls(0, metric, _raw=h)
+
+    @classmethod
+    def create_sharded(cls, devices, dimension: int, metric: str = "l2"):
+        """lance_b200_create_sharded: one handle over several devices of the box, same calls as a plain handle."""
+        err = C.create_string_buffer(ERR_LEN)
+        dv = np.ascontiguousarray(devices, np.int32)
+        h = lib().lance_b200_create_sharded(_ptr(dv), dv.shape[0], int(dimension), metric.encode(), err, ERR_LEN)
+        if not h:
+            raise LanceError("Lance create_sharded: " + err.value.decode())
+        return cls(0, metric, _raw=h)
+
+    def shard_rows(self) -> np.ndarray:
+        out = np.zeros(64, np.int64)
+        n = lib().lance_b200_sharded_rows(self._h, _ptr(out), 64)
+        if n < 0:
+            raise LanceError("not a sharded handle")
+        return out[:n].copy()
 
     def close(self):
         if getattr(self, "_h", None):

@@ -6,6 +6,7 @@
 #include <memory>
 #include <new>
 
+#include "sharded.h"
 #include "store.h"
 
 using lb::Store;
@@ -33,6 +34,10 @@ static std::string cstr(const char *s) { return s ? std::string(s) : std::string
 #define LB_HANDLE(fail_value)                               \
 	if (!handle) {                                          \
 		write_err(err_buf, err_buf_len, "null handle");     \
+		return fail_value;                                  \
+	}                                                       \
+	if (lb::as_sharded(handle)) {                           \
+		write_err(err_buf, err_buf_len, "not supported on a sharded handle"); \
 		return fail_value;                                  \
 	}                                                       \
 	Store *h = static_cast<Store *>(handle);
@@ -71,6 +76,11 @@ void *lance_open_detached(const char *db_path, const char *table_name, const cha
 void lance_free_detached(void *handle) {
 	if (!handle) return;
 	try {
+		if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+			lb::unregister_sharded(sh);
+			delete sh;
+			return;
+		}
 		delete static_cast<Store *>(handle);
 	} catch (...) {
 	}
@@ -80,15 +90,28 @@ int32_t lance_detached_has_extra_columns(void *handle) {
 	// rust_lib/src/ffi.rs:115-123
 	if (!handle) return 0;
 	try {
+		if (lb::ShardedStore *sh = lb::as_sharded(handle)) return sh->has_extra_columns() ? 1 : 0;
 		return static_cast<Store *>(handle)->has_extra_columns() ? 1 : 0;
 	} catch (...) {
 		return 0;
 	}
 }
 
-int32_t lance_detached_dimension(void *handle) { return handle ? static_cast<Store *>(handle)->dim() : 0; }
+int32_t lance_detached_dimension(void *handle) {
+	if (!handle) return 0;
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) return sh->dim();
+	return static_cast<Store *>(handle)->dim();
+}
 
 int64_t lance_detached_add(void *handle, const float *vector, int32_t dimension, char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("add failed: ", -1, {
+			if (dimension != sh->dim())
+				throw lb::Error("expected dimension " + std::to_string(sh->dim()) + ", got " + std::to_string(dimension));
+			return sh->add_host(vector, 1);
+		})
+	}
+
 	LB_HANDLE(-1)
 	LB_TRY("add failed: ", -1, {
 		if (dimension != h->dim())
@@ -99,6 +122,18 @@ int64_t lance_detached_add(void *handle, const float *vector, int32_t dimension,
 
 int32_t lance_detached_add_batch(void *handle, const float *vectors, int32_t num, int32_t dim, int64_t *out_labels,
                                  char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("add_batch failed: ", -1, {
+			if (dim != sh->dim())
+				throw lb::Error("expected dimension " + std::to_string(sh->dim()) + ", got " + std::to_string(dim));
+			if (num < 0) throw lb::Error("negative batch size");
+			const int64_t first = sh->add_host(vectors, num);
+			if (out_labels)
+				for (int32_t i = 0; i < num; i++) out_labels[i] = first + i;
+			return num;
+		})
+	}
+
 	LB_HANDLE(-1)
 	LB_TRY("add_batch failed: ", -1, {
 		if (dim != h->dim())
@@ -113,6 +148,17 @@ int32_t lance_detached_add_batch(void *handle, const float *vectors, int32_t num
 
 int32_t lance_detached_add_batch_arrow(void *handle, void *arrow_schema, void *arrow_array, int64_t *out_labels,
                                        char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("add_batch_arrow failed: ", -1, {
+			if (!arrow_schema || !arrow_array) throw lb::Error("null arrow schema/array");
+			int64_t n = 0;
+			const int64_t first = sh->add_arrow(arrow_schema, arrow_array, &n);
+			if (out_labels)
+				for (int64_t i = 0; i < n; i++) out_labels[i] = first + i;
+			return (int32_t)n;
+		})
+	}
+
 	// rust_lib/src/ffi.rs:148-182: consumes the array, borrows the schema, labels are consecutive
 	LB_HANDLE(-1)
 	if (!arrow_schema || !arrow_array) {
@@ -132,6 +178,18 @@ int32_t lance_detached_search_batch_predicate(void *handle, const float *queries
                                               int32_t nprobes, int32_t refine_factor, const char *predicate,
                                               int64_t *out_labels, float *out_distances, int32_t *out_counts,
                                               char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("search failed: ", -1, {
+			if (dim != sh->dim())
+				throw lb::Error("expected query dimension " + std::to_string(sh->dim()) + ", got " + std::to_string(dim));
+			if (nq < 0 || k < 0) throw lb::Error("negative batch size or k");
+			if (nq == 0) return 0;
+			if (!queries || !out_labels || !out_distances || !out_counts) throw lb::Error("null buffer");
+			sh->search_host(queries, nq, k, nprobes, refine_factor, nullptr, 0, predicate, out_labels, out_distances, out_counts);
+			return nq;
+		})
+	}
+
 	LB_HANDLE(-1)
 	LB_TRY("search failed: ", -1, {
 		if (dim != h->dim())
@@ -170,6 +228,28 @@ int32_t lance_detached_create_scalar_index(void *handle, const char *column, con
 	})
 }
 
+void *lance_b200_create_sharded(const int32_t *devices, int32_t n_devices, int32_t dimension, const char *metric,
+                                char *err_buf, int err_buf_len) {
+	LB_TRY("create_sharded failed: ", nullptr, {
+		if (!devices || n_devices <= 0) throw lb::Error("no devices given");
+		std::vector<int> dv(devices, devices + n_devices);
+		std::unique_ptr<lb::ShardedStore> sh(new lb::ShardedStore(dv, dimension, cstr(metric)));
+		lb::register_sharded(sh.get());
+		return sh.release();
+	})
+}
+
+int32_t lance_b200_sharded_rows(void *handle, int64_t *out_rows, int32_t capacity) {
+	lb::ShardedStore *sh = lb::as_sharded(handle);
+	if (!sh) return -1;
+	try {
+		for (int i = 0; i < sh->num_shards() && i < capacity; i++) out_rows[i] = sh->shard(i).rows();
+		return sh->num_shards();
+	} catch (...) {
+		return -1;
+	}
+}
+
 int32_t lance_b200_add_batch_labeled(void *handle, const float *vectors, int64_t num, int32_t dim, int64_t first_label,
                                      char *err_buf, int err_buf_len) {
 	LB_HANDLE(-1)
@@ -186,6 +266,14 @@ int32_t lance_b200_add_batch_labeled(void *handle, const float *vectors, int64_t
 int32_t lance_b200_set_column(void *handle, const char *name, int32_t type, int64_t first_label, int64_t count,
                               const void *values, const int64_t *offsets, const uint8_t *valid, char *err_buf,
                               int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("set_column failed: ", -1, {
+			if (type < 0 || type > lb::COL_STR) throw lb::Error("unknown column type");
+			sh->set_column(cstr(name), (lb::ColType)type, first_label, count, values, offsets, valid);
+			return 0;
+		})
+	}
+
 	LB_HANDLE(-1)
 	LB_TRY("set_column failed: ", -1, {
 		if (type < 0 || type > lb::COL_STR) throw lb::Error("unknown column type");
@@ -232,6 +320,19 @@ int32_t lance_detached_search_batch(void *handle, const float *queries, int32_t 
                                     int32_t nprobes, int32_t refine_factor, const uint32_t *allow_bitmap,
                                     int64_t bitmap_bits, int64_t *out_labels, float *out_distances,
                                     int32_t *out_counts, char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("search failed: ", -1, {
+			if (dim != sh->dim())
+				throw lb::Error("expected query dimension " + std::to_string(sh->dim()) + ", got " + std::to_string(dim));
+			if (nq < 0 || k < 0) throw lb::Error("negative batch size or k");
+			if (nq == 0) return 0;
+			if (!queries || !out_labels || !out_distances || !out_counts) throw lb::Error("null buffer");
+			sh->search_host(queries, nq, k, nprobes, refine_factor, allow_bitmap, bitmap_bits, nullptr, out_labels, out_distances,
+			                out_counts);
+			return nq;
+		})
+	}
+
 	LB_HANDLE(-1)
 	LB_TRY("search failed: ", -1, {
 		// rust_lib/src/lance_manager.rs:401-407
@@ -263,12 +364,26 @@ int32_t lance_detached_search(void *handle, const float *query, int32_t dim, int
 }
 
 int64_t lance_detached_count(void *handle, char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("count failed: ", -1, {
+			return sh->live_rows();
+		})
+	}
+
 	LB_HANDLE(-1)
 	LB_TRY("count failed: ", -1, { return h->live_rows(); })
 }
 
 int32_t lance_detached_delete_batch(void *handle, const int64_t *labels, int32_t count, char *err_buf,
                                     int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("delete failed: ", -1, {
+			if (count > 0 && !labels) throw lb::Error("null buffer");
+			sh->delete_labels(labels, count);
+			return 0;
+		})
+	}
+
 	LB_HANDLE(-1)
 	LB_TRY("delete_batch failed: ", -1, {
 		h->delete_labels(labels, count);
@@ -277,6 +392,7 @@ int32_t lance_detached_delete_batch(void *handle, const int64_t *labels, int32_t
 }
 
 int32_t lance_detached_delete(void *handle, int64_t label, char *err_buf, int err_buf_len) {
+	if (lb::as_sharded(handle)) return lance_detached_delete_batch(handle, &label, 1, err_buf, err_buf_len);
 	LB_HANDLE(-1)
 	LB_TRY("delete failed: ", -1, {
 		h->delete_labels(&label, 1);
@@ -302,6 +418,13 @@ int32_t lance_detached_create_hnsw_index(void *handle, int32_t, int32_t, char *e
 }
 
 int32_t lance_detached_compact(void *handle, char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("compact failed: ", -1, {
+			sh->compact();
+			return 0;
+		})
+	}
+
 	// rust_lib/src/ffi.rs:448-465 -> lance_manager.rs:553-566 (compact_files): tombstoned rows are dropped for good, the
 	// HBM they held is released, labels are kept
 	LB_HANDLE(-1)
@@ -313,6 +436,13 @@ int32_t lance_detached_compact(void *handle, char *err_buf, int err_buf_len) {
 
 int32_t lance_detached_get_vector(void *handle, int64_t label, float *out_vec, int32_t capacity, char *err_buf,
                                   int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("get_vector failed: ", -1, {
+			if (capacity < sh->dim()) throw lb::Error("output buffer too small");
+			sh->get_vector(label, out_vec);
+			return sh->dim();
+		})
+	}
 	LB_HANDLE(-1)
 	if (capacity < h->dim()) {
 		write_err(err_buf, err_buf_len, "output buffer too small");

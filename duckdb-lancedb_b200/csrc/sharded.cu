@@ -1,0 +1,274 @@
+// sharded.cu — see sharded.h.
+#include "sharded.h"
+
+#include <algorithm>
+#include <cmath>
+#include <shared_mutex>
+#include <unordered_set>
+
+namespace lb {
+
+static std::shared_mutex g_reg_mu;
+static std::unordered_set<void *> g_reg;
+
+ShardedStore *as_sharded(void *handle) {
+	std::shared_lock<std::shared_mutex> lk(g_reg_mu);
+	return g_reg.count(handle) ? static_cast<ShardedStore *>(handle) : nullptr;
+}
+void register_sharded(ShardedStore *s) {
+	std::unique_lock<std::shared_mutex> lk(g_reg_mu);
+	g_reg.insert(s);
+}
+void unregister_sharded(ShardedStore *s) {
+	std::unique_lock<std::shared_mutex> lk(g_reg_mu);
+	g_reg.erase(s);
+}
+
+ShardedStore::ShardedStore(const std::vector<int> &devices, int dim, const std::string &metric) : dim_(dim) {
+	if (devices.empty()) throw Error("a sharded handle needs at least one device");
+	int count = 0;
+	LB_CUDA(cudaGetDeviceCount(&count));
+	for (int d : devices)
+		if (d < 0 || d >= count) throw Error("device " + std::to_string(d) + " does not exist (" + std::to_string(count) + " visible)");
+	for (size_t i = 0; i < devices.size(); i++) {
+		shards_.emplace_back(new Store("", "shard" + std::to_string(i), dim, metric, devices[i]));
+		shards_.back()->force_explicit_labels();
+		workers_.emplace_back(new Worker());
+	}
+	for (size_t i = 0; i < workers_.size(); i++) {
+		Worker *w = workers_[i].get();
+		w->th = std::thread([w] {
+			std::unique_lock<std::mutex> lk(w->mu);
+			while (true) {
+				w->cv.wait(lk, [w] { return w->has_job || w->stop; });
+				if (w->stop) return;
+				std::function<void()> job = std::move(w->job);
+				w->has_job = false;
+				lk.unlock();
+				std::string err;
+				try {
+					job();
+				} catch (const std::exception &e) {
+					err = e.what();
+				} catch (...) {
+					err = "unknown error";
+				}
+				lk.lock();
+				w->error = err;
+				w->done = true;
+				w->cv.notify_all();
+			}
+		});
+	}
+}
+
+ShardedStore::~ShardedStore() {
+	for (auto &w : workers_) {
+		{
+			std::lock_guard<std::mutex> g(w->mu);
+			w->stop = true;
+		}
+		w->cv.notify_all();
+		if (w->th.joinable()) w->th.join();
+	}
+}
+
+void ShardedStore::run_on_all(const std::function<void(int)> &fn) {
+	for (size_t i = 0; i < workers_.size(); i++) {
+		Worker *w = workers_[i].get();
+		std::lock_guard<std::mutex> g(w->mu);
+		w->job = [&fn, i] { fn((int)i); };
+		w->has_job = true;
+		w->done = false;
+		w->error.clear();
+		w->cv.notify_all();
+	}
+	std::string first;
+	for (auto &w : workers_) {
+		std::unique_lock<std::mutex> lk(w->mu);
+		w->cv.wait(lk, [&w] { return w->done; });
+		if (first.empty() && !w->error.empty()) first = w->error;
+	}
+	if (!first.empty()) throw Error(first);
+}
+
+int ShardedStore::least_filled() {
+	int best = 0;
+	int64_t best_rows = -1;
+	for (size_t i = 0; i < shards_.size(); i++) {
+		const int64_t r = shards_[i]->rows();
+		if (best_rows < 0 || r < best_rows) best = (int)i, best_rows = r;
+	}
+	return best;
+}
+
+int ShardedStore::shard_of_label(int64_t label) {
+	auto it = std::upper_bound(chunk_first_.begin(), chunk_first_.end(), label);
+	if (it == chunk_first_.begin()) return -1;
+	return chunk_shard_[(size_t)(it - chunk_first_.begin()) - 1];
+}
+
+int64_t ShardedStore::add_host(const float *vectors, int64_t num) {
+	std::lock_guard<std::mutex> g(add_mu_);
+	const int64_t first = next_label_;
+	if (num <= 0) return first;
+	const int s = least_filled();
+	shards_[(size_t)s]->add_host_labeled(vectors, num, first);
+	chunk_first_.push_back(first);
+	chunk_shard_.push_back(s);
+	next_label_ += num;
+	return first;
+}
+
+int64_t ShardedStore::add_arrow(void *arrow_schema, void *arrow_array, int64_t *out_count) {
+	std::lock_guard<std::mutex> g(add_mu_);
+	const int s = least_filled();
+	int64_t n = 0;
+	const int64_t first = shards_[(size_t)s]->add_arrow(arrow_schema, arrow_array, &n, next_label_);
+	if (out_count) *out_count = n;
+	if (n > 0) {
+		chunk_first_.push_back(first);
+		chunk_shard_.push_back(s);
+		next_label_ += n;
+	}
+	return first;
+}
+
+void ShardedStore::define_columns_from_arrow(void *arrow_schema) {
+	for (auto &s : shards_) s->define_columns_from_arrow(arrow_schema);
+}
+
+void ShardedStore::set_column(const std::string &name, ColType type, int64_t first_label, int64_t count, const void *values,
+                              const int64_t *offsets, const uint8_t *valid) {
+	std::lock_guard<std::mutex> g(add_mu_);
+	// the range is cut at the boundaries of the appended batches; every piece goes to the shard that holds it
+	int64_t done = 0;
+	if (count == 0) {
+		for (auto &s : shards_) s->set_column(name, type, 0, 0, nullptr, nullptr, nullptr);
+		return;
+	}
+	while (done < count) {
+		const int64_t lab = first_label + done;
+		auto it = std::upper_bound(chunk_first_.begin(), chunk_first_.end(), lab);
+		if (it == chunk_first_.begin()) throw Error("column values for label " + std::to_string(lab) + " fall outside the table");
+		const size_t ci = (size_t)(it - chunk_first_.begin()) - 1;
+		const int64_t chunk_end = ci + 1 < chunk_first_.size() ? chunk_first_[ci + 1] : next_label_;
+		const int64_t piece = std::min(count - done, chunk_end - lab);
+		if (piece <= 0) throw Error("column values for label " + std::to_string(lab) + " fall outside the table");
+		const void *vals = values;
+		const int64_t *offs = offsets ? offsets + done : nullptr; // string offsets stay absolute into `values`
+		if (type == COL_I64 || type == COL_F64) vals = static_cast<const char *>(values) + (size_t)done * 8;
+		else if (type == COL_BOOL) vals = static_cast<const char *>(values) + (size_t)done;
+		shards_[(size_t)chunk_shard_[ci]]->set_column(name, type, lab, piece, vals, offs, valid ? valid + done : nullptr);
+		done += piece;
+	}
+}
+
+bool ShardedStore::has_extra_columns() {
+	for (auto &s : shards_)
+		if (s->has_extra_columns()) return true;
+	return false;
+}
+
+void ShardedStore::delete_labels(const int64_t *labels, int count) {
+	std::lock_guard<std::mutex> g(add_mu_);
+	std::vector<std::vector<int64_t>> per(shards_.size());
+	for (int i = 0; i < count; i++) {
+		const int s = shard_of_label(labels[i]);
+		if (s >= 0) per[(size_t)s].push_back(labels[i]);
+	}
+	for (size_t s = 0; s < shards_.size(); s++)
+		if (!per[s].empty()) shards_[s]->delete_labels(per[s].data(), (int)per[s].size());
+}
+
+int64_t ShardedStore::live_rows() {
+	int64_t n = 0;
+	for (auto &s : shards_) n += s->live_rows();
+	return n;
+}
+int64_t ShardedStore::rows() {
+	int64_t n = 0;
+	for (auto &s : shards_) n += s->rows();
+	return n;
+}
+
+void ShardedStore::get_vector(int64_t label, float *out) {
+	int s;
+	{
+		std::lock_guard<std::mutex> g(add_mu_);
+		s = shard_of_label(label);
+	}
+	if (s < 0) throw Error("label " + std::to_string(label) + " not found");
+	shards_[(size_t)s]->get_vector(label, out);
+}
+
+int64_t ShardedStore::compact() {
+	std::lock_guard<std::mutex> g(fan_mu_);
+	std::vector<int64_t> removed(shards_.size(), 0);
+	run_on_all([&](int s) { removed[(size_t)s] = shards_[(size_t)s]->compact(); });
+	int64_t n = 0;
+	for (auto r : removed) n += r;
+	return n;
+}
+
+void ShardedStore::search_host(const float *queries, int nq, int k, int nprobes, int refine, const uint32_t *allow,
+                               int64_t allow_bits, const char *predicate, int64_t *out_labels, float *out_dist,
+                               int32_t *out_counts) {
+	if (nq <= 0) return;
+	if (k <= 0) {
+		for (int i = 0; i < nq; i++) out_counts[i] = 0;
+		return;
+	}
+	std::lock_guard<std::mutex> g(fan_mu_);
+	const size_t G = shards_.size(), per = (size_t)nq * k;
+	stage_labels_.resize(G * per);
+	stage_dist_.resize(G * per);
+	stage_counts_.resize(G * (size_t)nq);
+	// every device searches its shard concurrently (one host thread per device issues and waits on that device's stream)
+	run_on_all([&](int s) {
+		Store &st = *shards_[(size_t)s];
+		int64_t *L = stage_labels_.data() + (size_t)s * per;
+		float *D = stage_dist_.data() + (size_t)s * per;
+		int32_t *C = stage_counts_.data() + (size_t)s * nq;
+		if (st.rows() == 0) {
+			std::fill(C, C + nq, 0);
+			return;
+		}
+		if (predicate && *predicate) st.search_host_predicate(queries, nq, k, nprobes, refine, predicate, L, D, C);
+		else st.search_host(queries, nq, k, nprobes, refine, allow, allow_bits, L, D, C);
+	});
+	// merge: per query a k-way merge of G ascending lists under (distance, label) — the order of make_key (common.cuh)
+	std::vector<int> pos(G);
+	for (int q = 0; q < nq; q++) {
+		std::fill(pos.begin(), pos.end(), 0);
+		int out = 0;
+		while (out < k) {
+			int best = -1;
+			u64 best_key = 0;
+			for (size_t s = 0; s < G; s++) {
+				if (pos[s] >= stage_counts_[s * (size_t)nq + q]) continue;
+				const size_t at = s * per + (size_t)q * k + (size_t)pos[s];
+				// labels of one table are far below 2^32 apart only by accident: compare (ordered distance, label) exactly
+				const u64 key_hi = (u64)float_to_ordered(stage_dist_[at]);
+				if (best < 0 || key_hi < (best_key >> 32) ||
+				    (key_hi == (best_key >> 32) && stage_labels_[at] < stage_labels_[(size_t)best * per + (size_t)q * k + (size_t)pos[(size_t)best]])) {
+					best = (int)s;
+					best_key = key_hi << 32;
+				}
+			}
+			if (best < 0) break;
+			const size_t at = (size_t)best * per + (size_t)q * k + (size_t)pos[(size_t)best];
+			out_labels[(size_t)q * k + out] = stage_labels_[at];
+			out_dist[(size_t)q * k + out] = stage_dist_[at];
+			pos[(size_t)best]++;
+			out++;
+		}
+		out_counts[q] = out;
+		for (int i = out; i < k; i++) {
+			out_labels[(size_t)q * k + i] = -1;
+			out_dist[(size_t)q * k + i] = INFINITY;
+		}
+	}
+}
+
+} // namespace lb

@@ -130,7 +130,9 @@ public:
 	bool column_info(int i, std::string *name, int32_t *type);
 	// Arrow C data interface ingest (rust_lib/src/ffi.rs:148-182): a struct array whose first FixedSizeList<float>
 	// child is the vector column and whose other children are extra columns; returns the first label
-	int64_t add_arrow(void *arrow_schema, void *arrow_array, int64_t *out_count);
+	// first_label >= 0: the rows take the caller's labels (sharded handles) instead of this store's counter
+	int64_t add_arrow(void *arrow_schema, void *arrow_array, int64_t *out_count, int64_t first_label = -1);
+	void force_explicit_labels(); // sharded handles: every shard speaks labels through its label array from the start
 	void define_columns_from_arrow(void *arrow_schema);
 	// everything on the device, enqueued on s
 	void search_device(const float *d_queries, int nq, int k, int nprobes, int refine, const uint32_t *d_allow,

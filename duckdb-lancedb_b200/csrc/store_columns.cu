@@ -139,7 +139,7 @@ void Store::define_columns_from_arrow(void *arrow_schema) {
 	columns_.grow(cap_rows_, copy_stream_);
 }
 
-int64_t Store::add_arrow(void *arrow_schema, void *arrow_array, int64_t *out_count) {
+int64_t Store::add_arrow(void *arrow_schema, void *arrow_array, int64_t *out_count, int64_t first_label) {
 	const ArrowSchema *s = static_cast<const ArrowSchema *>(arrow_schema);
 	ArrowArray *a = static_cast<ArrowArray *>(arrow_array);
 	struct Releaser { // the callee consumes the array (ffi.rs:148-182: "takes ownership of arrow_array")
@@ -169,7 +169,13 @@ int64_t Store::add_arrow(void *arrow_schema, void *arrow_array, int64_t *out_cou
 		if (!types[(size_t)i].ok) throw Error(bad_type(s->children[i]));
 		if (!c || c->length < n || c->n_buffers < (types[(size_t)i].type == COL_STR ? 3 : 2)) throw Error("malformed arrow column");
 	}
-	const int64_t first = add_host(vec, n);
+	int64_t first;
+	if (first_label >= 0) {
+		add_host_labeled(vec, n, first_label);
+		first = first_label;
+	} else {
+		first = add_host(vec, n);
+	}
 	if (out_count) *out_count = n;
 	if (n == 0) return first;
 	std::unique_lock<std::shared_mutex> lk(mu_);

@@ -66,6 +66,12 @@ bool Store::labels_explicit() {
 	return explicit_labels_;
 }
 
+void Store::force_explicit_labels() {
+	std::unique_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	make_labels_explicit();
+}
+
 void Store::make_labels_explicit() {
 	if (explicit_labels_) return;
 	if (index_ && label_base_ != 0) throw Error("cannot switch an indexed store with a label base to explicit labels");

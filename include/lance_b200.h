@@ -274,6 +274,20 @@ int64_t lance_b200_predicate_bitmap(void *handle, const char *predicate, uint32_
 int32_t lance_b200_add_batch_labeled(void *handle, const float *vectors, int64_t num, int32_t dim, int64_t first_label,
                                      char *err_buf, int err_buf_len);
 
+/* One handle over several GPUs of the box, in ONE process (the consumer is an embedded database — no
+ * launcher, no ranks).  devices[n_devices]: CUDA ordinals (a device may be named twice: two shards on it).  The
+ * returned handle is used with the SAME calls as a plain one — lance_detached_add / _add_batch / _add_batch_arrow,
+ * _search / _search_filtered / _search_batch / _search_predicate / _search_batch_predicate, _count, _delete /
+ * _delete_batch, _get_vector, _compact, _dimension, _has_extra_columns, lance_b200_set_column, lance_free_detached:
+ * whole appended batches go to the least-filled shard under one global label counter, a search runs on every device
+ * concurrently and the per-shard lists are merged under the library's (distance, label) order.  Index builds,
+ * persistence and the device-pointer entry points answer "not supported on a sharded handle".  NULL + message on
+ * failure. */
+void *lance_b200_create_sharded(const int32_t *devices, int32_t n_devices, int32_t dimension, const char *metric,
+                                char *err_buf, int err_buf_len);
+/* Rows held by each shard (out_rows[capacity]); returns the number of shards, -1 if `handle` is not sharded. */
+int32_t lance_b200_sharded_rows(void *handle, int64_t *out_rows, int32_t capacity);
+
 /* ---------------------------------------------------------------- allocation-free flat search
  * No counterpart in the reference: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Exact flat top-k of ONE
