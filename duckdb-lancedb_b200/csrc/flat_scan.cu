@@ -371,9 +371,13 @@ static void launch_scan1(const Scan1Params &p, int grid, size_t smem, cudaStream
 	// the kernel also has a few KB of static shared memory (radix-select histograms): raise the dynamic limit to what
 	// this launch needs, once per size
 	static std::mutex mu;
-	static size_t granted = 48 * 1024;
+	static size_t granted_by_device[64] = {0}; // the attribute is per device (in-process sharded handles)
 	{
 		std::lock_guard<std::mutex> g(mu);
+		int dev = 0;
+		LB_CUDA(cudaGetDevice(&dev));
+		size_t &granted = granted_by_device[dev & 63];
+		if (granted == 0) granted = 48 * 1024;
 		if (smem > granted) {
 			LB_CUDA(cudaFuncSetAttribute(flat_scan1_kernel<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 			granted = smem;

@@ -244,9 +244,13 @@ static void launch_adc(const AdcParams &ap, int nwarps, int S, int nq, size_t sm
 template <int NB>
 static void launch_ivfpq1(const Ivf1Params &p, int grid, size_t smem, cudaStream_t s) {
 	static std::mutex mu;
-	static size_t granted = 48 * 1024;
+	static size_t granted_by_device[64] = {0}; // the attribute is per device (in-process sharded handles)
 	{
 		std::lock_guard<std::mutex> g(mu);
+		int dev = 0;
+		LB_CUDA(cudaGetDevice(&dev));
+		size_t &granted = granted_by_device[dev & 63];
+		if (granted == 0) granted = 48 * 1024;
 		if (smem > granted) {
 			LB_CUDA(cudaFuncSetAttribute(ivfpq1_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 			granted = smem;
