@@ -447,21 +447,40 @@ void FlatGemm::rerun_flagged(const float *X, long long n, const uint32_t *delete
 	std::vector<uint32_t> hf(nq);
 	LB_CUDA(cudaMemcpyAsync(hf.data(), flag_out, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
 	LB_CUDA(cudaStreamSynchronize(s));
-	for (int q = 0; q < nq; q++) {
-		if (!hf[q]) continue;
-		FlatScanArgs a;
-		a.X = X, a.n = n, a.d = d, a.metric = im.metric;
-		a.dQ = Qchunk + (size_t)q * d;
-		a.nq = 1, a.k = k;
-		a.allow = d_allow, a.allow_bits = allow_bits, a.deleted = deleted, a.label_base = label_base;
-		a.out_labels = d_out_labels + (size_t)q * k;
-		a.out_dist = d_out_dist + (size_t)q * k;
-		a.out_counts = d_out_counts + q;
-		FlatScanPlan fp = plan_flat_scan(X, im.metric, d, k, 1, n, im.num_sms);
-		ws.work4.ensure(flat_scan_scratch_bytes(fp, k));
-		run_flat_scan(a, fp, ws.work4.p, s, launches);
-		(*fallback_queries)++;
+	std::vector<int> flagged;
+	for (int q = 0; q < nq; q++)
+		if (hf[q]) flagged.push_back(q);
+	if (flagged.empty()) return;
+	// The flagged queries are gathered and scanned TOGETHER (the exact scan takes four queries per pass over the table:
+	// a flagged batch costs ceil(m / 4) passes instead of m), all enqueued at once; results are scattered back.
+	const int m = (int)flagged.size();
+	const size_t qb = (size_t)m * d * sizeof(float), lb = (size_t)m * k * sizeof(int64_t), db = (size_t)m * k * sizeof(float);
+	const size_t off_l = (qb + 255) & ~(size_t)255, off_d = (off_l + lb + 255) & ~(size_t)255, off_c = (off_d + db + 255) & ~(size_t)255;
+	ws.rerun.ensure(off_c + (size_t)m * sizeof(int32_t));
+	char *base = static_cast<char *>(ws.rerun.p);
+	float *gq = reinterpret_cast<float *>(base);
+	int64_t *gl = reinterpret_cast<int64_t *>(base + off_l);
+	float *gd = reinterpret_cast<float *>(base + off_d);
+	int32_t *gc = reinterpret_cast<int32_t *>(base + off_c);
+	for (int i = 0; i < m; i++)
+		LB_CUDA(cudaMemcpyAsync(gq + (size_t)i * d, Qchunk + (size_t)flagged[(size_t)i] * d, (size_t)d * sizeof(float),
+		                        cudaMemcpyDeviceToDevice, s));
+	FlatScanArgs a;
+	a.X = X, a.n = n, a.d = d, a.metric = im.metric;
+	a.dQ = gq;
+	a.nq = m, a.k = k;
+	a.allow = d_allow, a.allow_bits = allow_bits, a.deleted = deleted, a.label_base = label_base;
+	a.out_labels = gl, a.out_dist = gd, a.out_counts = gc;
+	FlatScanPlan fp = plan_flat_scan(X, im.metric, d, k, m, n, im.num_sms);
+	ws.work4.ensure(flat_scan_scratch_bytes(fp, k));
+	run_flat_scan(a, fp, ws.work4.p, s, launches);
+	for (int i = 0; i < m; i++) {
+		const int q = flagged[(size_t)i];
+		LB_CUDA(cudaMemcpyAsync(d_out_labels + (size_t)q * k, gl + (size_t)i * k, (size_t)k * sizeof(int64_t), cudaMemcpyDeviceToDevice, s));
+		LB_CUDA(cudaMemcpyAsync(d_out_dist + (size_t)q * k, gd + (size_t)i * k, (size_t)k * sizeof(float), cudaMemcpyDeviceToDevice, s));
+		LB_CUDA(cudaMemcpyAsync(d_out_counts + q, gc + i, sizeof(int32_t), cudaMemcpyDeviceToDevice, s));
 	}
+	*fallback_queries += m;
 }
 
 // Completes the deferred overflow check of stream s: waits for the stream, and if some candidate list overflowed

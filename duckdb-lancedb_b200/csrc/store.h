@@ -39,6 +39,7 @@ struct DevBuf {
 struct Workspace {
 	cudaStream_t stream = nullptr; // owned (io workspaces only)
 	std::mutex mu;                 // held while work that uses the buffers is being enqueued
+	DevBuf rerun;      // gathered queries + results of the exact re-run of flagged tcgen05 queries (flat_gemm.cu)
 	DevBuf allow_rows; // a caller's label-indexed prefilter translated to row space (explicit labels)
 	DevBuf q, allow, out_labels, out_dist, out_counts, work, work2, work3, work4;
 	DevBuf probe_mat; // batched IVF probe: (distance, partition) keys [queries][P]
