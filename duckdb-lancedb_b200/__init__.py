@@ -85,6 +85,7 @@ SIGNATURES = {
     "lance_b200_predicate_bitmap": (_i64, [_vp, _cp, _vp, _i64, _vp, _vp] + _ERR),
     "lance_b200_flat_search_noalloc": (_i32, [_i32, _vp, _i64, _i32, _i32, _vp, _i32, _i64, _vp, _i64, _vp, _vp, _vp, _vp] + _ERR),
     "lance_b200_add_batch_labeled": (_i32, [_vp, _vp, _i64, _i32, _i64] + _ERR),
+    "lance_b200_add_batch_device_labels": (_i32, [_vp, _vp, _i64, _i32, _vp, _vp] + _ERR),
     "lance_b200_create_sharded": (_vp, [_vp, _i32, _i32, _cp] + _ERR),
     "lance_b200_sharded_rows": (_i32, [_vp, _vp, _i32]),
     "lance_detached_count": (_i64, [_vp] + _ERR),
@@ -233,6 +234,13 @@ class LanceHandle:
         v = _f32(vectors)
         self._check(lib().lance_b200_add_batch_labeled(self._h, _ptr(v), v.shape[0], v.shape[1], int(first_label), self._err,
                                                        ERR_LEN), "add_batch")
+
+    def add_batch_device_labels(self, dev_ptr: int, num: int, dim: int, labels, stream: int = 0):
+        """lance_b200_add_batch_device_labels: device rows with one (ascending) label each."""
+        l = np.ascontiguousarray(labels, np.int64)
+        assert l.shape[0] == num
+        self._check(lib().lance_b200_add_batch_device_labels(self._h, _ptr(dev_ptr), num, dim, _ptr(l),
+                                                             _ptr(stream) if stream else None, self._err, ERR_LEN), "add_batch")
 
     def add(self, vector) -> int:
         v = _f32(vector)

@@ -263,6 +263,19 @@ int32_t lance_b200_add_batch_labeled(void *handle, const float *vectors, int64_t
 	})
 }
 
+int32_t lance_b200_add_batch_device_labels(void *handle, const float *d_vectors, int64_t num, int32_t dim,
+                                           const int64_t *labels, void *stream, char *err_buf, int err_buf_len) {
+	LB_HANDLE(-1)
+	LB_TRY("add_batch failed: ", -1, {
+		if (dim != h->dim())
+			throw lb::Error("dimension mismatch: expected " + std::to_string(h->dim()) + ", got " + std::to_string(dim));
+		if (num < 0) throw lb::Error("negative count");
+		if (num > 0 && (!d_vectors || !labels)) throw lb::Error("null buffer");
+		h->add_device_with_labels(d_vectors, num, labels, static_cast<cudaStream_t>(stream));
+		return 0;
+	})
+}
+
 int32_t lance_b200_set_column(void *handle, const char *name, int32_t type, int64_t first_label, int64_t count,
                               const void *values, const int64_t *offsets, const uint8_t *valid, char *err_buf,
                               int err_buf_len) {

@@ -99,6 +99,9 @@ public:
 	// Rows with caller-chosen labels first_label .. first_label + num - 1 (first_label >= every label handed out so far):
 	// what a sharded handle uses to place chunks of one global label sequence on several devices (store_labels.cu)
 	void add_host_labeled(const float *vectors, int64_t num, int64_t first_label);
+	// device rows with an explicit, strictly ascending label per row (labels in host memory): what a partition-sharded
+	// IVF_PQ shard is loaded with (sharding.py)
+	void add_device_with_labels(const float *d_vectors, int64_t num, const int64_t *labels, cudaStream_t s);
 	// Drops the tombstoned rows for good (src/lance_index.cpp:728-751 Vacuum -> LanceDetachedCompact): vectors, extra
 	// columns and the IVF_PQ index are rewritten without them, labels are kept (they become explicit).  Returns the
 	// number of rows removed.

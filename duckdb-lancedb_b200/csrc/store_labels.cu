@@ -113,6 +113,25 @@ void Store::add_host_labeled(const float *vectors, int64_t num, int64_t first_la
 	n_rows_ += num;
 }
 
+void Store::add_device_with_labels(const float *d_vectors, int64_t num, const int64_t *labels, cudaStream_t s) {
+	std::unique_lock<std::shared_mutex> lk(mu_);
+	LB_CUDA(cudaSetDevice(device_));
+	if (num <= 0) return;
+	for (int64_t i = 0; i < num; i++)
+		if (labels[i] < (i ? labels[i - 1] + 1 : next_label_))
+			throw Error("labels must ascend strictly and start at or above " + std::to_string(next_label_));
+	make_labels_explicit();
+	ensure_capacity(n_rows_ + num);
+	LB_CUDA(cudaMemcpyAsync(X_.as<float>() + (size_t)n_rows_ * dim_, d_vectors, (size_t)num * dim_ * sizeof(float),
+	                        cudaMemcpyDeviceToDevice, s));
+	LB_CUDA(cudaStreamSynchronize(s));
+	row_labels_host_.resize((size_t)(n_rows_ + num));
+	std::copy(labels, labels + num, row_labels_host_.begin() + n_rows_);
+	LB_CUDA(cudaMemcpy(row_labels_.as<int64_t>() + n_rows_, labels, (size_t)num * sizeof(int64_t), cudaMemcpyHostToDevice));
+	next_label_ = labels[num - 1] + 1;
+	n_rows_ += num;
+}
+
 // ------------------------------------------------------------------------------------------------ compaction
 int64_t Store::compact() {
 	std::unique_lock<std::shared_mutex> lk(mu_);

@@ -104,3 +104,56 @@ class ShardedSearch:
         if g.rec.is_cuda:
             torch.cuda.current_stream().synchronize()
         return pending
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# IVF_PQ: shard BY PARTITION.  One global index (centroids and codebooks replicated, 13.4 MB at C3); the
+# inverted lists are dealt to the ranks whole, balanced by length, so every probed list is scanned on exactly one GPU.
+# Every rank probes the SAME nprobes partitions (same centroids, same arithmetic), scans the ones it owns (the others
+# are empty lists in its copy of the index) and refines with its own rows; the union of the ranks' candidates is the
+# one-GPU candidate set, so the merged top-k equals the one-GPU result.
+def assign_partitions(part_sizes, world: int):
+    """Longest-processing-time deal of the partitions to `world` ranks: -> owner[P] (int array)."""
+    import numpy as np
+
+    sizes = np.asarray(part_sizes, np.int64)
+    owner = np.zeros(sizes.shape[0], np.int32)
+    load = np.zeros(world, np.int64)
+    for p in np.argsort(-sizes, kind="stable"):
+        r = int(np.argmin(load))
+        owner[p] = r
+        load[r] += sizes[p]
+    return owner
+
+
+def ivfpq_partition_shard(pkg, index: dict, X_dev, rank: int, world: int, metric: str, stream: int = 0):
+    """Builds rank's shard handle from a global index in the exchange layout (`LanceHandle.get_ivfpq()` of a handle whose
+    label base is 0) and the device-resident table X_dev [rows, dim] (a torch tensor on this rank's device).
+    Returns (handle, owner): the handle holds only the rows of the partitions this rank owns, under their global
+    labels, and an index whose other partitions are empty."""
+    import numpy as np
+    import torch
+
+    off, ids, codes = index["part_offsets"], index["row_ids"], index["codes"]
+    P, dim = index["P"], index["dim"]
+    owner = assign_partitions(np.diff(off), world)
+    mine = np.flatnonzero(owner == rank)
+    seg = [np.arange(off[p], off[p + 1]) for p in mine]
+    pos = np.concatenate(seg) if seg else np.zeros(0, np.int64)  # positions in the exchange arrays, partition-major
+    labels = ids[pos]
+    order = np.argsort(labels, kind="stable")  # rows of the shard: ascending label
+    row_of_pos = np.empty_like(order)
+    row_of_pos[order] = np.arange(order.shape[0])
+    h = pkg.LanceHandle(dim, metric)
+    sorted_labels = labels[order]
+    if sorted_labels.shape[0]:
+        sel = torch.from_numpy(sorted_labels).to(X_dev.device)
+        step = 1 << 20
+        for lo in range(0, sel.shape[0], step):  # gather on the device, append with the global labels
+            rows = X_dev.index_select(0, sel[lo:lo + step]).contiguous()
+            h.add_batch_device_labels(rows.data_ptr(), rows.shape[0], dim, sorted_labels[lo:lo + step], stream)
+    sizes = np.where(owner == rank, np.diff(off), 0)
+    new_off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    # explicit labels: the exchange layout is in ROW numbers of the shard
+    h.set_ivfpq(index["centroids"], index["codebook"], new_off, row_of_pos.astype(np.int64), codes[pos])
+    return h, owner

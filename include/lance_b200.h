@@ -274,6 +274,12 @@ int64_t lance_b200_predicate_bitmap(void *handle, const char *predicate, uint32_
 int32_t lance_b200_add_batch_labeled(void *handle, const float *vectors, int64_t num, int32_t dim, int64_t first_label,
                                      char *err_buf, int err_buf_len);
 
+/* Device rows d_vectors[num][dim] with one label per row (labels[num] in HOST memory, strictly ascending, none below
+ * a label already handed out): how a partition-sharded IVF_PQ shard is loaded (duckdb-lancedb_b200/sharding.py).  On a
+ * store with explicit labels lance_b200_set_ivfpq / _get_ivfpq exchange ROW numbers, not labels.  Returns 0 or -1. */
+int32_t lance_b200_add_batch_device_labels(void *handle, const float *d_vectors, int64_t num, int32_t dim,
+                                           const int64_t *labels, void *stream, char *err_buf, int err_buf_len);
+
 /* One handle over several GPUs of the box, in ONE process (the consumer is an embedded database — no
  * launcher, no ranks).  devices[n_devices]: CUDA ordinals (a device may be named twice: two shards on it).  The
  * returned handle is used with the SAME calls as a plain one — lance_detached_add / _add_batch / _add_batch_arrow,
