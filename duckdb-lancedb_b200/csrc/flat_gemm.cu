@@ -68,6 +68,8 @@ static constexpr size_t TC_SMEM_MAX = 232448;
 struct FlatGemm::Impl {
 	int device, num_sms, dim, metric;
 	int Kreal16, Kpad, nkb, ksteps_last;
+	bool bias = false; // l2 on the K-streamed kernel: -|x|^2/2 is added in the epilogue from bias_buf (no extra K columns)
+	DevBuf bias_buf;   // fp32 [cap_rows + 256]
 	DevBuf shadow;   // bf16 [cap_rows][Kpad]
 	DevBuf max_norm; // one float (as bits)
 	long long rows_done = 0, cap_rows = 0;
@@ -111,8 +113,15 @@ struct FlatGemm::Impl {
 	}
 };
 
+static int gemm_variant_override();
+// l2 whose plain dimension lands on the K-streamed kernel (5..12 k-blocks) carries its -|x|^2/2 term in the epilogue
+static bool use_bias_epilogue(int dim, int metric) {
+	const int nkb_plain = (((dim + 15) & ~15) + 63) / 64;
+	return metric == METRIC_L2 && nkb_plain >= 5 && nkb_plain <= 12 && gemm_variant_override() != 1;
+}
+
 static void shape_for(int dim, int metric, int &Kreal16, int &Kpad, int &nkb, int &ksteps_last) {
-	int kr = metric == METRIC_L2 ? dim + 3 : dim;
+	int kr = (metric == METRIC_L2 && !use_bias_epilogue(dim, metric)) ? dim + 3 : dim;
 	Kreal16 = (kr + 15) & ~15;
 	Kpad = (Kreal16 + 63) & ~63;
 	nkb = Kpad / 64;
@@ -125,6 +134,7 @@ FlatGemm::FlatGemm(int device, int num_sms, int dim, int metric) : impl_(new Imp
 	impl_->dim = dim;
 	impl_->metric = metric;
 	shape_for(dim, metric, impl_->Kreal16, impl_->Kpad, impl_->nkb, impl_->ksteps_last);
+	impl_->bias = use_bias_epilogue(dim, metric);
 	impl_->max_norm.alloc(16); // [0] max |x| (float bits), [1] "a row with a non-finite norm exists"
 	LB_CUDA(cudaMemset(impl_->max_norm.p, 0, 16));
 	LB_CUDA(cudaEventCreateWithFlags(&impl_->shadow_ev, cudaEventDisableTiming));
@@ -155,6 +165,11 @@ void FlatGemm::sync_rows(const float *X, long long n, long long cap_rows, cudaSt
 	if (im.cap_rows < cap_rows || !im.shadow.p) {
 		// the store grew (and called invalidate()): rebuild the shadow at the new capacity
 		im.shadow.alloc((size_t)cap_rows * im.Kpad * 2 + 1024);
+		if (im.bias) {
+			// the epilogue reads whole 128-row tiles: rows beyond the table must hold finite values (zeros)
+			im.bias_buf.alloc(((size_t)cap_rows + 256) * sizeof(float));
+			LB_CUDA(cudaMemsetAsync(im.bias_buf.p, 0, im.bias_buf.bytes, s));
+		}
 		im.cap_rows = cap_rows;
 		im.rows_done = 0;
 		im.tmX_base = nullptr;
@@ -164,7 +179,8 @@ void FlatGemm::sync_rows(const float *X, long long n, long long cap_rows, cudaSt
 		long long cnt = n - im.rows_done;
 		shadow_rows_kernel<<<(unsigned)((cnt + 7) / 8), 256, 0, s>>>(X, im.rows_done, n, im.dim, im.metric, im.Kpad,
 		                                                             im.shadow.as<__nv_bfloat16>(),
-		                                                             im.max_norm.as<uint32_t>());
+		                                                             im.max_norm.as<uint32_t>(),
+		                                                             im.bias ? im.bias_buf.as<float>() : nullptr);
 		LB_CUDA(cudaGetLastError());
 		if (launches) (*launches)++;
 		im.rows_done = n;
@@ -272,6 +288,8 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
@@ -341,7 +359,8 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		const float *Qchunk = d_queries + (size_t)q0 * d;
 
 		prep_query_tiles_kernel<<<(nslots + 7) / 8, 256, 0, s>>>(Qchunk, nq, nslots, d, im.metric, Kpad,
-		                                                         im.max_norm.as<uint32_t>(), Qs, margin, thr, cnt, flag);
+		                                                         im.max_norm.as<uint32_t>(), Qs, margin, thr, cnt, flag,
+		                                                         im.bias ? 1 : 0);
 		LB_CUDA(cudaGetLastError());
 		(*launches)++;
 		CUtensorMap tmQ;
@@ -352,6 +371,8 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		p.n_rows = n, p.thr = thr, p.cnt = cnt, p.cand = cand, p.CAP = TC_CAP;
 		p.deleted = deleted, p.allow = d_allow, p.allow_bits = allow_bits;
 		p.Qs = Qs, p.Kpad = Kpad, p.EB = pl.EB;
+		p.bias = im.bias ? im.bias_buf.as<float>() : nullptr;
+		if (im.bias && !pl.tsk) throw Error("internal: the bias epilogue needs the K-streamed kernel");
 		static const int tsk_dbg = [] {
 			const char *e = getenv("LANCE_B200_TSK_DBG");
 			return e ? atoi(e) : 0;
@@ -372,7 +393,10 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 					at[0].id = cudaLaunchAttributeClusterDimension;
 					at[0].val.clusterDim.x = 2, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
 					cfg.attrs = at, cfg.numAttrs = 1;
-					LB_CUDA(cudaLaunchKernelEx(&cfg, flat_gemm_tsk_kernel<true>, im.tmX64, p));
+					if (im.bias) LB_CUDA(cudaLaunchKernelEx(&cfg, flat_gemm_tsk_kernel<true, true>, im.tmX64, p));
+					else LB_CUDA(cudaLaunchKernelEx(&cfg, flat_gemm_tsk_kernel<true>, im.tmX64, p));
+				} else if (im.bias) {
+					flat_gemm_tsk_kernel<false, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
 				} else {
 					flat_gemm_tsk_kernel<false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
 				}

@@ -27,7 +27,8 @@ static constexpr float GEMM_ACC_C = 3.6e-7f; // per accumulated term
 // zero padded to Kpad.  max_norm = max |x| over the converted rows (float bits, non-negative -> uint max).
 __global__ void __launch_bounds__(256) shadow_rows_kernel(const float *__restrict__ X, long long row_lo, long long row_hi,
                                                           int d, int metric, int Kpad, __nv_bfloat16 *__restrict__ Xs,
-                                                          uint32_t *__restrict__ max_norm_bits) {
+                                                          uint32_t *__restrict__ max_norm_bits,
+                                                          float *__restrict__ bias = nullptr) {
 	long long row = row_lo + (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if (row >= row_hi) return;
 	const unsigned lane = lane_id();
@@ -59,7 +60,9 @@ __global__ void __launch_bounds__(256) shadow_rows_kernel(const float *__restric
 	}
 	res2 = warp_sum(res2);
 	hat2 = warp_sum(hat2);
-	if (metric == METRIC_L2 && lane == 0) {
+	if (metric == METRIC_L2 && bias) {
+		if (lane == 0) bias[row] = -0.5f * s; // bias epilogue (K-streamed kernel): the term stays in fp32
+	} else if (metric == METRIC_L2 && lane == 0) {
 		float h = -0.5f * s;
 		__nv_bfloat16 h1 = __float2bfloat16_rn(h);
 		float r1 = h - __bfloat162float(h1);
@@ -91,7 +94,7 @@ __global__ void __launch_bounds__(256) prep_query_tiles_kernel(const float *__re
                                                                int metric, int Kpad, const uint32_t *__restrict__ max_norm_bits,
                                                                __nv_bfloat16 *__restrict__ Qs, float *__restrict__ margin,
                                                                float *__restrict__ thr, uint32_t *__restrict__ cnt,
-                                                               uint32_t *__restrict__ flag) {
+                                                               uint32_t *__restrict__ flag, int bias_mode = 0) {
 	int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if (q >= nslots) return;
 	const unsigned lane = lane_id();
@@ -100,7 +103,7 @@ __global__ void __launch_bounds__(256) prep_query_tiles_kernel(const float *__re
 	float s = 0.f, res2 = 0.f;
 	for (int i = lane; i < Kpad; i += 32) {
 		float v = (real && i < d) ? __ldg(Q + (size_t)q * d + i) : 0.f;
-		if (real && metric == METRIC_L2 && i >= d && i < d + 3) v = 1.0f; // exact in bf16: no residual
+		if (real && metric == METRIC_L2 && !bias_mode && i >= d && i < d + 3) v = 1.0f; // exact in bf16: no residual
 		else s = fmaf(v, v, s);
 		const __nv_bfloat16 b = __float2bfloat16_rn(v);
 		o[i] = b;
@@ -114,8 +117,10 @@ __global__ void __launch_bounds__(256) prep_query_tiles_kernel(const float *__re
 		const float rx = __uint_as_float(max_norm_bits[2]), xh = __uint_as_float(max_norm_bits[3]);
 		const float qn = sqrtf(s), rq = sqrtf(res2);
 		// full operand norms for the accumulation term: l2 rows carry -|x|^2/2, the query three ones
-		const float qfull = metric == METRIC_L2 ? sqrtf(s + 3.0f) : qn;
-		const float xfull = metric == METRIC_L2 ? sqrtf(xh * xh + 0.25f * xn * xn * xn * xn) * 1.01f : xh;
+		// (bias epilogue: the contraction is the plain inner product, the fp32 term adds one rounding of its own size)
+		const bool l2cols = metric == METRIC_L2 && !bias_mode;
+		const float qfull = l2cols ? sqrtf(s + 3.0f) : qn;
+		const float xfull = l2cols ? sqrtf(xh * xh + 0.25f * xn * xn * xn * xn) * 1.01f : xh;
 		const float err = 1.02f * (rq * xh + qn * rx) + GEMM_ACC_C * (float)Kpad * qfull * xfull + 1e-6f * (1.0f + xn * xn);
 		const float mg = 2.0f * err;
 		// a query (or table) whose bound is not finite cannot be certified: straight to the exact scan, emit nothing

@@ -38,6 +38,7 @@ struct GemmParams {
 	const void *Qs;          // bf16 [NG*QT*128][Kpad] query tiles in global memory (TMEM-resident variant)
 	int Kpad;
 	int EB;                  // per-(epilogue group, query) shared-memory emit buffer entries (0 = append directly)
+	const float *bias;       // K-streamed kernel, l2 with the bias epilogue: -|x|^2/2 per row (fp32), else null
 	int dbg;                 // LANCE_B200_TSK_DBG (ceiling experiments): 1 = epilogue drains but does not filter, 2 = X stages
 	                         // are loaded once and re-used (no TMA traffic), 4 = epilogue does not even read the accumulator
 };

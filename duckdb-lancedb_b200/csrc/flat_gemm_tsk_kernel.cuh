@@ -27,7 +27,10 @@ namespace lb {
 static constexpr int TSK_BN = GEMM_BN;                // rows of an X tile
 static constexpr int TSK_KB_BYTES = GEMM_KB_BYTES;    // one 64-wide k-block of a 128-row tile (16 KB)
 
-template <bool MC>
+// BIAS: the l2 score is <q, x> - |x|^2/2; instead of three extra bf16 K columns (which push D = 766..768 to a 13th
+// k-block that does not fit the 512 TMEM columns, and cost a 7th k-block at D = 384) the fp32 term is added to the
+// accumulator columns in the epilogue: 8 broadcast 128-bit loads + 32 adds per 32-column chunk, off the MMA's path.
+template <bool MC, bool BIAS = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p) {
 	extern __shared__ uint8_t smem_raw[];
@@ -198,6 +201,22 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 			tc::tc_fence_before();
 			__syncwarp();
 			if (lane == 0) tc::mbar_arrive(bar_tempty);
+			if (BIAS) {
+				// rows beyond the table read as zero scores + whatever the padded bias holds (0): they are filtered by row
+				const float4 *b4 = reinterpret_cast<const float4 *>(p.bias + row0);
+#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					const float4 ba = __ldg(b4 + j), bb = __ldg(b4 + 8 + j);
+					va[4 * j] = __float_as_uint(__uint_as_float(va[4 * j]) + ba.x);
+					va[4 * j + 1] = __float_as_uint(__uint_as_float(va[4 * j + 1]) + ba.y);
+					va[4 * j + 2] = __float_as_uint(__uint_as_float(va[4 * j + 2]) + ba.z);
+					va[4 * j + 3] = __float_as_uint(__uint_as_float(va[4 * j + 3]) + ba.w);
+					vb[4 * j] = __float_as_uint(__uint_as_float(vb[4 * j]) + bb.x);
+					vb[4 * j + 1] = __float_as_uint(__uint_as_float(vb[4 * j + 1]) + bb.y);
+					vb[4 * j + 2] = __float_as_uint(__uint_as_float(vb[4 * j + 2]) + bb.z);
+					vb[4 * j + 3] = __float_as_uint(__uint_as_float(vb[4 * j + 3]) + bb.w);
+				}
+			}
 			if (!(p.dbg & 5)) {
 				gemm_process_chunk_inline(p, va, thr, q, row0, eb);
 				gemm_process_chunk_inline(p, vb, thr, q, row0 + 32, eb);
