@@ -775,7 +775,8 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
         whole = ((ivf_query_bytes - shared) * B + shared) / step_s / 1e9
         roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
                 "step_achieved": whole, "step_frac": whole / peaks["hbm_gbs"],
-                "traffic": None, "kernel": "adc_scan_kernel (codes + row terms + ids of the probed lists + LUT)",
+                "traffic": None, "kernel": ("ivfpq1_kernel (one query: probe + lookup table + ADC scan + refine in one cooperative launch; bytes = the scan's)"
+                                           if B == 1 else "adc_scan_kernel (codes + row terms + ids of the probed lists + LUT)"),
                 "peak_source": peaks["source"], "avg_launch_ms": t * 1e3, "bytes_per_query_scan": adc_bytes,
                 "bytes_per_query_whole_search": ivf_query_bytes,
                 "step_bytes_note": "step level counts the whole search: per query scan bytes + refine rows, per batch centroid table + codebook"}
@@ -789,7 +790,8 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
         roof = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": a / peaks["hbm_gbs"],
                 "step_achieved": bytes_pass * launches_per_step / step_s / 1e9,
                 "step_frac": bytes_pass * launches_per_step / step_s / 1e9 / peaks["hbm_gbs"],
-                "traffic": None, "kernel": "flat_scan_kernel (fp32, <=4 queries per pass)", "peak_source": peaks["source"],
+                "traffic": None, "kernel": ("flat_scan1_kernel (fp32, one query: TMA-staged rows, register top-k)" if B == 1 and dim % 4 == 0
+                                           else "flat_scan_kernel (fp32, <=4 queries per pass)"), "peak_source": peaks["source"],
                 "launches_per_step": launches_per_step, "avg_launch_ms": t * 1e3, "selectivity": sel}
 
     if roof is not None:
