@@ -16,106 +16,127 @@ namespace lb {
 // validity word per warp.  HBM-bound: 8 B/row per distinct column the predicate names (C5: 80 MB for 10 M rows),
 // paid once per (predicate, epoch) — the result is cached on the device.
 __device__ __forceinline__ bool pred_cmp_i64(int cmp, long long a, long long b) {
-	switch (cmp) {
-	case CMP_EQ: return a == b;
-	case CMP_NE: return a != b;
-	case CMP_LT: return a < b;
-	case CMP_GT: return a > b;
-	case CMP_LE: return a <= b;
-	default: return a >= b;
-	}
+	return ((a < b ? 1 : (a > b ? 4 : 2)) & cmp) != 0;
 }
+// (a NaN is neither less nor greater: it lands on "equal", like the host mirror's evaluator)
 __device__ __forceinline__ bool pred_cmp_f64(int cmp, double a, double b) {
-	switch (cmp) {
-	case CMP_EQ: return a == b;
-	case CMP_NE: return a != b;
-	case CMP_LT: return a < b;
-	case CMP_GT: return a > b;
-	case CMP_LE: return a <= b;
-	default: return a >= b;
+	return ((a < b ? 1 : (a > b ? 4 : 2)) & cmp) != 0;
+}
+
+// PRED_U words (of 32 rows) per warp and iteration: the leaf loads of the PRED_U rows a thread owns are independent, so
+// every warp keeps PRED_U x 256 B in flight per column.
+static constexpr int PRED_U = 4;
+
+// A leaf in two phases, so that the PRED_U rows of a thread have all their loads in flight together: (1) the validity
+// word and the raw value are loaded unconditionally for rows inside the table (no load depends on another), (2) the
+// comparison runs on the loaded bits.
+__device__ __forceinline__ void pred_leaf_eval(const PredProgram &prog, const PredOp &o, bool in_range, uint32_t vword, int lane,
+                                               long long raw, bool &t, bool &f) {
+	t = false, f = false;
+	if (!in_range) return;
+	const bool valid = (vword >> lane) & 1u;
+	if (o.op == PRED_IS_NULL) {
+		t = !valid, f = valid;
+	} else if (o.op == PRED_NOT_NULL) {
+		t = valid, f = !valid;
+	} else if (valid) {
+		bool c = false, isnull = false;
+		if (o.op == PRED_CMP_I64) {
+			c = pred_cmp_i64(o.cmp, raw, o.ival);
+		} else if (o.op == PRED_CMP_F64) {
+			c = pred_cmp_f64(o.cmp, o.col_is_f64 ? __longlong_as_double(raw) : (double)raw, o.dval);
+		} else if (o.op == PRED_IN_I64) {
+			for (int j = 0; j < o.n_list; j++) c |= prog.aux_i64[o.aux_off + j] == raw;
+			isnull = !c && o.has_null;
+			if (o.negate) c = !c;
+		} else if (o.op == PRED_IN_F64) {
+			const double v = o.col_is_f64 ? __longlong_as_double(raw) : (double)raw;
+			for (int j = 0; j < o.n_list; j++) c |= prog.aux_f64[o.aux_off + j] == v;
+			isnull = !c && o.has_null;
+			if (o.negate) c = !c;
+		} else { // PRED_STR_LUT: raw = dictionary code
+			const uint8_t v = prog.aux_u8[o.aux_off + raw];
+			c = v == 1;
+			isnull = v == 2;
+		}
+		t = c && !isnull;
+		f = !c && !isnull;
 	}
 }
 
 __global__ void __launch_bounds__(256) eval_predicate_kernel(const __grid_constant__ PredProgram prog, long long n,
                                                               uint32_t *__restrict__ out, long long words) {
-	const long long word0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-	const long long wstride = (long long)gridDim.x * (blockDim.x >> 5);
+	const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
 	const int lane = threadIdx.x & 31;
-	for (long long w = word0; w < words; w += wstride) {
-		const long long r = w * 32 + lane;
-		const bool in_range = r < n;
-		uint32_t st = 0, sf = 0; // stack of (true, false) bits, bit i = depth i
+	for (long long wb = warp0 * PRED_U; wb < words; wb += nwarps * PRED_U) {
+		uint32_t st[PRED_U], sf[PRED_U]; // per row: stacks of (true, false) bits, bit i = depth i
+#pragma unroll
+		for (int u = 0; u < PRED_U; u++) st[u] = 0u, sf[u] = 0u;
 		int sp = 0;
 		for (int i = 0; i < prog.n_ops; i++) {
 			const PredOp &o = prog.ops[i];
-			if (o.op >= PRED_NOT) {
-				if (o.op == PRED_NOT) {
-					const uint32_t m = 1u << (sp - 1);
-					const uint32_t t = st & m, f = sf & m;
-					st = (st & ~m) | f;
-					sf = (sf & ~m) | t;
-				} else {
-					const uint32_t ma = 1u << (sp - 2), mb = 1u << (sp - 1);
-					const bool ta = st & ma, fa = sf & ma, tb = st & mb, fb = sf & mb;
+			if (o.op == PRED_NOT) {
+				const uint32_t m = 1u << (sp - 1);
+#pragma unroll
+				for (int u = 0; u < PRED_U; u++) {
+					const uint32_t t = st[u] & m, f = sf[u] & m;
+					st[u] = (st[u] & ~m) | f;
+					sf[u] = (sf[u] & ~m) | t;
+				}
+			} else if (o.op == PRED_AND || o.op == PRED_OR) {
+				const uint32_t ma = 1u << (sp - 2), mb = 1u << (sp - 1);
+#pragma unroll
+				for (int u = 0; u < PRED_U; u++) {
+					const bool ta = st[u] & ma, fa = sf[u] & ma, tb = st[u] & mb, fb = sf[u] & mb;
 					const bool t = o.op == PRED_AND ? (ta && tb) : (ta || tb);
 					const bool f = o.op == PRED_AND ? (fa || fb) : (fa && fb);
-					st = (st & ~(ma | mb)) | (t ? ma : 0u);
-					sf = (sf & ~(ma | mb)) | (f ? ma : 0u);
-					sp--;
+					st[u] = (st[u] & ~(ma | mb)) | (t ? ma : 0u);
+					sf[u] = (sf[u] & ~(ma | mb)) | (f ? ma : 0u);
 				}
-				continue;
-			}
-			bool t = false, f = false;
-			if (o.op == PRED_CONST) {
-				t = o.ival == 1;
-				f = o.ival == 0;
-			} else if (in_range) {
-				const bool valid = (o.valid[w] >> lane) & 1u;
-				if (o.op == PRED_IS_NULL) {
-					t = !valid, f = valid;
-				} else if (o.op == PRED_NOT_NULL) {
-					t = valid, f = !valid;
-				} else if (valid) {
-					bool c = false, isnull = false;
-					if (o.op == PRED_CMP_I64) {
-						c = pred_cmp_i64(o.cmp, static_cast<const long long *>(o.data)[r], o.ival);
-					} else if (o.op == PRED_CMP_F64) {
-						const double v = o.col_is_f64 ? static_cast<const double *>(o.data)[r]
-						                              : (double)static_cast<const long long *>(o.data)[r];
-						c = pred_cmp_f64(o.cmp, v, o.dval);
-					} else if (o.op == PRED_IN_I64) {
-						const long long v = static_cast<const long long *>(o.data)[r];
-						for (int j = 0; j < o.n_list; j++) c |= prog.aux_i64[o.aux_off + j] == v;
-						isnull = !c && o.has_null;
-						if (o.negate) c = !c;
-					} else if (o.op == PRED_IN_F64) {
-						const double v = o.col_is_f64 ? static_cast<const double *>(o.data)[r]
-						                              : (double)static_cast<const long long *>(o.data)[r];
-						for (int j = 0; j < o.n_list; j++) c |= prog.aux_f64[o.aux_off + j] == v;
-						isnull = !c && o.has_null;
-						if (o.negate) c = !c;
-					} else { // PRED_STR_LUT
-						const uint8_t v = prog.aux_u8[o.aux_off + static_cast<const int32_t *>(o.data)[r]];
-						c = v == 1;
-						isnull = v == 2;
+				sp--;
+			} else {
+				uint32_t vword[PRED_U];
+				long long raw[PRED_U];
+				const bool is_const = o.op == PRED_CONST, is_str = o.op == PRED_STR_LUT;
+				const bool wants_value = !is_const && o.op != PRED_IS_NULL && o.op != PRED_NOT_NULL;
+#pragma unroll
+				for (int u = 0; u < PRED_U; u++) { // phase 1: every load of the PRED_U rows, none depends on another
+					const long long w = wb + u, r = w * 32 + lane;
+					const bool in = !is_const && w < words && r < n;
+					vword[u] = in ? o.valid[w] : 0u;
+					raw[u] = 0;
+					if (in && wants_value)
+						raw[u] = is_str ? (long long)static_cast<const int32_t *>(o.data)[r] : static_cast<const long long *>(o.data)[r];
+				}
+#pragma unroll
+				for (int u = 0; u < PRED_U; u++) { // phase 2
+					bool t, f;
+					if (is_const) {
+						t = o.ival == 1, f = o.ival == 0;
+					} else {
+						const long long w = wb + u, r = w * 32 + lane;
+						pred_leaf_eval(prog, o, w < words && r < n, vword[u], lane, raw[u], t, f);
 					}
-					t = c && !isnull;
-					f = !c && !isnull;
+					st[u] |= t ? (1u << sp) : 0u;
+					sf[u] |= f ? (1u << sp) : 0u;
 				}
+				sp++;
 			}
-			st |= t ? (1u << sp) : 0u;
-			sf |= f ? (1u << sp) : 0u;
-			sp++;
 		}
-		const uint32_t word = __ballot_sync(0xffffffffu, in_range && (st & 1u));
-		if (lane == 0) out[w] = word;
+#pragma unroll
+		for (int u = 0; u < PRED_U; u++) {
+			const long long w = wb + u, r = w * 32 + lane;
+			const uint32_t word = __ballot_sync(0xffffffffu, w < words && r < n && (st[u] & 1u));
+			if (lane == 0 && w < words) out[w] = word;
+		}
 	}
 }
 
 void launch_eval_predicate(const PredProgram &prog, long long n, uint32_t *out, long long words, cudaStream_t s,
                            int64_t *launches) {
 	if (words <= 0) return;
-	const long long blocks = std::min<long long>((words + 7) / 8, 148 * 8);
+	const long long blocks = std::min<long long>((words + 8 * PRED_U - 1) / (8 * PRED_U), 148 * 8);
 	eval_predicate_kernel<<<(unsigned)blocks, 256, 0, s>>>(prog, n, out, words);
 	LB_CUDA(cudaGetLastError());
 	if (launches) (*launches)++;
@@ -470,25 +491,8 @@ struct Compiler {
 		fail("unexpected character");
 	}
 
-	static bool apply(int cmp, int v) {
-		switch (cmp) {
-		case CMP_EQ: return v == 0;
-		case CMP_NE: return v != 0;
-		case CMP_LT: return v < 0;
-		case CMP_GT: return v > 0;
-		case CMP_LE: return v <= 0;
-		default: return v >= 0;
-		}
-	}
-	static int flip(int cmp) {
-		switch (cmp) {
-		case CMP_LT: return CMP_GT;
-		case CMP_GT: return CMP_LT;
-		case CMP_LE: return CMP_GE;
-		case CMP_GE: return CMP_LE;
-		default: return cmp;
-		}
-	}
+	static bool apply(int cmp, int v) { return ((v < 0 ? 1 : (v > 0 ? 4 : 2)) & cmp) != 0; }
+	static int flip(int cmp) { return (cmp & 2) | ((cmp & 1) << 2) | ((cmp & 4) >> 2); }
 	void bind(PredOp &o, const ColumnStore::Column &c) {
 		if (!c.data || !c.valid) fail("column \"" + c.name + "\" holds no rows yet");
 		o.data = c.data;

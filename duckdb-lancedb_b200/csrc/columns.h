@@ -40,7 +40,8 @@ enum PredOpcode : int32_t {
 	PRED_AND = 9,
 	PRED_OR = 10,
 };
-enum PredCmp : int32_t { CMP_EQ = 0, CMP_NE = 1, CMP_LT = 2, CMP_GT = 3, CMP_LE = 4, CMP_GE = 5 };
+// a comparison as the set of orderings that satisfy it: bit 0 = less, bit 1 = equal, bit 2 = greater (branch-free on the device)
+enum PredCmp : int32_t { CMP_LT = 1, CMP_EQ = 2, CMP_LE = 3, CMP_GT = 4, CMP_NE = 5, CMP_GE = 6 };
 
 struct PredOp {
 	int32_t op = PRED_CONST;
