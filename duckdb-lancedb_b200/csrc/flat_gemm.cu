@@ -290,10 +290,14 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
-		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
-		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
-		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
-		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
+		LB_CUDA(cudaFuncSetAttribute(flat_gemm_ts_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(refresh_threshold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 		LB_CUDA(cudaFuncSetAttribute(rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 		LB_CUDA(cudaFuncSetAttribute(rerank_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
@@ -379,6 +383,32 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		}();
 		p.dbg = tsk_dbg;
 		long long t0 = 0, seg = seed_tiles;
+		// Seeding (TMEM-resident kernel, full batches): one pass over the first `sm_tiles` tiles that emits nothing and
+		// keeps the best score of every tile; the k-th largest of those is the threshold the geometric segments start
+		// from.  It replaces the segments below sm_tiles, whose loose thresholds let through hundreds of hits per query
+		// (on a 12.5 M-row shard they cost 0.3 ms of a 3.4 ms batch) by a pass that costs its MMAs only.
+		long long sm_tiles = one_tile ? 0 : 1024;
+		if (const char *e = getenv("LANCE_B200_TC_SEEDMAX")) sm_tiles = std::max(0, atoi(e));
+		if (pl.ts && !pl.tsk && sm_tiles >= 2 * (long long)k && sm_tiles <= TC_CAP && ntiles >= 2 * growth * sm_tiles) {
+			p.tile_lo = 0, p.tile_hi = sm_tiles;
+			p.R = (int)std::min<long long>(pl.R, sm_tiles);
+			int tix = timer ? timer->begin(KC_FLAT_GEMM, s) : -1;
+			switch (im.nkb) {
+			case 1: flat_gemm_ts_kernel<1, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+			case 2: flat_gemm_ts_kernel<2, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+			case 3: flat_gemm_ts_kernel<3, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+			default: flat_gemm_ts_kernel<4, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+			}
+			LB_CUDA(cudaGetLastError());
+			if (timer) timer->end(tix, s);
+			// the maxima stand in as a candidate list for one refresh (threshold only), then the list is emptied again
+			fill_u32_kernel<<<(nslots + 255) / 256, 256, 0, s>>>(cnt, nslots, (uint32_t)sm_tiles);
+			refresh_threshold_kernel<<<nq, 256, sel_smem, s>>>(cand, TC_CAP, cnt, thr, margin, flag, k, cap);
+			LB_CUDA(cudaGetLastError());
+			LB_CUDA(cudaMemsetAsync(cnt, 0, (size_t)nslots * 4, s));
+			(*launches) += 4;
+			seg = sm_tiles * growth; // the first emitting segment covers the seeded rows again
+		}
 		while (t0 < ntiles) {
 			long long t1 = std::min(ntiles, t0 + seg);
 			if (ntiles - t1 < seg) t1 = ntiles; // do not leave a short tail segment
@@ -402,10 +432,10 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 				}
 			} else if (pl.ts) {
 				switch (im.nkb) {
-				case 1: flat_gemm_ts_kernel<1><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-				case 2: flat_gemm_ts_kernel<2><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-				case 3: flat_gemm_ts_kernel<3><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-				default: flat_gemm_ts_kernel<4><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+				case 1: flat_gemm_ts_kernel<1, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+				case 2: flat_gemm_ts_kernel<2, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+				case 3: flat_gemm_ts_kernel<3, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+				default: flat_gemm_ts_kernel<4, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
 				}
 			} else {
 				flat_gemm_kernel<<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(tmQ, im.tmX, p);

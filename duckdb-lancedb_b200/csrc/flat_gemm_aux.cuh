@@ -132,6 +132,11 @@ __global__ void __launch_bounds__(256) prep_query_tiles_kernel(const float *__re
 	}
 }
 
+__global__ void fill_u32_kernel(uint32_t *__restrict__ dst, int n, uint32_t v) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) dst[i] = v;
+}
+
 // ------------------------------------------------------------------ threshold refresh between segments
 // One block per query.  A_k = k-th best approximate score among the candidates gathered so far (all live
 // rows): every true top-k row scores >= A_k - margin, so thr = A_k - margin and the list is compacted to

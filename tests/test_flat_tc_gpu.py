@@ -383,3 +383,47 @@ def test_tc_clustered_unit_norm_embeddings_vs_oracle(gpu, oracle_mod, metric, d,
         assert st["flat_tc_batches"] >= 1
         assert fb <= nq // 8, f"{fb} of {nq} queries fell back to the exact scan on clustered data"
         check_oracle(oracle_mod, X, Q[:8], L[:8], D[:8], C[:8], k, metric, what=f"tc clustered {metric} d={d}")
+
+
+@pytest.mark.parametrize("metric,d", [("dot", 128), ("l2", 64), ("cosine", 200)])
+def test_tc_tile_max_seeding_pass(gpu, oracle_mod, metric, d, monkeypatch):
+    """The threshold seeding pass of the TMEM-resident kernel (flat_gemm.cu "Seeding": per-tile maxima, no emission),
+    forced at a size the oracle can check (64 seed tiles instead of 1024), with deletions inside and outside the seeded
+    rows, a prefilter, a partial last tile and rows sorted so that the best rows of some queries share ONE tile (the
+    case in which the k-th tile maximum is a loose bound: still a bound, the result must not change)."""
+    n, k, nq = 150_001, 10, 300
+    rng = np.random.default_rng(4242 + d)
+    X = rng.standard_normal((n, d), dtype=np.float32)
+    Q = rng.standard_normal((nq, d), dtype=np.float32)
+    # tile 3 (rows 384..511) holds near-copies of query 0: its ten best rows sit in one tile
+    X[384:512] = Q[0] * (1.0 + 0.01 * rng.standard_normal((128, 1), dtype=np.float32)) + \
+        0.05 * rng.standard_normal((128, d), dtype=np.float32)
+    mask = rng.random(n) < 0.7
+    dele = np.concatenate([rng.choice(8192, 600, replace=False), 8192 + rng.choice(n - 8192, 3000, replace=False)])
+    deleted = np.zeros(n, bool)
+    deleted[dele] = True
+    monkeypatch.setenv("LANCE_B200_TC_SEEDMAX", "64")
+    with gpu.LanceHandle(d, metric) as h:
+        h.add_batch(X)
+        l0 = h.stats()["kernel_launches"]
+        L, D, C, fb = tc_search(h, Q, k)
+        seeded_launches = h.stats()["kernel_launches"] - l0
+        assert fb == 0
+        sel = np.array([0, 1, 2, 127, 128, 255, 299])
+        check_oracle(oracle_mod, X, Q[sel], L[sel], D[sel], C[sel], k, metric, what=f"seeded {metric}")
+        monkeypatch.setenv("LANCE_B200_TC_SEEDMAX", "0")
+        l0 = h.stats()["kernel_launches"]
+        L0, D0, C0, _ = tc_search(h, Q, k)
+        assert h.stats()["kernel_launches"] - l0 != seeded_launches, "the seeding pass did not run"
+        np.testing.assert_array_equal(L, L0)
+        np.testing.assert_array_equal(D, D0)
+        # with tombstones and a prefilter
+        monkeypatch.setenv("LANCE_B200_TC_SEEDMAX", "64")
+        h.delete_batch(dele)
+        allow = gpu.make_bitmap(mask)
+        L, D, C, fb = tc_search(h, Q, k, allow=allow)
+        check_oracle(oracle_mod, X, Q[sel], L[sel], D[sel], C[sel], k, metric, allow, oracle_mod.make_bitmap(deleted),
+                     what=f"seeded filtered {metric}")
+        for j in range(nq):
+            got = L[j, :C[j]]
+            assert mask[got].all() and not deleted[got].any()
