@@ -9,6 +9,7 @@
 // when the call returns (the C ABI hands results back in host buffers), so the exchange step of the multi-process form
 // (one NCCL all_gather, sharding.py) degenerates to a host-side k-way merge.
 #pragma once
+#include <atomic>
 #include <condition_variable>
 #include <functional>
 #include <memory>
@@ -52,10 +53,13 @@ private:
 		std::condition_variable cv;
 		std::function<void()> job;
 		bool has_job = false, done = false, stop = false;
+		std::atomic<bool> posted{false}, finished{false}; // lock-free mirrors of has_job / done for the polling phases
 		std::string error;
 	};
 	void run_on_all(const std::function<void(int)> &fn); // fn(shard) on every worker, waits, rethrows the first error
 	int least_filled();                                   // by rows held
+	// the shards' staged lists of queries [q_lo, q_hi) -> the caller's buffers
+	void merge_queries(int q_lo, int q_hi, int nq, int k, int64_t *out_labels, float *out_dist, int32_t *out_counts);
 
 	int dim_;
 	std::vector<std::unique_ptr<Store>> shards_;

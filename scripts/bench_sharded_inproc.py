@@ -19,10 +19,16 @@ G = pkg.device_count()
 rng = np.random.default_rng(1)
 Q = rng.standard_normal((B, d)).astype(np.float32)
 out = {"rows": rows, "dim": d, "batch": B, "k": k, "devices": G, "metric": "dot"}
-for name, handle in (("one_device", pkg.LanceHandle(d, "dot")), (f"sharded_{G}", pkg.LanceHandle.create_sharded(list(range(G)), d, "dot"))):
-    r2 = np.random.default_rng(2)
-    for lo in range(0, rows, 1 << 20):
-        handle.add_batch(r2.standard_normal((min(1 << 20, rows - lo), d)).astype(np.float32))
+import torch  # device memory for the generator only: the rows go in through the host-buffer C call
+
+handles = (("one_device", pkg.LanceHandle(d, "dot")), (f"sharded_{G}", pkg.LanceHandle.create_sharded(list(range(G)), d, "dot")))
+gen = torch.Generator(device="cuda:0")
+gen.manual_seed(2)
+for lo in range(0, rows, 1 << 20):
+    chunk = torch.randn((min(1 << 20, rows - lo), d), generator=gen, device="cuda:0", dtype=torch.float32).cpu().numpy()
+    for _, handle in handles:
+        handle.add_batch(chunk)
+for name, handle in handles:
     res = None
     for _ in range(3):
         res = handle.search_batch(Q, k)
