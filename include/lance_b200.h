@@ -81,7 +81,9 @@ int32_t lance_detached_delete_batch(void *handle, const int64_t *labels, int32_t
  * default" (lance_manager.rs:483-515): partitions = round(sqrt(n)), sub-vectors = dim/16 (dim/8, 1). */
 int32_t lance_detached_create_index(void *handle, int32_t num_partitions, int32_t num_sub_vectors, char *err_buf,
                                     int err_buf_len);
-/* rust_ffi.cpp:35-36: IVF_HNSW_SQ is outside north_star, returns -1 */
+/* rust_ffi.cpp:35-36 / ffi.rs:425-446 -> lance_manager.rs:521-551 (IVF_HNSW_SQ, replace = true).  Accepted, no graph is
+ * built: an existing IVF_PQ index is dropped (replaced) and searches are exact scans of the HBM-resident table from then
+ * on (recall 1.0).  m / ef_construction <= 0 = defaults, as in the reference. */
 int32_t lance_detached_create_hnsw_index(void *handle, int32_t m, int32_t ef_construction, char *err_buf,
                                          int err_buf_len);
 /* rust_ffi.cpp:37: nothing to compact in the device store, returns 0 */
