@@ -415,6 +415,12 @@ int32_t lance_detached_delete(void *handle, int64_t label, char *err_buf, int er
 
 int32_t lance_detached_create_index(void *handle, int32_t num_partitions, int32_t num_sub_vectors, char *err_buf,
                                     int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("create_index failed: ", -1, {
+			sh->create_index(num_partitions, num_sub_vectors); // one index per shard (sharded.h)
+			return 0;
+		})
+	}
 	LB_HANDLE(-1)
 	LB_TRY("create_index failed: ", -1, {
 		h->create_index(num_partitions, num_sub_vectors);
@@ -429,7 +435,12 @@ int32_t lance_detached_create_hnsw_index(void *handle, int32_t m, int32_t ef_con
 	// graph's.  The call is accepted (m, ef_construction <= 0 = defaults, as in the reference), an existing IVF_PQ index
 	// is dropped as a replaced index would be, and searches are exact from then on.
 	(void)m, (void)ef_construction;
-	if (lb::as_sharded(handle)) return 0; // sharded handles hold flat tables only: already exact
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("create_hnsw_index failed: ", -1, {
+			sh->drop_index();
+			return 0;
+		})
+	}
 	LB_HANDLE(-1)
 	LB_TRY("create_hnsw_index failed: ", -1, {
 		h->drop_index();
@@ -585,6 +596,12 @@ int32_t lance_b200_get_ivfpq(void *handle, lance_b200_ivfpq_info *info, float *c
 }
 
 int32_t lance_b200_drop_index(void *handle, char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("drop_index failed: ", -1, {
+			sh->drop_index();
+			return 0;
+		})
+	}
 	LB_HANDLE(-1)
 	LB_TRY("drop_index failed: ", -1, {
 		h->drop_index();
@@ -619,7 +636,8 @@ int32_t lance_b200_save(void *handle, char *err_buf, int err_buf_len) {
 int32_t lance_b200_stats(void *handle, lance_b200_stats_t *out) {
 	if (!handle || !out) return -1;
 	try {
-		static_cast<Store *>(handle)->stats(out);
+		if (lb::ShardedStore *sh = lb::as_sharded(handle)) sh->stats(out);
+		else static_cast<Store *>(handle)->stats(out);
 		return 0;
 	} catch (...) {
 		return -1;
@@ -627,13 +645,13 @@ int32_t lance_b200_stats(void *handle, lance_b200_stats_t *out) {
 }
 
 int32_t lance_b200_profile_enable(void *handle, int32_t on) {
-	if (!handle) return -1;
+	if (!handle || lb::as_sharded(handle)) return -1; // per-kernel timers belong to one device store
 	static_cast<Store *>(handle)->set_profile(on != 0);
 	return 0;
 }
 
 int32_t lance_b200_profile_read(void *handle, lance_b200_profile_t *out) {
-	if (!handle || !out) return -1;
+	if (!handle || !out || lb::as_sharded(handle)) return -1;
 	try {
 		static_cast<Store *>(handle)->read_profile(out);
 		return 0;
@@ -680,7 +698,8 @@ int32_t lance_b200_time_search_device(void *handle, const float *d_queries, int3
 
 int32_t lance_b200_set_flat_path(void *handle, int32_t mode) {
 	if (!handle || mode < 0 || mode > 2) return -1;
-	static_cast<Store *>(handle)->set_flat_path(mode);
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) sh->set_flat_path(mode);
+	else static_cast<Store *>(handle)->set_flat_path(mode);
 	return 0;
 }
 

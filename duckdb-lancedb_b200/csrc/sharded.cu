@@ -227,6 +227,45 @@ int64_t ShardedStore::compact() {
 	return n;
 }
 
+void ShardedStore::create_index(int num_partitions, int num_sub_vectors) {
+	std::lock_guard<std::mutex> g(fan_mu_);
+	if (rows() == 0) throw Error("cannot train an IVF_PQ index on an empty table");
+	run_on_all([&](int s) {
+		Store &st = *shards_[(size_t)s];
+		if (st.rows() > 0) st.create_index(num_partitions, num_sub_vectors);
+	});
+}
+
+void ShardedStore::drop_index() {
+	std::lock_guard<std::mutex> g(fan_mu_);
+	for (auto &s : shards_) s->drop_index();
+}
+
+bool ShardedStore::has_index() {
+	lance_b200_stats_t st;
+	stats(&st);
+	return st.has_index != 0;
+}
+
+// the shards' counters added up; device = the first shard's, has_index = any shard holds one
+void ShardedStore::stats(lance_b200_stats_t *out) {
+	lance_b200_stats_t sum = {};
+	for (size_t i = 0; i < shards_.size(); i++) {
+		lance_b200_stats_t st;
+		shards_[i]->stats(&st);
+		sum.kernel_launches += st.kernel_launches, sum.searches += st.searches, sum.flat_simt_batches += st.flat_simt_batches;
+		sum.flat_tc_batches += st.flat_tc_batches, sum.tc_fallback_queries += st.tc_fallback_queries;
+		sum.ivfpq_batches += st.ivfpq_batches, sum.rows += st.rows, sum.live_rows += st.live_rows;
+		if (i == 0) sum.device = st.device;
+		sum.has_index |= st.has_index;
+	}
+	*out = sum;
+}
+
+void ShardedStore::set_flat_path(int mode) {
+	for (auto &s : shards_) s->set_flat_path(mode);
+}
+
 void ShardedStore::search_host(const float *queries, int nq, int k, int nprobes, int refine, const uint32_t *allow,
                                int64_t allow_bits, const char *predicate, int64_t *out_labels, float *out_dist,
                                int32_t *out_counts) {

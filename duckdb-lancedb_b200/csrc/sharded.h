@@ -42,6 +42,14 @@ public:
 	int64_t rows();
 	void get_vector(int64_t label, float *out);
 	int64_t compact();
+	// IVF_PQ on a sharded table: every shard trains and keeps an index of ITS rows with the caller's parameters (the
+	// partition count is clamped to the shard's rows); a search probes nprobes lists on every shard and the lists are
+	// merged like flat results.  (The multi-process form shards ONE index by partition instead: DESIGN.md 6.0.)
+	void create_index(int num_partitions, int num_sub_vectors);
+	void drop_index();
+	bool has_index();
+	void stats(lance_b200_stats_t *out);
+	void set_flat_path(int mode);
 	// predicate (nullable) XOR allow bitmap (nullable, indexed by label)
 	void search_host(const float *queries, int nq, int k, int nprobes, int refine, const uint32_t *allow, int64_t allow_bits,
 	                 const char *predicate, int64_t *out_labels, float *out_dist, int32_t *out_counts);

@@ -288,9 +288,11 @@ int32_t lance_b200_add_batch_device_labels(void *handle, const float *d_vectors,
  * _search / _search_filtered / _search_batch / _search_predicate / _search_batch_predicate, _count, _delete /
  * _delete_batch, _get_vector, _compact, _dimension, _has_extra_columns, lance_b200_set_column, lance_free_detached:
  * whole appended batches go to the least-filled shard under one global label counter, a search runs on every device
- * concurrently and the per-shard lists are merged under the library's (distance, label) order.  Index builds,
- * persistence and the device-pointer entry points answer "not supported on a sharded handle".  NULL + message on
- * failure. */
+ * concurrently and the per-shard lists are merged under the library's (distance, label) order.
+ * lance_detached_create_index trains ONE IVF_PQ INDEX PER SHARD over that shard's rows with the caller's parameters (a
+ * search then probes nprobes lists on every shard); lance_detached_create_hnsw_index / lance_b200_drop_index drop them;
+ * lance_b200_stats adds the shards' counters up.  Persistence, the index exchange calls and the device-pointer entry
+ * points answer "not supported on a sharded handle".  NULL + message on failure. */
 void *lance_b200_create_sharded(const int32_t *devices, int32_t n_devices, int32_t dimension, const char *metric,
                                 char *err_buf, int err_buf_len);
 /* Rows held by each shard (out_rows[capacity]); returns the number of shards, -1 if `handle` is not sharded. */

@@ -78,8 +78,6 @@ def test_sharded_handle_predicates_and_unsupported_calls(gpu, oracle_mod):
         wl, _, wd = oracle_mod.flat_search(X, q, k, "l2", oracle_mod.make_bitmap(mask))
         assert_topk_parity(gl, gd, wl, wd, lambda lab: oracle_mod.distance_f64("l2", q, X[lab]), what="predicate")
         with pytest.raises(gpu.LanceError, match="not supported on a sharded handle"):
-            h.create_index(8, 4)
-        with pytest.raises(gpu.LanceError, match="not supported on a sharded handle"):
             h.save()
         with pytest.raises(gpu.LanceError, match="expected query dimension"):
             h.search(np.zeros(d + 1, np.float32), k)
@@ -87,3 +85,55 @@ def test_sharded_handle_predicates_and_unsupported_calls(gpu, oracle_mod):
         h.close()
     with pytest.raises(gpu.LanceError, match="does not exist"):
         gpu.LanceHandle.create_sharded([0, 99], d)
+
+
+@pytest.mark.parametrize("metric", ["l2", "cosine"])
+def test_sharded_handle_ivfpq_one_index_per_shard(gpu, oracle_mod, metric):
+    """create_index on a sharded handle: every shard trains an index of ITS rows with the caller's parameters; a search
+    probes nprobes lists on every shard and the shards' refined lists are merged.  (k-means sums with float atomics, so two
+    trainings of the same rows are not bit-identical: the checks are properties of the merged answer, not equality with
+    a second training.)"""
+    rng = np.random.default_rng(63)
+    n, d, k, P, M, nprobes = 40_000, 32, 10, 16, 8, 4
+    centers = rng.standard_normal((64, d)).astype(np.float32) * 3
+    X = (centers[rng.integers(0, 64, n)] + rng.standard_normal((n, d))).astype(np.float32)
+    Q = (centers[rng.integers(0, 64, 24)] + rng.standard_normal((24, d))).astype(np.float32)
+    half = n // 2
+    h = gpu.LanceHandle.create_sharded(_devices(gpu, 2), d, metric)
+    try:
+        h.add_batch(X[:half])  # the least-filled shard takes a whole batch: shard 0, then shard 1
+        h.add_batch(X[half:])
+        assert list(h.shard_rows()) == [half, n - half]
+        h.create_index(P, M)
+        st0 = h.stats()
+        assert st0["has_index"] == 1
+        L, D, C = h.search_batch(Q, k, nprobes=nprobes, refine_factor=3)
+        assert h.stats()["ivfpq_batches"] == st0["ivfpq_batches"] + 2, "both shards must answer from their index"
+        hits = 0
+        from_both = 0
+        for i in range(Q.shape[0]):
+            assert C[i] == k
+            got = [int(x) for x in L[i]]
+            assert len(set(got)) == k and all(0 <= g < n for g in got)
+            # refined distances are exact distances of the returned rows, and the list is in (distance, label) order
+            want_d = np.array([oracle_mod.distance_f64(metric, Q[i], X[g]) for g in got])
+            np.testing.assert_allclose(D[i], want_d, rtol=1e-4, atol=1e-5)
+            assert all((D[i, j], got[j]) <= (D[i, j + 1], got[j + 1]) for j in range(k - 1))
+            from_both += int(min(got) < half <= max(got))
+            wl, _, _ = oracle_mod.flat_search(X, Q[i], k, metric)
+            hits += len(set(got) & set(int(x) for x in wl))
+        assert from_both >= Q.shape[0] // 2, "results come from one shard only: the fan-out or the merge is broken"
+        assert hits >= 0.5 * k * Q.shape[0], f"recall {hits / (k * Q.shape[0]):.2f} of the approximate search is implausibly low"
+        # probing every list with a deep refine is the exact search
+        Lx, Dx, Cx = h.search_batch(Q[:4], k, nprobes=P, refine_factor=50)
+        for i in range(4):
+            wl, _, wd = oracle_mod.flat_search(X, Q[i], k, metric)
+            assert_topk_parity(Lx[i], Dx[i], wl, wd, lambda lab: oracle_mod.distance_f64(metric, Q[i], X[lab]), what=f"all lists q{i}")
+        # an HNSW request replaces the index: exact again
+        h.create_hnsw_index(16, 100)
+        assert h.stats()["has_index"] == 0
+        gl, gd = h.search(Q[0], k)
+        wl, _, wd = oracle_mod.flat_search(X, Q[0], k, metric)
+        assert_topk_parity(gl, gd, wl, wd, lambda lab: oracle_mod.distance_f64(metric, Q[0], X[lab]), what="after hnsw request")
+    finally:
+        h.close()
