@@ -382,39 +382,9 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 			return e ? atoi(e) : 0;
 		}();
 		p.dbg = tsk_dbg;
-		long long t0 = 0, seg = seed_tiles;
-		// Seeding (TMEM-resident kernel, full batches): one pass over the first `sm_tiles` tiles that emits nothing and
-		// keeps the best score of every tile; the k-th largest of those is the threshold the geometric segments start
-		// from.  It replaces the segments below sm_tiles, whose loose thresholds let through hundreds of hits per query
-		// (on a 12.5 M-row shard they cost 0.3 ms of a 3.4 ms batch) by a pass that costs its MMAs only.
-		long long sm_tiles = one_tile ? 0 : 1024;
-		if (const char *e = getenv("LANCE_B200_TC_SEEDMAX")) sm_tiles = std::max(0, atoi(e));
-		if (pl.ts && !pl.tsk && sm_tiles >= 2 * (long long)k && sm_tiles <= TC_CAP && ntiles >= 2 * growth * sm_tiles) {
-			p.tile_lo = 0, p.tile_hi = sm_tiles;
-			p.R = (int)std::min<long long>(pl.R, sm_tiles);
-			int tix = timer ? timer->begin(KC_FLAT_GEMM, s) : -1;
-			switch (im.nkb) {
-			case 1: flat_gemm_ts_kernel<1, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-			case 2: flat_gemm_ts_kernel<2, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-			case 3: flat_gemm_ts_kernel<3, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-			default: flat_gemm_ts_kernel<4, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
-			}
-			LB_CUDA(cudaGetLastError());
-			if (timer) timer->end(tix, s);
-			// the maxima stand in as a candidate list for one refresh (threshold only), then the list is emptied again
-			fill_u32_kernel<<<(nslots + 255) / 256, 256, 0, s>>>(cnt, nslots, (uint32_t)sm_tiles);
-			refresh_threshold_kernel<<<nq, 256, sel_smem, s>>>(cand, TC_CAP, cnt, thr, margin, flag, k, cap);
-			LB_CUDA(cudaGetLastError());
-			LB_CUDA(cudaMemsetAsync(cnt, 0, (size_t)nslots * 4, s));
-			(*launches) += 4;
-			seg = sm_tiles * growth; // the first emitting segment covers the seeded rows again
-		}
-		while (t0 < ntiles) {
-			long long t1 = std::min(ntiles, t0 + seg);
-			if (ntiles - t1 < seg) t1 = ntiles; // do not leave a short tail segment
-			p.tile_lo = t0, p.tile_hi = t1;
-			p.R = (int)std::min<long long>(pl.R, t1 - t0);
-			int tix = timer ? timer->begin(KC_FLAT_GEMM, s) : -1;
+		// one launch of the candidate kernel over tiles [p.tile_lo, p.tile_hi) (p.seed: the seeding variant)
+		auto launch_gemm = [&]() {
+			p.R = (int)std::min<long long>(pl.R, p.tile_hi - p.tile_lo);
 			if (pl.tsk) {
 				if (pl.mc) {
 					cudaLaunchConfig_t cfg = {};
@@ -431,16 +401,58 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 					flat_gemm_tsk_kernel<false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
 				}
 			} else if (pl.ts) {
-				switch (im.nkb) {
-				case 1: flat_gemm_ts_kernel<1, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-				case 2: flat_gemm_ts_kernel<2, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-				case 3: flat_gemm_ts_kernel<3, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-				default: flat_gemm_ts_kernel<4, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+				if (p.seed) {
+					switch (im.nkb) {
+					case 1: flat_gemm_ts_kernel<1, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+					case 2: flat_gemm_ts_kernel<2, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+					case 3: flat_gemm_ts_kernel<3, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+					default: flat_gemm_ts_kernel<4, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+					}
+				} else {
+					switch (im.nkb) {
+					case 1: flat_gemm_ts_kernel<1, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+					case 2: flat_gemm_ts_kernel<2, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+					case 3: flat_gemm_ts_kernel<3, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+					default: flat_gemm_ts_kernel<4, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+					}
 				}
 			} else {
 				flat_gemm_kernel<<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(tmQ, im.tmX, p);
 			}
 			LB_CUDA(cudaGetLastError());
+		};
+		long long t0 = 0, seg = seed_tiles;
+		// Seeding (both tensor-memory kernels): one pass over the first `sm_tiles` tiles that emits nothing and keeps the
+		// best score of every tile (K-streamed kernel: of every half tile); the k-th largest of those is the threshold the
+		// geometric segments start from.  It replaces the segments below sm_tiles, whose loose thresholds let through
+		// hundreds of hits per query (on a 12.5 M-row shard they cost 0.3 ms of a 3.4 ms batch), by a pass that costs its
+		// MMAs only.  Full batches on the TMEM-resident kernel seed with 1 024 tiles; the K-streamed kernel (large K,
+		// tables of a million rows) with 128, or k rounded up to 64 (measured on C2: B=64 0.490 -> 0.44 ms, B=4096
+		// 6.71 -> 6.49 ms with 128 tiles; 256 tiles 0.438 / 6.60 ms).
+		long long sm_tiles = pl.tsk ? std::min<long long>(1024, std::max<long long>(128, (k + 63) / 64 * 64)) : (one_tile ? 0 : 1024);
+		if (const char *e = getenv("LANCE_B200_TC_SEEDMAX")) sm_tiles = std::max(0, atoi(e));
+		const long long sm_entries = sm_tiles * (pl.tsk ? 2 : 1);
+		p.seed = 0;
+		if ((pl.ts || pl.tsk) && sm_entries >= 2 * (long long)k && sm_entries <= TC_CAP && ntiles >= 2 * growth * sm_tiles) {
+			p.tile_lo = 0, p.tile_hi = sm_tiles, p.seed = 1;
+			int tix = timer ? timer->begin(KC_FLAT_GEMM, s) : -1;
+			launch_gemm();
+			if (timer) timer->end(tix, s);
+			p.seed = 0;
+			// the maxima stand in as a candidate list for one refresh (threshold only), then the list is emptied again
+			fill_u32_kernel<<<(nslots + 255) / 256, 256, 0, s>>>(cnt, nslots, (uint32_t)sm_entries);
+			refresh_threshold_kernel<<<nq, 256, sel_smem, s>>>(cand, TC_CAP, cnt, thr, margin, flag, k, cap);
+			LB_CUDA(cudaGetLastError());
+			LB_CUDA(cudaMemsetAsync(cnt, 0, (size_t)nslots * 4, s));
+			(*launches) += 4;
+			seg = sm_tiles * growth; // the first emitting segment covers the seeded rows again
+		}
+		while (t0 < ntiles) {
+			long long t1 = std::min(ntiles, t0 + seg);
+			if (ntiles - t1 < seg) t1 = ntiles; // do not leave a short tail segment
+			p.tile_lo = t0, p.tile_hi = t1;
+			int tix = timer ? timer->begin(KC_FLAT_GEMM, s) : -1;
+			launch_gemm();
 			if (timer) timer->end(tix, s);
 			refresh_threshold_kernel<<<nq, 256, sel_smem, s>>>(cand, TC_CAP, cnt, thr, margin, flag, k, cap);
 			LB_CUDA(cudaGetLastError());

@@ -39,6 +39,7 @@ struct GemmParams {
 	int Kpad;
 	int EB;                  // per-(epilogue group, query) shared-memory emit buffer entries (0 = append directly)
 	const float *bias;       // K-streamed kernel, l2 with the bias epilogue: -|x|^2/2 per row (fp32), else null
+	int seed;                // K-streamed kernel: 1 = threshold seeding pass (per-half-tile maxima into cand, nothing emitted)
 	int dbg;                 // LANCE_B200_TSK_DBG (ceiling experiments): 1 = epilogue drains but does not filter, 2 = X stages
 	                         // are loaded once and re-used (no TMA traffic), 4 = epilogue does not even read the accumulator
 };

@@ -217,6 +217,28 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 					vb[4 * j + 3] = __float_as_uint(__uint_as_float(vb[4 * j + 3]) + bb.w);
 				}
 			}
+			if (p.seed) {
+				// threshold seeding pass (flat_gemm.cu "Seeding"): nothing is emitted, the best live score of this group's
+				// 64 rows goes to cand[q][2 (tile - tile_lo) + e]
+				float best = -INFINITY;
+#pragma unroll
+				for (int c = 0; c < 2; c++) {
+					const uint32_t live = gemm_chunk_valid(p, row0 + 32 * c);
+					const uint32_t(&v)[32] = c == 0 ? va : vb;
+					float m;
+					if (live == 0xFFFFFFFFu) {
+						m = gemm_chunk_max(v);
+					} else {
+						m = -INFINITY;
+#pragma unroll
+						for (int j = 0; j < 32; j++)
+							if ((live >> j) & 1u) m = fmaxf(m, __uint_as_float(v[j]));
+					}
+					best = fmaxf(best, m);
+				}
+				p.cand[(size_t)q * p.CAP + (size_t)(2 * (tile - p.tile_lo) + e)] = make_uint2(__float_as_uint(best), 0u);
+				continue;
+			}
 			if (!(p.dbg & 5)) {
 				gemm_process_chunk_inline(p, va, thr, q, row0, eb);
 				gemm_process_chunk_inline(p, vb, thr, q, row0 + 32, eb);

@@ -385,9 +385,11 @@ def test_tc_clustered_unit_norm_embeddings_vs_oracle(gpu, oracle_mod, metric, d,
         check_oracle(oracle_mod, X, Q[:8], L[:8], D[:8], C[:8], k, metric, what=f"tc clustered {metric} d={d}")
 
 
-@pytest.mark.parametrize("metric,d", [("dot", 128), ("l2", 64), ("cosine", 200)])
+@pytest.mark.parametrize("metric,d", [("dot", 128), ("l2", 64), ("cosine", 200),
+                                      # K-streamed kernel (half-tile maxima), plain and with the l2 bias epilogue
+                                      ("cosine", 320), ("l2", 704)])
 def test_tc_tile_max_seeding_pass(gpu, oracle_mod, metric, d, monkeypatch):
-    """The threshold seeding pass of the TMEM-resident kernel (flat_gemm.cu "Seeding": per-tile maxima, no emission),
+    """The threshold seeding pass of the tensor-memory kernels (flat_gemm.cu "Seeding": per-tile maxima, no emission),
     forced at a size the oracle can check (64 seed tiles instead of 1024), with deletions inside and outside the seeded
     rows, a prefilter, a partial last tile and rows sorted so that the best rows of some queries share ONE tile (the
     case in which the k-th tile maximum is a loose bound: still a bound, the result must not change)."""
