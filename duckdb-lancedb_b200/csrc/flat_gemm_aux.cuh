@@ -246,11 +246,14 @@ __global__ void __launch_bounds__(256) rerank_kernel(const float *__restrict__ X
 	const bool vec4 = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0) && ((reinterpret_cast<uintptr_t>(Q) & 15) == 0);
 	WarpSelect sel;
 	sel.init(bufs + (size_t)warp * cap, cap, k);
-	for (int i0 = warp * 32; i0 < c; i0 += 256) {
-		const int mine = i0 + lane;
-		const uint32_t myrow = mine < c ? list[mine].y : 0u;
+	// A short list (k = 10: a few dozen survivors) is dealt to ALL eight warps, ceil(c / 8) candidates each: the block's
+	// latency is one warp's chain of dependent row gathers, and 40 candidates on two warps were 16 of them in a row.
+	const int per = c <= 256 ? (c + 7) >> 3 : 32;
+	for (int base = 0; base < c; base += 8 * per) {
+		const int i0 = base + warp * per;
+		const int nb = max(0, min(per, c - i0));
+		const uint32_t myrow = (int)lane < nb ? list[i0 + lane].y : 0u;
 		float mydist = 0.f;
-		const int nb = min(32, c - i0);
 		for (int j = 0; j < nb; j += 2) {
 			const uint32_t r0 = __shfl_sync(0xFFFFFFFFu, myrow, j);
 			const uint32_t r1 = __shfl_sync(0xFFFFFFFFu, myrow, min(j + 1, nb - 1));
@@ -259,7 +262,7 @@ __global__ void __launch_bounds__(256) rerank_kernel(const float *__restrict__ X
 			if ((int)lane == j) mydist = d0;
 			if ((int)lane == j + 1) mydist = d1;
 		}
-		sel.push(mine < c, make_key(mydist, myrow));
+		sel.push((int)lane < nb, make_key(mydist, myrow));
 	}
 	sel.finalize();
 	if (lane == 0) cnts[warp] = sel.cnt;
