@@ -277,13 +277,8 @@ static GemmPlan plan_gemm(int tilesQ, int nkb, int num_sms) {
 	return best;
 }
 
-void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, const float *d_queries, int nq_total, int k,
-                      const uint32_t *d_allow, long long allow_bits, long long label_base, int64_t *d_out_labels,
-                      float *d_out_dist, int32_t *d_out_counts, Workspace &ws, cudaStream_t s, int64_t *launches,
-                      int64_t *fallback_queries, KernelTimer *timer, bool defer) {
-	Impl &im = *impl_;
-	finish(ws, s, launches, fallback_queries); // a previous deferred check on this stream still uses the scratch buffers
-	const int d = im.dim, Kpad = im.Kpad;
+// the opt-in shared-memory sizes of every kernel of this file, once per object
+static void ensure_attrs(FlatGemm::Impl &im) {
 	std::call_once(im.attr_once, [] {
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
 		LB_CUDA(cudaFuncSetAttribute(flat_gemm_tsk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_MAX));
@@ -302,6 +297,80 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 		LB_CUDA(cudaFuncSetAttribute(rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 		LB_CUDA(cudaFuncSetAttribute(rerank_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2048 * 8));
 	});
+}
+
+// query tiles of the next pass: at most TC_QCHUNK queries; when every CTA holds a single query tile (large K), a tile
+// count c with c * floor(SMs / c) close to the SM count (32 tiles on 148 SMs would idle 20 of them)
+static int pass_query_tiles(int nkb, int num_sms, long long remaining_queries) {
+	int rem_tiles = (int)((std::min<long long>(TC_QCHUNK, remaining_queries) + 127) / 128);
+	int take = rem_tiles;
+	const GemmPlan probe = plan_gemm(std::max(2, rem_tiles & ~1), nkb, num_sms);
+	if (plan_gemm(rem_tiles, nkb, num_sms).QT == 1 && rem_tiles > 1) {
+		// K-streamed kernel with multicast pairs: only EVEN tile counts pair up (24 + 8 tiles for a batch of 4096:
+		// 144 of 148 SMs in both passes, every X tile out of the L2 once per pair)
+		const bool want_even = probe.tsk && probe.mc && rem_tiles >= 4;
+		int best_used = 0;
+		for (int c = want_even ? (rem_tiles & ~1) : rem_tiles; c >= (rem_tiles + 1) / 2; c -= want_even ? 2 : 1) {
+			int used = c * std::max(1, num_sms / c);
+			if (used > num_sms) used = num_sms;
+			if (used * 100 >= num_sms * 95) {
+				take = c;
+				break;
+			}
+			if (used > best_used) best_used = used, take = c;
+		}
+	}
+	return take;
+}
+
+// one launch of the candidate kernel over tiles [p.tile_lo, p.tile_hi) (p.seed: the seeding variant)
+static void launch_candidates(FlatGemm::Impl &im, const GemmPlan &pl, GemmParams &p, const CUtensorMap &tmQ, cudaStream_t s) {
+	p.R = (int)std::min<long long>(pl.R, p.tile_hi - p.tile_lo);
+	if (pl.tsk) {
+		if (pl.mc) {
+			cudaLaunchConfig_t cfg = {};
+			cfg.gridDim = dim3(pl.NG * p.R), cfg.blockDim = dim3(GEMM_THREADS), cfg.dynamicSmemBytes = pl.smem, cfg.stream = s;
+			cudaLaunchAttribute at[1];
+			at[0].id = cudaLaunchAttributeClusterDimension;
+			at[0].val.clusterDim.x = 2, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
+			cfg.attrs = at, cfg.numAttrs = 1;
+			if (im.bias) LB_CUDA(cudaLaunchKernelEx(&cfg, flat_gemm_tsk_kernel<true, true>, im.tmX64, p));
+			else LB_CUDA(cudaLaunchKernelEx(&cfg, flat_gemm_tsk_kernel<true>, im.tmX64, p));
+		} else if (im.bias) {
+			flat_gemm_tsk_kernel<false, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+		} else {
+			flat_gemm_tsk_kernel<false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+		}
+	} else if (pl.ts) {
+		if (p.seed) {
+			switch (im.nkb) {
+			case 1: flat_gemm_ts_kernel<1, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+			case 2: flat_gemm_ts_kernel<2, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+			case 3: flat_gemm_ts_kernel<3, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+			default: flat_gemm_ts_kernel<4, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+			}
+		} else {
+			switch (im.nkb) {
+			case 1: flat_gemm_ts_kernel<1, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+			case 2: flat_gemm_ts_kernel<2, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+			case 3: flat_gemm_ts_kernel<3, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
+			default: flat_gemm_ts_kernel<4, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
+			}
+		}
+	} else {
+		flat_gemm_kernel<<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(tmQ, im.tmX, p);
+	}
+	LB_CUDA(cudaGetLastError());
+}
+
+void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, const float *d_queries, int nq_total, int k,
+                      const uint32_t *d_allow, long long allow_bits, long long label_base, int64_t *d_out_labels,
+                      float *d_out_dist, int32_t *d_out_counts, Workspace &ws, cudaStream_t s, int64_t *launches,
+                      int64_t *fallback_queries, KernelTimer *timer, bool defer) {
+	Impl &im = *impl_;
+	finish(ws, s, launches, fallback_queries); // a previous deferred check on this stream still uses the scratch buffers
+	const int d = im.dim, Kpad = im.Kpad;
+	ensure_attrs(im);
 	const int cap = warpsel_cap(k);
 	const size_t sel_smem = (size_t)8 * cap * sizeof(u64);
 	const long long ntiles = (n + GEMM_BN - 1) / GEMM_BN;
@@ -324,27 +393,7 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 	if (const char *e = getenv("LANCE_B200_TC_JUMP")) jump = std::max(2, atoi(e));
 
 	for (int q0 = 0, nq = 0; q0 < nq_total; q0 += nq) {
-		// queries per pass: at most TC_QCHUNK; when every CTA holds a single query tile (large K), take a tile
-		// count c with c * floor(SMs / c) close to the SM count (32 tiles on 148 SMs would idle 20 of them)
-		int rem_tiles = (std::min(TC_QCHUNK, nq_total - q0) + 127) / 128;
-		int take = rem_tiles;
-		const GemmPlan probe = plan_gemm(std::max(2, rem_tiles & ~1), im.nkb, im.num_sms);
-		if (plan_gemm(rem_tiles, im.nkb, im.num_sms).QT == 1 && rem_tiles > 1) {
-			// K-streamed kernel with multicast pairs: only EVEN tile counts pair up (24 + 8 tiles for a batch of 4096:
-			// 144 of 148 SMs in both passes, every X tile out of the L2 once per pair)
-			const bool want_even = probe.tsk && probe.mc && rem_tiles >= 4;
-			int best_used = 0;
-			for (int c = want_even ? (rem_tiles & ~1) : rem_tiles; c >= (rem_tiles + 1) / 2; c -= want_even ? 2 : 1) {
-				int used = c * std::max(1, im.num_sms / c);
-				if (used > im.num_sms) used = im.num_sms;
-				if (used * 100 >= im.num_sms * 95) {
-					take = c;
-					break;
-				}
-				if (used > best_used) best_used = used, take = c;
-			}
-		}
-		nq = std::min(take * 128, nq_total - q0);
+		nq = std::min(pass_query_tiles(im.nkb, im.num_sms, nq_total - q0) * 128, nq_total - q0);
 		const int tilesQ = (nq + 127) / 128;
 		GemmPlan pl = plan_gemm(tilesQ, im.nkb, im.num_sms);
 		const int nslots = pl.NG * pl.QT * 128;
@@ -382,45 +431,7 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 			return e ? atoi(e) : 0;
 		}();
 		p.dbg = tsk_dbg;
-		// one launch of the candidate kernel over tiles [p.tile_lo, p.tile_hi) (p.seed: the seeding variant)
-		auto launch_gemm = [&]() {
-			p.R = (int)std::min<long long>(pl.R, p.tile_hi - p.tile_lo);
-			if (pl.tsk) {
-				if (pl.mc) {
-					cudaLaunchConfig_t cfg = {};
-					cfg.gridDim = dim3(pl.NG * p.R), cfg.blockDim = dim3(GEMM_THREADS), cfg.dynamicSmemBytes = pl.smem, cfg.stream = s;
-					cudaLaunchAttribute at[1];
-					at[0].id = cudaLaunchAttributeClusterDimension;
-					at[0].val.clusterDim.x = 2, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
-					cfg.attrs = at, cfg.numAttrs = 1;
-					if (im.bias) LB_CUDA(cudaLaunchKernelEx(&cfg, flat_gemm_tsk_kernel<true, true>, im.tmX64, p));
-					else LB_CUDA(cudaLaunchKernelEx(&cfg, flat_gemm_tsk_kernel<true>, im.tmX64, p));
-				} else if (im.bias) {
-					flat_gemm_tsk_kernel<false, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
-				} else {
-					flat_gemm_tsk_kernel<false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
-				}
-			} else if (pl.ts) {
-				if (p.seed) {
-					switch (im.nkb) {
-					case 1: flat_gemm_ts_kernel<1, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-					case 2: flat_gemm_ts_kernel<2, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-					case 3: flat_gemm_ts_kernel<3, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-					default: flat_gemm_ts_kernel<4, true><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
-					}
-				} else {
-					switch (im.nkb) {
-					case 1: flat_gemm_ts_kernel<1, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-					case 2: flat_gemm_ts_kernel<2, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-					case 3: flat_gemm_ts_kernel<3, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p); break;
-					default: flat_gemm_ts_kernel<4, false><<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(im.tmX, p);
-					}
-				}
-			} else {
-				flat_gemm_kernel<<<pl.NG * p.R, GEMM_THREADS, pl.smem, s>>>(tmQ, im.tmX, p);
-			}
-			LB_CUDA(cudaGetLastError());
-		};
+		auto launch_gemm = [&]() { launch_candidates(im, pl, p, tmQ, s); };
 		long long t0 = 0, seg = seed_tiles;
 		// Seeding (both tensor-memory kernels): one pass over the first `sm_tiles` tiles that emits nothing and keeps the
 		// best score of every tile (K-streamed kernel: of every half tile); the k-th largest of those is the threshold the
@@ -502,6 +513,62 @@ void FlatGemm::search(const float *X, long long n, const uint32_t *deleted, cons
 			rerun_flagged(X, n, deleted, Qchunk, nq, k, d_allow, allow_bits, label_base, d_out_labels + (size_t)q0 * k,
 			              d_out_dist + (size_t)q0 * k, d_out_counts + q0, flag_out, ws, s, launches, fallback_queries);
 	}
+}
+
+bool FlatGemm::nearest_supported(int dim, int metric, long long table_rows) {
+	if (metric == METRIC_COSINE || dim < 16 || gemm_variant_override() == 1) return false;
+	int Kreal16, Kpad, nkb, ks;
+	shape_for(dim, metric, Kreal16, Kpad, nkb, ks);
+	if (nkb > 12) return false; // neither the TMEM-resident (<= 4 k-blocks) nor the K-streamed kernel
+	const long long entries = (table_rows + GEMM_BN - 1) / GEMM_BN * (nkb > 4 ? 2 : 1);
+	return table_rows >= 256 && entries <= 4096;
+}
+
+bool FlatGemm::nearest(const float *table, long long table_rows, const float *d_points, long long npts, int32_t *d_out_idx,
+                       Workspace &ws, cudaStream_t s, int64_t *launches) {
+	Impl &im = *impl_;
+	if (!nearest_supported(im.dim, im.metric, table_rows)) return false;
+	if (!plan_gemm(1, im.nkb, im.num_sms).ts && !plan_gemm(1, im.nkb, im.num_sms).tsk) return false;
+	ensure_attrs(im);
+	sync_rows(table, table_rows, table_rows, s, launches);
+	const int d = im.dim, Kpad = im.Kpad;
+	const long long ntiles = (table_rows + GEMM_BN - 1) / GEMM_BN;
+	CUtensorMap tmQ_unused = {};
+	for (long long q0 = 0; q0 < npts;) {
+		const int nq = (int)std::min<long long>((long long)pass_query_tiles(im.nkb, im.num_sms, npts - q0) * 128, npts - q0);
+		const GemmPlan pl = plan_gemm((nq + 127) / 128, im.nkb, im.num_sms);
+		if (!pl.ts && !pl.tsk) throw Error("internal: nearest() planned the all-shared kernel");
+		const int nslots = pl.NG * pl.QT * 128;
+		const int E = (int)(ntiles * (pl.tsk ? 2 : 1));
+		ws.work2.ensure((size_t)nslots * Kpad * 2 + 1024);
+		ws.work3.ensure((size_t)nslots * 5 * 4 + 64);
+		ws.work.ensure((size_t)nslots * E * sizeof(uint2));
+		__nv_bfloat16 *Qs = ws.work2.as<__nv_bfloat16>();
+		float *margin = ws.work3.as<float>();
+		float *thr = margin + nslots;
+		uint32_t *cnt = reinterpret_cast<uint32_t *>(thr + nslots);
+		uint32_t *flag = cnt + nslots;
+		const float *Qchunk = d_points + (size_t)q0 * d;
+		prep_query_tiles_kernel<<<(nslots + 7) / 8, 256, 0, s>>>(Qchunk, nq, nslots, d, im.metric, Kpad,
+		                                                         im.max_norm.as<uint32_t>(), Qs, margin, thr, cnt, flag,
+		                                                         im.bias ? 1 : 0);
+		LB_CUDA(cudaGetLastError());
+		GemmParams p;
+		p.nkb = im.nkb, p.ksteps_last = im.ksteps_last, p.QT = pl.QT, p.KS = pl.KS, p.S = pl.S, p.NG = pl.NG;
+		p.n_rows = table_rows, p.thr = thr, p.cnt = cnt, p.cand = ws.work.as<uint2>(), p.CAP = E;
+		p.deleted = nullptr, p.allow = nullptr, p.allow_bits = 0;
+		p.Qs = Qs, p.Kpad = Kpad, p.EB = pl.EB;
+		p.bias = im.bias ? im.bias_buf.as<float>() : nullptr;
+		p.dbg = 0, p.seed = 1;
+		p.tile_lo = 0, p.tile_hi = ntiles;
+		launch_candidates(im, pl, p, tmQ_unused, s);
+		nearest_from_maxima_kernel<<<(nq + 7) / 8, 256, 0, s>>>(ws.work.as<uint2>(), E, E, table, d, im.metric, Qchunk, nq,
+		                                                         d_out_idx + q0);
+		LB_CUDA(cudaGetLastError());
+		if (launches) *launches += 3;
+		q0 += nq;
+	}
+	return true;
 }
 
 void FlatGemm::rerun_flagged(const float *X, long long n, const uint32_t *deleted, const float *Qchunk, int nq, int k,

@@ -226,6 +226,44 @@ __global__ void __launch_bounds__(256) refresh_threshold_kernel(uint2 *__restric
 	}
 }
 
+// ------------------------------------------------------------------ nearest row from the seeding pass's maxima
+// FlatGemm::nearest: entries[q][0..E) = (best bf16 score, its row) of every (half) tile of the table.  One warp per point:
+// the four best entries (one per lane at most), the exact fp32 distance of the point to their rows, argmin (ties to the
+// lower row, as nearest_center_kernel).
+__global__ void __launch_bounds__(256) nearest_from_maxima_kernel(const uint2 *__restrict__ entries, int stride, int E,
+                                                                  const float *__restrict__ table, int d, int metric,
+                                                                  const float *__restrict__ Q, int nq, int32_t *__restrict__ out) {
+	const int q = blockIdx.x * 8 + (threadIdx.x >> 5);
+	if (q >= nq) return;
+	const unsigned lane = lane_id();
+	const uint2 *list = entries + (size_t)q * stride;
+	float bs = -__int_as_float(0x7F800000);
+	uint32_t br = 0xFFFFFFFFu;
+	for (int e = lane; e < E; e += 32) {
+		const uint2 c = list[e];
+		const float sc = __uint_as_float(c.x);
+		if (sc > bs || (sc == bs && c.y < br)) bs = sc, br = c.y;
+	}
+	const float *qv = Q + (size_t)q * d;
+	const bool vec4 = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(table) & 15) == 0) && ((reinterpret_cast<uintptr_t>(Q) & 15) == 0);
+	float best_d = __int_as_float(0x7F800000);
+	uint32_t best_row = 0xFFFFFFFFu;
+	for (int t = 0; t < 4; t++) {
+		float ms = bs;
+		uint32_t mr = br;
+		for (int o = 16; o; o >>= 1) {
+			const float os = __shfl_xor_sync(0xFFFFFFFFu, ms, o);
+			const uint32_t orow = __shfl_xor_sync(0xFFFFFFFFu, mr, o);
+			if (os > ms || (os == ms && orow < mr)) ms = os, mr = orow;
+		}
+		if (mr == 0xFFFFFFFFu) break; // warp-uniform: no entry left
+		const float dist = warp_exact_distance(metric, qv, table + (size_t)mr * d, d, vec4);
+		if (dist < best_d || (dist == best_d && mr < best_row)) best_d = dist, best_row = mr;
+		if (br == mr) bs = -__int_as_float(0x7F800000), br = 0xFFFFFFFFu; // rows are distinct across entries
+	}
+	if (lane == 0) out[q] = best_row == 0xFFFFFFFFu ? 0 : (int32_t)best_row;
+}
+
 // ------------------------------------------------------------------ exact re-rank (warp_exact_distance: exact.cuh)
 // One block per query: exact fp32 distance of every surviving candidate, fused top-k, sorted output.
 __global__ void __launch_bounds__(256) rerank_kernel(const float *__restrict__ X, int d, int metric,

@@ -211,6 +211,29 @@ __device__ __forceinline__ float gemm_chunk_max(const uint32_t (&r)[32]) {
 	return fmaxf(tc::fmax3(m1, m2, m3), m4);
 }
 
+// Seeding pass: the best live score of a 32-row chunk and the row that holds it (lowest row on equal scores), folded
+// into the running (best, best_row) of the tile.
+__device__ __forceinline__ void gemm_chunk_best(const GemmParams &p, const uint32_t (&v)[32], long long row0, float &best,
+                                                uint32_t &best_row) {
+	const uint32_t live = gemm_chunk_valid(p, row0);
+	float m;
+	if (live == 0xFFFFFFFFu) {
+		m = gemm_chunk_max(v);
+	} else {
+		m = -INFINITY;
+#pragma unroll
+		for (int j = 0; j < 32; j++)
+			if ((live >> j) & 1u) m = fmaxf(m, __uint_as_float(v[j]));
+	}
+	if (m > best) {
+		int idx = 0;
+#pragma unroll
+		for (int j = 31; j >= 0; j--)
+			if (((live >> j) & 1u) && __uint_as_float(v[j]) == m) idx = j;
+		best = m, best_row = (uint32_t)row0 + (uint32_t)idx;
+	}
+}
+
 __device__ __forceinline__ void gemm_park_chunk(const GemmParams &p, const uint32_t (&r)[32], float thr, int q, long long row0,
                                                 const EmitBuf &eb, uint32_t *pend, int chunk) {
 	const bool hit = gemm_chunk_max(r) >= thr;

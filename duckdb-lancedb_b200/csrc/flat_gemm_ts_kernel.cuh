@@ -15,8 +15,8 @@
 namespace lb {
 
 // SEED = true is the threshold seeding pass (flat_gemm.cu "seeding"): nothing is emitted; the epilogue reduces every
-// 128-row tile to the best score of its live rows and stores it at cand[q][tile - tile_lo].x, so the pass runs at the
-// speed of its MMAs.  The k-th largest of those maxima is the score of k distinct rows, i.e. a lower bound of the k-th
+// 128-row tile to the best score of its live rows and stores it with its row at cand[q][tile - tile_lo], so the pass runs at
+// the speed of its MMAs.  The k-th largest of those maxima is the score of k distinct rows, i.e. a lower bound of the k-th
 // best score over the seeded rows, and almost always equal to it (the k best of 131 072 rows rarely share a tile).
 template <int NKB, bool SEED>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -166,27 +166,23 @@ flat_gemm_ts_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p)
 				uint32_t va[32], vb[32];
 				if constexpr (SEED) {
 					float best = -INFINITY;
+					uint32_t best_row = 0u;
 					tc::tmem_ld32(taddr, va);
-#pragma unroll
-					for (int c = 0; c < 4; c++) {
-						tmem_wait_regs(va);
-						const uint32_t live = gemm_chunk_valid(p, row0 + 32 * c);
-						float m;
-						if (live == 0xFFFFFFFFu) {
-							m = gemm_chunk_max(va);
-						} else {
-							m = -INFINITY;
-#pragma unroll
-							for (int j = 0; j < 32; j++)
-								if ((live >> j) & 1u) m = fmaxf(m, __uint_as_float(va[j]));
-						}
-						if (c < 3) tc::tmem_ld32(taddr + 32 * (c + 1), va);
-						best = fmaxf(best, m);
-					}
+					tmem_wait_regs(va);
+					tc::tmem_ld32(taddr + 32, vb);
+					gemm_chunk_best(p, va, row0, best, best_row);
+					tmem_wait_regs(vb);
+					tc::tmem_ld32(taddr + 64, va);
+					gemm_chunk_best(p, vb, row0 + 32, best, best_row);
+					tmem_wait_regs(va);
+					tc::tmem_ld32(taddr + 96, vb);
+					gemm_chunk_best(p, va, row0 + 64, best, best_row);
+					tmem_wait_regs(vb);
 					tc::tc_fence_before();
 					__syncwarp();
 					if (lane == 0) tc::mbar_arrive(bar_tempty + 8u * e);
-					p.cand[(size_t)q * p.CAP + (size_t)(tile - p.tile_lo)] = make_uint2(__float_as_uint(best), 0u);
+					gemm_chunk_best(p, vb, row0 + 96, best, best_row);
+					p.cand[(size_t)q * p.CAP + (size_t)(tile - p.tile_lo)] = make_uint2(__float_as_uint(best), best_row);
 					continue;
 				}
 				tc::tmem_ld32(taddr, va);

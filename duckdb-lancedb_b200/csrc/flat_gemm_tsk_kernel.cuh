@@ -219,24 +219,12 @@ flat_gemm_tsk_kernel(const __grid_constant__ CUtensorMap tmX, const GemmParams p
 			}
 			if (p.seed) {
 				// threshold seeding pass (flat_gemm.cu "Seeding"): nothing is emitted, the best live score of this group's
-				// 64 rows goes to cand[q][2 (tile - tile_lo) + e]
+				// 64 rows and that row go to cand[q][2 (tile - tile_lo) + e]
 				float best = -INFINITY;
-#pragma unroll
-				for (int c = 0; c < 2; c++) {
-					const uint32_t live = gemm_chunk_valid(p, row0 + 32 * c);
-					const uint32_t(&v)[32] = c == 0 ? va : vb;
-					float m;
-					if (live == 0xFFFFFFFFu) {
-						m = gemm_chunk_max(v);
-					} else {
-						m = -INFINITY;
-#pragma unroll
-						for (int j = 0; j < 32; j++)
-							if ((live >> j) & 1u) m = fmaxf(m, __uint_as_float(v[j]));
-					}
-					best = fmaxf(best, m);
-				}
-				p.cand[(size_t)q * p.CAP + (size_t)(2 * (tile - p.tile_lo) + e)] = make_uint2(__float_as_uint(best), 0u);
+				uint32_t best_row = 0u;
+				gemm_chunk_best(p, va, row0, best, best_row);
+				gemm_chunk_best(p, vb, row0 + 32, best, best_row);
+				p.cand[(size_t)q * p.CAP + (size_t)(2 * (tile - p.tile_lo) + e)] = make_uint2(__float_as_uint(best), best_row);
 				continue;
 			}
 			if (!(p.dbg & 5)) {

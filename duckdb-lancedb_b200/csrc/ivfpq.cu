@@ -30,6 +30,7 @@
 #include <mutex>
 
 #include "exact.cuh"
+#include "flat_gemm.h"
 #include "flat_scan1.cuh"
 #include "tc_ptx.cuh"
 #include "topk.cuh"

@@ -9,12 +9,20 @@
 // on a strided sample of at most 256*P rows, and centre sums use fp32 atomics.
 #pragma once
 
+// `tc` (nullable, whole-row k-means only): the assignment step runs on the tensor cores (FlatGemm::nearest) — the
+// centres are re-converted to their bf16 shadow every iteration, the points stream through as query tiles
 static void kmeans_device(const float *X, long long n, int ldx, int dd, int Z, float *C, int nc, int is_dot,
                           const float *sub_base, const int32_t *sub_idx, int iters, int32_t *assign, float *sums,
-                          int *counts, cudaStream_t s, int64_t *launches) {
+                          int *counts, cudaStream_t s, int64_t *launches, FlatGemm *tc = nullptr, Workspace *tc_ws = nullptr) {
 	for (int it = 0; it < iters; it++) {
-		nearest_center_kernel<<<dim3(blocks_for(n, NC_BM), 1, Z), 256, 0, s>>>(X, n, ldx, dd, C, nc, is_dot, sub_base,
-		                                                                        sub_idx, assign, n);
+		bool assigned = false;
+		if (tc && Z == 1 && ldx == dd && !sub_base) {
+			tc->invalidate();
+			assigned = tc->nearest(C, nc, X, n, assign, *tc_ws, s, launches);
+		}
+		if (!assigned)
+			nearest_center_kernel<<<dim3(blocks_for(n, NC_BM), 1, Z), 256, 0, s>>>(X, n, ldx, dd, C, nc, is_dot, sub_base,
+			                                                                        sub_idx, assign, n);
 		LB_CUDA(cudaGetLastError());
 		LB_CUDA(cudaMemsetAsync(sums, 0, (size_t)Z * nc * dd * sizeof(float), s));
 		LB_CUDA(cudaMemsetAsync(counts, 0, (size_t)Z * nc * sizeof(int), s));
@@ -83,8 +91,23 @@ void Store::create_index(int num_partitions, int num_sub_vectors) {
 	assign.alloc((size_t)std::max<long long>(ns, (long long)M * ns_pq) * sizeof(int32_t));
 	sums.alloc((size_t)std::max<long long>((long long)P * d, (long long)M * 256 * dsub) * sizeof(float));
 	counts.alloc((size_t)std::max<long long>(P, (long long)M * 256) * sizeof(int));
+	// The partition-level assignments (k-means over the sample, then every row of the table) are 2 n P d flops — 64 + 63
+	// TFLOP at C3, 7.8 s of an 8.5 s build on the CUDA cores: they run on the tensor cores when the shape has a
+	// tensor-memory kernel (FlatGemm::nearest: bf16 tile maxima, then the exact fp32 distance to the rows of the four best
+	// tiles).  LANCE_B200_TRAIN_TC=0 keeps the CUDA-core kernel.
+	std::unique_ptr<FlatGemm> tc;
+	std::unique_ptr<Workspace> tc_ws;
+	{
+		const char *e = getenv("LANCE_B200_TRAIN_TC");
+		const int train_metric = is_dot ? METRIC_DOT : METRIC_L2;
+		if (!(e && atoi(e) == 0) && d >= 64 && FlatGemm::nearest_supported(d, train_metric, P)) {
+			tc.reset(new FlatGemm(device_, num_sms_, d, train_metric));
+			tc_ws.reset(new Workspace(false));
+		}
+	}
 	kmeans_device(S.as<float>(), ns, d, d, 1, ix->centroids.as<float>(), P, is_dot, nullptr, nullptr, iters,
-	              assign.as<int32_t>(), sums.as<float>(), counts.as<int>(), s, &launches);
+	              assign.as<int32_t>(), sums.as<float>(), counts.as<int>(), s, &launches, tc.get(), tc_ws.get());
+	if (tc) tc->invalidate(); // the last iteration moved the centres once more
 
 	// ---- PQ codebooks on residuals (l2 / cosine) or raw rows (dot)
 	DevBuf part_of_sample;
@@ -121,8 +144,9 @@ void Store::create_index(int num_partitions, int num_sub_vectors) {
 			launches++;
 		}
 		int32_t *pa = part_assign.as<int32_t>() + r0;
-		nearest_center_kernel<<<dim3(blocks_for(c, NC_BM), 1, 1), 256, 0, s>>>(Xc, c, d, d, ix->centroids.as<float>(), P, is_dot,
-		                                                                       nullptr, nullptr, pa, c);
+		if (!(tc && tc->nearest(ix->centroids.as<float>(), P, Xc, c, pa, *tc_ws, s, &launches)))
+			nearest_center_kernel<<<dim3(blocks_for(c, NC_BM), 1, 1), 256, 0, s>>>(Xc, c, d, d, ix->centroids.as<float>(), P,
+			                                                                       is_dot, nullptr, nullptr, pa, c);
 		LB_CUDA(cudaGetLastError());
 		nearest_center_kernel<<<dim3(blocks_for(c, NC_BM), 1, M), 256, 0, s>>>(Xc, c, d, dsub, ix->codebook.as<float>(), 256, 0,
 		                                                                       is_dot ? nullptr : ix->centroids.as<float>(),

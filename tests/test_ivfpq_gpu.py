@@ -361,3 +361,60 @@ def test_ivfpq_sharded_by_partition(gpu):
             finally:
                 for s in shards:
                     s.close()
+
+
+@pytest.mark.parametrize("metric,d", [("l2", 128), ("dot", 128), ("l2", 320), ("cosine", 320)])
+def test_trainer_assignment_on_the_tensor_cores(gpu, oracle_mod, metric, d, monkeypatch):
+    """Partition-level assignments of the trainer on the tensor cores (FlatGemm::nearest: bf16 tile maxima of the
+    centroid table, exact fp32 distance to the rows of the four best tiles).  d=128 takes the TMEM-resident kernel (l2 as
+    three extra bf16 columns), d=320 the K-streamed one (l2 as the bias epilogue; cosine trains on unit rows under l2).
+    The exported assignment must be the nearest centroid; the index must search as well as the CUDA-core-trained one."""
+    rng = np.random.default_rng(1234 + d)
+    n, P, M, k = 60_000, 256, 16, 10
+    centers = rng.standard_normal((400, d), dtype=np.float32) * 2
+    X = (centers[rng.integers(0, 400, n)] + rng.standard_normal((n, d), dtype=np.float32)).astype(np.float32)
+    Q = (centers[rng.integers(0, 400, 32)] + rng.standard_normal((32, d), dtype=np.float32)).astype(np.float32)
+    Xn = X / np.linalg.norm(X, axis=1, keepdims=True) if metric == "cosine" else X
+
+    def build(tc):
+        monkeypatch.setenv("LANCE_B200_TRAIN_TC", "1" if tc else "0")
+        h = gpu.LanceHandle(d, metric)
+        h.add_batch(X)
+        l0 = h.stats()["kernel_launches"]
+        h.create_index(P, M)
+        return h, h.stats()["kernel_launches"] - l0
+
+    def recall(h):
+        L, _, C = h.search_batch(Q, k, nprobes=16, refine_factor=3)
+        hits = 0
+        for i in range(Q.shape[0]):
+            wl, _, _ = oracle_mod.flat_search(X, Q[i], k, metric)
+            hits += len(set(int(x) for x in L[i, :C[i]]) & set(int(x) for x in wl))
+        return hits / (k * Q.shape[0])
+
+    h_tc, launches_tc = build(True)
+    h_cc, launches_cc = build(False)
+    try:
+        assert launches_tc != launches_cc, "the tensor-core assignment did not run"
+        g = h_tc.get_ivfpq()
+        off = g["part_offsets"]
+        assert off[0] == 0 and off[-1] == n and sorted(g["row_ids"].tolist()) == list(range(n))
+        assert (np.diff(off) > 0).sum() >= P // 2, "k-means collapsed"
+        C64 = g["centroids"].astype(np.float64)
+        exact = 0
+        sample = rng.integers(0, n, 400)
+        for pos in sample:
+            row = int(g["row_ids"][pos])
+            p = int(np.searchsorted(off, pos, side="right") - 1)
+            x = Xn[row].astype(np.float64)
+            sc = -(C64 @ x) if metric == "dot" else ((C64 - x) ** 2).sum(1)
+            tol = 1e-5 * abs(sc.min()) + 1e-5
+            exact += int(sc[p] <= sc.min() + tol)
+            # never far from the nearest: a miss can only be a bf16 near-tie inside one tile of the centroid table
+            assert sc[p] <= sc.min() + 0.02 * abs(sc.min()) + 1e-3, f"row {row}: partition {p} is not near the best"
+        assert exact >= 0.99 * len(sample), f"only {exact} of {len(sample)} sampled rows sit in their nearest partition"
+        r_tc, r_cc = recall(h_tc), recall(h_cc)
+        assert r_tc >= r_cc - 0.05, f"recall {r_tc:.2f} (tensor cores) vs {r_cc:.2f} (CUDA cores)"
+    finally:
+        h_tc.close()
+        h_cc.close()
