@@ -22,6 +22,10 @@ namespace lb {
 // of the three-term split.
 static constexpr float GEMM_ACC_C = 3.6e-7f; // per accumulated term
 
+__device__ __forceinline__ void lazy_atomic_max(uint32_t *p, uint32_t v) {
+	if (v > __ldca(p)) atomicMax(p, v);
+}
+
 // ------------------------------------------------------------------ shadow rows
 // One warp per row: Xs[row] = bf16 of  x (dot) | x/|x| (cosine) | [x, -|x|^2/2 as three bf16 terms] (l2),
 // zero padded to Kpad.  max_norm = max |x| over the converted rows (float bits, non-negative -> uint max).
@@ -80,9 +84,11 @@ __global__ void __launch_bounds__(256) shadow_rows_kernel(const float *__restric
 		if (metric != METRIC_COSINE && !(nrm <= 3.0e38f)) {
 			atomicOr(max_norm_bits + 1, 1u);
 		} else {
-			if (metric != METRIC_COSINE) atomicMax(max_norm_bits, __float_as_uint(nrm));
-			atomicMax(max_norm_bits + 2, __float_as_uint(sqrtf(res2)));
-			atomicMax(max_norm_bits + 3, __float_as_uint(sqrtf(hat2)));
+			// a running maximum grows O(log n) times: look at the (L1-cached, possibly stale = smaller) word first instead of
+			// sending three same-address atomics per row to one L2 slice (100 M rows: 101 ms of atomics around 13 ms of copying)
+			if (metric != METRIC_COSINE) lazy_atomic_max(max_norm_bits, __float_as_uint(nrm));
+			lazy_atomic_max(max_norm_bits + 2, __float_as_uint(sqrtf(res2)));
+			lazy_atomic_max(max_norm_bits + 3, __float_as_uint(sqrtf(hat2)));
 		}
 	}
 }
