@@ -403,6 +403,7 @@ void run_flat_scan1(const FlatScanArgs &a, void *scratch, int num_sms, cudaStrea
 	}
 	const long long units = ((a.n + 7) >> 3) - (a.row_begin >> 3);
 	int grid = (int)std::min<long long>(std::max<long long>((units + SCAN1_WARPS - 1) / SCAN1_WARPS, 1), num_sms);
+	p.unit_shift = scan1_unit_shift(a.n - a.row_begin, grid);
 	const size_t smem = scan1_smem(a.d, a.k).total;
 	int tix = a.timer ? a.timer->begin(KC_FLAT_SCAN, s) : -1;
 	switch (a.metric) {

@@ -161,6 +161,7 @@ int main(int argc, char **argv) {
 			int grid = (int)std::min<long long>((units + SCAN1_WARPS - 1) / SCAN1_WARPS, (long long)sms * per_sm);
 			cudaMalloc(&slots, (size_t)grid * scan1_slot_keys(k) * 8);
 			p.slots = slots;
+			p.unit_shift = getenv("SCAN1_UNIT_SHIFT") ? atoi(getenv("SCAN1_UNIT_SHIFT")) : scan1_unit_shift(n, grid);
 			float t8 = 0, t16 = 0;
 			for (int flushed = 1; flushed >= 0; flushed--) {
 				switch (met) {
