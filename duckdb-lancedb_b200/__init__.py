@@ -87,6 +87,8 @@ SIGNATURES = {
     "lance_b200_add_batch_labeled": (_i32, [_vp, _vp, _i64, _i32, _i64] + _ERR),
     "lance_b200_add_batch_device_labels": (_i32, [_vp, _vp, _i64, _i32, _vp, _vp] + _ERR),
     "lance_b200_create_sharded": (_vp, [_vp, _i32, _i32, _cp] + _ERR),
+    "lance_b200_create_sharded_at": (_vp, [_cp, _cp, _vp, _i32, _i32, _cp] + _ERR),
+    "lance_b200_open_sharded": (_vp, [_cp, _cp, _cp, _vp, _i32] + _ERR),
     "lance_b200_sharded_rows": (_i32, [_vp, _vp, _i32]),
     "lance_detached_count": (_i64, [_vp] + _ERR),
     "lance_detached_delete": (_i32, [_vp, _i64] + _ERR),
@@ -185,13 +187,28 @@ class LanceHandle:
         return cls(0, metric, _raw=h)
 
     @classmethod
-    def create_sharded(cls, devices, dimension: int, metric: str = "l2"):
-        """lance_b200_create_sharded: one handle over several devices of the box, same calls as a plain handle."""
+    def create_sharded(cls, devices, dimension: int, metric: str = "l2", db_path: str | None = None, table: str = "vectors"):
+        """lance_b200_create_sharded[_at]: one handle over several devices of the box, same calls as a plain handle
+        (db_path given: it can be saved and reopened with open_sharded)."""
         err = C.create_string_buffer(ERR_LEN)
         dv = np.ascontiguousarray(devices, np.int32)
-        h = lib().lance_b200_create_sharded(_ptr(dv), dv.shape[0], int(dimension), metric.encode(), err, ERR_LEN)
+        if db_path is None:
+            h = lib().lance_b200_create_sharded(_ptr(dv), dv.shape[0], int(dimension), metric.encode(), err, ERR_LEN)
+        else:
+            h = lib().lance_b200_create_sharded_at(str(db_path).encode(), table.encode(), _ptr(dv), dv.shape[0], int(dimension),
+                                                   metric.encode(), err, ERR_LEN)
         if not h:
             raise LanceError("Lance create_sharded: " + err.value.decode())
+        return cls(0, metric, _raw=h)
+
+    @classmethod
+    def open_sharded(cls, db_path: str, devices, metric: str = "l2", table: str = "vectors"):
+        """lance_b200_open_sharded: reopens what save() of a create_sharded(..., db_path=...) handle wrote."""
+        err = C.create_string_buffer(ERR_LEN)
+        dv = np.ascontiguousarray(devices, np.int32)
+        h = lib().lance_b200_open_sharded(str(db_path).encode(), table.encode(), metric.encode(), _ptr(dv), dv.shape[0], err, ERR_LEN)
+        if not h:
+            raise LanceError("Lance open_sharded: " + err.value.decode())
         return cls(0, metric, _raw=h)
 
     def shard_rows(self) -> np.ndarray:

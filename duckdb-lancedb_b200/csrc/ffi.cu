@@ -239,6 +239,28 @@ void *lance_b200_create_sharded(const int32_t *devices, int32_t n_devices, int32
 	})
 }
 
+void *lance_b200_create_sharded_at(const char *db_path, const char *table_name, const int32_t *devices, int32_t n_devices,
+                                   int32_t dimension, const char *metric, char *err_buf, int err_buf_len) {
+	LB_TRY("create_sharded failed: ", nullptr, {
+		if (!devices || n_devices <= 0) throw lb::Error("no devices given");
+		std::vector<int> dv(devices, devices + n_devices);
+		std::unique_ptr<lb::ShardedStore> sh(new lb::ShardedStore(dv, dimension, cstr(metric), cstr(db_path), cstr(table_name)));
+		lb::register_sharded(sh.get());
+		return sh.release();
+	})
+}
+
+void *lance_b200_open_sharded(const char *db_path, const char *table_name, const char *metric, const int32_t *devices,
+                              int32_t n_devices, char *err_buf, int err_buf_len) {
+	LB_TRY("open_sharded failed: ", nullptr, {
+		if (!devices || n_devices <= 0) throw lb::Error("no devices given");
+		std::vector<int> dv(devices, devices + n_devices);
+		std::unique_ptr<lb::ShardedStore> sh(lb::ShardedStore::open(cstr(db_path), cstr(table_name), cstr(metric), dv));
+		lb::register_sharded(sh.get());
+		return sh.release();
+	})
+}
+
 int32_t lance_b200_sharded_rows(void *handle, int64_t *out_rows, int32_t capacity) {
 	lb::ShardedStore *sh = lb::as_sharded(handle);
 	if (!sh) return -1;
@@ -626,6 +648,12 @@ int32_t lance_b200_ivfpq_search_debug(void *handle, const float *query, int32_t 
 }
 
 int32_t lance_b200_save(void *handle, char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("save failed: ", -1, {
+			sh->save();
+			return 0;
+		})
+	}
 	LB_HANDLE(-1)
 	LB_TRY("save failed: ", -1, {
 		h->save();

@@ -26,17 +26,87 @@ void unregister_sharded(ShardedStore *s) {
 	g_reg.erase(s);
 }
 
-ShardedStore::ShardedStore(const std::vector<int> &devices, int dim, const std::string &metric) : dim_(dim) {
+static void check_devices(const std::vector<int> &devices) {
 	if (devices.empty()) throw Error("a sharded handle needs at least one device");
 	int count = 0;
 	LB_CUDA(cudaGetDeviceCount(&count));
 	for (int d : devices)
 		if (d < 0 || d >= count) throw Error("device " + std::to_string(d) + " does not exist (" + std::to_string(count) + " visible)");
+}
+
+static std::string shard_table(const std::string &table, size_t i) {
+	return (table.empty() ? std::string("vectors") : table) + ".shard" + std::to_string(i);
+}
+static std::string manifest_path(const std::string &db_path, const std::string &table) {
+	return db_path + "/" + (table.empty() ? std::string("vectors") : table) + ".b200shards";
+}
+
+ShardedStore::ShardedStore(const std::vector<int> &devices, int dim, const std::string &metric, const std::string &db_path,
+                           const std::string &table)
+    : dim_(dim), db_path_(db_path), table_(table) {
+	check_devices(devices);
 	for (size_t i = 0; i < devices.size(); i++) {
-		shards_.emplace_back(new Store("", "shard" + std::to_string(i), dim, metric, devices[i]));
+		shards_.emplace_back(new Store(db_path, shard_table(table, i), dim, metric, devices[i]));
 		shards_.back()->force_explicit_labels();
-		workers_.emplace_back(new Worker());
 	}
+	start_workers();
+}
+
+void ShardedStore::save() {
+	if (db_path_.empty()) throw Error("sharded handle has no db_path to save under");
+	std::lock_guard<std::mutex> g(fan_mu_);
+	std::lock_guard<std::mutex> a(add_mu_);
+	run_on_all([&](int s) { shards_[(size_t)s]->save(); });
+	const std::string path = manifest_path(db_path_, table_);
+	FILE *f = fopen((path + ".tmp").c_str(), "w");
+	if (!f) throw Error("cannot write " + path);
+	bool ok = fprintf(f, "LB200SHARDS 1\n%zu %d %lld %zu\n", shards_.size(), dim_, (long long)next_label_, chunk_first_.size()) > 0;
+	for (size_t i = 0; i < chunk_first_.size() && ok; i++)
+		ok = fprintf(f, "%lld %d\n", (long long)chunk_first_[i], chunk_shard_[i]) > 0;
+	ok = (fclose(f) == 0) && ok;
+	if (!ok || rename((path + ".tmp").c_str(), path.c_str()) != 0) throw Error("cannot write " + path);
+}
+
+ShardedStore *ShardedStore::open(const std::string &db_path, const std::string &table, const std::string &metric,
+                                 const std::vector<int> &devices) {
+	check_devices(devices);
+	const std::string path = manifest_path(db_path, table);
+	FILE *f = fopen(path.c_str(), "r");
+	if (!f) throw Error("no saved sharded store at " + path);
+	char magic[32] = {0};
+	int version = 0, dim = 0;
+	size_t G = 0, nchunks = 0;
+	long long next_label = 0;
+	bool ok = fscanf(f, "%31s %d", magic, &version) == 2 && std::string(magic) == "LB200SHARDS" && version == 1 &&
+	          fscanf(f, "%zu %d %lld %zu", &G, &dim, &next_label, &nchunks) == 4;
+	std::unique_ptr<ShardedStore> sh(new ShardedStore());
+	if (ok) {
+		sh->chunk_first_.resize(nchunks);
+		sh->chunk_shard_.resize(nchunks);
+		for (size_t i = 0; i < nchunks && ok; i++) {
+			long long first = 0;
+			int shard = 0;
+			ok = fscanf(f, "%lld %d", &first, &shard) == 2 && shard >= 0 && (size_t)shard < G &&
+			     (i == 0 || first > sh->chunk_first_[i - 1]);
+			sh->chunk_first_[i] = first, sh->chunk_shard_[i] = shard;
+		}
+	}
+	fclose(f);
+	if (!ok) throw Error("corrupt sharded manifest " + path);
+	if (G != devices.size())
+		throw Error("the table was saved with " + std::to_string(G) + " shards, " + std::to_string(devices.size()) + " devices were given");
+	sh->dim_ = dim, sh->db_path_ = db_path, sh->table_ = table, sh->next_label_ = next_label;
+	for (size_t i = 0; i < G; i++) {
+		sh->shards_.emplace_back(Store::open(db_path, shard_table(table, i), metric, devices[i]));
+		if (sh->shards_.back()->dim() != dim) throw Error("shard " + std::to_string(i) + " has another dimension than the manifest");
+		sh->shards_.back()->force_explicit_labels();
+	}
+	sh->start_workers();
+	return sh.release();
+}
+
+void ShardedStore::start_workers() {
+	for (size_t i = 0; i < shards_.size(); i++) workers_.emplace_back(new Worker());
 	for (size_t i = 0; i < workers_.size(); i++) {
 		Worker *w = workers_[i].get();
 		w->th = std::thread([w] {

@@ -24,8 +24,15 @@ namespace lb {
 
 class ShardedStore {
 public:
-	ShardedStore(const std::vector<int> &devices, int dim, const std::string &metric);
+	// db_path empty: in memory only.  Else shard i persists as table "<table>.shard<i>" under db_path (store.bin each) and
+	// save() adds "<db_path>/<table>.b200shards": shard count, label counter and the batch -> shard map.
+	ShardedStore(const std::vector<int> &devices, int dim, const std::string &metric, const std::string &db_path = "",
+	             const std::string &table = "");
 	~ShardedStore();
+	void save();
+	// reopens what save() wrote; devices.size() must be the saved shard count (shard i goes to devices[i])
+	static ShardedStore *open(const std::string &db_path, const std::string &table, const std::string &metric,
+	                          const std::vector<int> &devices);
 
 	int dim() const { return dim_; }
 	int num_shards() const { return (int)shards_.size(); }
@@ -55,6 +62,9 @@ public:
 	                 const char *predicate, int64_t *out_labels, float *out_dist, int32_t *out_counts);
 
 private:
+	ShardedStore() = default; // open()
+	void start_workers();
+	std::string db_path_, table_;
 	struct Worker { // one host thread per shard: it owns that device's calls of a fan-out
 		std::thread th;
 		std::mutex mu;
@@ -69,7 +79,7 @@ private:
 	// the shards' staged lists of queries [q_lo, q_hi) -> the caller's buffers
 	void merge_queries(int q_lo, int q_hi, int nq, int k, int64_t *out_labels, float *out_dist, int32_t *out_counts);
 
-	int dim_;
+	int dim_ = 0;
 	std::vector<std::unique_ptr<Store>> shards_;
 	std::vector<std::unique_ptr<Worker>> workers_;
 	std::mutex add_mu_;   // appends are serialised: they draw from one label counter

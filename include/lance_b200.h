@@ -291,10 +291,19 @@ int32_t lance_b200_add_batch_device_labels(void *handle, const float *d_vectors,
  * concurrently and the per-shard lists are merged under the library's (distance, label) order.
  * lance_detached_create_index trains ONE IVF_PQ INDEX PER SHARD over that shard's rows with the caller's parameters (a
  * search then probes nprobes lists on every shard); lance_detached_create_hnsw_index / lance_b200_drop_index drop them;
- * lance_b200_stats adds the shards' counters up.  Persistence, the index exchange calls and the device-pointer entry
- * points answer "not supported on a sharded handle".  NULL + message on failure. */
+ * lance_b200_stats adds the shards' counters up; lance_b200_save works on a handle made by lance_b200_create_sharded_at.
+ * The index exchange calls and the device-pointer entry points answer "not supported on a sharded handle".  NULL + message on failure. */
 void *lance_b200_create_sharded(const int32_t *devices, int32_t n_devices, int32_t dimension, const char *metric,
                                 char *err_buf, int err_buf_len);
+/* The same handle with a place on disk: shard i persists as table "<table_name>.shard<i>" under db_path (one store.bin
+ * each: rows, tombstones, labels, extra columns, its IVF_PQ index) and lance_b200_save adds "<table_name>.b200shards"
+ * (shard count, label counter, batch -> shard map).  lance_b200_open_sharded reopens it; n_devices must be the saved
+ * shard count (shard i goes to devices[i]).  These stand where LanceIndex::LoadFromStorage calls lance_open_detached
+ * (src/lance_index.cpp:584) when the index was created over several GPUs. */
+void *lance_b200_create_sharded_at(const char *db_path, const char *table_name, const int32_t *devices, int32_t n_devices,
+                                   int32_t dimension, const char *metric, char *err_buf, int err_buf_len);
+void *lance_b200_open_sharded(const char *db_path, const char *table_name, const char *metric, const int32_t *devices,
+                              int32_t n_devices, char *err_buf, int err_buf_len);
 /* Rows held by each shard (out_rows[capacity]); returns the number of shards, -1 if `handle` is not sharded. */
 int32_t lance_b200_sharded_rows(void *handle, int64_t *out_rows, int32_t capacity);
 

@@ -77,8 +77,10 @@ def test_sharded_handle_predicates_and_unsupported_calls(gpu, oracle_mod):
         gl, gd = h.search_predicate(q, k, "score < 25 AND lang = 'fr'")
         wl, _, wd = oracle_mod.flat_search(X, q, k, "l2", oracle_mod.make_bitmap(mask))
         assert_topk_parity(gl, gd, wl, wd, lambda lab: oracle_mod.distance_f64("l2", q, X[lab]), what="predicate")
+        with pytest.raises(gpu.LanceError, match="no db_path to save under"):
+            h.save()  # an in-memory sharded handle (lance_b200_create_sharded); see test_sharded_handle_save_and_reopen
         with pytest.raises(gpu.LanceError, match="not supported on a sharded handle"):
-            h.save()
+            h.get_ivfpq()
         with pytest.raises(gpu.LanceError, match="expected query dimension"):
             h.search(np.zeros(d + 1, np.float32), k)
     finally:
@@ -135,5 +137,54 @@ def test_sharded_handle_ivfpq_one_index_per_shard(gpu, oracle_mod, metric):
         gl, gd = h.search(Q[0], k)
         wl, _, wd = oracle_mod.flat_search(X, Q[0], k, metric)
         assert_topk_parity(gl, gd, wl, wd, lambda lab: oracle_mod.distance_f64(metric, Q[0], X[lab]), what="after hnsw request")
+    finally:
+        h.close()
+
+
+def test_sharded_handle_save_and_reopen(gpu, oracle_mod, tmp_path):
+    """A sharded handle with a place on disk (lance_b200_create_sharded_at): every shard writes its store.bin, the manifest
+    keeps the label counter and the batch -> shard map; the reopened handle answers like the one that was saved
+    (test/sql/lance_persist.test semantics for an index spread over several GPUs)."""
+    rng = np.random.default_rng(64)
+    n, d, k = 12_000, 24, 8
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    score = rng.integers(0, 50, n).astype(np.int64)
+    Q = rng.standard_normal((6, d)).astype(np.float32)
+    db = str(tmp_path / "db")
+    h = gpu.LanceHandle.create_sharded(_devices(gpu, 3), d, "cosine", db_path=db, table="docs")
+    dead = rng.choice(n, 900, replace=False).astype(np.int64)
+    try:
+        for lo in range(0, n, 1500):
+            h.add_batch(X[lo:lo + 1500])
+        h.set_column("score", score)
+        h.delete_batch(dead)
+        before = h.search_batch(Q, k)
+        before_pred = h.search_batch_predicate(Q, k, "score >= 40")
+        rows_before = h.shard_rows()
+        h.save()
+    finally:
+        h.close()
+    with pytest.raises(gpu.LanceError, match="saved with 3 shards"):
+        gpu.LanceHandle.open_sharded(db, _devices(gpu, 2), "cosine", table="docs")
+    with pytest.raises(gpu.LanceError, match="no saved sharded store"):
+        gpu.LanceHandle.open_sharded(db, _devices(gpu, 3), "cosine", table="other")
+    h = gpu.LanceHandle.open_sharded(db, _devices(gpu, 3), "cosine", table="docs")
+    try:
+        assert h.dim == d and h.count() == n - 900 and np.array_equal(h.shard_rows(), rows_before)
+        after = h.search_batch(Q, k)
+        after_pred = h.search_batch_predicate(Q, k, "score >= 40")
+        for a, b in zip(before + before_pred, after + after_pred):
+            np.testing.assert_array_equal(a, b)
+        alive = np.ones(n, bool)
+        alive[dead] = False
+        wl, _, wd = oracle_mod.flat_search(X, Q[0], k, "cosine", oracle_mod.make_bitmap(alive))
+        assert_topk_parity(after[0][0], after[1][0], wl, wd, lambda lab: oracle_mod.distance_f64("cosine", Q[0], X[lab]), what="reopened")
+        # the label sequence goes on where it stopped, deletes still find their shard
+        Y = rng.standard_normal((100, d)).astype(np.float32)
+        first = h.add_batch(Y)
+        assert int(np.atleast_1d(first)[0]) == n
+        assert np.array_equal(h.get_vector(n + 7), Y[7])
+        h.delete_batch(np.array([5 if 5 not in dead else int(np.flatnonzero(alive)[0])], np.int64))
+        assert h.count() == n - 900 + 100 - 1
     finally:
         h.close()
