@@ -44,10 +44,42 @@ static std::string cstr(const char *s) { return s ? std::string(s) : std::string
 
 extern "C" {
 
+// LANCE_B200_DEVICES="0,1,2,3" (or "all"): lance_create_detached[_from_arrow] spread the table over those devices — the
+// sharded handle of sharded.h behind the reference's own entry points, so the unmodified extension reaches every GPU.
+// Unset or one device: a plain one-device store.
+static std::vector<int> env_devices() {
+	std::vector<int> dv;
+	const char *e = getenv("LANCE_B200_DEVICES");
+	if (!e || !*e) return dv;
+	if (std::string(e) == "all") {
+		int count = 0;
+		if (cudaGetDeviceCount(&count) != cudaSuccess) count = 0;
+		for (int i = 0; i < count; i++) dv.push_back(i);
+		return dv;
+	}
+	const char *p = e;
+	while (*p) {
+		char *end = nullptr;
+		const long v = strtol(p, &end, 10);
+		if (end == p) throw lb::Error(std::string("LANCE_B200_DEVICES: cannot parse \"") + e + "\"");
+		dv.push_back((int)v);
+		p = end;
+		while (*p == ',' || *p == ' ') p++;
+	}
+	return dv;
+}
+
 void *lance_create_detached(const char *db_path, int32_t dimension, const char *metric, const char *table_name,
                             char *err_buf, int err_buf_len) {
 	LB_TRY("create failed: ", nullptr, {
-		return new Store(cstr(db_path), cstr(table_name), dimension, cstr(metric), lb::default_device());
+		const std::vector<int> dv = env_devices();
+		if (dv.size() > 1) {
+			std::unique_ptr<lb::ShardedStore> sh(new lb::ShardedStore(dv, dimension, cstr(metric), cstr(db_path), cstr(table_name)));
+			lb::register_sharded(sh.get());
+			return static_cast<void *>(sh.release());
+		}
+		return static_cast<void *>(new Store(cstr(db_path), cstr(table_name), dimension, cstr(metric),
+		                                     dv.size() == 1 ? dv[0] : lb::default_device()));
 	})
 }
 
@@ -61,16 +93,41 @@ void *lance_create_detached_from_arrow(const char *db_path, void *arrow_schema, 
 	}
 	LB_TRY("create_from_arrow failed: ", nullptr, {
 		const int dim = lb::arrow_schema_vector_dim(arrow_schema);
-		std::unique_ptr<Store> st(new Store(cstr(db_path), cstr(table_name), dim, cstr(metric), lb::default_device()));
+		const std::vector<int> dv = env_devices();
+		if (dv.size() > 1) {
+			std::unique_ptr<lb::ShardedStore> sh(new lb::ShardedStore(dv, dim, cstr(metric), cstr(db_path), cstr(table_name)));
+			sh->define_columns_from_arrow(arrow_schema);
+			lb::register_sharded(sh.get());
+			return static_cast<void *>(sh.release());
+		}
+		std::unique_ptr<Store> st(new Store(cstr(db_path), cstr(table_name), dim, cstr(metric),
+		                                    dv.size() == 1 ? dv[0] : lb::default_device()));
 		st->define_columns_from_arrow(arrow_schema);
-		return st.release();
+		return static_cast<void *>(st.release());
 	})
 }
 
 void *lance_open_detached(const char *db_path, const char *table_name, const char *metric, char *err_buf,
                           int err_buf_len) {
-	LB_TRY("open failed: ", nullptr,
-	       { return Store::open(cstr(db_path), cstr(table_name), cstr(metric), lb::default_device()); })
+	LB_TRY("open failed: ", nullptr, {
+		// a table that was saved sharded reopens sharded: on LANCE_B200_DEVICES when it names as many devices as there are
+		// shards, else shard i on device i modulo the visible ones
+		const int G = lb::ShardedStore::saved_shards(cstr(db_path), cstr(table_name));
+		std::vector<int> dv = env_devices();
+		if (G > 0) {
+			if ((int)dv.size() != G) {
+				int count = 1;
+				if (cudaGetDeviceCount(&count) != cudaSuccess || count < 1) count = 1;
+				dv.clear();
+				for (int i = 0; i < G; i++) dv.push_back(i % count);
+			}
+			std::unique_ptr<lb::ShardedStore> sh(lb::ShardedStore::open(cstr(db_path), cstr(table_name), cstr(metric), dv));
+			lb::register_sharded(sh.get());
+			return static_cast<void *>(sh.release());
+		}
+		return static_cast<void *>(Store::open(cstr(db_path), cstr(table_name), cstr(metric),
+		                                       dv.size() == 1 ? dv[0] : lb::default_device()));
+	})
 }
 
 void lance_free_detached(void *handle) {
@@ -343,6 +400,46 @@ int32_t lance_detached_merge(void *target_handle, void *source_handle, const int
 		write_err(err_buf, err_buf_len, "null handle");
 		return -1;
 	}
+	if (lb::as_sharded(target_handle) || lb::as_sharded(source_handle)) {
+		// a sharded side: the listed live rows of the source travel through the host (get_vector / add), in the order of
+		// the list as it stands in the source; same contract, no device-to-device gather
+		LB_TRY("merge failed: ", -1, {
+			if (target_handle == source_handle) throw lb::Error("cannot merge an index into itself");
+			lb::ShardedStore *ts = lb::as_sharded(target_handle);
+			lb::ShardedStore *ss = lb::as_sharded(source_handle);
+			const int dim_t = ts ? ts->dim() : static_cast<Store *>(target_handle)->dim();
+			const int dim_s = ss ? ss->dim() : static_cast<Store *>(source_handle)->dim();
+			if (dim_t != dim_s)
+				throw lb::Error("dimension mismatch: expected " + std::to_string(dim_t) + ", got " + std::to_string(dim_s));
+			if (live_count < 0) throw lb::Error("negative count");
+			std::vector<int64_t> sorted(live_source_labels, live_source_labels + live_count);
+			std::sort(sorted.begin(), sorted.end());
+			sorted.erase(std::unique(sorted.begin(), sorted.end()), sorted.end());
+			std::vector<float> rows;
+			std::vector<int64_t> olds;
+			std::vector<float> one((size_t)dim_s);
+			for (int64_t lab : sorted) {
+				try {
+					if (ss) ss->get_vector(lab, one.data());
+					else static_cast<Store *>(source_handle)->get_vector(lab, one.data());
+				} catch (const lb::Error &) {
+					continue; // unknown or deleted in the source: not merged
+				}
+				rows.insert(rows.end(), one.begin(), one.end());
+				olds.push_back(lab);
+			}
+			const int64_t m = (int64_t)olds.size();
+			if (m == 0) return 0;
+			int64_t first;
+			if (ts) first = ts->add_host(rows.data(), m);
+			else first = static_cast<Store *>(target_handle)->add_host(rows.data(), m);
+			for (int64_t i = 0; i < m; i++) {
+				if (out_old_labels) out_old_labels[i] = olds[(size_t)i];
+				if (out_new_labels) out_new_labels[i] = first + i;
+			}
+			return (int)m;
+		})
+	}
 	void *handle = target_handle;
 	LB_HANDLE(-1)
 	LB_TRY("merge failed: ", -1, {
@@ -509,6 +606,13 @@ int32_t lance_detached_get_vector(void *handle, int64_t label, float *out_vec, i
 
 int32_t lance_detached_get_all_vectors(void *handle, int64_t *out_labels, float *out_vectors, int64_t *out_count,
                                        char *err_buf, int err_buf_len) {
+	if (lb::ShardedStore *sh = lb::as_sharded(handle)) {
+		LB_TRY("get_all_vectors failed: ", -1, {
+			const int64_t c = sh->get_all(out_labels, out_vectors);
+			if (out_count) *out_count = c;
+			return 0;
+		})
+	}
 	LB_HANDLE(-1)
 	LB_TRY("get_all_vectors failed: ", -1, {
 		int64_t c = h->get_all(out_labels, out_vectors);

@@ -67,6 +67,17 @@ void ShardedStore::save() {
 	if (!ok || rename((path + ".tmp").c_str(), path.c_str()) != 0) throw Error("cannot write " + path);
 }
 
+int ShardedStore::saved_shards(const std::string &db_path, const std::string &table) {
+	FILE *f = fopen(manifest_path(db_path, table).c_str(), "r");
+	if (!f) return 0;
+	char magic[32] = {0};
+	int version = 0;
+	size_t G = 0;
+	const bool ok = fscanf(f, "%31s %d %zu", magic, &version, &G) == 3 && std::string(magic) == "LB200SHARDS";
+	fclose(f);
+	return ok ? (int)G : 0;
+}
+
 ShardedStore *ShardedStore::open(const std::string &db_path, const std::string &table, const std::string &metric,
                                  const std::vector<int> &devices) {
 	check_devices(devices);
@@ -286,6 +297,16 @@ void ShardedStore::get_vector(int64_t label, float *out) {
 	}
 	if (s < 0) throw Error("label " + std::to_string(label) + " not found");
 	shards_[(size_t)s]->get_vector(label, out);
+}
+
+int64_t ShardedStore::get_all(int64_t *out_labels, float *out_vectors) {
+	int64_t total = 0;
+	for (auto &s : shards_) {
+		const int64_t c = s->get_all(out_labels ? out_labels + total : nullptr,
+		                             out_vectors ? out_vectors + (size_t)total * (size_t)dim_ : nullptr);
+		total += c;
+	}
+	return total;
 }
 
 int64_t ShardedStore::compact() {

@@ -30,6 +30,7 @@ public:
 	             const std::string &table = "");
 	~ShardedStore();
 	void save();
+	static int saved_shards(const std::string &db_path, const std::string &table); // 0: no sharded table saved there
 	// reopens what save() wrote; devices.size() must be the saved shard count (shard i goes to devices[i])
 	static ShardedStore *open(const std::string &db_path, const std::string &table, const std::string &metric,
 	                          const std::vector<int> &devices);
@@ -48,6 +49,7 @@ public:
 	int64_t live_rows();
 	int64_t rows();
 	void get_vector(int64_t label, float *out);
+	int64_t get_all(int64_t *out_labels, float *out_vectors); // live rows of every shard, shard by shard; returns the count
 	int64_t compact();
 	// IVF_PQ on a sharded table: every shard trains and keeps an index of ITS rows with the caller's parameters (the
 	// partition count is clamped to the shard's rows); a search probes nprobes lists on every shard and the lists are

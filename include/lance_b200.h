@@ -32,7 +32,10 @@ extern "C" {
 /* ===================================================================== Part 1: reference symbols */
 
 /* rust_ffi.cpp:9-10 / ffi.rs:37-57.  metric: "l2" (default), "cosine", "dot"|"ip"
- * (lance_manager.rs:493-497).  db_path/table_name are recorded; the device store is the index. */
+ * (lance_manager.rs:493-497).  db_path/table_name are recorded; the device store is the index.
+ * Environment LANCE_B200_DEVICES="0,1,.." | "all" (more than one device): this call, lance_create_detached_from_arrow and
+ * lance_open_detached (for a table saved that way) return a SHARDED handle (lance_b200_create_sharded_at below) — the
+ * unmodified extension then uses every listed GPU. */
 void *lance_create_detached(const char *db_path, int32_t dimension, const char *metric, const char *table_name,
                             char *err_buf, int err_buf_len);
 /* rust_ffi.cpp:11-12 / ffi.rs:62-87.  Multi-column Arrow ingest is outside the kNN path: returns NULL. */
@@ -86,7 +89,7 @@ int32_t lance_detached_create_index(void *handle, int32_t num_partitions, int32_
  * on (recall 1.0).  m / ef_construction <= 0 = defaults, as in the reference. */
 int32_t lance_detached_create_hnsw_index(void *handle, int32_t m, int32_t ef_construction, char *err_buf,
                                          int err_buf_len);
-/* rust_ffi.cpp:37: nothing to compact in the device store, returns 0 */
+/* rust_ffi.cpp:37 / ffi.rs:448-465 -> lance_manager.rs:553-566: tombstoned rows are dropped for good (HBM released), labels kept */
 int32_t lance_detached_compact(void *handle, char *err_buf, int err_buf_len);
 /* rust_ffi.cpp:38-39 / ffi.rs:472-503: returns dim, or -1 (unknown/deleted label, small buffer) */
 int32_t lance_detached_get_vector(void *handle, int64_t label, float *out_vec, int32_t capacity, char *err_buf,

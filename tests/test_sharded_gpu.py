@@ -188,3 +188,49 @@ def test_sharded_handle_save_and_reopen(gpu, oracle_mod, tmp_path):
         assert h.count() == n - 900 + 100 - 1
     finally:
         h.close()
+
+
+def test_reference_entry_points_shard_by_environment(gpu, oracle_mod, tmp_path, monkeypatch):
+    """LANCE_B200_DEVICES: the reference's own lance_create_detached / lance_open_detached hand out a sharded handle, so the
+    unmodified extension spreads an index over the GPUs.  Includes MergeIndexes' calls (lance_detached_merge,
+    lance_detached_get_all_vectors: src/lance_index.cpp:620-700) with a sharded side."""
+    rng = np.random.default_rng(65)
+    n, d, k = 6000, 20, 5
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    q = rng.standard_normal(d).astype(np.float32)
+    ndev = gpu.device_count()
+    monkeypatch.setenv("LANCE_B200_DEVICES", ",".join(str(i % ndev) for i in range(3)))
+    db = str(tmp_path / "db")
+    h = gpu.LanceHandle(d, "l2", db_path=db, table_name="t")  # lance_create_detached
+    try:
+        assert len(h.shard_rows()) == 3
+        for lo in range(0, n, 1000):
+            h.add_batch(X[lo:lo + 1000])
+        gl, gd = h.search(q, k)
+        wl, _, wd = oracle_mod.flat_search(X, q, k, "l2")
+        assert_topk_parity(gl, gd, wl, wd, lambda lab: oracle_mod.distance_f64("l2", q, X[lab]), what="env-sharded")
+        labs, vecs = h.get_all_vectors()
+        order = np.argsort(labs)
+        assert np.array_equal(labs[order], np.arange(n)) and np.array_equal(vecs[order], X)
+        h.save()
+    finally:
+        h.close()
+    h = gpu.LanceHandle.open(db, "t", "l2")  # lance_open_detached finds the manifest
+    monkeypatch.delenv("LANCE_B200_DEVICES")
+    plain = gpu.LanceHandle(d, "l2")
+    try:
+        assert len(h.shard_rows()) == 3 and h.count() == n
+        gl2, gd2 = h.search(q, k)
+        np.testing.assert_array_equal(gl, gl2)
+        # merge a plain index into the sharded one and the other way round
+        Y = rng.standard_normal((50, d)).astype(np.float32)
+        plain.add_batch(Y)
+        old, new = h.merge(plain, np.arange(0, 50, 2))
+        assert list(old) == list(range(0, 50, 2)) and list(new) == list(range(n, n + 25))
+        assert np.array_equal(h.get_vector(n + 3), Y[6]) and h.count() == n + 25
+        old, new = plain.merge(h, np.array([7, 8, 10 ** 9]))
+        assert list(old) == [7, 8] and list(new) == [50, 51]
+        assert np.array_equal(plain.get_vector(51), X[8])
+    finally:
+        h.close()
+        plain.close()
