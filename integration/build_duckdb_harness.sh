@@ -36,4 +36,5 @@ assert s.count(old) == 1
 open(d + "/lance_optimizer_filter_tie_neutral.test", "w").write(
     s.replace(old, old[:-2] + "3\n").replace("lance_optimizer_filter.test", "lance_optimizer_filter_tie_neutral.test"))
 PY
+gcc -O2 $ROOT/integration/bench/sql_latency.c -I $REF/duckdb/src/include -L $OUT -lduckdb -Wl,-rpath,'$ORIGIN' -o $OUT/sql_latency
 echo "staged: $(ls $OUT)"
