@@ -635,6 +635,7 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
     flush_buf = torch.empty(512 << 20, dtype=torch.uint8, device=dev) if need_flush else None
 
     wall_ms = [0.0]
+    per_step_ms = []  # device time of every timed step, where steps are timed one by one (L2 flushed between them)
 
     def flush_l2():
         flush_buf[: 256 << 20].fill_(1)
@@ -656,6 +657,7 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
             wall_ms[0] = (time.perf_counter() - t0) * 1e3
             b.barrier()
             ms = float(per.sum())
+            per_step_ms[:] = [float(v) for v in per]
         elif need_flush:
             evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(nsteps)]
             wall = 0.0
@@ -669,6 +671,7 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
                 e.synchronize()
             b.barrier()
             ms = sum(a.elapsed_time(e) for a, e in evs)
+            per_step_ms[:] = [a.elapsed_time(e) for a, e in evs]
             wall_ms[0] = wall * 1e3
         else:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -707,6 +710,7 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
         ss.merges = 0
     t_region = time.perf_counter()
     ms = timed(lambda: step_device(Qd.data_ptr()), steps)
+    step_times = sorted(per_step_ms)
     prof = h.profile_read()
     h.profile_enable(False)
     st1 = h.stats()
@@ -824,6 +828,9 @@ def measure(b: Bench, tab: Table, wl, name, steps, headline):
             "e2e": {"value": qps_e2e, "unit": "queries/s", "h2d_bytes_per_step": int(Qh.numel() * 4 + (allow_host.nbytes if allow_host is not None and world == 1 and predicate is None else 0)),
                     "d2h_bytes_per_step": int(Lh.numel() * 8 + Dh.numel() * 4 + Ch.numel() * 4), "ms_per_step": ms_e2e / steps},
             "gpu_launches": int(launches), "roofline": roof, "first_step_ms": first_step_ms,
+            **({"step_ms_quantiles": {"min": step_times[0], "p50": step_times[len(step_times) // 2],
+                                      "p99": step_times[min(len(step_times) - 1, int(0.99 * len(step_times)))],
+                                      "max": step_times[-1], "n": len(step_times)}} if step_times else {}),
             **({"prefilter": {"predicate": predicate, "evaluated": "on the device over the HBM-resident column, bitmap cached per (predicate, epoch)",
                               "e2e_host_bitmap_ms_per_step": ms_e2e_bitmap / steps,
                               "host_bitmap_h2d_bytes_per_step": int(allow_host.nbytes)}} if predicate is not None else {}),
