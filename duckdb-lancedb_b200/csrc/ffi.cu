@@ -78,6 +78,7 @@ void *lance_create_detached(const char *db_path, int32_t dimension, const char *
 			lb::register_sharded(sh.get());
 			return static_cast<void *>(sh.release());
 		}
+		lb::ShardedStore::forget(cstr(db_path), cstr(table_name)); // a new plain table replaces a sharded one of that name
 		return static_cast<void *>(new Store(cstr(db_path), cstr(table_name), dimension, cstr(metric),
 		                                     dv.size() == 1 ? dv[0] : lb::default_device()));
 	})
@@ -100,6 +101,7 @@ void *lance_create_detached_from_arrow(const char *db_path, void *arrow_schema, 
 			lb::register_sharded(sh.get());
 			return static_cast<void *>(sh.release());
 		}
+		lb::ShardedStore::forget(cstr(db_path), cstr(table_name));
 		std::unique_ptr<Store> st(new Store(cstr(db_path), cstr(table_name), dim, cstr(metric),
 		                                    dv.size() == 1 ? dv[0] : lb::default_device()));
 		st->define_columns_from_arrow(arrow_schema);

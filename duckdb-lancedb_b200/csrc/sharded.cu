@@ -78,6 +78,10 @@ int ShardedStore::saved_shards(const std::string &db_path, const std::string &ta
 	return ok ? (int)G : 0;
 }
 
+void ShardedStore::forget(const std::string &db_path, const std::string &table) {
+	if (!db_path.empty()) remove(manifest_path(db_path, table).c_str());
+}
+
 ShardedStore *ShardedStore::open(const std::string &db_path, const std::string &table, const std::string &metric,
                                  const std::vector<int> &devices) {
 	check_devices(devices);

@@ -31,6 +31,7 @@ public:
 	~ShardedStore();
 	void save();
 	static int saved_shards(const std::string &db_path, const std::string &table); // 0: no sharded table saved there
+	static void forget(const std::string &db_path, const std::string &table);      // a plain table takes that name: drop the manifest
 	// reopens what save() wrote; devices.size() must be the saved shard count (shard i goes to devices[i])
 	static ShardedStore *open(const std::string &db_path, const std::string &table, const std::string &metric,
 	                          const std::vector<int> &devices);
