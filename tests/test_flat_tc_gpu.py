@@ -385,26 +385,31 @@ def test_tc_clustered_unit_norm_embeddings_vs_oracle(gpu, oracle_mod, metric, d,
         check_oracle(oracle_mod, X, Q[:8], L[:8], D[:8], C[:8], k, metric, what=f"tc clustered {metric} d={d}")
 
 
-@pytest.mark.parametrize("metric,d", [("dot", 128), ("l2", 64), ("cosine", 200),
-                                      # K-streamed kernel (half-tile maxima), plain and with the l2 bias epilogue
-                                      ("cosine", 320), ("l2", 704)])
-def test_tc_tile_max_seeding_pass(gpu, oracle_mod, metric, d, monkeypatch):
+@pytest.mark.parametrize("metric,d,k,seed_tiles", [("dot", 128, 10, 64), ("l2", 64, 10, 64), ("cosine", 200, 10, 64),
+                                                   # K-streamed kernel (half-tile maxima), plain and with the l2 bias epilogue
+                                                   ("cosine", 320, 10, 64), ("l2", 704, 10, 64),
+                                                   # larger k (the k-th of 128 / 256 maxima), odd dimension
+                                                   ("l2", 100, 50, 128), ("cosine", 320, 100, 128)])
+def test_tc_tile_max_seeding_pass(gpu, oracle_mod, metric, d, k, seed_tiles, monkeypatch):
     """The threshold seeding pass of the tensor-memory kernels (flat_gemm.cu "Seeding": per-tile maxima, no emission),
     forced at a size the oracle can check (64 seed tiles instead of 1024), with deletions inside and outside the seeded
     rows, a prefilter, a partial last tile and rows sorted so that the best rows of some queries share ONE tile (the
     case in which the k-th tile maximum is a loose bound: still a bound, the result must not change)."""
-    n, k, nq = 150_001, 10, 300
+    n, nq = 150_001, 300
     rng = np.random.default_rng(4242 + d)
+    monkeypatch.setenv("LANCE_B200_TC_GROWTH", "2")  # the pass needs 2 x growth x seed tiles of table: keep it small here
     X = rng.standard_normal((n, d), dtype=np.float32)
     Q = rng.standard_normal((nq, d), dtype=np.float32)
-    # tile 3 (rows 384..511) holds near-copies of query 0: its ten best rows sit in one tile
+    # tile 3 (rows 384..511) holds near-copies of query 0: its best rows sit in one tile.  (Looser copies for the larger k:
+    # a cosine distance of 1e-3 is 1 - 0.999 in fp32, which cannot rank 100 such rows to 1e-5 relative — nor can the reference.)
+    noise = 0.05 if k <= 10 else 0.3
     X[384:512] = Q[0] * (1.0 + 0.01 * rng.standard_normal((128, 1), dtype=np.float32)) + \
-        0.05 * rng.standard_normal((128, d), dtype=np.float32)
+        noise * rng.standard_normal((128, d), dtype=np.float32)
     mask = rng.random(n) < 0.7
     dele = np.concatenate([rng.choice(8192, 600, replace=False), 8192 + rng.choice(n - 8192, 3000, replace=False)])
     deleted = np.zeros(n, bool)
     deleted[dele] = True
-    monkeypatch.setenv("LANCE_B200_TC_SEEDMAX", "64")
+    monkeypatch.setenv("LANCE_B200_TC_SEEDMAX", str(seed_tiles))
     with gpu.LanceHandle(d, metric) as h:
         h.add_batch(X)
         l0 = h.stats()["kernel_launches"]
@@ -420,7 +425,7 @@ def test_tc_tile_max_seeding_pass(gpu, oracle_mod, metric, d, monkeypatch):
         np.testing.assert_array_equal(L, L0)
         np.testing.assert_array_equal(D, D0)
         # with tombstones and a prefilter
-        monkeypatch.setenv("LANCE_B200_TC_SEEDMAX", "64")
+        monkeypatch.setenv("LANCE_B200_TC_SEEDMAX", str(seed_tiles))
         h.delete_batch(dele)
         allow = gpu.make_bitmap(mask)
         L, D, C, fb = tc_search(h, Q, k, allow=allow)
